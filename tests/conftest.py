@@ -1,0 +1,33 @@
+"""pytest configuration: registers the `gpu` marker and puts the repo root (for `oracle`)
+and the product directory (for `pcm_frontend`) on sys.path."""
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "voice-enabled-browser-automation_b200")
+for p in (ROOT, PKG):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def golden_dir():
+    return GOLDEN
+
+
+@pytest.fixture(scope="session")
+def ctx():
+    """One pcm_frontend.Context on cuda:0 for the whole GPU test session."""
+    import pcm_frontend
+
+    c = pcm_frontend.Context(0)
+    yield c
+    c.close()
