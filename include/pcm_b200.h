@@ -1,0 +1,142 @@
+/*
+ * pcm_b200.h -- C ABI of libpcm_b200.so, the B200 (sm_100a) PCM front-end.
+ *
+ * Drop-in scope: the mic-audio front-end of the reference's browser client
+ *   floatTo16BitPCM(float32: Float32Array): Int16Array          apps/web/src/App.tsx:7-16
+ *   resampleTo16k(input: Float32Array, rate: number): Float32Array   apps/web/src/App.tsx:18-32
+ *   pcm16 = floatTo16BitPCM(resampleTo16k(buf, rate))           apps/web/src/App.tsx:281-282
+ * batched over many concurrent sessions.  The reference has no FFI of its own;
+ * these entry points are what an N-API addon for that path binds (see
+ * INTEGRATION.md, voice-enabled-browser-automation_b200/node/).  The bytes they
+ * produce go, unchanged, to DeepgramClient.sendAudio (apps/voice/src/deepgram.ts:16,55-58).
+ *
+ * Conventions
+ *   - every function returns a pcmb200_status (0 = ok); nothing throws across the ABI;
+ *   - the caller owns every buffer it passes; the context owns its own staging memory;
+ *   - a context is bound to one CUDA device and is NOT thread-safe (one per device per thread);
+ *   - `mem` says where the caller's in/out buffers live:
+ *       PCMB200_MEM_HOST    host memory (pinned is faster).  The call copies in, computes,
+ *                           copies out and returns when the output is complete (synchronous,
+ *                           like the reference's functions).
+ *       PCMB200_MEM_DEVICE  device memory of the context's device.  The call enqueues work on
+ *                           the context's stream and returns; use pcmb200_sync().
+ *   - sample layout of a batch: row-major [row][sample]; a row is one frame of one session
+ *     (rows = sessions x ticks).  pitch_* are in ELEMENTS, not bytes.
+ *   - there is no CPU fallback: without a usable CUDA device pcmb200_ctx_create fails.
+ */
+#ifndef PCM_B200_H
+#define PCM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define PCMB200_API __declspec(dllexport)
+#else
+#define PCMB200_API __attribute__((visibility("default")))
+#endif
+
+typedef struct pcmb200_ctx pcmb200_ctx;
+
+typedef enum pcmb200_status {
+    PCMB200_OK = 0,
+    PCMB200_ERR_INVALID = 1,    /* bad argument (null pointer, bad mem kind, misuse) */
+    PCMB200_ERR_RANGE = 2,      /* the reference would throw RangeError (invalid typed-array length) */
+    PCMB200_ERR_CUDA = 3,       /* a CUDA call failed; see pcmb200_last_error */
+    PCMB200_ERR_NO_DEVICE = 4,  /* no usable CUDA device: the library has no CPU fallback */
+    PCMB200_ERR_NOMEM = 5,      /* host or device allocation failed */
+    PCMB200_ERR_CAPACITY = 6    /* caller's output buffer is too small */
+} pcmb200_status;
+
+typedef enum pcmb200_mem {
+    PCMB200_MEM_HOST = 0,
+    PCMB200_MEM_DEVICE = 1
+} pcmb200_mem;
+
+/* ---- library / context ---------------------------------------------------------------- */
+
+/* ABI version: major * 1000 + minor. */
+PCMB200_API int pcmb200_version(void);
+PCMB200_API const char *pcmb200_status_string(int status);
+/* Number of CUDA devices visible to this process (0 and PCMB200_ERR_NO_DEVICE if none). */
+PCMB200_API int pcmb200_device_count(int *count);
+/* Create a context on `device` (creates a stream, events and an empty staging pool). */
+PCMB200_API int pcmb200_ctx_create(int device, pcmb200_ctx **out);
+PCMB200_API int pcmb200_ctx_destroy(pcmb200_ctx *ctx);
+/* Message of the last failure on this context (ctx may be NULL: last failure of this thread). */
+PCMB200_API const char *pcmb200_last_error(const pcmb200_ctx *ctx);
+/* Wait for everything enqueued on the context's stream. */
+PCMB200_API int pcmb200_sync(pcmb200_ctx *ctx);
+/* Number of this library's kernels launched through the context so far. */
+PCMB200_API int pcmb200_launch_count(const pcmb200_ctx *ctx, uint64_t *launches);
+/* Name, SM count and total memory of the context's device. */
+PCMB200_API int pcmb200_device_info(const pcmb200_ctx *ctx, char *name, size_t name_cap,
+                                    int *sm_count, size_t *total_mem);
+
+/* ---- frame arithmetic (host side, data independent) --------------------------------------- */
+
+/* Output length of resampleTo16k for an n_in-sample input: n_in at 16 kHz (App.tsx:22), else
+ * floor(n_in / (in_rate / 16000)) in binary64 (App.tsx:23-24).  PCMB200_ERR_RANGE where the
+ * reference's `new Float32Array(newLen)` throws (rate <= 0 ...); a NaN length gives 0. */
+PCMB200_API int pcmb200_resample_len(size_t n_in, double in_rate, size_t *n_out);
+/* The pick index of each of n_out output samples, from the reference's sequential binary64
+ * running sum `idx += ratio` (App.tsx:26-30).  0xFFFFFFFF marks a pick outside the input. */
+PCMB200_API int pcmb200_index_table(size_t n_in, double in_rate, size_t n_out, uint32_t *idx);
+
+/* ---- memory --------------------------------------------------------------------------------- */
+
+PCMB200_API int pcmb200_device_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr);
+PCMB200_API int pcmb200_device_free(pcmb200_ctx *ctx, void *ptr);
+/* Page-locked host memory: H2D/D2H of pinned buffers runs at PCIe speed and overlaps compute. */
+PCMB200_API int pcmb200_pinned_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr);
+PCMB200_API int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr);
+/* Blocking copies on the context's stream. */
+PCMB200_API int pcmb200_memcpy_h2d(pcmb200_ctx *ctx, void *dst_device, const void *src_host, size_t bytes);
+PCMB200_API int pcmb200_memcpy_d2h(pcmb200_ctx *ctx, void *dst_host, const void *src_device, size_t bytes);
+PCMB200_API int pcmb200_memset_device(pcmb200_ctx *ctx, void *dst_device, int value, size_t bytes);
+
+/* ---- the hot path ---------------------------------------------------------------------------- */
+
+/* floatTo16BitPCM (App.tsx:7-16) over n samples: clamp to [-1,1], scale by 0x8000 (negative) or
+ * 0x7fff, truncate toward zero; NaN -> 0.  Bit-exact with the reference's binary64 arithmetic. */
+PCMB200_API int pcmb200_encode_f32_s16(pcmb200_ctx *ctx, const float *in, int16_t *out, size_t n, int mem);
+
+/* resampleTo16k (App.tsx:18-32): nearest-sample pick with the reference's running-sum indices,
+ * Float32 in, Float32 out (bit patterns copied unmodified).  out_cap is in elements; *n_out is
+ * set to the produced length.  At 16 kHz the reference returns its input; here that is a copy. */
+PCMB200_API int pcmb200_resample_to_16k(pcmb200_ctx *ctx, const float *in, size_t n_in, double in_rate,
+                                        float *out, size_t out_cap, size_t *n_out, int mem);
+
+/* The fused frame path (App.tsx:281-282) over a batch: for each of `rows` frames of n_in samples
+ * at in_rate, out_row = floatTo16BitPCM(resampleTo16k(in_row, in_rate)); no intermediate Float32
+ * array is materialised.  Every frame restarts the pick phase at 0 and drops its tail, as the
+ * reference does at each flush (App.tsx:26, :286-287).  *n_out (may be NULL) receives the
+ * per-row output length; pitch_out must be >= that length. */
+PCMB200_API int pcmb200_frames_encode(pcmb200_ctx *ctx, const float *in, size_t pitch_in,
+                                      int16_t *out, size_t pitch_out, uint32_t rows, uint32_t n_in,
+                                      double in_rate, int mem, size_t *n_out);
+
+/* ---- measurement helpers (used by bench.py and the tests; not part of the reference surface) -- */
+
+/* Fill a device matrix with the benchmark's synthetic audio: per row
+ * x[n] = A*sin(2*pi*f*n/rate) + 0.05*u, f = 110 + 7*(session mod 512) Hz, A = 1.2 for every 8th
+ * session else 0.5, u ~ U[-1,1) from a counter-based hash of (seed, session, n);
+ * session = row0 + row. */
+PCMB200_API int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out_device, size_t pitch, uint32_t rows,
+                                   uint32_t n, double rate, uint64_t seed, uint64_t row0);
+/* CUDA-event stopwatch on the context's stream: everything the context enqueues between start and
+ * stop (the pipelined host path included) is inside the measured interval. */
+PCMB200_API int pcmb200_timer_start(pcmb200_ctx *ctx);
+PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
+/* Tuning knobs for sweeps: "block" (threads per block), "blocks_per_sm", "unroll",
+ * "path" (0 auto, 1 force the gather kernel), "slice_bytes" (host pipeline slice), "store_hint". */
+PCMB200_API int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCM_B200_H */

@@ -44,6 +44,12 @@
 ORACLE_API int16_t oracle_to_int16(double v)
 {
     if (!isfinite(v)) return 0;                    /* NaN, +Inf, -Inf -> +0 */
+    if (v > -2147483648.0 && v < 2147483648.0) {
+        /* common case, what a JS engine's typed-array store does: truncate to int32, keep the
+         * low 16 bits (two's complement) */
+        int32_t t = (int32_t)v;                    /* C conversion truncates toward zero */
+        return (int16_t)(uint16_t)((uint32_t)t & 0xFFFFu);
+    }
     double t = trunc(v);                           /* sign(v) * floor(abs(v)) */
     double m = fmod(t, 65536.0);                   /* C fmod keeps the sign of t */
     if (m < 0) m += 65536.0;                       /* int16bit = int modulo 2^16 */

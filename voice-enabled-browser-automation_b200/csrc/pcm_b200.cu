@@ -1,0 +1,703 @@
+// pcm_b200.cu -- C ABI (include/pcm_b200.h) over the kernels in pcm_kernels.cuh.
+//
+// Host-side runtime of the PCM front-end: context (device, stream, events), pick-index table
+// cache, staging pool + 3-stream H2D | kernel | D2H pipeline for host-resident batches, kernel
+// selection by ratio and alignment.  No PyTorch, no NCCL (sessions never exchange data), no CPU
+// compute path: if the device is missing the context cannot be created.
+#include "../../include/pcm_b200.h"
+#include "pcm_kernels.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace pcmb200;
+
+namespace {
+
+constexpr int kSlots = 3;
+constexpr size_t kMaxLuts = 32;
+
+struct Lut {
+    uint64_t rate_bits = 0;
+    uint32_t n_in = 0, n_out = 0;
+    uint32_t *dev = nullptr;
+    std::vector<uint32_t> host;
+};
+
+struct Slot {
+    cudaStream_t st = nullptr;
+    cudaEvent_t done = nullptr;
+    void *d_in = nullptr;
+    size_t in_cap = 0;
+    void *d_out = nullptr;
+    size_t out_cap = 0;
+};
+
+struct Tuning {
+    int block = 256;
+    int blocks_per_sm = 0;   // 0 = fill the SM (2048 / block)
+    int unroll = 0;          // 0 = per-ratio default
+    int path = 0;            // 1 = force the general pick kernel
+    int store_hint = 0;
+    size_t slice_bytes = 32u << 20;
+};
+
+thread_local std::string g_err;
+
+}  // namespace
+
+struct pcmb200_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_fork = nullptr, t0 = nullptr, t1 = nullptr;
+    bool timing = false;
+    uint64_t launches = 0;
+    Slot slots[kSlots];
+    std::vector<Lut> luts;
+    Tuning tune;
+    std::string err;
+};
+
+namespace {
+
+int fail(pcmb200_ctx *ctx, int status, const std::string &msg)
+{
+    g_err = msg;
+    if (ctx) ctx->err = msg;
+    return status;
+}
+
+#define CU(call)                                                                                     \
+    do {                                                                                             \
+        cudaError_t e__ = (call);                                                                    \
+        if (e__ != cudaSuccess)                                                                      \
+            return fail(ctx, e__ == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA, \
+                        std::string(#call) + ": " + cudaGetErrorString(e__));                        \
+    } while (0)
+
+#define NEED(cond, msg)                                                 \
+    do {                                                                \
+        if (!(cond)) return fail(ctx, PCMB200_ERR_INVALID, (msg));      \
+    } while (0)
+
+inline size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+// App.tsx:22-24.  status: 0 ok, PCMB200_ERR_RANGE where `new Float32Array(newLen)` throws.
+int resample_len(size_t n_in, double rate, size_t *n_out)
+{
+    if (rate == 16000.0) { *n_out = n_in; return PCMB200_OK; }
+    const double ratio = rate / 16000.0;
+    const double len = std::floor((double)n_in / ratio);
+    if (len != len) { *n_out = 0; return PCMB200_OK; }           // ToIndex(NaN) = 0
+    if (len < 0 || len > 4294967295.0) { *n_out = 0; return PCMB200_ERR_RANGE; }
+    *n_out = (size_t)len;
+    return PCMB200_OK;
+}
+
+// App.tsx:26-30: the reference's own loop, run once per (rate, length) on the host.  The table
+// depends only on (rate, n_in), never on sample data.
+void build_index_table(size_t n_in, double rate, size_t n_out, uint32_t *idx)
+{
+    const double ratio = rate / 16000.0;
+    double pos = 0.0;
+    for (size_t i = 0; i < n_out; i++) {
+        const double f = std::floor(pos);
+        idx[i] = (f >= 0 && f < (double)n_in) ? (uint32_t)f : 0xFFFFFFFFu;
+        pos += ratio;
+    }
+}
+
+// Integer ratio (rate a multiple of 16 kHz)?  Then idx = i * R exactly.
+bool integer_ratio(double rate, uint32_t *R)
+{
+    const double ratio = rate / 16000.0;
+    if (!(ratio >= 1.0 && ratio <= 65536.0)) return false;
+    const double fl = std::floor(ratio);
+    if (fl != ratio) return false;
+    *R = (uint32_t)fl;
+    return true;
+}
+
+int get_lut(pcmb200_ctx *ctx, uint32_t n_in, double rate, uint32_t n_out, const uint32_t **dev)
+{
+    uint64_t bits;
+    std::memcpy(&bits, &rate, 8);
+    for (auto &l : ctx->luts)
+        if (l.rate_bits == bits && l.n_in == n_in && l.n_out == n_out) { *dev = l.dev; return PCMB200_OK; }
+    if (ctx->luts.size() >= kMaxLuts) {   // evict the oldest; make sure nothing in flight reads it
+        CU(cudaDeviceSynchronize());
+        CU(cudaFree(ctx->luts.front().dev));
+        ctx->luts.erase(ctx->luts.begin());
+    }
+    Lut l;
+    l.rate_bits = bits;
+    l.n_in = n_in;
+    l.n_out = n_out;
+    try { l.host.resize(n_out); } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "index table: host allocation failed"); }
+    build_index_table(n_in, rate, n_out, l.host.data());
+    CU(cudaMalloc((void **)&l.dev, (size_t)n_out * 4));
+    // synchronous upload: the table is tiny and is built once per (rate, frame length)
+    cudaError_t e = cudaMemcpy(l.dev, l.host.data(), (size_t)n_out * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(l.dev); return fail(ctx, PCMB200_ERR_CUDA, std::string("index table upload: ") + cudaGetErrorString(e)); }
+    *dev = l.dev;
+    ctx->luts.push_back(std::move(l));
+    return PCMB200_OK;
+}
+
+// Persistent grid: one wave of resident blocks (SM count x blocks that fit per SM), fewer if
+// there is less work.  `resident` comes from the occupancy calculator for the kernel at hand.
+int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int resident)
+{
+    int bps = ctx->tune.blocks_per_sm > 0 ? ctx->tune.blocks_per_sm : resident;
+    if (bps < 1) bps = 1;
+    unsigned long long cap = (unsigned long long)ctx->sm_count * (unsigned long long)bps;
+    unsigned long long g = tiles < cap ? tiles : cap;
+    return g < 1 ? 1 : (int)g;
+}
+
+template <typename K>
+int resident_blocks(K kernel, int block)
+{
+    int n = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) {
+        cudaGetLastError();
+        n = 2048 / block;
+    }
+    return n;
+}
+
+template <int R, int U>
+void launch_decim(pcmb200_ctx *ctx, cudaStream_t st, bool dense, const float *in, size_t pitch_in, int16_t *out,
+                  size_t pitch_out, uint32_t rows, uint32_t cpr, uint32_t tail)
+{
+    const int block = ctx->tune.block;
+    const unsigned long long n_chunks = (unsigned long long)rows * cpr;
+    unsigned long long tiles = (n_chunks + (unsigned long long)block * U - 1) / ((unsigned long long)block * U);
+    if (tail) {   // make sure the tail loop has threads even when there are few chunks
+        unsigned long long t = ((unsigned long long)rows * tail + block - 1) / block;
+        if (t > tiles) tiles = t;
+    }
+    if (dense) {
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block));
+        k_decim_int<R, U, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
+    } else {
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block));
+        k_decim_int<R, U, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
+    }
+}
+
+template <int R>
+void launch_decim_u(pcmb200_ctx *ctx, cudaStream_t st, int U, bool dense, const float *in, size_t pitch_in,
+                    int16_t *out, size_t pitch_out, uint32_t rows, uint32_t cpr, uint32_t tail)
+{
+    switch (U) {
+    case 1: launch_decim<R, 1>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+    case 2: launch_decim<R, 2>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+    default: launch_decim<R, 4>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+    }
+}
+
+int default_unroll(uint32_t R)
+{
+    switch (R) {
+    case 1: return 4;
+    case 2: return 2;
+    case 3: return 2;
+    default: return 1;
+    }
+}
+
+// Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
+int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
+                  size_t pitch_out, uint32_t rows, uint32_t n_in, double rate, uint32_t n_out)
+{
+    if (rows == 0 || n_out == 0) return PCMB200_OK;
+    uint32_t R = 0;
+    const bool is_int = integer_ratio(rate, &R);
+    const bool fast_ok = is_int && (R == 1 || R == 2 || R == 3 || R == 4 || R == 6) && ctx->tune.path != 1 &&
+                         aligned(in, 32) && aligned(out, 16) && (pitch_in % 8 == 0 || rows == 1) &&
+                         (pitch_out % 8 == 0 || rows == 1);
+    if (fast_ok) {
+        // rows are split so that a launch indexes its chunks with 32 bits when it must divide
+        const uint32_t cpr = n_out / 8, tail = n_out % 8;
+        const bool dense = (tail == 0) && (rows == 1 || (pitch_in == (size_t)cpr * 8 * R && pitch_out == (size_t)cpr * 8));
+        int U = ctx->tune.unroll > 0 ? ctx->tune.unroll : default_unroll(R);
+        if (U == 3) U = 2;
+        if (U > 4) U = 4;
+        uint32_t max_rows = rows;
+        if (!dense && cpr > 0) {
+            const unsigned long long lim = 0xFFFFFFFFull / cpr;
+            if (lim < max_rows) max_rows = (uint32_t)(lim ? lim : 1);
+        }
+        for (uint32_t r0 = 0; r0 < rows; r0 += max_rows) {
+            const uint32_t nr = (rows - r0 < max_rows) ? rows - r0 : max_rows;
+            const float *pi = in + (size_t)r0 * pitch_in;
+            int16_t *po = out + (size_t)r0 * pitch_out;
+            switch (R) {
+            case 1: launch_decim_u<1>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 2: launch_decim_u<2>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 3: launch_decim_u<3>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 4: launch_decim_u<4>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            default: launch_decim_u<6>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            }
+            ctx->launches++;
+        }
+        CU(cudaGetLastError());
+        return PCMB200_OK;
+    }
+
+    const uint32_t *lut = nullptr;
+    if (!is_int) {
+        int s = get_lut(ctx, n_in, rate, n_out, &lut);
+        if (s) return s;
+    }
+    const bool pair32 = aligned(out, 4) && (pitch_out % 2 == 0 || rows == 1);
+    const int block = ctx->tune.block;
+    const unsigned long long n_pairs = (unsigned long long)rows * ((n_out + 1u) / 2u);
+    int U = ctx->tune.unroll > 0 ? ctx->tune.unroll : 4;
+    U = U >= 4 ? 4 : (U >= 2 ? 2 : 1);
+    const unsigned long long tiles = (n_pairs + (unsigned long long)block * U - 1) / ((unsigned long long)block * U);
+#define PICK(UU)                                                                                                      \
+    do {                                                                                                              \
+        if (pair32) {                                                                                                 \
+            const int grid = grid_for(ctx, tiles, resident_blocks(k_pick_encode<UU, true>, block));                   \
+            k_pick_encode<UU, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, n_out, lut, R, n_pairs); \
+        } else {                                                                                                      \
+            const int grid = grid_for(ctx, tiles, resident_blocks(k_pick_encode<UU, false>, block));                  \
+            k_pick_encode<UU, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, n_out, lut, R, n_pairs); \
+        }                                                                                                             \
+    } while (0)
+    if (U == 4) PICK(4); else if (U == 2) PICK(2); else PICK(1);
+#undef PICK
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCMB200_OK;
+}
+
+int slot_reserve(pcmb200_ctx *ctx, Slot &s, size_t in_bytes, size_t out_bytes)
+{
+    if (s.in_cap < in_bytes) {
+        CU(cudaStreamSynchronize(s.st));
+        if (s.d_in) CU(cudaFree(s.d_in));
+        s.d_in = nullptr; s.in_cap = 0;
+        CU(cudaMalloc(&s.d_in, in_bytes));
+        s.in_cap = in_bytes;
+    }
+    if (s.out_cap < out_bytes) {
+        CU(cudaStreamSynchronize(s.st));
+        if (s.d_out) CU(cudaFree(s.d_out));
+        s.d_out = nullptr; s.out_cap = 0;
+        CU(cudaMalloc(&s.d_out, out_bytes));
+        s.out_cap = out_bytes;
+    }
+    return PCMB200_OK;
+}
+
+// Host-resident batch: rows are cut into slices; slice k runs H2D -> kernel -> D2H on stream
+// k % 3, so the upload of one slice overlaps the kernel of the previous and the download of the one
+// before.  The three streams fork from / join the context's stream through events, so the
+// context's stopwatch and pcmb200_sync cover them.
+int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
+                uint32_t rows, uint32_t n_in, double rate, uint32_t n_out)
+{
+    if (rows == 0 || n_out == 0) return PCMB200_OK;
+    const size_t dpi = round_up(n_in, 8), dpo = round_up(n_out, 8);
+    size_t rps = ctx->tune.slice_bytes / (dpi * 4);
+    if (rps < 1) rps = 1;
+    if (rps > rows) rps = rows;
+    const size_t n_slices = (rows + rps - 1) / rps;
+    const int used = n_slices < (size_t)kSlots ? (int)n_slices : kSlots;
+
+    for (int i = 0; i < used; i++) {
+        int s = slot_reserve(ctx, ctx->slots[i], rps * dpi * 4, rps * dpo * 2);
+        if (s) return s;
+    }
+    CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    for (int i = 0; i < used; i++) CU(cudaStreamWaitEvent(ctx->slots[i].st, ctx->ev_fork, 0));
+
+    for (size_t k = 0; k < n_slices; k++) {
+        Slot &s = ctx->slots[k % kSlots];
+        const size_t r0 = k * rps;
+        const uint32_t nr = (uint32_t)((rows - r0 < rps) ? rows - r0 : rps);
+        const float *hin = in + r0 * pitch_in;
+        int16_t *hout = out + r0 * pitch_out;
+        if (pitch_in == dpi || nr == 1)
+            CU(cudaMemcpyAsync(s.d_in, hin, ((size_t)(nr - 1) * dpi + n_in) * 4, cudaMemcpyHostToDevice, s.st));
+        else
+            CU(cudaMemcpy2DAsync(s.d_in, dpi * 4, hin, pitch_in * 4, (size_t)n_in * 4, nr, cudaMemcpyHostToDevice, s.st));
+        int st = launch_frames(ctx, s.st, (const float *)s.d_in, dpi, (int16_t *)s.d_out, dpo, nr, n_in, rate, n_out);
+        if (st) return st;
+        if (pitch_out == dpo || nr == 1)
+            CU(cudaMemcpyAsync(hout, s.d_out, ((size_t)(nr - 1) * dpo + n_out) * 2, cudaMemcpyDeviceToHost, s.st));
+        else
+            CU(cudaMemcpy2DAsync(hout, pitch_out * 2, s.d_out, dpo * 2, (size_t)n_out * 2, nr, cudaMemcpyDeviceToHost, s.st));
+    }
+    for (int i = 0; i < used; i++) {
+        CU(cudaEventRecord(ctx->slots[i].done, ctx->slots[i].st));
+        CU(cudaStreamWaitEvent(ctx->stream, ctx->slots[i].done, 0));
+    }
+    return PCMB200_OK;
+}
+
+}  // namespace
+
+// ================================= C ABI ==========================================================
+
+extern "C" {
+
+int pcmb200_version(void) { return 1000; }
+
+const char *pcmb200_status_string(int status)
+{
+    switch (status) {
+    case PCMB200_OK: return "ok";
+    case PCMB200_ERR_INVALID: return "invalid argument";
+    case PCMB200_ERR_RANGE: return "RangeError: invalid typed array length";
+    case PCMB200_ERR_CUDA: return "CUDA error";
+    case PCMB200_ERR_NO_DEVICE: return "no usable CUDA device (this library has no CPU fallback)";
+    case PCMB200_ERR_NOMEM: return "out of memory";
+    case PCMB200_ERR_CAPACITY: return "output buffer too small";
+    default: return "unknown status";
+    }
+}
+
+int pcmb200_device_count(int *count)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(count, "pcmb200_device_count: count is NULL");
+    *count = 0;
+    cudaError_t e = cudaGetDeviceCount(count);
+    if (e != cudaSuccess || *count <= 0) {
+        *count = 0;
+        cudaGetLastError();
+        return fail(nullptr, PCMB200_ERR_NO_DEVICE, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+    }
+    return PCMB200_OK;
+}
+
+int pcmb200_ctx_create(int device, pcmb200_ctx **out)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(out, "pcmb200_ctx_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    if (pcmb200_device_count(&n) != PCMB200_OK) return PCMB200_ERR_NO_DEVICE;
+    if (device < 0 || device >= n) return fail(nullptr, PCMB200_ERR_INVALID, "pcmb200_ctx_create: device ordinal out of range");
+    pcmb200_ctx *c = new (std::nothrow) pcmb200_ctx();
+    if (!c) return fail(nullptr, PCMB200_ERR_NOMEM, "pcmb200_ctx_create: host allocation failed");
+    c->device = device;
+    ctx = c;
+    cudaError_t e;
+#define CREATE_STEP(call)                                                                   \
+    if ((e = (call)) != cudaSuccess) {                                                      \
+        std::string m = std::string(#call) + ": " + cudaGetErrorString(e);                  \
+        pcmb200_ctx_destroy(c);                                                             \
+        return fail(nullptr, PCMB200_ERR_CUDA, m);                                          \
+    }
+    CREATE_STEP(cudaSetDevice(device));
+    CREATE_STEP(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CREATE_STEP(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CREATE_STEP(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CREATE_STEP(cudaEventCreate(&c->t0));
+    CREATE_STEP(cudaEventCreate(&c->t1));
+    for (int i = 0; i < kSlots; i++) {
+        CREATE_STEP(cudaStreamCreateWithFlags(&c->slots[i].st, cudaStreamNonBlocking));
+        CREATE_STEP(cudaEventCreateWithFlags(&c->slots[i].done, cudaEventDisableTiming));
+    }
+#undef CREATE_STEP
+    *out = c;
+    return PCMB200_OK;
+}
+
+int pcmb200_ctx_destroy(pcmb200_ctx *ctx)
+{
+    if (!ctx) return PCMB200_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (auto &l : ctx->luts) cudaFree(l.dev);
+    for (int i = 0; i < kSlots; i++) {
+        if (ctx->slots[i].d_in) cudaFree(ctx->slots[i].d_in);
+        if (ctx->slots[i].d_out) cudaFree(ctx->slots[i].d_out);
+        if (ctx->slots[i].done) cudaEventDestroy(ctx->slots[i].done);
+        if (ctx->slots[i].st) cudaStreamDestroy(ctx->slots[i].st);
+    }
+    if (ctx->t0) cudaEventDestroy(ctx->t0);
+    if (ctx->t1) cudaEventDestroy(ctx->t1);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    cudaGetLastError();
+    delete ctx;
+    return PCMB200_OK;
+}
+
+const char *pcmb200_last_error(const pcmb200_ctx *ctx) { return ctx ? ctx->err.c_str() : g_err.c_str(); }
+
+int pcmb200_sync(pcmb200_ctx *ctx)
+{
+    NEED(ctx, "pcmb200_sync: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCMB200_OK;
+}
+
+int pcmb200_launch_count(const pcmb200_ctx *c, uint64_t *launches)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(c && launches, "pcmb200_launch_count: NULL argument");
+    *launches = c->launches;
+    return PCMB200_OK;
+}
+
+int pcmb200_device_info(const pcmb200_ctx *c, char *name, size_t name_cap, int *sm_count, size_t *total_mem)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(c, "pcmb200_device_info: ctx is NULL");
+    cudaDeviceProp p;
+    CU(cudaGetDeviceProperties(&p, c->device));
+    if (name && name_cap) { std::strncpy(name, p.name, name_cap - 1); name[name_cap - 1] = 0; }
+    if (sm_count) *sm_count = p.multiProcessorCount;
+    if (total_mem) *total_mem = p.totalGlobalMem;
+    return PCMB200_OK;
+}
+
+int pcmb200_resample_len(size_t n_in, double in_rate, size_t *n_out)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(n_out, "pcmb200_resample_len: n_out is NULL");
+    int s = resample_len(n_in, in_rate, n_out);
+    if (s) return fail(nullptr, s, "pcmb200_resample_len: RangeError: invalid typed array length");
+    return PCMB200_OK;
+}
+
+int pcmb200_index_table(size_t n_in, double in_rate, size_t n_out, uint32_t *idx)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(idx || n_out == 0, "pcmb200_index_table: idx is NULL");
+    build_index_table(n_in, in_rate, n_out, idx);
+    return PCMB200_OK;
+}
+
+int pcmb200_device_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr)
+{
+    NEED(ctx && ptr, "pcmb200_device_alloc: NULL argument");
+    *ptr = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaMalloc(ptr, bytes ? bytes : 1));
+    return PCMB200_OK;
+}
+
+int pcmb200_device_free(pcmb200_ctx *ctx, void *ptr)
+{
+    NEED(ctx, "pcmb200_device_free: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    if (ptr) CU(cudaFree(ptr));
+    return PCMB200_OK;
+}
+
+int pcmb200_pinned_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr)
+{
+    NEED(ctx && ptr, "pcmb200_pinned_alloc: NULL argument");
+    *ptr = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault));
+    return PCMB200_OK;
+}
+
+int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr)
+{
+    NEED(ctx, "pcmb200_pinned_free: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    if (ptr) CU(cudaFreeHost(ptr));
+    return PCMB200_OK;
+}
+
+int pcmb200_memcpy_h2d(pcmb200_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    NEED(ctx && (bytes == 0 || (dst && src)), "pcmb200_memcpy_h2d: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    if (bytes) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCMB200_OK;
+}
+
+int pcmb200_memcpy_d2h(pcmb200_ctx *ctx, void *dst, const void *src, size_t bytes)
+{
+    NEED(ctx && (bytes == 0 || (dst && src)), "pcmb200_memcpy_d2h: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    if (bytes) CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCMB200_OK;
+}
+
+int pcmb200_memset_device(pcmb200_ctx *ctx, void *dst, int value, size_t bytes)
+{
+    NEED(ctx && (bytes == 0 || dst), "pcmb200_memset_device: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    if (bytes) CU(cudaMemsetAsync(dst, value, bytes, ctx->stream));
+    return PCMB200_OK;
+}
+
+int pcmb200_frames_encode(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
+                          uint32_t rows, uint32_t n_in, double in_rate, int mem, size_t *n_out_p)
+{
+    NEED(ctx, "pcmb200_frames_encode: ctx is NULL");
+    NEED(mem == PCMB200_MEM_HOST || mem == PCMB200_MEM_DEVICE, "pcmb200_frames_encode: bad mem kind");
+    size_t n_out = 0;
+    int s = resample_len(n_in, in_rate, &n_out);
+    if (s) return fail(ctx, s, "pcmb200_frames_encode: RangeError: invalid typed array length");
+    if (n_out_p) *n_out_p = n_out;
+    if (rows == 0 || n_out == 0) return PCMB200_OK;
+    NEED(in && out, "pcmb200_frames_encode: NULL buffer");
+    NEED(pitch_in >= n_in || rows == 1, "pcmb200_frames_encode: pitch_in < n_in");
+    NEED(pitch_out >= n_out || rows == 1, "pcmb200_frames_encode: pitch_out < output length");
+    CU(cudaSetDevice(ctx->device));
+    if (mem == PCMB200_MEM_DEVICE)
+        return launch_frames(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, in_rate, (uint32_t)n_out);
+    if (in_rate != 16000.0) {   // build / fetch the pick table before the streams fork
+        uint32_t R;
+        if (!integer_ratio(in_rate, &R)) {
+            const uint32_t *lut;
+            s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
+            if (s) return s;
+        }
+    }
+    s = frames_host(ctx, in, pitch_in, out, pitch_out, rows, n_in, in_rate, (uint32_t)n_out);
+    if (s) return s;
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCMB200_OK;
+}
+
+int pcmb200_encode_f32_s16(pcmb200_ctx *ctx, const float *in, int16_t *out, size_t n, int mem)
+{
+    NEED(ctx, "pcmb200_encode_f32_s16: ctx is NULL");
+    NEED(mem == PCMB200_MEM_HOST || mem == PCMB200_MEM_DEVICE, "pcmb200_encode_f32_s16: bad mem kind");
+    if (n == 0) return PCMB200_OK;
+    NEED(in && out, "pcmb200_encode_f32_s16: NULL buffer");
+    // Length-preserving and position-independent, so a long buffer is cut into 4 Mi-sample rows
+    // (keeps every launch's indices in 32 bits and gives the host pipeline slices to overlap).
+    const size_t row = (size_t)1 << 22;
+    const size_t full = n / row, rem = n % row;
+    size_t done = 0;
+    while (done < full) {
+        const uint32_t nr = (uint32_t)((full - done) < 512 ? (full - done) : 512);
+        int s = pcmb200_frames_encode(ctx, in + done * row, row, out + done * row, row, nr, (uint32_t)row, 16000.0, mem, nullptr);
+        if (s) return s;
+        done += nr;
+    }
+    if (rem) return pcmb200_frames_encode(ctx, in + full * row, rem, out + full * row, rem, 1, (uint32_t)rem, 16000.0, mem, nullptr);
+    return PCMB200_OK;
+}
+
+int pcmb200_resample_to_16k(pcmb200_ctx *ctx, const float *in, size_t n_in, double in_rate, float *out,
+                            size_t out_cap, size_t *n_out_p, int mem)
+{
+    NEED(ctx, "pcmb200_resample_to_16k: ctx is NULL");
+    NEED(mem == PCMB200_MEM_HOST || mem == PCMB200_MEM_DEVICE, "pcmb200_resample_to_16k: bad mem kind");
+    NEED(n_in <= 0xFFFFFFFFull, "pcmb200_resample_to_16k: input longer than 2^32-1 samples");
+    size_t n_out = 0;
+    int s = resample_len(n_in, in_rate, &n_out);
+    if (s) return fail(ctx, s, "pcmb200_resample_to_16k: RangeError: invalid typed array length");
+    if (n_out_p) *n_out_p = n_out;
+    if (n_out == 0) return PCMB200_OK;
+    NEED(in && out, "pcmb200_resample_to_16k: NULL buffer");
+    if (out_cap < n_out) return fail(ctx, PCMB200_ERR_CAPACITY, "pcmb200_resample_to_16k: out_cap < output length");
+    CU(cudaSetDevice(ctx->device));
+    uint32_t R = 1;
+    const uint32_t *lut = nullptr;
+    if (in_rate != 16000.0 && !integer_ratio(in_rate, &R)) {
+        s = get_lut(ctx, (uint32_t)n_in, in_rate, (uint32_t)n_out, &lut);
+        if (s) return s;
+    }
+    const float *din = in;
+    float *dout = out;
+    if (mem == PCMB200_MEM_HOST) {
+        Slot &sl = ctx->slots[0];
+        s = slot_reserve(ctx, sl, n_in * 4, n_out * 4);
+        if (s) return s;
+        CU(cudaMemcpyAsync(sl.d_in, in, n_in * 4, cudaMemcpyHostToDevice, ctx->stream));
+        din = (const float *)sl.d_in;
+        dout = (float *)sl.d_out;
+    }
+    const int block = 256;
+    const int grid = grid_for(ctx, (n_out + block - 1) / block, 2048 / block);
+    k_pick_f32<<<grid, block, 0, ctx->stream>>>((const uint32_t *)din, n_in, (uint32_t *)dout, n_out, (uint32_t)n_in,
+                                               (uint32_t)n_out, lut, R, n_out);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (mem == PCMB200_MEM_HOST) {
+        CU(cudaMemcpyAsync(out, dout, n_out * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return PCMB200_OK;
+}
+
+int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out, size_t pitch, uint32_t rows, uint32_t n, double rate,
+                       uint64_t seed, uint64_t row0)
+{
+    NEED(ctx, "pcmb200_synth_fill: ctx is NULL");
+    if (rows == 0 || n == 0) return PCMB200_OK;
+    NEED(out && pitch >= n && rate > 0, "pcmb200_synth_fill: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    const unsigned long long total = (unsigned long long)rows * n;
+    const int grid = grid_for(ctx, (total + 255) / 256, 8);
+    k_synth<<<grid, 256, 0, ctx->stream>>>(out, pitch, rows, n, (float)(1.0 / rate), seed, row0);
+    CU(cudaGetLastError());
+    return PCMB200_OK;
+}
+
+int pcmb200_timer_start(pcmb200_ctx *ctx)
+{
+    NEED(ctx, "pcmb200_timer_start: ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->t0, ctx->stream));
+    ctx->timing = true;
+    return PCMB200_OK;
+}
+
+int pcmb200_timer_stop(pcmb200_ctx *ctx, float *ms)
+{
+    NEED(ctx && ms, "pcmb200_timer_stop: NULL argument");
+    NEED(ctx->timing, "pcmb200_timer_stop: timer was not started");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventRecord(ctx->t1, ctx->stream));
+    CU(cudaEventSynchronize(ctx->t1));
+    CU(cudaEventElapsedTime(ms, ctx->t0, ctx->t1));
+    ctx->timing = false;
+    return PCMB200_OK;
+}
+
+int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
+{
+    NEED(ctx && key, "pcmb200_tune: NULL argument");
+    const std::string k(key);
+    if (k == "block") {
+        NEED(value >= 32 && value <= 512 && value % 32 == 0, "pcmb200_tune: block must be a multiple of 32 in [32, 512]");
+        ctx->tune.block = (int)value;
+    } else if (k == "blocks_per_sm") {
+        NEED(value >= 0 && value <= 32, "pcmb200_tune: blocks_per_sm must be in [0, 32]");
+        ctx->tune.blocks_per_sm = (int)value;
+    } else if (k == "unroll") {
+        NEED(value >= 0 && value <= 4, "pcmb200_tune: unroll must be 0 (default), 1, 2 or 4");
+        ctx->tune.unroll = (int)value;
+    } else if (k == "path") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: path must be 0 or 1");
+        ctx->tune.path = (int)value;
+    } else if (k == "store_hint") {
+        NEED(value >= 0 && value <= 2, "pcmb200_tune: store_hint must be 0, 1 or 2");
+        ctx->tune.store_hint = (int)value;
+    } else if (k == "slice_bytes") {
+        NEED(value >= 4096, "pcmb200_tune: slice_bytes must be >= 4096");
+        ctx->tune.slice_bytes = (size_t)value;
+    } else {
+        return fail(ctx, PCMB200_ERR_INVALID, "pcmb200_tune: unknown key " + k);
+    }
+    return PCMB200_OK;
+}
+
+}  // extern "C"

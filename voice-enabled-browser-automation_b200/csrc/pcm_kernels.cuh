@@ -1,0 +1,247 @@
+// pcm_kernels.cuh -- device code of the B200 PCM front-end (sm_100a).
+//
+// Everything here is HBM-bound streaming work: one pass over Float32 frames in, Int16 frames
+// out, 4*N_in + 2*N_out algorithmic bytes per frame and a handful of ALU ops per sample.  No
+// tensor cores, no shared-memory reuse (the reference's decimator has zero taps: it PICKS
+// samples, App.tsx:27-30), so the design rules are: 256-bit / 128-bit fully coalesced global
+// accesses, enough independent loads in flight per SM to cover HBM latency, streaming cache
+// hints so 4.7 GB ticks do not thrash L2, and persistent grids sized in multiples of the SM count.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pcmb200 {
+
+// ---- 256-bit global load (sm_100+: LDG.E.256), read-only path, no L1 allocation, L2 evict-first
+struct __align__(32) f32x8 { float v[8]; };
+
+__device__ __forceinline__ f32x8 ld_stream_256(const float *p)
+{
+    f32x8 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::evict_first.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]),
+                   "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+                 : "l"(p));
+    return r;
+}
+
+// 128-bit store; `hint` is a launch-uniform tuning knob (0 default write-back, 1 streaming .cs,
+// 2 L1::no_allocate).
+__device__ __forceinline__ void st_128(int16_t *p, uint4 v, int hint)
+{
+    if (hint == 1)
+        asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    else if (hint == 2)
+        asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    else
+        *reinterpret_cast<uint4 *>(p) = v;
+}
+
+// ---- the encoder (App.tsx:10-14), bit-exact without any binary64 arithmetic ------------------
+// JS computes v = s * 0x7fff (or 0x8000) exactly-rounded in binary64 -- for a float32 s the
+// product has <= 39 significant bits, so it is EXACT -- and the Int16Array store truncates toward
+// zero.  A round-to-nearest fp32 product is wrong (it can round up to an integer the exact product
+// never reaches).  A round-TOWARD-ZERO fp32 product is right: every integer below 2^24 is an fp32
+// value, so rounding the exact product toward zero can never cross an integer, hence
+// trunc(RZ32(s*c)) == trunc(s*c).  The clamp to [-1,1] commutes with the (monotonic) scaling and
+// becomes a saturating s32->s16 pack; cvt.rzi maps NaN to 0 and +-Inf to INT_MAX/INT_MIN, which
+// the saturating pack turns into 32767 / -32768, exactly what clamp-then-scale gives.
+// Checked exhaustively over all 2^32 float32 bit patterns (tests/test_gpu_exhaustive.py).
+// Must NOT be compiled with --use_fast_math / -ftz=true (denormal inputs must not flush).
+__device__ __forceinline__ int enc_s32(float s)
+{
+    const float c = (s < 0.0f) ? 32768.0f : 32767.0f;   // NaN and -0 take the 0x7fff side, like JS `s < 0`
+    return __float2int_rz(__fmul_rz(s, c));
+}
+__device__ __forceinline__ uint32_t pack_s16x2_sat(int lo, int hi)
+{
+    uint32_t d;
+    asm("cvt.pack.sat.s16.s32 %0, %1, %2;" : "=r"(d) : "r"(hi), "r"(lo));   // d = {sat16(hi), sat16(lo)}
+    return d;
+}
+__device__ __forceinline__ int16_t enc_s16(float s)
+{
+    return (int16_t)(pack_s16x2_sat(enc_s32(s), 0) & 0xFFFFu);
+}
+
+// ---- kernel 1: integer-ratio decimate + encode, 256-bit loads / 128-bit stores ----------------
+// One work item ("chunk") = 8 consecutive output samples of one row = 8*R consecutive input floats
+// (R = in_rate / 16000, an integer; R = 1 is encode-only).  A thread reads the chunk with R
+// 256-bit loads (each warp-level load touches 32 whole 32-byte sectors), keeps every R-th float
+// (the running sum idx += R is exact, so floor(idx) = i*R, App.tsx:27-29), encodes and writes one
+// 128-bit store; a warp's stores cover 512 contiguous bytes.  U chunks per thread are issued
+// before the first use, so R*U*32 bytes per thread are in flight.
+//   DENSE: rows are back to back with n_in == 8*R*cpr, so chunk w starts at in + w*8*R and the
+//   whole batch is one flat stream (no division).  Otherwise row = w / cpr.
+// Requirements (checked by the launcher): in 32-byte aligned, pitch_in % 8 == 0, out 16-byte
+// aligned, pitch_out % 8 == 0.  The n_out % 8 tail of each row is done by scalar code at the end.
+template <int R, int U, bool DENSE>
+__global__ void __launch_bounds__(512)
+k_decim_int(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict__ out, size_t pitch_out,
+            uint32_t rows, uint32_t cpr, uint32_t tail, unsigned long long n_chunks, int hint)
+{
+    const unsigned long long tile_chunks = (unsigned long long)blockDim.x * U;
+    const unsigned long long n_tiles = (n_chunks + tile_chunks - 1) / tile_chunks;
+
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const unsigned long long w0 = tile * tile_chunks + threadIdx.x;
+        const bool full = (tile + 1) * tile_chunks <= n_chunks;
+        f32x8 v[U][R];
+        int16_t *dst[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const unsigned long long w = w0 + (unsigned long long)u * blockDim.x;
+            dst[u] = nullptr;
+            if (full || w < n_chunks) {
+                const float *src;
+                if (DENSE) {
+                    src = in + w * (8ull * R);
+                    dst[u] = out + w * 8ull;
+                } else {
+                    const uint32_t w32 = (uint32_t)w;
+                    const uint32_t r = w32 / cpr, c = w32 - r * cpr;
+                    src = in + (size_t)r * pitch_in + (size_t)c * (8u * R);
+                    dst[u] = out + (size_t)r * pitch_out + (size_t)c * 8u;
+                }
+#pragma unroll
+                for (int k = 0; k < R; k++) v[u][k] = ld_stream_256(src + 8 * k);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (full || dst[u] != nullptr) {
+                int e[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) e[j] = enc_s32(v[u][(j * R) / 8].v[(j * R) % 8]);
+                uint4 o;
+                o.x = pack_s16x2_sat(e[0], e[1]);
+                o.y = pack_s16x2_sat(e[2], e[3]);
+                o.z = pack_s16x2_sat(e[4], e[5]);
+                o.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(dst[u], o, hint);
+            }
+        }
+    }
+
+    if (tail) {   // the last n_out % 8 samples of every row
+        const unsigned long long total = (unsigned long long)rows * tail;
+        for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+             t += (unsigned long long)gridDim.x * blockDim.x) {
+            const size_t r = (size_t)(t / tail);
+            const uint32_t o = cpr * 8u + (uint32_t)(t - (unsigned long long)r * tail);
+            out[r * pitch_out + o] = enc_s16(__ldg(in + r * pitch_in + (size_t)o * R));
+        }
+    }
+}
+
+// ---- kernel 2: general pick + encode (any ratio, any alignment) -----------------------------------
+// For rates whose ratio is not an integer (44.1 kHz family: the reference's running binary64 sum
+// drifts from the rational index) the pick indices come from a table built on the host
+// with the reference's own sequential loop and shared by every row of the batch (`lut`, n_out
+// entries, L1/L2 resident).  lut == nullptr means idx = o * stride (integer ratio, used when the
+// buffers do not meet kernel 1's alignment rules).
+// A work item is a PAIR of adjacent outputs (o, o+1) of one row; lane i of a warp takes pair
+// w0 + i, so one warp-level gather touches a ~64*ratio*4-byte contiguous span (every sector of it
+// is used) and one warp-level store writes 128 contiguous bytes.  U pairs per thread in flight.
+//   PAIR32: out rows are 4-byte aligned (base % 4 == 0, pitch_out even) -> 32-bit stores;
+//   otherwise 16-bit stores.
+template <int U, bool PAIR32>
+__global__ void __launch_bounds__(512)
+k_pick_encode(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict__ out, size_t pitch_out,
+              uint32_t n_in, uint32_t n_out, const uint32_t *__restrict__ lut, uint32_t stride,
+              unsigned long long n_pairs)
+{
+    const uint32_t ppr = (n_out + 1u) >> 1;   // pairs per row
+    const unsigned long long tile_pairs = (unsigned long long)blockDim.x * U;
+    const unsigned long long n_tiles = (n_pairs + tile_pairs - 1) / tile_pairs;
+
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const unsigned long long w0 = tile * tile_pairs + threadIdx.x;
+        float a[U], b[U];
+        int16_t *dst[U];
+        bool two[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const unsigned long long w = w0 + (unsigned long long)u * blockDim.x;
+            dst[u] = nullptr;
+            two[u] = false;
+            a[u] = b[u] = 0.0f;
+            if (w < n_pairs) {
+                const unsigned long long r = w / ppr;
+                const uint32_t o = (uint32_t)(w - r * ppr) * 2u;
+                const float *row = in + (size_t)r * pitch_in;
+                dst[u] = out + (size_t)r * pitch_out + o;
+                two[u] = (o + 1u < n_out);
+                uint32_t i0, i1 = 0xFFFFFFFFu;
+                if (lut) {
+                    i0 = __ldg(lut + o);
+                    if (two[u]) i1 = __ldg(lut + o + 1);
+                } else {
+                    i0 = o * stride;
+                    i1 = i0 + stride;
+                }
+                // a pick outside the input reads `undefined` in JS -> NaN -> 0 after the encoder
+                a[u] = (i0 < n_in) ? __ldg(row + i0) : __int_as_float(0x7FC00000);
+                b[u] = (two[u] && i1 < n_in) ? __ldg(row + i1) : __int_as_float(0x7FC00000);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (dst[u] != nullptr) {
+                const uint32_t p = pack_s16x2_sat(enc_s32(a[u]), enc_s32(b[u]));
+                if (PAIR32 && two[u]) {
+                    *reinterpret_cast<uint32_t *>(dst[u]) = p;
+                } else {
+                    dst[u][0] = (int16_t)(p & 0xFFFFu);
+                    if (two[u]) dst[u][1] = (int16_t)(p >> 16);
+                }
+            }
+        }
+    }
+}
+
+// ---- kernel 3: resampleTo16k alone (Float32 -> Float32 picks; App.tsx:18-32) ------------------------
+// Only for signature parity with the reference's stand-alone function; the batched product path is
+// the fused kernels above.  Bit patterns are moved as 32-bit words so NaN payloads survive.
+__global__ void __launch_bounds__(256)
+k_pick_f32(const uint32_t *__restrict__ in, size_t pitch_in, uint32_t *__restrict__ out, size_t pitch_out,
+           uint32_t n_in, uint32_t n_out, const uint32_t *__restrict__ lut, uint32_t stride,
+           unsigned long long total)
+{
+    for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long r = t / n_out;
+        const uint32_t o = (uint32_t)(t - r * n_out);
+        const uint32_t i = lut ? __ldg(lut + o) : o * stride;
+        out[(size_t)r * pitch_out + o] = (i < n_in) ? __ldg(in + (size_t)r * pitch_in + i) : 0x7FC00000u;
+    }
+}
+
+// ---- synthetic audio for the benchmarks -----------------------------------------------
+__device__ __forceinline__ uint64_t mix64(uint64_t z)
+{
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+k_synth(float *__restrict__ out, size_t pitch, uint32_t rows, uint32_t n, float inv_rate,
+        uint64_t seed, uint64_t row0)
+{
+    const unsigned long long total = (unsigned long long)rows * n;
+    for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (unsigned long long)gridDim.x * blockDim.x) {
+        const uint32_t r = (uint32_t)(t / n);
+        const uint32_t k = (uint32_t)(t - (unsigned long long)r * n);
+        const uint64_t session = row0 + r;
+        const float f = 110.0f + 7.0f * (float)(session & 511u);
+        const float amp = ((session & 7u) == 7u) ? 1.2f : 0.5f;
+        const uint64_t h = mix64(mix64(seed ^ (session * 0xD1342543DE82EF95ull)) + k);
+        const float u = (float)(uint32_t)(h >> 40) * (1.0f / 8388608.0f) - 1.0f;   // U[-1, 1)
+        out[(size_t)r * pitch + k] = amp * sinpif(2.0f * f * (float)k * inv_rate) + 0.05f * u;
+    }
+}
+
+}  // namespace pcmb200
