@@ -30,9 +30,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "voice-enabled-browser-automation_b200"))
 
+RATE = 48000.0
 METRIC = "pcm_input_samples_per_s"
 UNIT = "samples/s"
-RATE = 48000.0
 FALLBACK_HBM_GBS = 6650.0     # B200_PROFILING.md fallback, used only if MEASURED_PEAKS.json is absent
 
 
@@ -45,6 +45,7 @@ def parse_args(argv=None):
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--sessions", type=int, default=1 << 20, help="concurrent sessions (per GPU when --scaling weak)")
     ap.add_argument("--frame-ms", type=int, default=20)
+    ap.add_argument("--rate", type=float, default=48000.0, help="capture rate of every session (Hz); BASELINE uses 48000")
     ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
                     help="weak: every GPU holds --sessions sessions; strong: --sessions are sharded over the GPUs")
     ap.add_argument("--no-e2e", action="store_true")
@@ -52,7 +53,10 @@ def parse_args(argv=None):
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
     ap.add_argument("--ref-sessions", type=int, default=1 << 16, help="sessions per step of --impl reference")
     ap.add_argument("--tune", default="", help="comma list key=value passed to pcmb200_tune (sweeps)")
-    return ap.parse_args(argv)
+    args = ap.parse_args(argv)
+    global RATE
+    RATE = float(args.rate)
+    return args
 
 
 def dist_env():
@@ -184,7 +188,7 @@ def hbm_peak():
 
 
 def workload_name(args, n_in, n_out):
-    return (f"BASELINE configs[3]: {args.sessions} concurrent 48 kHz mono sessions, {args.frame_ms} ms frames "
+    return (f"BASELINE configs[3]: {args.sessions} concurrent {RATE / 1000:g} kHz mono sessions, {args.frame_ms} ms frames "
             f"({n_in} in -> {n_out} out), decimate to 16 kHz + int16 encode + framing")
 
 
@@ -303,7 +307,9 @@ def run_b200(args):
     peak, peak_src = hbm_peak()
     achieved = algo_bytes * (args.steps / max(launches, 1)) / (kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "k_decim_int<3,U,dense>",
+                "traffic": None, "peak_source": peak_src,
+                "kernel": ("k_decim_int<R=%d>" % int(RATE // 16000)) if RATE % 16000 == 0 and int(RATE // 16000) in (1, 2, 3, 4, 6)
+                and "path=1" not in args.tune else "k_pick_encode",
                 "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": kernel_ms}
     tr = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu capture
     if os.path.exists(tr):
@@ -362,7 +368,7 @@ def run_b200(args):
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32->s16 (fp32 RZ product, exact)",
                 "data": "synthetic sine+noise generated on device (pcmb200_synth_fill, seed 0x5EED)",
                 "config": {"workload": workload_name(args, n_in, n_out), "sessions_per_gpu": S,
-                           "sessions_total": int(units / (n_in * args.steps)), "rate_hz": 48000,
+                           "sessions_total": int(units / (n_in * args.steps)), "rate_hz": RATE,
                            "frame_ms": args.frame_ms, "n_in": n_in, "n_out": n_out,
                            "parallelism": f"session-affine shards x{world}, no collectives",
                            "l2": f"inputs larger than L2: {n_buf} alternating tick buffers of {algo_bytes / 1e9:.2f} GB each",

@@ -42,7 +42,8 @@ struct Tuning {
     int blocks_per_sm = 0;   // 0 = fill the SM (2048 / block)
     int unroll = 0;          // 0 = per-ratio default
     int path = 0;            // 1 = force the general pick kernel
-    int store_hint = 0;
+    int store_hint = 1;      // st.global.cs: output frames are written once and not re-read
+    int coalesced = 1;       // dense integer-ratio batches: warp-coalesced kernel (1b) instead of kernel 1
     size_t slice_bytes = 32u << 20;
 };
 
@@ -152,9 +153,13 @@ int get_lut(pcmb200_ctx *ctx, uint32_t n_in, double rate, uint32_t n_out, const 
 
 // Persistent grid: one wave of resident blocks (SM count x blocks that fit per SM), fewer if
 // there is less work.  `resident` comes from the occupancy calculator for the kernel at hand.
-int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int resident)
+int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int resident, int preferred = 0)
 {
-    int bps = ctx->tune.blocks_per_sm > 0 ? ctx->tune.blocks_per_sm : resident;
+    // `preferred` (blocks per SM) is the measured sweet spot of a kernel: on B200 these streaming
+    // kernels peak with roughly 100 KB of loads in flight per SM and lose a few percent with more
+    // (profiles/sweep_r1.md), so the default grid is smaller than what would fit.
+    int bps = ctx->tune.blocks_per_sm > 0 ? ctx->tune.blocks_per_sm
+                                          : (preferred > 0 && preferred < resident ? preferred : resident);
     if (bps < 1) bps = 1;
     unsigned long long cap = (unsigned long long)ctx->sm_count * (unsigned long long)bps;
     unsigned long long g = tiles < cap ? tiles : cap;
@@ -184,11 +189,37 @@ void launch_decim(pcmb200_ctx *ctx, cudaStream_t st, bool dense, const float *in
         if (t > tiles) tiles = t;
     }
     if (dense) {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block));
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block), 768 / block);
         k_decim_int<R, U, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
     } else {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block));
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block), 768 / block);
         k_decim_int<R, U, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
+    }
+}
+
+template <int R, int U>
+void launch_coal(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *out, unsigned long long n_tiles)
+{
+    const int block = ctx->tune.block;
+    const int warps = block / 32;
+    const size_t smem = (size_t)warps * U * 256 * sizeof(int16_t);
+    int resident = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_decim_coal<R, U>, block, smem) != cudaSuccess || resident < 1) {
+        cudaGetLastError();
+        resident = 2048 / block;
+    }
+    const unsigned long long blocks_needed = (n_tiles + (unsigned long long)warps * U - 1) / ((unsigned long long)warps * U);
+    const int grid = grid_for(ctx, blocks_needed, resident, 1024 / (block * U));
+    k_decim_coal<R, U><<<grid, block, smem, st>>>(in, out, n_tiles, ctx->tune.store_hint);
+}
+
+template <int R>
+void launch_coal_u(pcmb200_ctx *ctx, cudaStream_t st, int U, const float *in, int16_t *out, unsigned long long n_tiles)
+{
+    switch (U) {
+    case 1: launch_coal<R, 1>(ctx, st, in, out, n_tiles); break;
+    case 2: launch_coal<R, 2>(ctx, st, in, out, n_tiles); break;
+    default: launch_coal<R, 4>(ctx, st, in, out, n_tiles); break;
     }
 }
 
@@ -205,12 +236,7 @@ void launch_decim_u(pcmb200_ctx *ctx, cudaStream_t st, int U, bool dense, const 
 
 int default_unroll(uint32_t R)
 {
-    switch (R) {
-    case 1: return 4;
-    case 2: return 2;
-    case 3: return 2;
-    default: return 1;
-    }
+    return R == 1 ? 2 : 1;   // measured: 64-96 bytes of loads in flight per thread are enough
 }
 
 // Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
@@ -230,6 +256,34 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
         int U = ctx->tune.unroll > 0 ? ctx->tune.unroll : default_unroll(R);
         if (U == 3) U = 2;
         if (U > 4) U = 4;
+        if (dense && R > 1 && ctx->tune.coalesced) {
+            // flat stream: full 256-output warp tiles go to the coalesced kernel, the rest to kernel 1
+            const unsigned long long total_out = (unsigned long long)rows * cpr * 8ull;
+            const unsigned long long n_tiles = total_out / 256ull;
+            if (n_tiles) {
+                switch (R) {
+                case 2: launch_coal_u<2>(ctx, st, U, in, out, n_tiles); break;
+                case 3: launch_coal_u<3>(ctx, st, U, in, out, n_tiles); break;
+                case 4: launch_coal_u<4>(ctx, st, U, in, out, n_tiles); break;
+                default: launch_coal_u<6>(ctx, st, U, in, out, n_tiles); break;
+                }
+                ctx->launches++;
+            }
+            const unsigned long long rest_chunks = (total_out - n_tiles * 256ull) / 8ull;
+            if (rest_chunks) {
+                const float *pi = in + n_tiles * 256ull * R;
+                int16_t *po = out + n_tiles * 256ull;
+                switch (R) {
+                case 2: launch_decim_u<2>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                case 3: launch_decim_u<3>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                case 4: launch_decim_u<4>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                default: launch_decim_u<6>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                }
+                ctx->launches++;
+            }
+            CU(cudaGetLastError());
+            return PCMB200_OK;
+        }
         uint32_t max_rows = rows;
         if (!dense && cpr > 0) {
             const unsigned long long lim = 0xFFFFFFFFull / cpr;
@@ -691,6 +745,9 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "store_hint") {
         NEED(value >= 0 && value <= 2, "pcmb200_tune: store_hint must be 0, 1 or 2");
         ctx->tune.store_hint = (int)value;
+    } else if (k == "coalesced") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: coalesced must be 0 or 1");
+        ctx->tune.coalesced = (int)value;
     } else if (k == "slice_bytes") {
         NEED(value >= 4096, "pcmb200_tune: slice_bytes must be >= 4096");
         ctx->tune.slice_bytes = (size_t)value;

@@ -134,6 +134,70 @@ k_decim_int(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict__
     }
 }
 
+// ---- kernel 1b: integer-ratio decimate + encode for DENSE batches, fully coalesced -------------
+// Same arithmetic as kernel 1, different data movement.  In kernel 1 a lane reads its own 8*R
+// consecutive floats, so for R > 1 one warp-level load touches 32-byte pieces 32*R bytes apart
+// and every 128-byte line is requested R times (with a quarter of its sectors each time).  Here a
+// WARP owns 256 consecutive outputs = 256*R consecutive floats and reads them with R warp-level
+// 256-bit loads that are each 1024 contiguous bytes (one request per line, all four sectors).  A
+// lane then holds 8*R floats of which exactly 8 are picks, but not 8 consecutive ones, so the
+// encoded int16 go through a 512-byte per-warp shared-memory tile and come back as one 128-bit,
+// fully coalesced store per lane.  Needs the batch to be one flat stream: rows back to back,
+// n_in == R * n_out (then the picks are the floats whose flat index is a multiple of R).
+template <int R, int U>
+__global__ void __launch_bounds__(512)
+k_decim_coal(const float *__restrict__ in, int16_t *__restrict__ out, unsigned long long n_tiles, int hint)
+{
+    extern __shared__ __align__(16) int16_t smem_tiles[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int warps_per_block = blockDim.x >> 5;
+    int16_t *my = smem_tiles + (size_t)warp * (U * 256);
+    constexpr int M = (8 + R - 1) / R;   // max picks in one 8-float group
+
+    const unsigned long long stride = (unsigned long long)gridDim.x * warps_per_block * U;
+    for (unsigned long long t0 = ((unsigned long long)blockIdx.x * warps_per_block + warp) * U; t0 < n_tiles; t0 += stride) {
+        f32x8 v[U][R];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (t0 + u < n_tiles) {
+                const float *src = in + (t0 + u) * (256ull * R) + lane * 8;
+#pragma unroll
+                for (int k = 0; k < R; k++) v[u][k] = ld_stream_256(src + 256 * k);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (t0 + u < n_tiles) {
+#pragma unroll
+                for (int k = 0; k < R; k++) {
+                    const int b = 256 * k + lane * 8;          // first float of this group within the tile
+                    const int e0 = (R - b % R) % R;            // offset of the first pick in the group
+                    const int j0 = (b + e0) / R;               // its output index within the tile
+#pragma unroll
+                    for (int m = 0; m < M; m++) {
+                        float x = 0.0f;
+                        bool have = false;
+#pragma unroll
+                        for (int e = 0; e < R; e++)
+                            if (e + m * R < 8 && e0 == e) { x = v[u][k].v[(e + m * R) & 7]; have = true; }
+                        if (have) my[u * 256 + j0 + m] = enc_s16(x);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (t0 + u < n_tiles) {
+                const uint4 o = *reinterpret_cast<const uint4 *>(my + u * 256 + lane * 8);
+                st_128(out + (t0 + u) * 256ull + lane * 8, o, hint);
+            }
+        }
+        __syncwarp();
+    }
+}
+
 // ---- kernel 2: general pick + encode (any ratio, any alignment) -----------------------------------
 // For rates whose ratio is not an integer (44.1 kHz family: the reference's running binary64 sum
 // drifts from the rational index) the pick indices come from a table built on the host

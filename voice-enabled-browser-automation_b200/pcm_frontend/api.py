@@ -48,15 +48,17 @@ class DeviceBuffer:
         self.ptr = p.value
 
     def offset(self, nbytes: int) -> int:
-        return self.ptr + int(nbytes)
+        return int(self.ptr + int(nbytes))
 
     def upload(self, host: np.ndarray, byte_offset: int = 0):
         host = np.ascontiguousarray(host)
+        byte_offset = int(byte_offset)
         assert byte_offset + host.nbytes <= self.nbytes
         check(load().pcmb200_memcpy_h2d(self.ctx.handle, self.ptr + byte_offset, host.ctypes.data, host.nbytes), self.ctx.handle)
 
     def download(self, dtype, count: int, byte_offset: int = 0) -> np.ndarray:
-        out = np.empty(count, dtype=dtype)
+        out = np.empty(int(count), dtype=dtype)
+        byte_offset = int(byte_offset)
         assert byte_offset + out.nbytes <= self.nbytes
         check(load().pcmb200_memcpy_d2h(self.ctx.handle, out.ctypes.data, self.ptr + byte_offset, out.nbytes), self.ctx.handle)
         return out
@@ -201,15 +203,17 @@ class Context:
                       out: Optional[np.ndarray] = None) -> np.ndarray:
         """floatTo16BitPCM(resampleTo16k(row, rate)) for every row of a [rows, pitch] float32 batch
         (App.tsx:281-282), fused on the device.  Returns [rows, n_out] int16."""
-        assert batch.ndim == 2 and batch.dtype == np.float32 and (batch.shape[1] == 0 or batch.strides[1] == 4)
+        if batch.ndim != 2 or batch.dtype != np.float32:
+            raise TypeError("expected a 2-D float32 batch [rows, samples]")
+        assert batch.size == 0 or batch.strides[1] == 4, "samples of a row must be contiguous"
         rows = batch.shape[0]
-        pitch_in = batch.strides[0] // 4 if rows > 1 else max(batch.shape[1], 1)
+        pitch_in = batch.strides[0] // 4 if rows > 1 and batch.size else max(batch.shape[1], 1)
         n_in = batch.shape[1] if n_in is None else int(n_in)
         n_out = resample_len(n_in, rate)
         if out is None:
             out = np.empty((rows, n_out), dtype=np.int16)
         assert out.dtype == np.int16 and out.shape[0] == rows and out.shape[1] >= n_out
-        pitch_out = out.strides[0] // 2 if rows > 1 and out.shape[1] else max(out.shape[1], 1)
+        pitch_out = out.strides[0] // 2 if rows > 1 and out.size else max(out.shape[1], 1)
         got = C.c_size_t(0)
         check(self._L.pcmb200_frames_encode(self.handle, batch.ctypes.data, pitch_in, out.ctypes.data, pitch_out,
                                             rows, n_in, float(rate), MEM_HOST, C.byref(got)), self.handle)
@@ -219,8 +223,8 @@ class Context:
     def frames_encode_ptr(self, in_ptr: int, pitch_in: int, out_ptr: int, pitch_out: int, rows: int,
                           n_in: int, rate: float, mem: int = MEM_DEVICE) -> int:
         got = C.c_size_t(0)
-        check(self._L.pcmb200_frames_encode(self.handle, in_ptr, pitch_in, out_ptr, pitch_out, rows, n_in,
-                                            float(rate), mem, C.byref(got)), self.handle)
+        check(self._L.pcmb200_frames_encode(self.handle, int(in_ptr), int(pitch_in), int(out_ptr), int(pitch_out),
+                                            int(rows), int(n_in), float(rate), int(mem), C.byref(got)), self.handle)
         return int(got.value)
 
     def encode_ptr(self, in_ptr: int, out_ptr: int, n: int, mem: int = MEM_DEVICE):
