@@ -187,6 +187,16 @@ def hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def kernel_name(args):
+    """The kernel pcmb200_frames_encode selects for a dense device-resident batch at RATE."""
+    r = int(RATE // 16000)
+    if RATE % 16000 != 0 or r not in (1, 2, 3, 4, 6) or "path=1" in args.tune:
+        return "k_pick_encode"
+    if r == 1 or "coalesced=0" in args.tune:
+        return f"k_decim_int<R={r}>"
+    return f"k_decim_coal<R={r}>"
+
+
 def workload_name(args, n_in, n_out):
     return (f"BASELINE configs[3]: {args.sessions} concurrent {RATE / 1000:g} kHz mono sessions, {args.frame_ms} ms frames "
             f"({n_in} in -> {n_out} out), decimate to 16 kHz + int16 encode + framing")
@@ -308,8 +318,7 @@ def run_b200(args):
     achieved = algo_bytes * (args.steps / max(launches, 1)) / (kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src,
-                "kernel": ("k_decim_int<R=%d>" % int(RATE // 16000)) if RATE % 16000 == 0 and int(RATE // 16000) in (1, 2, 3, 4, 6)
-                and "path=1" not in args.tune else "k_pick_encode",
+                "kernel": kernel_name(args),
                 "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": kernel_ms}
     tr = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu capture
     if os.path.exists(tr):

@@ -363,6 +363,10 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
     if (rows == 0 || n_out == 0) return PCMB200_OK;
     const size_t dpi = round_up(n_in, 8), dpo = round_up(n_out, 8);
     size_t rps = ctx->tune.slice_bytes / (dpi * 4);
+    // keep every slice a whole number of 256-output warp tiles so it needs one launch, not two
+    size_t tile_rows = 256;
+    for (size_t a = n_out, b = 256; b;) { size_t t = a % b; a = b; b = t; tile_rows = 256 / a; }
+    if (rps > tile_rows) rps -= rps % tile_rows;
     if (rps < 1) rps = 1;
     if (rps > rows) rps = rows;
     const size_t n_slices = (rows + rps - 1) / rps;
