@@ -136,6 +136,31 @@ PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
  * "path" (0 auto, 1 force the gather kernel), "slice_bytes" (host pipeline slice), "store_hint". */
 PCMB200_API int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value);
 
+/* ---- allocation-free variant ------------------------------------------------------------------ */
+
+/* No counterpart in the reference (which allocates fresh typed arrays on every call); added for
+ * callers that must not allocate device memory while they run: a real-time tick thread that cannot
+ * take the device-wide stall of cudaMalloc/cudaFree, or a process whose GPU memory is already owned
+ * by another framework's allocator, where a late cudaMalloc fails.
+ *
+ * Same result as pcmb200_frames_encode(..., PCMB200_MEM_DEVICE) for device-resident `in` / `out`,
+ * computed by the general pick kernel with its index table in a fixed 64 KiB array inside the
+ * library (held by every GPU that loads the library, until the process exits).  No context is
+ * needed and nothing is allocated, on the device or the host.
+ *   - limit: at most PCMB200_NOALLOC_MAX_OUT output samples per frame (about 1 s of 16 kHz audio);
+ *     longer frames return PCMB200_ERR_CAPACITY (message via pcmb200_last_error(NULL));
+ *   - the device holding in/out must be the calling thread's current device; `cuda_stream` is a
+ *     cudaStream_t (NULL = default stream); wait != 0 blocks until the output is complete;
+ *   - the first call on a device resolves the array's address: make it at start-up, before any
+ *     stream capture;
+ *   - all calls on a device share the array and it keeps the last call's table: calls whose GPU work
+ *     may overlap (issued on different streams) race and must be serialised by the caller; calls on
+ *     one stream are ordered by the stream and are safe. */
+#define PCMB200_NOALLOC_MAX_OUT 16384u
+PCMB200_API int pcmb200_frames_encode_noalloc(const float *in_device, size_t pitch_in, int16_t *out_device,
+                                              size_t pitch_out, uint32_t rows, uint32_t n_in, double in_rate,
+                                              void *cuda_stream, int wait, size_t *n_out);
+
 #ifdef __cplusplus
 }
 #endif

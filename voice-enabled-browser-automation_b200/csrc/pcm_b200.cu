@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -762,3 +763,114 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
 }
 
 }  // extern "C"
+
+// ================================= allocation-free entry point =====================================
+// pcmb200_frames_encode_noalloc: the general pick + encode kernel (k_pick_encode) with its pick-index
+// table held in a fixed array inside the library image instead of a cudaMalloc'd buffer.
+//
+// Who needs it.  The normal entry points grow a table cache and a staging pool with cudaMalloc the
+// first time they see a new (rate, frame length).  Two kinds of caller cannot live with that:
+//   * a voice server's real-time tick thread: cudaMalloc / cudaFree synchronise the whole device and
+//     take an unbounded time, so one new frame length would stall every session's audio;
+//   * a process that shares the GPU with an inference server whose caching allocator has already
+//     taken all device memory: a late cudaMalloc simply fails there.
+// This entry point never allocates (no cudaMalloc, cudaFree, cudaHostAlloc, stream or event
+// creation, no heap use on the host either): the caller passes device-resident input and output
+// and a stream; the only scratch is g_noalloc_table below.
+//
+// What to know before using it.
+//   * Limit: frames of at most PCMB200_NOALLOC_MAX_OUT (16384) output samples, about one second of
+//     16 kHz audio.  Longer frames are refused with PCMB200_ERR_CAPACITY.  The array costs 64 KiB
+//     of device memory on every GPU that loads the library, until the process exits.
+//   * The first call on each device looks up the array's device address; make that first call
+//     during start-up, and before any stream capture begins.
+//   * All calls on one device share the one array.  It keeps whatever the previous call wrote
+//     (entries past the current frame's length are stale and are never read; nothing in it has to
+//     start at zero, every entry a launch reads is rewritten first when the frame shape changes).
+//     Two calls whose GPU work can overlap (issued on different streams) race on it: serialise
+//     them.  Calls on one stream are ordered by the stream (the table upload of the second waits
+//     for the kernel of the first) and are safe.
+//   * The device that holds `in` and `out` must be the calling thread's current device.
+namespace {
+
+constexpr uint32_t kNoallocMaxOut = PCMB200_NOALLOC_MAX_OUT;
+constexpr int kNoallocMaxDevices = 64;
+
+// The scratch itself.  In HOST code this name is only a stand-in for the symbol; it is not a device
+// address and must never be handed to a kernel.  The address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) uint32_t g_noalloc_table[kNoallocMaxOut];
+
+struct NoallocDevice {
+    uint32_t *table = nullptr;     // device address of g_noalloc_table on this device
+    bool valid = false;            // table currently holds (rate_bits, n_in, n_out)
+    uint64_t rate_bits = 0;
+    uint32_t n_in = 0, n_out = 0;
+};
+NoallocDevice g_noalloc_dev[kNoallocMaxDevices];
+uint32_t g_noalloc_host[kNoallocMaxOut];   // host image of the table (static: no heap)
+std::mutex g_noalloc_mutex;
+
+}  // namespace
+
+extern "C" int pcmb200_frames_encode_noalloc(const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
+                                             uint32_t rows, uint32_t n_in, double in_rate, void *cuda_stream,
+                                             int wait, size_t *n_out_p)
+{
+    pcmb200_ctx *ctx = nullptr;   // errors go to the calling thread's slot: pcmb200_last_error(NULL)
+    size_t n_out = 0;
+    int s = resample_len(n_in, in_rate, &n_out);
+    if (s) return fail(nullptr, s, "pcmb200_frames_encode_noalloc: RangeError: invalid typed array length");
+    if (n_out_p) *n_out_p = n_out;
+    if (n_out > kNoallocMaxOut)
+        return fail(nullptr, PCMB200_ERR_CAPACITY,
+                    "pcmb200_frames_encode_noalloc: frame has " + std::to_string(n_out) +
+                        " output samples, the built-in table holds at most " + std::to_string(kNoallocMaxOut) +
+                        "; use pcmb200_frames_encode for longer frames");
+    if (rows == 0 || n_out == 0) return PCMB200_OK;
+    NEED(in && out, "pcmb200_frames_encode_noalloc: NULL buffer");
+    NEED(pitch_in >= n_in || rows == 1, "pcmb200_frames_encode_noalloc: pitch_in < n_in");
+    NEED(pitch_out >= n_out || rows == 1, "pcmb200_frames_encode_noalloc: pitch_out < output length");
+
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    int dev = -1;
+    CU(cudaGetDevice(&dev));
+    NEED(dev >= 0 && dev < kNoallocMaxDevices, "pcmb200_frames_encode_noalloc: device ordinal above 63");
+
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    NoallocDevice &d = g_noalloc_dev[dev];
+    if (!d.table) {   // once per device, with that device current
+        uint32_t *p = nullptr;
+        CU(cudaGetSymbolAddress((void **)&p, g_noalloc_table));
+        NEED(p != nullptr, "pcmb200_frames_encode_noalloc: cudaGetSymbolAddress returned NULL");
+        d.table = p;
+    }
+    uint64_t bits;
+    std::memcpy(&bits, &in_rate, 8);
+    if (!(d.valid && d.rate_bits == bits && d.n_in == n_in && d.n_out == (uint32_t)n_out)) {
+        d.valid = false;
+        build_index_table(n_in, in_rate, n_out, g_noalloc_host);       // App.tsx:26-30, on the host
+        // pageable source: the call returns once g_noalloc_host has been staged, so the static host
+        // image may be reused by the next call
+        CU(cudaMemcpyAsync(d.table, g_noalloc_host, n_out * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+        d.rate_bits = bits;
+        d.n_in = n_in;
+        d.n_out = (uint32_t)n_out;
+        d.valid = true;
+    }
+
+    const bool pair32 = aligned(out, 4) && (pitch_out % 2 == 0 || rows == 1);
+    const int block = 256;
+    const unsigned long long n_pairs = (unsigned long long)rows * ((n_out + 1u) / 2u);
+    const unsigned long long tiles = (n_pairs + (unsigned long long)block * 4 - 1) / ((unsigned long long)block * 4);
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const unsigned long long cap = (unsigned long long)sms * 8ull;
+    const int grid = (int)(tiles < cap ? (tiles ? tiles : 1) : cap);
+    if (pair32)
+        k_pick_encode<4, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, (uint32_t)n_out, d.table, 0, n_pairs);
+    else
+        k_pick_encode<4, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, (uint32_t)n_out, d.table, 0, n_pairs);
+    CU(cudaGetLastError());
+    if (wait) CU(cudaStreamSynchronize(st));
+    return PCMB200_OK;
+}
