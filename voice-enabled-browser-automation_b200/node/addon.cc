@@ -1,0 +1,224 @@
+// addon.cc -- thin N-API shim over the C ABI of libpcm_b200.so (include/pcm_b200.h).
+//
+// Exports the reference's two signatures unchanged (apps/web/src/App.tsx:7, :18-21) plus the batched
+// frame call, so `floatTo16BitPCM(resampleTo16k(buf, rate)).buffer` (App.tsx:281-284) keeps working
+// and its bytes go to the unchanged DeepgramClient.sendAudio (apps/voice/src/deepgram.ts:55-58).
+// All logic lives in the C ABI library; this file only validates arguments, moves pointers and maps
+// status codes to JS exceptions.  No CPU fallback: if no CUDA device is usable, module load throws.
+#include "napi_min.h"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/pcm_b200.h"
+
+namespace {
+
+pcmb200_ctx *g_ctx = nullptr;
+
+bool throw_status(napi_env env, int status)
+{
+    if (status == PCMB200_OK) return false;
+    const char *msg = pcmb200_last_error(g_ctx);
+    if (!msg || !*msg) msg = pcmb200_last_error(nullptr);
+    if (!msg || !*msg) msg = pcmb200_status_string(status);
+    char code[32];
+    std::snprintf(code, sizeof code, "PCMB200_%d", status);
+    if (status == PCMB200_ERR_RANGE) napi_throw_range_error(env, code, msg);   // `new Float32Array(newLen)` would throw
+    else napi_throw_error(env, code, msg);
+    return true;
+}
+
+// Returns the Float32Array's data pointer / length, or throws TypeError (an extension: the
+// reference does not validate, TypeScript does it at compile time).
+bool get_f32(napi_env env, napi_value v, const float **data, size_t *len)
+{
+    bool is_ta = false;
+    napi_typedarray_type t;
+    void *p = nullptr;
+    if (napi_is_typedarray(env, v, &is_ta) != napi_ok || !is_ta ||
+        napi_get_typedarray_info(env, v, &t, len, &p, nullptr, nullptr) != napi_ok || t != napi_float32_array) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "expected a Float32Array");
+        return false;
+    }
+    *data = static_cast<const float *>(p);
+    return true;
+}
+
+napi_value make_typed(napi_env env, napi_typedarray_type t, size_t len, size_t elem, void **data)
+{
+    napi_value ab = nullptr, ta = nullptr;
+    if (napi_create_arraybuffer(env, len * elem, data, &ab) != napi_ok) return nullptr;
+    if (napi_create_typedarray(env, t, len, ab, 0, &ta) != napi_ok) return nullptr;
+    return ta;
+}
+
+// floatTo16BitPCM(float32: Float32Array): Int16Array            App.tsx:7-16
+napi_value FloatTo16BitPCM(napi_env env, napi_callback_info info)
+{
+    size_t argc = 1;
+    napi_value argv[1];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    const float *in;
+    size_t n;
+    if (argc < 1 || !get_f32(env, argv[0], &in, &n)) return nullptr;
+    void *out = nullptr;
+    napi_value res = make_typed(env, napi_int16_array, n, 2, &out);   // a fresh array, like `new Int16Array(len)`
+    if (!res) return nullptr;
+    if (throw_status(env, pcmb200_encode_f32_s16(g_ctx, in, static_cast<int16_t *>(out), n, PCMB200_MEM_HOST))) return nullptr;
+    return res;
+}
+
+// resampleTo16k(input: Float32Array, inputSampleRate: number): Float32Array     App.tsx:18-32
+napi_value ResampleTo16k(napi_env env, napi_callback_info info)
+{
+    size_t argc = 2;
+    napi_value argv[2];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    const float *in;
+    size_t n;
+    double rate = 0;
+    if (argc < 2 || !get_f32(env, argv[0], &in, &n)) return nullptr;
+    if (napi_get_value_double(env, argv[1], &rate) != napi_ok) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "inputSampleRate must be a number");
+        return nullptr;
+    }
+    if (rate == 16000.0) return argv[0];                               // App.tsx:22 returns the same object
+    size_t n_out = 0;
+    if (throw_status(env, pcmb200_resample_len(n, rate, &n_out))) return nullptr;
+    void *out = nullptr;
+    napi_value res = make_typed(env, napi_float32_array, n_out, 4, &out);
+    if (!res) return nullptr;
+    size_t got = 0;
+    if (throw_status(env, pcmb200_resample_to_16k(g_ctx, in, n, rate, static_cast<float *>(out), n_out, &got, PCMB200_MEM_HOST)))
+        return nullptr;
+    return res;
+}
+
+// framesEncode(batch: Float32Array, rows: number, nIn: number, rate: number, out?: Int16Array): Int16Array
+// One fused floatTo16BitPCM(resampleTo16k(row, rate)) per row (App.tsx:281-282), rows dense.
+napi_value FramesEncode(napi_env env, napi_callback_info info)
+{
+    size_t argc = 5;
+    napi_value argv[5];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    const float *in;
+    size_t n;
+    uint32_t rows = 0, n_in = 0;
+    double rate = 0;
+    if (argc < 4 || !get_f32(env, argv[0], &in, &n)) return nullptr;
+    if (napi_get_value_uint32(env, argv[1], &rows) != napi_ok || napi_get_value_uint32(env, argv[2], &n_in) != napi_ok ||
+        napi_get_value_double(env, argv[3], &rate) != napi_ok || (size_t)rows * n_in > n) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "framesEncode(batch, rows, nIn, rate): rows * nIn exceeds batch.length");
+        return nullptr;
+    }
+    size_t n_out = 0;
+    if (throw_status(env, pcmb200_resample_len(n_in, rate, &n_out))) return nullptr;
+    void *out = nullptr;
+    napi_value res = nullptr;
+    if (argc >= 5) {   // caller-provided (e.g. pinned) output
+        bool is_ta = false;
+        napi_typedarray_type t;
+        size_t len = 0;
+        if (napi_is_typedarray(env, argv[4], &is_ta) != napi_ok || !is_ta ||
+            napi_get_typedarray_info(env, argv[4], &t, &len, &out, nullptr, nullptr) != napi_ok ||
+            t != napi_int16_array || len < (size_t)rows * n_out) {
+            napi_throw_type_error(env, "PCMB200_TYPE", "out must be an Int16Array of at least rows * resampleLen(nIn, rate)");
+            return nullptr;
+        }
+        res = argv[4];
+    } else {
+        res = make_typed(env, napi_int16_array, (size_t)rows * n_out, 2, &out);
+        if (!res) return nullptr;
+    }
+    if (throw_status(env, pcmb200_frames_encode(g_ctx, in, n_in, static_cast<int16_t *>(out), n_out, rows, n_in, rate,
+                                                PCMB200_MEM_HOST, nullptr)))
+        return nullptr;
+    return res;
+}
+
+// resampleLen(n: number, rate: number): number                   App.tsx:23-24
+napi_value ResampleLen(napi_env env, napi_callback_info info)
+{
+    size_t argc = 2;
+    napi_value argv[2];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    double n = 0, rate = 0;
+    if (argc < 2 || napi_get_value_double(env, argv[0], &n) != napi_ok || napi_get_value_double(env, argv[1], &rate) != napi_ok || n < 0) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "resampleLen(n, rate)");
+        return nullptr;
+    }
+    size_t n_out = 0;
+    if (throw_status(env, pcmb200_resample_len((size_t)n, rate, &n_out))) return nullptr;
+    napi_value r = nullptr;
+    napi_create_double(env, (double)n_out, &r);
+    return r;
+}
+
+void free_pinned(napi_env, void *data, void *) { pcmb200_pinned_free(g_ctx, data); }
+
+// allocPinnedFloat32(n) / allocPinnedInt16(n): typed arrays over page-locked memory, so JS fills
+// H2D-ready buffers and receives D2H results without a staging copy.
+napi_value alloc_pinned(napi_env env, napi_callback_info info, napi_typedarray_type t, size_t elem)
+{
+    size_t argc = 1;
+    napi_value argv[1];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    double n = 0;
+    if (argc < 1 || napi_get_value_double(env, argv[0], &n) != napi_ok || n < 0) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "length must be a non-negative number");
+        return nullptr;
+    }
+    void *p = nullptr;
+    if (throw_status(env, pcmb200_pinned_alloc(g_ctx, (size_t)n * elem, &p))) return nullptr;
+    napi_value ab = nullptr, ta = nullptr;
+    if (napi_create_external_arraybuffer(env, p, (size_t)n * elem, free_pinned, nullptr, &ab) != napi_ok ||
+        napi_create_typedarray(env, t, (size_t)n, ab, 0, &ta) != napi_ok) {
+        pcmb200_pinned_free(g_ctx, p);
+        napi_throw_error(env, "PCMB200_NAPI", "could not wrap pinned memory");
+        return nullptr;
+    }
+    return ta;
+}
+napi_value AllocPinnedFloat32(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_float32_array, 4); }
+napi_value AllocPinnedInt16(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_int16_array, 2); }
+
+void cleanup(void *)
+{
+    pcmb200_ctx_destroy(g_ctx);
+    g_ctx = nullptr;
+}
+
+napi_value Init(napi_env env, napi_value exports)
+{
+    int device = 0;
+    if (const char *e = std::getenv("PCMB200_DEVICE")) device = std::atoi(e);
+    if (throw_status(env, pcmb200_ctx_create(device, &g_ctx))) return nullptr;   // loud failure, no CPU path
+    napi_add_env_cleanup_hook(env, cleanup, nullptr);
+    const napi_property_descriptor props[] = {
+        {"floatTo16BitPCM", nullptr, FloatTo16BitPCM, nullptr, nullptr, nullptr, 0, nullptr},
+        {"resampleTo16k", nullptr, ResampleTo16k, nullptr, nullptr, nullptr, 0, nullptr},
+        {"framesEncode", nullptr, FramesEncode, nullptr, nullptr, nullptr, 0, nullptr},
+        {"resampleLen", nullptr, ResampleLen, nullptr, nullptr, nullptr, 0, nullptr},
+        {"allocPinnedFloat32", nullptr, AllocPinnedFloat32, nullptr, nullptr, nullptr, 0, nullptr},
+        {"allocPinnedInt16", nullptr, AllocPinnedInt16, nullptr, nullptr, nullptr, 0, nullptr},
+    };
+    napi_define_properties(env, exports, sizeof props / sizeof props[0], props);
+    return exports;
+}
+
+napi_module g_module = {1, 0, __FILE__, Init, "pcm_b200_napi", nullptr, {nullptr, nullptr, nullptr, nullptr}};
+
+}  // namespace
+
+// Node resolves this symbol (Node-API module version 1) when it dlopens the .node file.
+extern "C" __attribute__((visibility("default"))) napi_value napi_register_module_v1(napi_env env, napi_value exports)
+{
+    return Init(env, exports);
+}
+extern "C" __attribute__((constructor)) void pcmb200_napi_register(void)
+{
+    // legacy registration path; harmless when napi_register_module_v1 is used
+    (void)g_module;
+}

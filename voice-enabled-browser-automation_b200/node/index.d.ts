@@ -1,0 +1,11 @@
+/** Same signature and result as the reference's helper (apps/web/src/App.tsx:7-16). */
+export function floatTo16BitPCM(float32: Float32Array): Int16Array;
+/** Same signature and result as the reference's helper (apps/web/src/App.tsx:18-32); returns `input` itself at 16 kHz. */
+export function resampleTo16k(input: Float32Array, inputSampleRate: number): Float32Array;
+/** floatTo16BitPCM(resampleTo16k(row, rate)) for `rows` dense rows of `nIn` samples (App.tsx:281-282), fused on the GPU. */
+export function framesEncode(batch: Float32Array, rows: number, nIn: number, rate: number, out?: Int16Array): Int16Array;
+/** Math.floor(n / (rate / 16000)) as the reference computes it (App.tsx:23-24); throws RangeError where `new Float32Array` would. */
+export function resampleLen(n: number, rate: number): number;
+/** Typed arrays over page-locked host memory (no staging copy on H2D / D2H). */
+export function allocPinnedFloat32(length: number): Float32Array;
+export function allocPinnedInt16(length: number): Int16Array;

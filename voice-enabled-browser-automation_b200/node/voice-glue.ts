@@ -1,0 +1,49 @@
+// voice-glue.ts -- what apps/voice/src/server.ts gains to convert on the GPU (INTEGRATION.md section 4).
+// Frames that arrive within one tick are grouped by (rate, length), converted with ONE framesEncode
+// call per group, and each session's slice is passed to the unchanged DeepgramClient.sendAudio
+// (apps/voice/src/deepgram.ts:55-58).  New glue, not a behaviour of the reference.
+import { allocPinnedFloat32, allocPinnedInt16, framesEncode, resampleLen } from "./index";
+
+type Sink = (pcm16: Buffer) => void;
+type Group = { rate: number; nIn: number; frames: Float32Array[]; sinks: Sink[] };
+
+export class FrameBatcher {
+  private groups = new Map<string, Group>();
+  private pinIn = allocPinnedFloat32(1 << 20);
+  private pinOut = allocPinnedInt16(1 << 19);
+  private timer: NodeJS.Timeout;
+
+  constructor(opts: { tickMs?: number } = {}) {
+    this.timer = setInterval(() => this.flush(), opts.tickMs ?? 20);
+  }
+
+  /** One Float32 frame of one session (the bytes of a WS binary message). */
+  push(_sessionId: string, rate: number, data: Buffer, sink: Sink): void {
+    const f32 = new Float32Array(data.buffer, data.byteOffset, data.byteLength >> 2);
+    const key = `${rate}:${f32.length}`;
+    let g = this.groups.get(key);
+    if (!g) this.groups.set(key, (g = { rate, nIn: f32.length, frames: [], sinks: [] }));
+    g.frames.push(f32);
+    g.sinks.push(sink);
+  }
+
+  flush(): void {
+    for (const g of this.groups.values()) {
+      const rows = g.frames.length;
+      const nOut = resampleLen(g.nIn, g.rate);
+      if (rows * g.nIn > this.pinIn.length) this.pinIn = allocPinnedFloat32(2 * rows * g.nIn);
+      if (rows * nOut > this.pinOut.length) this.pinOut = allocPinnedInt16(2 * rows * nOut);
+      g.frames.forEach((f, r) => this.pinIn.set(f, r * g.nIn));
+      framesEncode(this.pinIn, rows, g.nIn, g.rate, this.pinOut);
+      g.sinks.forEach((sink, r) =>
+        // copy out of the shared pinned block: sendAudio may keep the Buffer beyond this tick
+        sink(Buffer.from(Buffer.from(this.pinOut.buffer, this.pinOut.byteOffset + r * nOut * 2, nOut * 2))));
+    }
+    this.groups.clear();
+  }
+
+  close(): void {
+    clearInterval(this.timer);
+    this.flush();
+  }
+}
