@@ -312,6 +312,7 @@ def run_b200(args):
     sampler.in_region = False
     launches = ctx.launches - l0
     dist.barrier()
+    launches_all = int(dist.reduce(float(launches), "sum"))
     units, ms_max, value = aggregate(dist, float(S) * n_in * args.steps, ms)
     kernel_ms = ms / max(launches, 1)                  # the timed region holds nothing but these launches
     peak, peak_src = hbm_peak()
@@ -382,7 +383,7 @@ def run_b200(args):
                            "parallelism": f"session-affine shards x{world}, no collectives",
                            "l2": f"inputs larger than L2: {n_buf} alternating tick buffers of {algo_bytes / 1e9:.2f} GB each",
                            "tune": args.tune or "defaults"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all,
                 "clocks": sampler.summary(),
                 "output_samples_per_s": value * n_out / n_in, "device": ctx.device_info()["name"]}
         print(json.dumps(line), flush=True)

@@ -300,3 +300,25 @@ def test_launch_counter_counts_kernels(ctx):
     before = ctx.launches
     ctx.floatTo16BitPCM(np.zeros(1000, np.float32))
     assert ctx.launches == before + 1
+
+
+@pytest.mark.parametrize("rate,n_in", [(16000, 320), (48000, 960), (44100, 882)])
+def test_tick_graph_replay(ctx, rate, n_in):
+    """A recorded tick replays on new data in the same buffers and stays bit-exact."""
+    rng = np.random.RandomState(n_in + 1)
+    rows = 1024
+    n_out = oracle.resample_len(n_in, rate)
+    d_in = ctx.device_buffer(rows * n_in * 4)
+    d_out = ctx.device_buffer(rows * n_out * 2)
+    g = ctx.tick_graph(d_in.ptr, n_in, d_out.ptr, n_out, rows, n_in, rate)
+    before = ctx.launches
+    for _ in range(3):
+        x = _audio(rng, rows, n_in)
+        d_in.upload(x)
+        g.launch()
+        ctx.sync()
+        got = d_out.download(np.int16, rows * n_out).reshape(rows, n_out)
+        assert np.array_equal(got, oracle.frames(x, n_in, rate))
+    assert ctx.launches == before + 3
+    g.destroy()
+    d_in.free(); d_out.free()

@@ -363,7 +363,13 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
 {
     if (rows == 0 || n_out == 0) return PCMB200_OK;
     const size_t dpi = round_up(n_in, 8), dpo = round_up(n_out, 8);
-    size_t rps = ctx->tune.slice_bytes / (dpi * 4);
+    // slice size: the tuned maximum (32 MB) for big batches; small batches are still cut into ~8
+    // slices (>= 1 MB each) so that their upload, kernel and download overlap too
+    size_t slice_bytes = ctx->tune.slice_bytes;
+    const size_t total_in = (size_t)rows * dpi * 4;
+    if (total_in / 8 < slice_bytes) slice_bytes = total_in / 8 > (1u << 20) ? total_in / 8 : (1u << 20);
+    if (slice_bytes > ctx->tune.slice_bytes) slice_bytes = ctx->tune.slice_bytes;
+    size_t rps = slice_bytes / (dpi * 4);
     // keep every slice a whole number of 256-output warp tiles so it needs one launch, not two
     size_t tile_rows = 256;
     for (size_t a = n_out, b = 256; b;) { size_t t = a % b; a = b; b = t; tile_rows = 256 / a; }
@@ -763,6 +769,76 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
 }
 
 }  // extern "C"
+
+// ================================= per-tick CUDA graph ================================================
+struct pcmb200_tick_graph {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    uint64_t kernels = 0;
+};
+
+extern "C" int pcmb200_tick_graph_create(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out,
+                                         size_t pitch_out, uint32_t rows, uint32_t n_in, double in_rate,
+                                         pcmb200_tick_graph **graph)
+{
+    NEED(ctx && graph, "pcmb200_tick_graph_create: NULL argument");
+    *graph = nullptr;
+    size_t n_out = 0;
+    int s = resample_len(n_in, in_rate, &n_out);
+    if (s) return fail(ctx, s, "pcmb200_tick_graph_create: RangeError: invalid typed array length");
+    NEED(rows > 0 && n_out > 0 && in && out, "pcmb200_tick_graph_create: empty tick or NULL buffer");
+    NEED((pitch_in >= n_in && pitch_out >= n_out) || rows == 1, "pcmb200_tick_graph_create: pitch too small");
+    CU(cudaSetDevice(ctx->device));
+    uint32_t R;
+    if (!integer_ratio(in_rate, &R)) {   // the table upload must not happen inside the capture
+        const uint32_t *lut;
+        s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
+        if (s) return s;
+    }
+    pcmb200_tick_graph *g = new (std::nothrow) pcmb200_tick_graph();
+    if (!g) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_tick_graph_create: host allocation failed");
+    const uint64_t before = ctx->launches;
+    CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    s = launch_frames(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, in_rate, (uint32_t)n_out);
+    cudaError_t e = cudaStreamEndCapture(ctx->stream, &g->graph);
+    g->kernels = ctx->launches - before;
+    ctx->launches = before;   // recorded, not run
+    if (s || e != cudaSuccess || !g->graph) {
+        if (g->graph) cudaGraphDestroy(g->graph);
+        delete g;
+        cudaGetLastError();
+        return s ? s : fail(ctx, PCMB200_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+    }
+    e = cudaGraphInstantiate(&g->exec, g->graph, 0);
+    if (e != cudaSuccess) {
+        cudaGraphDestroy(g->graph);
+        delete g;
+        return fail(ctx, PCMB200_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+    }
+    *graph = g;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_tick_graph_launch(pcmb200_ctx *ctx, pcmb200_tick_graph *graph)
+{
+    NEED(ctx && graph && graph->exec, "pcmb200_tick_graph_launch: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaGraphLaunch(graph->exec, ctx->stream));
+    ctx->launches += graph->kernels;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_tick_graph_destroy(pcmb200_ctx *ctx, pcmb200_tick_graph *graph)
+{
+    NEED(ctx, "pcmb200_tick_graph_destroy: ctx is NULL");
+    if (!graph) return PCMB200_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (graph->exec) cudaGraphExecDestroy(graph->exec);
+    if (graph->graph) cudaGraphDestroy(graph->graph);
+    delete graph;
+    return PCMB200_OK;
+}
 
 // ================================= allocation-free entry point =====================================
 // pcmb200_frames_encode_noalloc: the general pick + encode kernel (k_pick_encode) with its pick-index

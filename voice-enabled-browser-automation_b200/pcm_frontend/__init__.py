@@ -25,6 +25,7 @@ from .api import (  # noqa: F401
     Context,
     DeviceBuffer,
     PinnedBuffer,
+    TickGraph,
     default_context,
     floatTo16BitPCM,
     frames_encode,
@@ -35,7 +36,7 @@ from .api import (  # noqa: F401
 )
 
 __all__ = [
-    "Context", "DeviceBuffer", "PinnedBuffer", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
+    "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
     "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",
 ]

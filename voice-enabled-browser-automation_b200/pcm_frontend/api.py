@@ -236,8 +236,32 @@ class Context:
                                               C.byref(got), mem), self.handle)
         return int(got.value)
 
+    def tick_graph(self, in_ptr: int, pitch_in: int, out_ptr: int, pitch_out: int, rows: int, n_in: int,
+                   rate: float) -> "TickGraph":
+        """Record one device-resident tick as a CUDA graph (pcmb200_tick_graph_create)."""
+        return TickGraph(self, in_ptr, pitch_in, out_ptr, pitch_out, rows, n_in, rate)
+
     def synth_fill(self, out_ptr: int, pitch: int, rows: int, n: int, rate: float, seed: int = 0x5EED, row0: int = 0):
         check(self._L.pcmb200_synth_fill(self.handle, out_ptr, pitch, rows, n, float(rate), seed, row0), self.handle)
+
+
+class TickGraph:
+    """A recorded tick; launch() replays it on the context's stream."""
+
+    def __init__(self, ctx: Context, in_ptr, pitch_in, out_ptr, pitch_out, rows, n_in, rate):
+        self.ctx = ctx
+        h = C.c_void_p()
+        check(ctx._L.pcmb200_tick_graph_create(ctx.handle, int(in_ptr), int(pitch_in), int(out_ptr), int(pitch_out),
+                                               int(rows), int(n_in), float(rate), C.byref(h)), ctx.handle)
+        self.handle = h.value
+
+    def launch(self):
+        check(self.ctx._L.pcmb200_tick_graph_launch(self.ctx.handle, self.handle), self.ctx.handle)
+
+    def destroy(self):
+        if self.handle and self.ctx.handle:
+            check(self.ctx._L.pcmb200_tick_graph_destroy(self.ctx.handle, self.handle), self.ctx.handle)
+        self.handle = None
 
 
 def _as_f32_1d(a) -> np.ndarray:

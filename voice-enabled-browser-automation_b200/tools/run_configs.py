@@ -1,0 +1,187 @@
+#!/usr/bin/env python3
+"""Measures BASELINE.json configs 1, 2, 3 and 5 on one B200 (config 4 is bench.py itself).
+
+    python voice-enabled-browser-automation_b200/tools/run_configs.py --out gpurun_out/configs.json
+
+Every GPU figure is timed with CUDA events on the context's stream after warm-up; CPU figures are
+the oracle port (oracle/pcm_oracle.c) on this box's host cores, on the same input bits.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+import oracle  # noqa: E402  (measurement baseline + checker only)
+import pcm_frontend  # noqa: E402
+from pcm_frontend import MEM_DEVICE, MEM_HOST  # noqa: E402
+
+try:
+    PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:
+    PEAK = 6650.0
+
+
+def timed(ctx, fn, reps, warm=3):
+    for _ in range(warm):
+        fn()
+    ctx.sync()
+    ctx.timer_start()
+    for _ in range(reps):
+        fn()
+    return ctx.timer_stop() / reps
+
+
+def config1(ctx):
+    """One 1 s 48 kHz mono buffer: resample -> encode (the reference's own call sequence)."""
+    n = 48000
+    d = ctx.device_buffer(n * 4)
+    ctx.synth_fill(d.ptr, n, 1, n, 48000)
+    ctx.sync()
+    x = d.download(np.float32, n)
+    L = oracle.lib()
+    out = np.empty(16000, np.int16)
+    ts = []
+    for _ in range(1000):
+        t0 = time.perf_counter_ns()
+        L.oracle_frame(x.ctypes.data_as(C.POINTER(C.c_float)), n, 48000.0, out.ctypes.data_as(C.POINTER(C.c_int16)))
+        ts.append(time.perf_counter_ns() - t0)
+    cpu_ns = statistics.median(ts)
+    got = ctx.frames_encode(x.reshape(1, n), 48000)[0]
+    assert np.array_equal(got, out)
+    two = ctx.floatTo16BitPCM(ctx.resampleTo16k(x, 48000))
+    assert np.array_equal(two, out)
+    ts = []
+    for _ in range(300):
+        t0 = time.perf_counter_ns()
+        ctx.frames_encode(x.reshape(1, n), 48000)
+        ts.append(time.perf_counter_ns() - t0)
+    gpu_fused_ns = statistics.median(ts)
+    ts = []
+    for _ in range(300):
+        t0 = time.perf_counter_ns()
+        ctx.floatTo16BitPCM(ctx.resampleTo16k(x, 48000))
+        ts.append(time.perf_counter_ns() - t0)
+    gpu_two_ns = statistics.median(ts)
+    return {"config": 1, "n_in": n, "n_out": 16000, "node": "Node unavailable on this box",
+            "cpu_oracle_1thread_ns_per_in_sample": cpu_ns / n, "cpu_oracle_us_per_call": cpu_ns / 1e3,
+            "gpu_host_call_fused_us": gpu_fused_ns / 1e3, "gpu_host_call_two_functions_us": gpu_two_ns / 1e3,
+            "note": "single stream: H2D + launch + D2H latency dominates, the GPU does not beat one CPU core"}
+
+
+def config2(ctx):
+    """1,024 x 16 kHz x 20 ms encode-only: steady state over 2,048 ticks per launch + single-tick latency."""
+    S, n, T = 1024, 320, 2048
+    rows = S * T
+    d_in, d_out = ctx.device_buffer(rows * n * 4), ctx.device_buffer(rows * n * 2)
+    ctx.synth_fill(d_in.ptr, n, rows, n, 16000)
+    ctx.sync()
+    ms = timed(ctx, lambda: ctx.frames_encode_ptr(d_in.ptr, n, d_out.ptr, n, rows, n, 16000, MEM_DEVICE), 20)
+    algo = rows * n * 6
+    tick = timed(ctx, lambda: ctx.frames_encode_ptr(d_in.ptr, n, d_out.ptr, n, S, n, 16000, MEM_DEVICE), 2000, warm=20)
+    g = ctx.tick_graph(d_in.ptr, n, d_out.ptr, n, S, n, 16000)
+    tick_g = timed(ctx, g.launch, 2000, warm=20)
+    # host-observed latency of one tick (launch + sync)
+    ts = []
+    for _ in range(500):
+        t0 = time.perf_counter_ns()
+        g.launch()
+        ctx.sync()
+        ts.append(time.perf_counter_ns() - t0)
+    g.destroy()
+    x = d_in.download(np.float32, S * n).reshape(S, n)
+    assert np.array_equal(d_out.download(np.int16, S * n).reshape(S, n), oracle.frames(x, n, 16000))
+    d_in.free(); d_out.free()
+    return {"config": 2, "sessions": S, "n": n, "ticks_per_launch": T, "working_set_gb": algo / 1e9,
+            "steady_ms_per_launch": ms, "steady_samples_per_s": rows * n / (ms * 1e-3),
+            "steady_gbs": algo / (ms * 1e-3) / 1e9, "steady_frac_of_measured_peak": algo / (ms * 1e-3) / 1e9 / PEAK,
+            "single_tick_us_plain_launch_back_to_back": tick * 1e3, "single_tick_us_graph_replay_back_to_back": tick_g * 1e3,
+            "single_tick_us_graph_launch_plus_sync_host_clock": statistics.median(ts) / 1e3,
+            "note": "one tick is 1.97 MB (L2 resident, 0.3 us of HBM time): only the steady-state line is compared with the HBM roofline"}
+
+
+def config3(ctx, ms_frame):
+    """65,536 x 48 kHz frames, 16 distinct tick buffers (4.7 GB at 20 ms) rotated to defeat L2."""
+    S, n_in = 65536, 48 * ms_frame
+    n_out = n_in // 3
+    ticks = 16 if ms_frame == 20 else 8
+    bufs = [(ctx.device_buffer(S * n_in * 4), ctx.device_buffer(S * n_out * 2)) for _ in range(ticks)]
+    for t, (di, _) in enumerate(bufs):
+        ctx.synth_fill(di.ptr, n_in, S, n_in, 48000, 0x5EED + t, 0)
+    ctx.sync()
+    state = {"i": 0}
+
+    def one():
+        di, do = bufs[state["i"] % ticks]
+        state["i"] += 1
+        ctx.frames_encode_ptr(di.ptr, n_in, do.ptr, n_out, S, n_in, 48000, MEM_DEVICE)
+    ms = timed(ctx, one, 10 * ticks, warm=ticks)
+    algo = S * (n_in * 4 + n_out * 2)
+    x = bufs[0][0].download(np.float32, 4096 * n_in).reshape(4096, n_in)
+    assert np.array_equal(bufs[0][1].download(np.int16, 4096 * n_out).reshape(4096, n_out), oracle.frames(x, n_in, 48000, threads=8))
+    for di, do in bufs:
+        di.free(); do.free()
+    return {"config": 3, "sessions": S, "frame_ms": ms_frame, "n_in": n_in, "n_out": n_out, "distinct_ticks": ticks,
+            "bytes_per_tick": algo, "us_per_tick": ms * 1e3, "in_samples_per_s": S * n_in / (ms * 1e-3),
+            "gbs": algo / (ms * 1e-3) / 1e9, "frac_of_measured_peak": algo / (ms * 1e-3) / 1e9 / PEAK}
+
+
+def config5(ctx):
+    """Host-resident end to end through pinned buffers; frame sweep 10-100 ms; vs raw PCIe and vs the CPU."""
+    cap = 1 << 30
+    pin_in = ctx.pinned(cap // 4, np.float32)
+    pin_out = ctx.pinned(cap // 8, np.int16)
+    dev = ctx.device_buffer(cap)
+    h2d = timed(ctx, lambda: ctx.memcpy_h2d(dev.ptr, pin_in.ptr, cap), 5, warm=1)
+    d2h = timed(ctx, lambda: ctx.memcpy_d2h(pin_in.ptr, dev.ptr, cap), 5, warm=1)
+    res = {"config": 5, "pinned_h2d_gbs": cap / (h2d * 1e-3) / 1e9, "pinned_d2h_gbs": cap / (d2h * 1e-3) / 1e9, "points": []}
+    cores = os.cpu_count() or 1
+    for ms_frame in (10, 20, 40, 60, 100):
+        n_in = 48 * ms_frame
+        n_out = n_in // 3
+        for batch_bytes in (1 << 20, 1 << 24, 1 << 27, 1 << 30):
+            S = max(1, batch_bytes // (n_in * 4))
+            ctx.synth_fill(dev.ptr, n_in, S, n_in, 48000)
+            ctx.sync()
+            ctx.memcpy_d2h(pin_in.ptr, dev.ptr, S * n_in * 4)
+            reps = 3 if batch_bytes >= (1 << 27) else 30
+            ms = timed(ctx, lambda: ctx.frames_encode_ptr(pin_in.ptr, n_in, pin_out.ptr, n_out, S, n_in, 48000, MEM_HOST), reps, warm=2)
+            x = pin_in.array[: S * n_in].reshape(S, n_in)
+            rows_cpu = min(S, 1 << 15)
+            t0 = time.perf_counter()
+            want = oracle.frames(x[:rows_cpu], n_in, 48000, threads=min(cores, rows_cpu))
+            cpu_dt = time.perf_counter() - t0
+            assert np.array_equal(pin_out.array[: rows_cpu * n_out].reshape(rows_cpu, n_out), want)
+            res["points"].append({"frame_ms": ms_frame, "sessions": S, "batch_mb": S * n_in * 4 / 2**20, "ms_per_batch": ms,
+                                  "in_samples_per_s": S * n_in / (ms * 1e-3), "h2d_gbs": S * n_in * 4 / (ms * 1e-3) / 1e9,
+                                  "frac_of_pinned_h2d": S * n_in * 4 / (ms * 1e-3) / 1e9 / res["pinned_h2d_gbs"],
+                                  "cpu_all_cores_samples_per_s": rows_cpu * n_in / cpu_dt, "cpu_cores": cores})
+    pin_in.free(); pin_out.free(); dev.free()
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    ctx = pcm_frontend.Context(0)
+    results = {"device": ctx.device_info(), "host_cores": os.cpu_count(), "hbm_peak_gbs": PEAK, "configs": []}
+    for fn in (lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+        r = fn()
+        results["configs"].append(r)
+        print(json.dumps(r), flush=True)
+    if args.out:
+        json.dump(results, open(args.out, "w"), indent=1)
+    ctx.close()
+
+
+if __name__ == "__main__":
+    main()
