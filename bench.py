@@ -190,8 +190,10 @@ def hbm_peak():
 def kernel_name(args):
     """The kernel pcmb200_frames_encode selects for a dense device-resident batch at RATE."""
     r = int(RATE // 16000)
-    if RATE % 16000 != 0 or r not in (1, 2, 3, 4, 6) or "path=1" in args.tune:
+    if "path=1" in args.tune or "tile=0" in args.tune and RATE % 16000 != 0:
         return "k_pick_encode"
+    if RATE % 16000 != 0 or r not in (1, 2, 3, 4, 6) or "path=2" in args.tune:
+        return "k_tile_pick (cp.async.bulk tile staging)"
     if r == 1 or "coalesced=0" in args.tune:
         return f"k_decim_int<R={r}>"
     return f"k_decim_coal<R={r}>"

@@ -322,3 +322,31 @@ def test_tick_graph_replay(ctx, rate, n_in):
     assert ctx.launches == before + 3
     g.destroy()
     d_in.free(); d_out.free()
+
+
+@pytest.mark.parametrize("rate,n_in", [(44100, 882), (22050, 441), (11025, 1103), (8000, 160), (44100, 2646),
+                                        (88200, 1764), (48000, 960), (80000, 1600), (37800, 756)])
+def test_tile_staged_kernel_matches_general_kernel(ctx, rate, n_in):
+    """Kernel 2b (TMA bulk copy -> shared memory -> table picks) against kernel 2 and the oracle, on
+    dense device batches whose row count is not a multiple of the tile height."""
+    rng = np.random.RandomState(n_in * 7)
+    n_out = oracle.resample_len(n_in, rate)
+    for rows in (1, 37, 1031, 4099):
+        x = _audio(rng, rows, n_in)
+        want = oracle.frames(x, n_in, rate)
+        d_in = ctx.device_buffer(x.nbytes)
+        d_out = ctx.device_buffer(rows * n_out * 2 + 64)
+        d_in.upload(x)
+        for tune in (dict(path=2, tile=1, stages=2), dict(path=2, tile=1, stages=3, tile_kb=12),
+                     dict(path=2, tile=1, stages=1, tile_kb=56), dict(path=1, tile=0)):
+            ctx.tune(**tune)
+            try:
+                d_out.memset(0x55)
+                ctx.frames_encode_ptr(d_in.ptr, n_in, d_out.ptr, n_out, rows, n_in, rate)
+                ctx.sync()
+            finally:
+                ctx.tune(path=0, tile=1, stages=2, tile_kb=28)
+            raw = d_out.download(np.int16, rows * n_out + 32)
+            assert np.array_equal(raw[: rows * n_out].reshape(rows, n_out), want), (rate, rows, tune)
+            assert (raw[rows * n_out:] == 0x5555).all()
+        d_in.free(); d_out.free()

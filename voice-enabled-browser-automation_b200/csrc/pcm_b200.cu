@@ -45,6 +45,9 @@ struct Tuning {
     int path = 0;            // 1 = force the general pick kernel
     int store_hint = 1;      // st.global.cs: output frames are written once and not re-read
     int coalesced = 1;       // dense integer-ratio batches: warp-coalesced kernel (1b) instead of kernel 1
+    int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
+    int tile_kb = 28;        // target tile size of kernel 2b
+    int stages = 2;          // tiles in flight per CTA in kernel 2b
     size_t slice_bytes = 32u << 20;
 };
 
@@ -240,6 +243,58 @@ int default_unroll(uint32_t R)
     return R == 1 ? 2 : 1;   // measured: 64-96 bytes of loads in flight per thread are enough
 }
 
+// Kernel 2b (TMA tile-staged picks) for dense batches of short frames.  Returns the number of rows it
+// took (a multiple of the tile height; 0 if the batch does not qualify); the caller sends the rest
+// to kernel 2.
+template <int STAGES>
+cudaError_t launch_tile_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *out, uint32_t n_in,
+                          uint32_t n_out, uint32_t K, unsigned long long n_tiles, const uint32_t *lut, uint32_t R,
+                          uint32_t tile_stride, size_t smem)
+{
+    cudaError_t e = cudaFuncSetAttribute(k_tile_pick<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int resident = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_tile_pick<STAGES>, 256, smem);
+    if (e != cudaSuccess || resident < 1) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;
+    // measured sweet spot: about 112 KB of tiles in flight per SM (profiles/r01_sweep_tile.json)
+    int preferred = (int)((112u * 1024u) / ((size_t)STAGES * tile_stride));
+    if (preferred < 1) preferred = 1;
+    const int grid = grid_for(ctx, n_tiles, resident, preferred);
+    k_tile_pick<STAGES><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, ctx->tune.store_hint);
+    return cudaGetLastError();
+}
+
+uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
+                     size_t pitch_out, uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R)
+{
+    if (!ctx->tune.tile || pitch_in != n_in || pitch_out != n_out || (n_out % 8) != 0 || n_out > 8192) return 0;
+    if (!aligned(in, 16) || !aligned(out, 16)) return 0;
+    uint32_t k0 = 4;                                   // smallest row group whose bytes are a multiple of 16
+    if (n_in % 4 == 0) k0 = 1; else if (n_in % 2 == 0) k0 = 2;
+    const size_t group_bytes = (size_t)k0 * n_in * 4;
+    const size_t target = (size_t)ctx->tune.tile_kb * 1024;
+    if (group_bytes > 64 * 1024) return 0;             // frames too long to stage whole: kernel 2 handles them
+    uint32_t K = (uint32_t)(target / group_bytes) * k0;
+    if (K < k0) K = k0;
+    if (rows < K) return 0;
+    const unsigned long long n_tiles = rows / K;
+    const uint32_t tile_bytes = K * n_in * 4;
+    const uint32_t tile_stride = (tile_bytes + 127u) & ~127u;
+    const int stages = ctx->tune.stages;
+    const size_t smem = (size_t)stages * tile_stride + (lut ? ((n_out * 4u + 15u) & ~15u) : 0u) + (size_t)stages * 8;
+    if (smem > 200 * 1024) return 0;
+    cudaError_t e;
+    switch (stages) {
+    case 1: e = launch_tile_k<1>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
+    case 2: e = launch_tile_k<2>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
+    case 3: e = launch_tile_k<3>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
+    default: e = launch_tile_k<4>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
+    }
+    if (e != cudaSuccess) { cudaGetLastError(); return 0; }   // fall back to kernel 2 for the whole batch
+    ctx->launches++;
+    return (uint32_t)(n_tiles * K);
+}
+
 // Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
 int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
                   size_t pitch_out, uint32_t rows, uint32_t n_in, double rate, uint32_t n_out)
@@ -247,7 +302,7 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
     if (rows == 0 || n_out == 0) return PCMB200_OK;
     uint32_t R = 0;
     const bool is_int = integer_ratio(rate, &R);
-    const bool fast_ok = is_int && (R == 1 || R == 2 || R == 3 || R == 4 || R == 6) && ctx->tune.path != 1 &&
+    const bool fast_ok = is_int && (R == 1 || R == 2 || R == 3 || R == 4 || R == 6) && ctx->tune.path == 0 &&
                          aligned(in, 32) && aligned(out, 16) && (pitch_in % 8 == 0 || rows == 1) &&
                          (pitch_out % 8 == 0 || rows == 1);
     if (fast_ok) {
@@ -312,6 +367,13 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
         int s = get_lut(ctx, n_in, rate, n_out, &lut);
         if (s) return s;
     }
+    if (ctx->tune.path != 1) {
+        const uint32_t took = launch_tile(ctx, st, in, pitch_in, out, pitch_out, rows, n_in, n_out, lut, R);
+        if (took == rows) return PCMB200_OK;
+        in += (size_t)took * pitch_in;
+        out += (size_t)took * pitch_out;
+        rows -= took;
+    }
     const bool pair32 = aligned(out, 4) && (pitch_out % 2 == 0 || rows == 1);
     const int block = ctx->tune.block;
     const unsigned long long n_pairs = (unsigned long long)rows * ((n_out + 1u) / 2u);
@@ -362,7 +424,11 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
                 uint32_t rows, uint32_t n_in, double rate, uint32_t n_out)
 {
     if (rows == 0 || n_out == 0) return PCMB200_OK;
-    const size_t dpi = round_up(n_in, 8), dpo = round_up(n_out, 8);
+    // staging pitch: integer ratios keep rows 32-byte / 16-byte aligned for kernels 1/1b; other
+    // ratios are staged dense so the tile-staged kernel 2b applies
+    uint32_t Rtmp = 0;
+    const bool int_ratio = integer_ratio(rate, &Rtmp);
+    const size_t dpi = int_ratio ? round_up(n_in, 8) : n_in, dpo = int_ratio ? round_up(n_out, 8) : n_out;
     // slice size: the tuned maximum (32 MB) for big batches; small batches are still cut into ~8
     // slices (>= 1 MB each) so that their upload, kernel and download overlap too
     size_t slice_bytes = ctx->tune.slice_bytes;
@@ -751,7 +817,7 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
         NEED(value >= 0 && value <= 4, "pcmb200_tune: unroll must be 0 (default), 1, 2 or 4");
         ctx->tune.unroll = (int)value;
     } else if (k == "path") {
-        NEED(value == 0 || value == 1, "pcmb200_tune: path must be 0 or 1");
+        NEED(value >= 0 && value <= 2, "pcmb200_tune: path must be 0 (auto), 1 (general kernel) or 2 (general path, tile kernel allowed)");
         ctx->tune.path = (int)value;
     } else if (k == "store_hint") {
         NEED(value >= 0 && value <= 2, "pcmb200_tune: store_hint must be 0, 1 or 2");
@@ -759,6 +825,15 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "coalesced") {
         NEED(value == 0 || value == 1, "pcmb200_tune: coalesced must be 0 or 1");
         ctx->tune.coalesced = (int)value;
+    } else if (k == "tile") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: tile must be 0 or 1");
+        ctx->tune.tile = (int)value;
+    } else if (k == "tile_kb") {
+        NEED(value >= 4 && value <= 96, "pcmb200_tune: tile_kb must be in [4, 96]");
+        ctx->tune.tile_kb = (int)value;
+    } else if (k == "stages") {
+        NEED(value >= 1 && value <= 4, "pcmb200_tune: stages must be in [1, 4]");
+        ctx->tune.stages = (int)value;
     } else if (k == "slice_bytes") {
         NEED(value >= 4096, "pcmb200_tune: slice_bytes must be >= 4096");
         ctx->tune.slice_bytes = (size_t)value;

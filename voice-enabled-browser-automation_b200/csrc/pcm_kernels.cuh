@@ -264,6 +264,130 @@ k_pick_encode(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict
     }
 }
 
+// ---- kernel 2b: tile-staged pick + encode for DENSE batches of short frames (any ratio) -----------
+// The 44.1 kHz family needs table-driven picks at irregular offsets; doing that straight from global
+// memory (kernel 2) costs sector-granular gathers.  Here a CTA walks over tiles of K whole frames
+// (K * n_in * 4 bytes, contiguous because rows are dense).  One elected thread moves each tile
+// global -> shared with a single bulk async copy (cp.async.bulk, the TMA engine's 1-D mode,
+// SASS UBLKCP) that completes on an mbarrier; STAGES tiles are in flight per CTA, so the copy of
+// tile i+1 runs while tile i is gathered.  All 256 threads then read their picks from shared
+// memory through a copy of the pick table (also in shared memory), encode, and write one 128-bit
+// streaming store per 8 outputs; consecutive lanes write consecutive 16-byte chunks.
+// Requirements (launcher): in 16-byte aligned, rows dense (pitch_in == n_in, pitch_out == n_out),
+// n_out % 8 == 0, K * n_in % 4 == 0, tile + table fit in shared memory.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int STAGES>
+__global__ void __launch_bounds__(256)
+k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_in, uint32_t n_out,
+            uint32_t rows_per_tile, unsigned long long n_tiles, const uint32_t *__restrict__ lut, uint32_t stride,
+            uint32_t tile_stride_bytes, int hint)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // layout: [STAGES][tile_stride_bytes] | table u32[n_out] (only if lut) | mbarriers
+    float *tiles = reinterpret_cast<float *>(smem_raw);
+    uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)STAGES * tile_stride_bytes);
+    const uint32_t tab_bytes = lut ? ((n_out * 4u + 15u) & ~15u) : 0u;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)STAGES * tile_stride_bytes + tab_bytes);
+
+    const uint32_t tile_bytes = rows_per_tile * n_in * 4u;
+    const uint32_t cpr = n_out >> 3;                             // 8-output chunks per row
+    const uint32_t chunks_per_tile = rows_per_tile * cpr;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (lut)
+        for (uint32_t i = threadIdx.x; i < n_out; i += blockDim.x) tab[i] = __ldg(lut + i);
+    __syncthreads();
+
+    // prologue: fill the pipeline
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) {
+            const unsigned long long t = blockIdx.x + (unsigned long long)s * gridDim.x;
+            if (t < n_tiles) {
+                mbar_expect_tx(&bars[s], tile_bytes);
+                bulk_g2s(reinterpret_cast<unsigned char *>(tiles) + (size_t)s * tile_stride_bytes,
+                         reinterpret_cast<const unsigned char *>(in) + t * (unsigned long long)tile_bytes, tile_bytes, &bars[s]);
+            }
+        }
+    }
+
+    uint32_t it = 0;
+    for (unsigned long long t = blockIdx.x; t < n_tiles; t += gridDim.x, it++) {
+        const int s = it % STAGES;
+        const uint32_t parity = (it / STAGES) & 1u;
+        mbar_wait(&bars[s], parity);
+        const float *tile = reinterpret_cast<const float *>(reinterpret_cast<const unsigned char *>(tiles) + (size_t)s * tile_stride_bytes);
+        int16_t *dst_tile = out + t * (unsigned long long)chunks_per_tile * 8ull;
+        for (uint32_t g = threadIdx.x; g < chunks_per_tile; g += blockDim.x) {
+            const uint32_t rr = g / cpr, c = g - rr * cpr;
+            const float *row = tile + rr * n_in;
+            uint32_t idx[8];
+            if (lut) {
+                const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
+                const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
+                idx[0] = a.x; idx[1] = a.y; idx[2] = a.z; idx[3] = a.w;
+                idx[4] = b.x; idx[5] = b.y; idx[6] = b.z; idx[7] = b.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; j++) idx[j] = (8u * c + j) * stride;
+            }
+            int e[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                // a pick outside the frame reads `undefined` in JS -> NaN -> 0
+                const float x = (idx[j] < n_in) ? row[idx[j]] : __int_as_float(0x7FC00000);
+                e[j] = enc_s32(x);
+            }
+            uint4 o;
+            o.x = pack_s16x2_sat(e[0], e[1]);
+            o.y = pack_s16x2_sat(e[2], e[3]);
+            o.z = pack_s16x2_sat(e[4], e[5]);
+            o.w = pack_s16x2_sat(e[6], e[7]);
+            st_128(dst_tile + (size_t)g * 8u, o, hint);
+        }
+        __syncthreads();   // everyone is done reading stage s
+        if (threadIdx.x == 0) {
+            const unsigned long long tn = t + (unsigned long long)STAGES * gridDim.x;
+            if (tn < n_tiles) {
+                mbar_expect_tx(&bars[s], tile_bytes);
+                bulk_g2s(reinterpret_cast<unsigned char *>(tiles) + (size_t)s * tile_stride_bytes,
+                         reinterpret_cast<const unsigned char *>(in) + tn * (unsigned long long)tile_bytes, tile_bytes, &bars[s]);
+            }
+        }
+    }
+}
+
 // ---- kernel 3: resampleTo16k alone (Float32 -> Float32 picks; App.tsx:18-32) ------------------------
 // Only for signature parity with the reference's stand-alone function; the batched product path is
 // the fused kernels above.  Bit patterns are moved as 32-bit words so NaN payloads survive.

@@ -54,6 +54,12 @@ def main():
                      for u, p in itertools.product((1, 2), (1, 2, 3, 4, 6))]
         grid += [dict(path=1, coalesced=0, block=b, unroll=u, blocks_per_sm=0, store_hint=0)
                  for b, u in itertools.product((128, 256, 512), (1, 2, 4))]
+        grid = [dict(tile=0, tile_kb=28, stages=2, **t) for t in grid]
+        if n_out % 8 == 0:
+            grid += [dict(path=2, coalesced=0, block=256, unroll=0, blocks_per_sm=p, store_hint=1, tile=1, tile_kb=kb, stages=st)
+                     for kb, st, p in itertools.product((8, 14, 20, 28, 40, 56), (1, 2, 3, 4), (0,))]
+            grid += [dict(path=2, coalesced=0, block=256, unroll=0, blocks_per_sm=p, store_hint=1, tile=1, tile_kb=kb, stages=2)
+                     for kb, p in itertools.product((14, 28), (1, 2, 3, 4))]
         for t in grid:
             ctx.tune(**t)
             for i in range(3):
@@ -70,17 +76,17 @@ def main():
             print(json.dumps(r), flush=True)
         for di, do in bufs:
             di.free(); do.free()
-    ctx.tune(path=0, coalesced=1, block=256, unroll=0, blocks_per_sm=0, store_hint=0)
+    ctx.tune(path=0, coalesced=1, block=256, unroll=0, blocks_per_sm=0, store_hint=1, tile=1, tile_kb=28, stages=2)
     if args.out:
         json.dump(results, open(args.out, "w"), indent=0)
     best = {}
     for r in results:
-        k = (r["rate"], r["frame_ms"], r["path"], r["coalesced"])
+        k = (r["rate"], r["frame_ms"], r["path"], r["coalesced"], r["tile"])
         if k not in best or r["gbs"] > best[k]["gbs"]:
             best[k] = r
     print("---- best per (rate, frame_ms, path, coalesced) ----")
     for k, r in sorted(best.items()):
-        print(k, f"{r['gbs']:.0f} GB/s frac {r['frac']:.3f}", {x: r[x] for x in ("block", "unroll", "blocks_per_sm", "store_hint")})
+        print(k, f"{r['gbs']:.0f} GB/s frac {r['frac']:.3f}", {x: r[x] for x in ("block", "unroll", "blocks_per_sm", "store_hint", "tile_kb", "stages")})
 
 
 if __name__ == "__main__":
