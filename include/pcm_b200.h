@@ -120,6 +120,22 @@ PCMB200_API int pcmb200_frames_encode(pcmb200_ctx *ctx, const float *in, size_t 
                                       int16_t *out, size_t pitch_out, uint32_t rows, uint32_t n_in,
                                       double in_rate, int mem, size_t *n_out);
 
+/* ---- frames + level meter ----------------------------------------------------------------------- */
+
+/* pcmb200_frames_encode plus the reference's audio level meter (App.tsx:267-271), fused so the
+ * samples are read from HBM once: for every whole `quantum` (128 = the AudioWorklet render quantum,
+ * App.tsx:46-55) of every frame, rms = Math.sqrt(sum(x*x) / quantum) in binary64 in sample order,
+ * and per session level = Math.max(rms, level * 0.85) (setLevel, App.tsx:271).  Device-resident
+ * buffers; asynchronous on the context's stream.
+ *   level_state  [rows] doubles, in/out: each session's level before / after this frame
+ *   levels       [rows][n_in / quantum] doubles (level after every quantum) or NULL
+ * The trailing n_in % quantum samples of a frame are not metered (the reference's frames are whole
+ * multiples of the quantum). */
+PCMB200_API int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in_device, size_t pitch_in,
+                                            int16_t *out_device, size_t pitch_out, uint32_t rows, uint32_t n_in,
+                                            double in_rate, uint32_t quantum, double *level_state_device,
+                                            double *levels_device, size_t *n_out);
+
 /* ---- per-tick replay --------------------------------------------------------------------------- */
 
 /* A tick whose buffers, shape and rate do not change (the steady state of a fleet: same sessions,

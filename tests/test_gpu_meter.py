@@ -1,0 +1,74 @@
+"""GPU parity of the fused level meter (App.tsx:267-271) against the oracle:
+binary64 results must be BIT-identical (sequential accumulation order is preserved on the device)."""
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_levels(x, n_in, state, quantum=128):
+    nq = n_in // quantum
+    lv = np.empty((x.shape[0], nq), dtype=np.float64)
+    for r in range(x.shape[0]):
+        lv[r] = oracle.level_meter(x[r, : nq * quantum], quantum, state[r])
+    return lv
+
+
+@pytest.mark.parametrize("rate,n_in,rows", [(48000, 2944, 700), (48000, 960, 1031), (44100, 882, 517), (16000, 320, 300),
+                                             (48000, 128, 64), (44100, 2646, 100), (48000, 96000, 3), (32000, 641, 50)])
+def test_fused_meter_bitwise(ctx, rate, n_in, rows):
+    rng = np.random.RandomState(n_in + rows)
+    n_out = oracle.resample_len(n_in, rate)
+    nq = n_in // 128
+    x = (rng.uniform(-1, 1, size=(rows, n_in)) * rng.uniform(0.01, 1.0, size=(rows, 1))).astype(np.float32)
+    if nq:
+        x[0, 5] = np.float32(np.nan)            # NaN poisons that session's level for good (Math.max semantics)
+        x[1, 3] = np.float32(np.inf)
+    state = rng.uniform(0, 1, rows)
+    state[2 % rows] = 0.0
+    d_in = ctx.device_buffer(x.nbytes)
+    d_out = ctx.device_buffer(max(rows * n_out * 2, 16))
+    d_state = ctx.device_buffer(rows * 8)
+    d_lv = ctx.device_buffer(max(rows * nq * 8, 16))
+    d_in.upload(x)
+    d_state.upload(state)
+    got_n = ctx.frames_encode_meter_ptr(d_in.ptr, n_in, d_out.ptr, n_out, rows, n_in, rate, d_state.ptr, d_lv.ptr)
+    ctx.sync()
+    assert got_n == n_out
+    pcm = d_out.download(np.int16, rows * n_out).reshape(rows, n_out)
+    assert np.array_equal(pcm, oracle.frames(x, n_in, rate))          # the PCM is unchanged by the fusion
+    want = _oracle_levels(x, n_in, state)
+    got = d_lv.download(np.float64, rows * nq).reshape(rows, nq)
+    assert got.view(np.uint64).tolist() == want.view(np.uint64).tolist() if rows * nq < 5000 else \
+        np.array_equal(got.view(np.uint64), want.view(np.uint64))
+    new_state = d_state.download(np.float64, rows)
+    expect_state = want[:, -1] if nq else state
+    assert np.array_equal(new_state.view(np.uint64), expect_state.view(np.uint64))
+    # second frame continues the decay chain from the stored state; no per-quantum trace this time
+    x2 = (x * 0.1).astype(np.float32)
+    d_in.upload(x2)
+    ctx.frames_encode_meter_ptr(d_in.ptr, n_in, d_out.ptr, n_out, rows, n_in, rate, d_state.ptr, None)
+    ctx.sync()
+    want2 = _oracle_levels(x2, n_in, expect_state)
+    s2 = d_state.download(np.float64, rows)
+    assert np.array_equal(s2.view(np.uint64), (want2[:, -1] if nq else expect_state).view(np.uint64))
+    for d in (d_in, d_out, d_state, d_lv):
+        d.free()
+
+
+def test_meter_fallback_kernel_on_pitched_rows(ctx):
+    rng = np.random.RandomState(9)
+    rows, n_in, pitch = 77, 960, 1000
+    x = np.zeros((rows, pitch), np.float32)
+    x[:, :n_in] = rng.uniform(-1, 1, size=(rows, n_in))
+    state = np.zeros(rows)
+    d_in, d_out = ctx.device_buffer(x.nbytes), ctx.device_buffer(rows * 320 * 2)
+    d_state, d_lv = ctx.device_buffer(rows * 8), ctx.device_buffer(rows * 7 * 8)
+    d_in.upload(x); d_state.upload(state)
+    ctx.frames_encode_meter_ptr(d_in.ptr, pitch, d_out.ptr, 320, rows, n_in, 48000, d_state.ptr, d_lv.ptr)
+    ctx.sync()
+    want = _oracle_levels(x, n_in, state)
+    assert np.array_equal(d_lv.download(np.float64, rows * 7).reshape(rows, 7).view(np.uint64), want.view(np.uint64))
+    assert np.array_equal(d_out.download(np.int16, rows * 320).reshape(rows, 320), oracle.frames(x, n_in, 48000))

@@ -246,26 +246,31 @@ int default_unroll(uint32_t R)
 // Kernel 2b (TMA tile-staged picks) for dense batches of short frames.  Returns the number of rows it
 // took (a multiple of the tile height; 0 if the batch does not qualify); the caller sends the rest
 // to kernel 2.
-template <int STAGES>
+template <int STAGES, bool METER>
 cudaError_t launch_tile_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *out, uint32_t n_in,
                           uint32_t n_out, uint32_t K, unsigned long long n_tiles, const uint32_t *lut, uint32_t R,
-                          uint32_t tile_stride, size_t smem)
+                          uint32_t tile_stride, size_t smem, const MeterArgs &meter)
 {
-    cudaError_t e = cudaFuncSetAttribute(k_tile_pick<STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_tile_pick<STAGES, METER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int resident = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_tile_pick<STAGES>, 256, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_tile_pick<STAGES, METER>, 256, smem);
     if (e != cudaSuccess || resident < 1) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;
     // measured sweet spot: about 112 KB of tiles in flight per SM (profiles/r01_sweep_tile.json)
     int preferred = (int)((112u * 1024u) / ((size_t)STAGES * tile_stride));
     if (preferred < 1) preferred = 1;
     const int grid = grid_for(ctx, n_tiles, resident, preferred);
-    k_tile_pick<STAGES><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, ctx->tune.store_hint);
+    k_tile_pick<STAGES, METER><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride,
+                                                      ctx->tune.store_hint, meter);
     return cudaGetLastError();
 }
 
+// Kernel 2b (TMA tile-staged picks, optionally with the fused level meter) for dense batches of
+// short frames.  Returns the number of rows it took (a multiple of the tile height; 0 if the batch
+// does not qualify); the caller sends the rest to the other kernels.
 uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
-                     size_t pitch_out, uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R)
+                     size_t pitch_out, uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R,
+                     const MeterArgs *meter = nullptr)
 {
     if (!ctx->tune.tile || pitch_in != n_in || pitch_out != n_out || (n_out % 8) != 0 || n_out > 8192) return 0;
     if (!aligned(in, 16) || !aligned(out, 16)) return 0;
@@ -273,24 +278,30 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
     if (n_in % 4 == 0) k0 = 1; else if (n_in % 2 == 0) k0 = 2;
     const size_t group_bytes = (size_t)k0 * n_in * 4;
     const size_t target = (size_t)ctx->tune.tile_kb * 1024;
-    if (group_bytes > 64 * 1024) return 0;             // frames too long to stage whole: kernel 2 handles them
+    if (group_bytes > 64 * 1024) return 0;             // frames too long to stage whole: other kernels handle them
     uint32_t K = (uint32_t)(target / group_bytes) * k0;
     if (K < k0) K = k0;
     if (rows < K) return 0;
     const unsigned long long n_tiles = rows / K;
     const uint32_t tile_bytes = K * n_in * 4;
     const uint32_t tile_stride = (tile_bytes + 127u) & ~127u;
-    const int stages = ctx->tune.stages;
-    const size_t smem = (size_t)stages * tile_stride + (lut ? ((n_out * 4u + 15u) & ~15u) : 0u) + (size_t)stages * 8;
+    const int stages = meter ? 2 : ctx->tune.stages;
+    size_t smem = (size_t)stages * tile_stride + (lut ? ((n_out * 4u + 15u) & ~15u) : 0u) + (size_t)((stages + 1) & ~1) * 8;
+    if (meter) smem += (size_t)K * meter->nq * sizeof(double);
     if (smem > 200 * 1024) return 0;
+    const MeterArgs none{0, 0, nullptr, nullptr};
     cudaError_t e;
-    switch (stages) {
-    case 1: e = launch_tile_k<1>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
-    case 2: e = launch_tile_k<2>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
-    case 3: e = launch_tile_k<3>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
-    default: e = launch_tile_k<4>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem); break;
+    if (meter) {
+        e = launch_tile_k<2, true>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, *meter);
+    } else {
+        switch (stages) {
+        case 1: e = launch_tile_k<1, false>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, none); break;
+        case 2: e = launch_tile_k<2, false>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, none); break;
+        case 3: e = launch_tile_k<3, false>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, none); break;
+        default: e = launch_tile_k<4, false>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, none); break;
+        }
     }
-    if (e != cudaSuccess) { cudaGetLastError(); return 0; }   // fall back to kernel 2 for the whole batch
+    if (e != cudaSuccess) { cudaGetLastError(); return 0; }   // fall back to the other kernels for the whole batch
     ctx->launches++;
     return (uint32_t)(n_tiles * K);
 }
@@ -844,6 +855,51 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
 }
 
 }  // extern "C"
+
+// ================================= frames + level meter ===============================================
+extern "C" int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out,
+                                           size_t pitch_out, uint32_t rows, uint32_t n_in, double in_rate,
+                                           uint32_t quantum, double *level_state, double *levels, size_t *n_out_p)
+{
+    NEED(ctx, "pcmb200_frames_encode_meter: ctx is NULL");
+    NEED(quantum >= 1, "pcmb200_frames_encode_meter: quantum must be >= 1");
+    size_t n_out = 0;
+    int s = resample_len(n_in, in_rate, &n_out);
+    if (s) return fail(ctx, s, "pcmb200_frames_encode_meter: RangeError: invalid typed array length");
+    if (n_out_p) *n_out_p = n_out;
+    if (rows == 0) return PCMB200_OK;
+    NEED(in && level_state && (out || n_out == 0), "pcmb200_frames_encode_meter: NULL buffer");
+    NEED(pitch_in >= n_in || rows == 1, "pcmb200_frames_encode_meter: pitch_in < n_in");
+    NEED(pitch_out >= n_out || rows == 1, "pcmb200_frames_encode_meter: pitch_out < output length");
+    CU(cudaSetDevice(ctx->device));
+    MeterArgs m{quantum, n_in / quantum, level_state, levels};
+    uint32_t took = 0;
+    if (n_out > 0 && m.nq > 0 && ctx->tune.path != 1) {
+        uint32_t R = 0;
+        const uint32_t *lut = nullptr;
+        if (!integer_ratio(in_rate, &R)) {
+            s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
+            if (s) return s;
+        }
+        took = launch_tile(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, &m);
+    }
+    if (took < rows) {   // rows the fused kernel did not take: the plain frame path + the stand-alone meter
+        const uint32_t rest = rows - took;
+        if (n_out > 0) {
+            s = launch_frames(ctx, ctx->stream, in + (size_t)took * pitch_in, pitch_in, out + (size_t)took * pitch_out,
+                              pitch_out, rest, n_in, in_rate, (uint32_t)n_out);
+            if (s) return s;
+        }
+        if (m.nq > 0) {
+            MeterArgs mr{quantum, m.nq, level_state + took, levels ? levels + (size_t)took * m.nq : nullptr};
+            const int grid = grid_for(ctx, (rest + 127) / 128, 16);
+            k_level_meter<<<grid, 128, 0, ctx->stream>>>(in + (size_t)took * pitch_in, pitch_in, rest, mr);
+            ctx->launches++;
+            CU(cudaGetLastError());
+        }
+    }
+    return PCMB200_OK;
+}
 
 // ================================= per-tick CUDA graph ================================================
 struct pcmb200_tick_graph {

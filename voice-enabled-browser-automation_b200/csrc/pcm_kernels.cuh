@@ -303,11 +303,30 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-template <int STAGES>
+// Level meter of the reference's capture handler (App.tsx:267-271), fused into kernel 2b: while a
+// tile of frames sits in shared memory, every whole `quantum` (128 samples, the AudioWorklet
+// render quantum) of every frame gets rms = sqrt(sum(x*x) / quantum) in binary64, accumulated in
+// sample order (x*x is exact in binary64, so one DFMA per sample reproduces JS's multiply-then-add
+// rounding), and each session's level follows level = max(rms, level * 0.85) over its quanta
+// (Math.max: NaN if either side is NaN).  0 extra DRAM read bytes; 8 bytes written per session
+// (+ 8 per quantum if the per-quantum trace is requested).
+struct MeterArgs {
+    uint32_t quantum;     // samples per quantum (128)
+    uint32_t nq;          // whole quanta per frame = n_in / quantum
+    double *state;        // [rows] in/out: level of each session
+    double *levels;       // [rows][nq] level after every quantum, or nullptr
+};
+
+__device__ __forceinline__ double js_max(double a, double b)
+{
+    return (a != a || b != b) ? __longlong_as_double(0x7FF8000000000000ll) : (a > b ? a : b);
+}
+
+template <int STAGES, bool METER>
 __global__ void __launch_bounds__(256)
 k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_in, uint32_t n_out,
             uint32_t rows_per_tile, unsigned long long n_tiles, const uint32_t *__restrict__ lut, uint32_t stride,
-            uint32_t tile_stride_bytes, int hint)
+            uint32_t tile_stride_bytes, int hint, MeterArgs meter)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     // layout: [STAGES][tile_stride_bytes] | table u32[n_out] (only if lut) | mbarriers
@@ -315,6 +334,7 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
     uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)STAGES * tile_stride_bytes);
     const uint32_t tab_bytes = lut ? ((n_out * 4u + 15u) & ~15u) : 0u;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)STAGES * tile_stride_bytes + tab_bytes);
+    double *rms_s = reinterpret_cast<double *>(bars + ((STAGES + 1) & ~1));   // METER: [rows_per_tile * nq]
 
     const uint32_t tile_bytes = rows_per_tile * n_in * 4u;
     const uint32_t cpr = n_out >> 3;                             // 8-output chunks per row
@@ -376,6 +396,38 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
             o.w = pack_s16x2_sat(e[6], e[7]);
             st_128(dst_tile + (size_t)g * 8u, o, hint);
         }
+        if (METER) {
+            // one lane per quantum; lanes run the 128 sequential steps SKEWED by their lane id, so at
+            // any instant the 32 lanes of a warp read 32 different banks while each lane still
+            // accumulates its own quantum strictly in sample order
+            const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+            const uint32_t quanta = rows_per_tile * meter.nq;
+            for (uint32_t base = warp * 32u; base < quanta; base += nwarps * 32u) {
+                const uint32_t qg = base + lane;
+                const bool valid = qg < quanta;
+                const uint32_t rr = valid ? qg / meter.nq : 0u, q = valid ? qg - rr * meter.nq : 0u;
+                const float *src = tile + rr * n_in + q * meter.quantum;
+                double sum = 0.0;
+                for (uint32_t i = 0; i < meter.quantum + 31u; i++) {
+                    const uint32_t k = i - lane;
+                    if (valid && k < meter.quantum) {   // unsigned: also false while i < lane
+                        const double x = (double)src[k];
+                        sum = __fma_rn(x, x, sum);
+                    }
+                }
+                if (valid) rms_s[qg] = __dsqrt_rn(__ddiv_rn(sum, (double)meter.quantum));
+            }
+            __syncthreads();
+            for (uint32_t rr = threadIdx.x; rr < rows_per_tile; rr += blockDim.x) {
+                const unsigned long long row = t * rows_per_tile + rr;
+                double lv = meter.state[row];
+                for (uint32_t q = 0; q < meter.nq; q++) {
+                    lv = js_max(rms_s[rr * meter.nq + q], __dmul_rn(lv, 0.85));
+                    if (meter.levels) meter.levels[row * meter.nq + q] = lv;
+                }
+                meter.state[row] = lv;
+            }
+        }
         __syncthreads();   // everyone is done reading stage s
         if (threadIdx.x == 0) {
             const unsigned long long tn = t + (unsigned long long)STAGES * gridDim.x;
@@ -402,6 +454,27 @@ k_pick_f32(const uint32_t *__restrict__ in, size_t pitch_in, uint32_t *__restric
         const uint32_t o = (uint32_t)(t - r * n_out);
         const uint32_t i = lut ? __ldg(lut + o) : o * stride;
         out[(size_t)r * pitch_out + o] = (i < n_in) ? __ldg(in + (size_t)r * pitch_in + i) : 0x7FC00000u;
+    }
+}
+
+// ---- kernel 4: level meter alone (any layout; one thread per session, sequential) ----------------------
+// Fallback for batches kernel 2b cannot take (pitched rows, long frames).  Correct, not fast.
+__global__ void __launch_bounds__(128)
+k_level_meter(const float *__restrict__ in, size_t pitch_in, uint32_t rows, MeterArgs meter)
+{
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+        const float *row = in + (size_t)r * pitch_in;
+        double lv = meter.state[r];
+        for (uint32_t q = 0; q < meter.nq; q++) {
+            double sum = 0.0;
+            for (uint32_t k = 0; k < meter.quantum; k++) {
+                const double x = (double)__ldg(row + (size_t)q * meter.quantum + k);
+                sum = __fma_rn(x, x, sum);
+            }
+            lv = js_max(__dsqrt_rn(__ddiv_rn(sum, (double)meter.quantum)), __dmul_rn(lv, 0.85));
+            if (meter.levels) meter.levels[(size_t)r * meter.nq + q] = lv;
+        }
+        meter.state[r] = lv;
     }
 }
 

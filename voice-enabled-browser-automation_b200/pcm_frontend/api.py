@@ -236,6 +236,15 @@ class Context:
                                               C.byref(got), mem), self.handle)
         return int(got.value)
 
+    def frames_encode_meter_ptr(self, in_ptr: int, pitch_in: int, out_ptr: int, pitch_out: int, rows: int, n_in: int,
+                                rate: float, state_ptr: int, levels_ptr: Optional[int] = None, quantum: int = 128) -> int:
+        """Fused frames + level meter (App.tsx:267-271, :281-282) on device buffers."""
+        got = C.c_size_t(0)
+        check(self._L.pcmb200_frames_encode_meter(self.handle, int(in_ptr), int(pitch_in), int(out_ptr), int(pitch_out),
+                                                  int(rows), int(n_in), float(rate), int(quantum), int(state_ptr),
+                                                  int(levels_ptr) if levels_ptr else None, C.byref(got)), self.handle)
+        return int(got.value)
+
     def tick_graph(self, in_ptr: int, pitch_in: int, out_ptr: int, pitch_out: int, rows: int, n_in: int,
                    rate: float) -> "TickGraph":
         """Record one device-resident tick as a CUDA graph (pcmb200_tick_graph_create)."""
