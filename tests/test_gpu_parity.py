@@ -325,7 +325,8 @@ def test_tick_graph_replay(ctx, rate, n_in):
 
 
 @pytest.mark.parametrize("rate,n_in", [(44100, 882), (22050, 441), (11025, 1103), (8000, 160), (44100, 2646),
-                                        (88200, 1764), (48000, 960), (80000, 1600), (37800, 756)])
+                                        (88200, 1764), (48000, 960), (80000, 1600), (37800, 756),
+                                        (48000, 2944), (44100, 1000), (96000, 1927), (48000, 128 * 47), (16000, 333)])
 def test_tile_staged_kernel_matches_general_kernel(ctx, rate, n_in):
     """Kernel 2b (TMA bulk copy -> shared memory -> table picks) against kernel 2 and the oracle, on
     dense device batches whose row count is not a multiple of the tile height."""

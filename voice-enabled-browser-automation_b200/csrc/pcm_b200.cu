@@ -48,6 +48,8 @@ struct Tuning {
     int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
     int tile_kb = 28;        // target tile size of kernel 2b
     int stages = 2;          // tiles in flight per CTA in kernel 2b
+    int meter_tile_kb = 104; // kernel 2b with the fused level meter: tile size ...
+    int meter_stages = 1;    // ... and stages (1 or 2)
     size_t slice_bytes = 32u << 20;
 };
 
@@ -259,6 +261,7 @@ cudaError_t launch_tile_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, in
     // measured sweet spot: about 112 KB of tiles in flight per SM (profiles/r01_sweep_tile.json)
     int preferred = (int)((112u * 1024u) / ((size_t)STAGES * tile_stride));
     if (preferred < 1) preferred = 1;
+    if (METER) preferred = 0;   // the meter's 128-step binary64 chains are latency-bound: fill the SM
     const int grid = grid_for(ctx, n_tiles, resident, preferred);
     k_tile_pick<STAGES, METER><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride,
                                                       ctx->tune.store_hint, meter);
@@ -272,27 +275,31 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
                      size_t pitch_out, uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R,
                      const MeterArgs *meter = nullptr)
 {
-    if (!ctx->tune.tile || pitch_in != n_in || pitch_out != n_out || (n_out % 8) != 0 || n_out > 8192) return 0;
+    if (!ctx->tune.tile || pitch_in != n_in || pitch_out != n_out || n_out == 0 || n_out > 8192) return 0;
     if (!aligned(in, 16) || !aligned(out, 16)) return 0;
     uint32_t k0 = 4;                                   // smallest row group whose bytes are a multiple of 16
     if (n_in % 4 == 0) k0 = 1; else if (n_in % 2 == 0) k0 = 2;
+    // ... and whose outputs are a whole number of 8-sample (16-byte) chunks
+    const uint32_t ko = n_out % 8 == 0 ? 1 : (n_out % 4 == 0 ? 2 : (n_out % 2 == 0 ? 4 : 8));
+    if (ko > k0) k0 = ko;
     const size_t group_bytes = (size_t)k0 * n_in * 4;
-    const size_t target = (size_t)ctx->tune.tile_kb * 1024;
-    if (group_bytes > 64 * 1024) return 0;             // frames too long to stage whole: other kernels handle them
+    const size_t target = (size_t)(meter ? ctx->tune.meter_tile_kb : ctx->tune.tile_kb) * 1024;
+    if (group_bytes > 96 * 1024) return 0;             // frames too long to stage whole: other kernels handle them
     uint32_t K = (uint32_t)(target / group_bytes) * k0;
     if (K < k0) K = k0;
     if (rows < K) return 0;
     const unsigned long long n_tiles = rows / K;
     const uint32_t tile_bytes = K * n_in * 4;
     const uint32_t tile_stride = (tile_bytes + 127u) & ~127u;
-    const int stages = meter ? 2 : ctx->tune.stages;
+    const int stages = meter ? (ctx->tune.meter_stages) : ctx->tune.stages;
     size_t smem = (size_t)stages * tile_stride + (lut ? ((n_out * 4u + 15u) & ~15u) : 0u) + (size_t)((stages + 1) & ~1) * 8;
     if (meter) smem += (size_t)K * meter->nq * sizeof(double);
     if (smem > 200 * 1024) return 0;
     const MeterArgs none{0, 0, nullptr, nullptr};
     cudaError_t e;
     if (meter) {
-        e = launch_tile_k<2, true>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, *meter);
+        if (stages == 1) e = launch_tile_k<1, true>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, *meter);
+        else e = launch_tile_k<2, true>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, *meter);
     } else {
         switch (stages) {
         case 1: e = launch_tile_k<1, false>(ctx, st, in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride, smem, none); break;
@@ -842,6 +849,12 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "tile_kb") {
         NEED(value >= 4 && value <= 96, "pcmb200_tune: tile_kb must be in [4, 96]");
         ctx->tune.tile_kb = (int)value;
+    } else if (k == "meter_tile_kb") {
+        NEED(value >= 4 && value <= 160, "pcmb200_tune: meter_tile_kb must be in [4, 160]");
+        ctx->tune.meter_tile_kb = (int)value;
+    } else if (k == "meter_stages") {
+        NEED(value == 1 || value == 2, "pcmb200_tune: meter_stages must be 1 or 2");
+        ctx->tune.meter_stages = (int)value;
     } else if (k == "stages") {
         NEED(value >= 1 && value <= 4, "pcmb200_tune: stages must be in [1, 4]");
         ctx->tune.stages = (int)value;

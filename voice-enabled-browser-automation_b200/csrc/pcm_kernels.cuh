@@ -273,8 +273,8 @@ k_pick_encode(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict
 // tile i+1 runs while tile i is gathered.  All 256 threads then read their picks from shared
 // memory through a copy of the pick table (also in shared memory), encode, and write one 128-bit
 // streaming store per 8 outputs; consecutive lanes write consecutive 16-byte chunks.
-// Requirements (launcher): in 16-byte aligned, rows dense (pitch_in == n_in, pitch_out == n_out),
-// n_out % 8 == 0, K * n_in % 4 == 0, tile + table fit in shared memory.
+// Requirements (launcher): in and out 16-byte aligned, rows dense (pitch_in == n_in, pitch_out ==
+// n_out), K * n_in % 4 == 0 and K * n_out % 8 == 0, tile + table fit in shared memory.
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
@@ -317,6 +317,35 @@ struct MeterArgs {
     double *levels;       // [rows][nq] level after every quantum, or nullptr
 };
 
+// |x| widened to binary64 WITHOUT the F2F.F64.F32 conversion: on B200 that instruction runs on the
+// XU pipe at 16 lanes/clk/SM, and at one conversion per input sample it (not HBM) bounded the
+// fused meter (ncu: XU 112 % busy, FP64 13 %).  For a normal float the binary64 image is a pure
+// re-packing of the same bits: exponent re-biased by 1023-127 = 896, 23 mantissa bits moved to the
+// top of the 52.  Zero stays zero; denormals, Inf and NaN (rare in audio) take the real conversion.
+// The sign is dropped because only x*x is needed.
+__device__ __forceinline__ double widen_abs(float x)
+{
+    // branch-free (a branch per sample costs more than the arithmetic: BSSY/BSYNC pairs serialise
+    // the four-sample step).  Denormals are first scaled by 2^24 (exact) into the normal range.
+    const uint32_t a0 = __float_as_uint(x) & 0x7FFFFFFFu;
+    const bool small = a0 < 0x00800000u;
+    const uint32_t a = small ? __float_as_uint(__uint_as_float(a0) * 16777216.0f) : a0;   // |x| (* 2^24)
+    uint32_t hi = (a >> 3) + (small ? 0x38000000u - (24u << 20) : 0x38000000u);
+    if (a >= 0x7F800000u) hi = 0x7FF00000u | ((a & 0x007FFFFFu) >> 3);                     // Inf / NaN
+    if (a == 0u) hi = 0u;                                                                   // +-0
+    return __hiloint2double((int)hi, (int)(a << 29));
+}
+
+// sqrt(sum / quantum): for a power-of-two quantum the division is an exact scaling, so the (software)
+// IEEE division is replaced by one multiplication with the same result.
+__device__ __forceinline__ double rms_of(double sum, uint32_t quantum)
+{
+    const bool pow2 = (quantum & (quantum - 1u)) == 0u;
+    const double inv = __hiloint2double((int)((1023u - (31u - (uint32_t)__clz((int)quantum))) << 20), 0);   // 2^-log2(quantum)
+    const double mean = pow2 ? sum * inv : __ddiv_rn(sum, (double)quantum);
+    return __dsqrt_rn(mean);
+}
+
 __device__ __forceinline__ double js_max(double a, double b)
 {
     return (a != a || b != b) ? __longlong_as_double(0x7FF8000000000000ll) : (a > b ? a : b);
@@ -337,8 +366,9 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
     double *rms_s = reinterpret_cast<double *>(bars + ((STAGES + 1) & ~1));   // METER: [rows_per_tile * nq]
 
     const uint32_t tile_bytes = rows_per_tile * n_in * 4u;
-    const uint32_t cpr = n_out >> 3;                             // 8-output chunks per row
-    const uint32_t chunks_per_tile = rows_per_tile * cpr;
+    const uint32_t cpr = n_out >> 3;                             // 8-output chunks per row (rows_aligned)
+    const bool rows_aligned = (n_out & 7u) == 0u;
+    const uint32_t chunks_per_tile = (rows_per_tile * n_out) >> 3;   // launcher: rows_per_tile * n_out % 8 == 0
 
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -370,23 +400,38 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
         const float *tile = reinterpret_cast<const float *>(reinterpret_cast<const unsigned char *>(tiles) + (size_t)s * tile_stride_bytes);
         int16_t *dst_tile = out + t * (unsigned long long)chunks_per_tile * 8ull;
         for (uint32_t g = threadIdx.x; g < chunks_per_tile; g += blockDim.x) {
-            const uint32_t rr = g / cpr, c = g - rr * cpr;
-            const float *row = tile + rr * n_in;
-            uint32_t idx[8];
-            if (lut) {
-                const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
-                const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
-                idx[0] = a.x; idx[1] = a.y; idx[2] = a.z; idx[3] = a.w;
-                idx[4] = b.x; idx[5] = b.y; idx[6] = b.z; idx[7] = b.w;
-            } else {
+            uint32_t idx[8];     // offset of each pick inside the tile (0xFFFFFFFF: outside its frame)
+            if (rows_aligned) {
+                const uint32_t rr = g / cpr, c = g - rr * cpr;
+                const uint32_t base = rr * n_in;
+                if (lut) {
+                    const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
+                    const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
+                    idx[0] = a.x; idx[1] = a.y; idx[2] = a.z; idx[3] = a.w;
+                    idx[4] = b.x; idx[5] = b.y; idx[6] = b.z; idx[7] = b.w;
+                } else {
 #pragma unroll
-                for (int j = 0; j < 8; j++) idx[j] = (8u * c + j) * stride;
+                    for (int j = 0; j < 8; j++) idx[j] = (8u * c + j) * stride;
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j++) idx[j] = idx[j] < n_in ? base + idx[j] : 0xFFFFFFFFu;
+            } else {
+                // frames whose length is not a multiple of 8 outputs (the reference's real frames:
+                // 23 quanta at 48 kHz -> 981 outputs): a chunk is 8 consecutive outputs of the tile's
+                // flat output and may run over a frame boundary
+                uint32_t rr = (8u * g) / n_out, o = 8u * g - rr * n_out;
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const uint32_t i = lut ? tab[o] : o * stride;
+                    idx[j] = i < n_in ? rr * n_in + i : 0xFFFFFFFFu;
+                    if (++o == n_out) { o = 0; rr++; }
+                }
             }
             int e[8];
 #pragma unroll
             for (int j = 0; j < 8; j++) {
                 // a pick outside the frame reads `undefined` in JS -> NaN -> 0
-                const float x = (idx[j] < n_in) ? row[idx[j]] : __int_as_float(0x7FC00000);
+                const float x = (idx[j] != 0xFFFFFFFFu) ? tile[idx[j]] : __int_as_float(0x7FC00000);
                 e[j] = enc_s32(x);
             }
             uint4 o;
@@ -397,32 +442,81 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
             st_128(dst_tile + (size_t)g * 8u, o, hint);
         }
         if (METER) {
-            // one lane per quantum; lanes run the 128 sequential steps SKEWED by their lane id, so at
-            // any instant the 32 lanes of a warp read 32 different banks while each lane still
-            // accumulates its own quantum strictly in sample order
+            // the session levels are needed only after the meter: fetch them now so the global-memory
+            // latency hides behind it (threads 0..rows_per_tile-1 own one session of the tile each)
+            double lv_in = 0.0;
+            if (threadIdx.x < rows_per_tile) lv_in = meter.state[t * rows_per_tile + threadIdx.x];
+            // One lane per quantum, strictly in sample order (binary64 rounding depends on it).  All
+            // quanta start 128 floats apart, i.e. in the same bank, so lanes are SKEWED: at any step
+            // the lanes that share a shared-memory access phase read different banks, while each
+            // lane still walks its own quantum front to back.
             const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
             const uint32_t quanta = rows_per_tile * meter.nq;
-            for (uint32_t base = warp * 32u; base < quanta; base += nwarps * 32u) {
-                const uint32_t qg = base + lane;
-                const bool valid = qg < quanta;
-                const uint32_t rr = valid ? qg / meter.nq : 0u, q = valid ? qg - rr * meter.nq : 0u;
-                const float *src = tile + rr * n_in + q * meter.quantum;
-                double sum = 0.0;
-                for (uint32_t i = 0; i < meter.quantum + 31u; i++) {
-                    const uint32_t k = i - lane;
-                    if (valid && k < meter.quantum) {   // unsigned: also false while i < lane
-                        const double x = (double)src[k];
-                        sum = __fma_rn(x, x, sum);
+            if ((n_in & 3u) == 0u && (meter.quantum & 3u) == 0u) {
+                // 128-bit path: a quantum is G granules of 4 floats; an LDS.128 is served 8 lanes at a
+                // time, so a skew of (lane & 7) granules is enough.  Work is dealt to 8-lane groups
+                // warp-first, so a tile's few dozen quanta spread over all warps (latency hiding)
+                // instead of filling one or two.  The next granule is fetched while the current one
+                // goes through its four dependent DFMAs.
+                const uint32_t sub = lane & 7u;
+                const uint32_t octet = (lane >> 3) * nwarps + warp, octets = nwarps * 4u;
+                const uint32_t G = meter.quantum >> 2;
+                for (uint32_t base = octet * 8u; base < quanta; base += octets * 8u) {
+                    const uint32_t qg = base + sub;
+                    const bool valid = qg < quanta;
+                    const uint32_t rr = valid ? qg / meter.nq : 0u, q = valid ? qg - rr * meter.nq : 0u;
+                    const float4 *src4 = reinterpret_cast<const float4 *>(tile + rr * n_in + q * meter.quantum);
+                    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    float4 cur = (valid && sub == 0u) ? src4[0] : zero4;
+                    double sum = 0.0;
+                    // No branches inside: a lane that has not started or has finished feeds zeros
+                    // (sum + 0*0 leaves sum unchanged, NaN and Inf included).
+                    for (uint32_t i = 0; i < G + 7u; i++) {
+                        const uint32_t gn = i - sub + 1u;     // next granule; wraps to 0 one step before the start
+                        const float4 v = src4[gn < G ? gn : G - 1u];
+                        const float4 nxt = (valid && gn < G) ? v : zero4;
+                        const double x0 = widen_abs(cur.x), x1 = widen_abs(cur.y), x2 = widen_abs(cur.z), x3 = widen_abs(cur.w);
+                        sum = __fma_rn(x0, x0, sum);
+                        sum = __fma_rn(x1, x1, sum);
+                        sum = __fma_rn(x2, x2, sum);
+                        sum = __fma_rn(x3, x3, sum);
+                        cur = nxt;
                     }
+                    if (valid) rms_s[qg] = rms_of(sum, meter.quantum);
                 }
-                if (valid) rms_s[qg] = __dsqrt_rn(__ddiv_rn(sum, (double)meter.quantum));
+            } else {
+                // scalar path (frames whose rows are not 16-byte aligned in the tile): skew by lane
+                for (uint32_t base = warp * 32u; base < quanta; base += nwarps * 32u) {
+                    const uint32_t qg = base + lane;
+                    const bool valid = qg < quanta;
+                    const uint32_t rr = valid ? qg / meter.nq : 0u, q = valid ? qg - rr * meter.nq : 0u;
+                    const float *src = tile + rr * n_in + q * meter.quantum;
+                    double sum = 0.0;
+                    for (uint32_t i = 0; i < meter.quantum + 31u; i++) {
+                        const uint32_t k = i - lane;
+                        if (valid && k < meter.quantum) {   // unsigned: also false while i < lane
+                            const double x = widen_abs(src[k]);
+                            sum = __fma_rn(x, x, sum);
+                        }
+                    }
+                    if (valid) rms_s[qg] = rms_of(sum, meter.quantum);
+                }
             }
             __syncthreads();
             for (uint32_t rr = threadIdx.x; rr < rows_per_tile; rr += blockDim.x) {
                 const unsigned long long row = t * rows_per_tile + rr;
-                double lv = meter.state[row];
+                double lv = rr == threadIdx.x ? lv_in : meter.state[row];
+                // Math.max(rms, level * 0.85): NaN if either is NaN, and a NaN level stays NaN
+                // (NaN * 0.85).  NaN-ness is tracked with integer tests so each step costs one DMUL and
+                // one DSETP on the (long-latency) FP64 pipe.
+                bool poisoned = lv != lv;
                 for (uint32_t q = 0; q < meter.nq; q++) {
-                    lv = js_max(rms_s[rr * meter.nq + q], __dmul_rn(lv, 0.85));
+                    const double rms = rms_s[rr * meter.nq + q];
+                    const uint32_t hi = (uint32_t)__double2hiint(rms) & 0x7FFFFFFFu;
+                    poisoned |= hi > 0x7FF00000u || (hi == 0x7FF00000u && __double2loint(rms) != 0);
+                    const double dec = __dmul_rn(lv, 0.85);
+                    lv = rms > dec ? rms : dec;
+                    if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
                     if (meter.levels) meter.levels[row * meter.nq + q] = lv;
                 }
                 meter.state[row] = lv;
@@ -468,10 +562,10 @@ k_level_meter(const float *__restrict__ in, size_t pitch_in, uint32_t rows, Mete
         for (uint32_t q = 0; q < meter.nq; q++) {
             double sum = 0.0;
             for (uint32_t k = 0; k < meter.quantum; k++) {
-                const double x = (double)__ldg(row + (size_t)q * meter.quantum + k);
+                const double x = widen_abs(__ldg(row + (size_t)q * meter.quantum + k));
                 sum = __fma_rn(x, x, sum);
             }
-            lv = js_max(__dsqrt_rn(__ddiv_rn(sum, (double)meter.quantum)), __dmul_rn(lv, 0.85));
+            lv = js_max(rms_of(sum, meter.quantum), __dmul_rn(lv, 0.85));
             if (meter.levels) meter.levels[(size_t)r * meter.nq + q] = lv;
         }
         meter.state[r] = lv;

@@ -168,13 +168,64 @@ def config5(ctx):
     return res
 
 
+def meter(ctx, n_in, S):
+    """8f next-1: frames + fused level meter vs frames alone on the same dense batch."""
+    n_out = n_in // 3
+    nq = n_in // 128
+    bufs = [(ctx.device_buffer(S * n_in * 4), ctx.device_buffer(S * n_out * 2)) for _ in range(2)]
+    for t, (di, _) in enumerate(bufs):
+        ctx.synth_fill(di.ptr, n_in, S, n_in, 48000, 0x5EED + t, 0)
+    st = ctx.device_buffer(S * 8)
+    st.memset(0)
+    ctx.sync()
+    k = {"i": 0}
+
+    def plain():
+        di, do = bufs[k["i"] % 2]; k["i"] += 1
+        ctx.frames_encode_ptr(di.ptr, n_in, do.ptr, n_out, S, n_in, 48000, MEM_DEVICE)
+
+    def fused():
+        di, do = bufs[k["i"] % 2]; k["i"] += 1
+        ctx.frames_encode_meter_ptr(di.ptr, n_in, do.ptr, n_out, S, n_in, 48000, st.ptr, None)
+    ms_plain = timed(ctx, plain, 20)
+    ms_fused = timed(ctx, fused, 20)
+    algo = S * (n_in * 4 + n_out * 2)
+    algo_m = algo + S * 16          # + level state read and written
+    for di, do in bufs:
+        di.free(); do.free()
+    st.free()
+    return {"config": "next-1 fused level meter", "sessions": S, "n_in": n_in, "quanta_per_frame": nq,
+            "frames_only_ms": ms_plain, "frames_only_gbs": algo / (ms_plain * 1e-3) / 1e9,
+            "frames_plus_meter_ms": ms_fused, "frames_plus_meter_gbs": algo_m / (ms_fused * 1e-3) / 1e9,
+            "frac_of_measured_peak": algo_m / (ms_fused * 1e-3) / 1e9 / PEAK,
+            "in_samples_per_s": S * n_in / (ms_fused * 1e-3)}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
-    args = ap.parse_args()
     ctx = pcm_frontend.Context(0)
     results = {"device": ctx.device_info(), "host_cores": os.cpu_count(), "hbm_peak_gbs": PEAK, "configs": []}
-    for fn in (lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    ap.add_argument("--only-meter", action="store_true")
+    ap.add_argument("--sweep-meter", action="store_true")
+    args = ap.parse_args()
+    if args.sweep_meter:
+        for kb in (12, 20, 28, 40, 56, 80, 104):
+            for stg in (1, 2):
+                for bps in (0, 1, 2, 3, 4, 6):
+                    try:
+                        ctx.tune(meter_tile_kb=kb, meter_stages=stg, blocks_per_sm=bps)
+                        for n_in, S in ((960, 1 << 19), (2944, 1 << 17)):
+                            r = meter(ctx, n_in, S)
+                            print(json.dumps(dict(kb=kb, stages=stg, bps=bps, n_in=n_in, ms=r["frames_plus_meter_ms"], frac=r["frac_of_measured_peak"])), flush=True)
+                    except Exception as e:
+                        print("skip", kb, stg, bps, e)
+        return
+    if args.only_meter:
+        for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18)):
+            print(json.dumps(fn()), flush=True)
+        return
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)
