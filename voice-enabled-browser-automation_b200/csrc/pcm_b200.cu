@@ -48,7 +48,7 @@ struct Tuning {
     int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
     int tile_kb = 28;        // target tile size of kernel 2b
     int stages = 2;          // tiles in flight per CTA in kernel 2b
-    int meter_tile_kb = 104; // kernel 2b with the fused level meter: tile size ...
+    int meter_tile_kb = 56;  // kernel 2b with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
     size_t slice_bytes = 32u << 20;
 };

@@ -346,6 +346,17 @@ __device__ __forceinline__ double rms_of(double sum, uint32_t quantum)
     return __dsqrt_rn(mean);
 }
 
+// The cheap form used in the meter's inner loop: exact for zeros and normal floats.  `odd` collects
+// a flag for the rare inputs it gets wrong (denormal, Inf, NaN); the caller then redoes that
+// quantum with widen_abs.
+__device__ __forceinline__ double widen_abs_fast(float x, bool &odd)
+{
+    const uint32_t a = __float_as_uint(x) & 0x7FFFFFFFu;
+    odd |= (a - 0x00800000u >= 0x7F000000u) && a != 0u;
+    const uint32_t hi = a ? (a >> 3) + 0x38000000u : 0u;
+    return __hiloint2double((int)hi, (int)(a << 29));
+}
+
 __device__ __forceinline__ double js_max(double a, double b)
 {
     return (a != a || b != b) ? __longlong_as_double(0x7FF8000000000000ll) : (a > b ? a : b);
@@ -454,12 +465,10 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
             const uint32_t quanta = rows_per_tile * meter.nq;
             if ((n_in & 3u) == 0u && (meter.quantum & 3u) == 0u) {
                 // 128-bit path: a quantum is G granules of 4 floats; an LDS.128 is served 8 lanes at a
-                // time, so a skew of (lane & 7) granules is enough.  Work is dealt to 8-lane groups
-                // warp-first, so a tile's few dozen quanta spread over all warps (latency hiding)
-                // instead of filling one or two.  The next granule is fetched while the current one
-                // goes through its four dependent DFMAs.
+                // time, so a skew of (lane & 7) granules is enough.  The next granule is fetched while
+                // the current one goes through its four dependent DFMAs.
                 const uint32_t sub = lane & 7u;
-                const uint32_t octet = (lane >> 3) * nwarps + warp, octets = nwarps * 4u;
+                const uint32_t octet = warp * 4u + (lane >> 3), octets = nwarps * 4u;   // packed: the loop is issue-bound
                 const uint32_t G = meter.quantum >> 2;
                 for (uint32_t base = octet * 8u; base < quanta; base += octets * 8u) {
                     const uint32_t qg = base + sub;
@@ -469,18 +478,28 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
                     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
                     float4 cur = (valid && sub == 0u) ? src4[0] : zero4;
                     double sum = 0.0;
+                    bool odd = false;
                     // No branches inside: a lane that has not started or has finished feeds zeros
                     // (sum + 0*0 leaves sum unchanged, NaN and Inf included).
                     for (uint32_t i = 0; i < G + 7u; i++) {
                         const uint32_t gn = i - sub + 1u;     // next granule; wraps to 0 one step before the start
                         const float4 v = src4[gn < G ? gn : G - 1u];
                         const float4 nxt = (valid && gn < G) ? v : zero4;
-                        const double x0 = widen_abs(cur.x), x1 = widen_abs(cur.y), x2 = widen_abs(cur.z), x3 = widen_abs(cur.w);
+                        const double x0 = widen_abs_fast(cur.x, odd), x1 = widen_abs_fast(cur.y, odd),
+                                     x2 = widen_abs_fast(cur.z, odd), x3 = widen_abs_fast(cur.w, odd);
                         sum = __fma_rn(x0, x0, sum);
                         sum = __fma_rn(x1, x1, sum);
                         sum = __fma_rn(x2, x2, sum);
                         sum = __fma_rn(x3, x3, sum);
                         cur = nxt;
+                    }
+                    if (odd) {   // rare: the quantum holds a denormal, Inf or NaN -> redo it exactly
+                        sum = 0.0;
+                        const float *src = reinterpret_cast<const float *>(src4);
+                        for (uint32_t k = 0; k < meter.quantum; k++) {
+                            const double x = widen_abs(src[k]);
+                            sum = __fma_rn(x, x, sum);
+                        }
                     }
                     if (valid) rms_s[qg] = rms_of(sum, meter.quantum);
                 }
