@@ -136,6 +136,32 @@ PCMB200_API int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in_de
                                             double in_rate, uint32_t quantum, double *level_state_device,
                                             double *levels_device, size_t *n_out);
 
+/* ---- capture aggregator -------------------------------------------------------------------------- */
+
+/* Device-side restatement of the reference's capture aggregator (App.tsx:148-157, :273-288): each
+ * session appends 128-sample quanta; the quantum that arrives with now - lastSend >= desired_ms
+ * flushes the session's WHOLE buffer as one frame, pcm16 = floatTo16BitPCM(resampleTo16k(buf, rate))
+ * (:281-282), and resets buffer and lastSend (:286-287).  The wall clock is injected: arrival_ms[i]
+ * is performance.now() at quantum i.  Sessions of one aggregator share the capture rate.
+ *   max_frame_quanta  longest frame, in quanta (a push that would exceed it is rejected whole)
+ *   max_push_quanta   most quanta in one push;   max_out_samples_per_push  output arena (host path) */
+typedef struct pcmb200_aggregator pcmb200_aggregator;
+PCMB200_API int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
+                                          double desired_ms, uint32_t max_frame_quanta, uint32_t max_push_quanta,
+                                          size_t max_out_samples_per_push, pcmb200_aggregator **agg);
+PCMB200_API int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *agg);
+/* Initial state / stop() of the reference (App.tsx:148-157, :325-330): empty buffer, lastSend = now. */
+PCMB200_API int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t session, double now_ms);
+/* Append n_quanta quanta, in arrival order (quantum i belongs to sessions[i], samples + i*quantum),
+ * and convert every frame that flushes.  Frame f (in flush order) is frame_len[f] int16 samples of
+ * session frame_session[f] at out + frame_offset[f] (offsets are multiples of 8 samples).
+ * Host `out`: returns when the frames are on the host.  Device `out`: asynchronous (pcmb200_sync). */
+PCMB200_API int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t n_quanta,
+                                        const uint32_t *sessions, const double *arrival_ms, const float *samples,
+                                        int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
+                                        uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
+                                        uint32_t max_frames, uint32_t *n_frames);
+
 /* ---- per-tick replay --------------------------------------------------------------------------- */
 
 /* A tick whose buffers, shape and rate do not change (the steady state of a fleet: same sessions,

@@ -7,6 +7,7 @@
 #include "../../include/pcm_b200.h"
 #include "pcm_kernels.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -981,6 +982,253 @@ extern "C" int pcmb200_tick_graph_destroy(pcmb200_ctx *ctx, pcmb200_tick_graph *
     if (graph->exec) cudaGraphExecDestroy(graph->exec);
     if (graph->graph) cudaGraphDestroy(graph->graph);
     delete graph;
+    return PCMB200_OK;
+}
+
+// ================================= device-side aggregator ======================
+// Host scheduler + device rings restating the reference's capture aggregator (App.tsx:148-157,
+// :273-288): per session, 128-sample quanta are appended to a buffer; when a quantum arrives with
+// now - lastSend >= desiredMs the WHOLE buffer (a multiple of 128 samples, e.g. 23 quanta = 2944
+// samples at 48 kHz) is converted with floatTo16BitPCM(resampleTo16k(buf, rate)) and the buffer and
+// lastSend are reset.  The wall clock is injected: every quantum carries its arrival time.
+struct pcmb200_aggregator {
+    uint32_t max_sessions = 0, quantum = 128, half_quanta = 0, max_push = 0;
+    size_t out_cap = 0;
+    double rate = 0, desired_ms = 60;
+    float *ring = nullptr;                 // [max_sessions][2][half_quanta * quantum]
+    float *d_stage = nullptr;              // [max_push][quantum] upload area for host-resident quanta
+    int16_t *d_out = nullptr;              // [out_cap] when the caller's output is host memory
+    uint32_t *d_slot = nullptr, *d_src_row = nullptr;
+    unsigned long long *d_dst_off = nullptr;
+    uint32_t *h_slot = nullptr, *h_src_row = nullptr;   // pinned staging of the three index arrays
+    unsigned long long *h_dst_off = nullptr;
+    cudaEvent_t uploaded = nullptr;
+    std::vector<uint32_t> fill;
+    std::vector<uint8_t> half;
+    std::vector<double> last_send;
+    std::vector<uint32_t> pending[2];      // round id (+1) in which that half was flushed
+    uint32_t round_id = 0;
+};
+
+namespace {
+struct AggFrame { uint32_t src_row, nq, session; unsigned long long off; uint32_t n_out; };
+struct AggRound { uint32_t q0, q1, f0, f1; };
+struct AggUndo { uint32_t s, fill; uint8_t half; double last; uint32_t p0, p1; };
+}  // namespace
+
+extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
+                                         double desired_ms, uint32_t max_frame_quanta, uint32_t max_push_quanta,
+                                         size_t max_out_samples_per_push, pcmb200_aggregator **out)
+{
+    NEED(ctx && out, "pcmb200_aggregator_create: NULL argument");
+    *out = nullptr;
+    NEED(max_sessions > 0 && quantum > 0 && max_frame_quanta > 0 && max_push_quanta > 0 && max_out_samples_per_push > 0,
+         "pcmb200_aggregator_create: sizes must be positive");
+    NEED(in_rate > 0 && desired_ms == desired_ms, "pcmb200_aggregator_create: bad rate / desired_ms");
+    size_t probe = 0;
+    int s = resample_len((size_t)max_frame_quanta * quantum, in_rate, &probe);
+    if (s) return fail(ctx, s, "pcmb200_aggregator_create: RangeError: invalid typed array length");
+    CU(cudaSetDevice(ctx->device));
+    pcmb200_aggregator *a = new (std::nothrow) pcmb200_aggregator();
+    if (!a) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed");
+    a->max_sessions = max_sessions; a->quantum = quantum; a->half_quanta = max_frame_quanta; a->max_push = max_push_quanta;
+    a->out_cap = max_out_samples_per_push; a->rate = in_rate; a->desired_ms = desired_ms;
+    cudaError_t e = cudaSuccess;
+    try {
+        a->fill.assign(max_sessions, 0); a->half.assign(max_sessions, 0); a->last_send.assign(max_sessions, 0.0);
+        a->pending[0].assign(max_sessions, 0); a->pending[1].assign(max_sessions, 0);
+    } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
+    const size_t ring_bytes = (size_t)max_sessions * 2 * max_frame_quanta * quantum * sizeof(float);
+#define AGG_STEP(call) if (e == cudaSuccess) e = (call)
+    AGG_STEP(cudaMalloc((void **)&a->ring, ring_bytes));
+    AGG_STEP(cudaMalloc((void **)&a->d_stage, (size_t)max_push_quanta * quantum * sizeof(float)));
+    AGG_STEP(cudaMalloc((void **)&a->d_out, max_out_samples_per_push * sizeof(int16_t)));
+    AGG_STEP(cudaMalloc((void **)&a->d_slot, (size_t)max_push_quanta * 4));
+    AGG_STEP(cudaMalloc((void **)&a->d_src_row, (size_t)max_push_quanta * 4));
+    AGG_STEP(cudaMalloc((void **)&a->d_dst_off, (size_t)max_push_quanta * 8));
+    AGG_STEP(cudaHostAlloc((void **)&a->h_slot, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
+    AGG_STEP(cudaHostAlloc((void **)&a->h_src_row, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
+    AGG_STEP(cudaHostAlloc((void **)&a->h_dst_off, (size_t)max_push_quanta * 8, cudaHostAllocDefault));
+    AGG_STEP(cudaEventCreateWithFlags(&a->uploaded, cudaEventDisableTiming));
+    AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_bytes, ctx->stream));
+#undef AGG_STEP
+    if (e != cudaSuccess) {
+        std::string m = std::string("pcmb200_aggregator_create: ") + cudaGetErrorString(e);
+        pcmb200_aggregator_destroy(ctx, a);
+        cudaGetLastError();
+        return fail(ctx, e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA, m);
+    }
+    *out = a;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *a)
+{
+    NEED(ctx, "pcmb200_aggregator_destroy: ctx is NULL");
+    if (!a) return PCMB200_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(a->ring); cudaFree(a->d_stage); cudaFree(a->d_out); cudaFree(a->d_slot); cudaFree(a->d_src_row); cudaFree(a->d_dst_off);
+    if (a->h_slot) cudaFreeHost(a->h_slot);
+    if (a->h_src_row) cudaFreeHost(a->h_src_row);
+    if (a->h_dst_off) cudaFreeHost(a->h_dst_off);
+    if (a->uploaded) cudaEventDestroy(a->uploaded);
+    cudaGetLastError();
+    delete a;
+    return PCMB200_OK;
+}
+
+// App.tsx:325-330 (stop) / :148-157 (initial state): empty buffer, lastSend = now.
+extern "C" int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t session, double now_ms)
+{
+    NEED(ctx && a, "pcmb200_aggregator_reset_session: NULL argument");
+    NEED(session < a->max_sessions, "pcmb200_aggregator_reset_session: session out of range");
+    a->fill[session] = 0;
+    a->last_send[session] = now_ms;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n_quanta,
+                                       const uint32_t *sessions, const double *arrival_ms, const float *samples,
+                                       int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
+                                       uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
+                                       uint32_t max_frames, uint32_t *n_frames)
+{
+    NEED(ctx && a && n_frames, "pcmb200_aggregator_push: NULL argument");
+    *n_frames = 0;
+    if (n_quanta == 0) return PCMB200_OK;
+    NEED(sessions && arrival_ms && samples && out, "pcmb200_aggregator_push: NULL buffer");
+    NEED((samples_mem == PCMB200_MEM_HOST || samples_mem == PCMB200_MEM_DEVICE) &&
+         (out_mem == PCMB200_MEM_HOST || out_mem == PCMB200_MEM_DEVICE), "pcmb200_aggregator_push: bad mem kind");
+    NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push: more quanta than max_push_quanta");
+    for (uint32_t i = 0; i < n_quanta; i++)
+        NEED(sessions[i] < a->max_sessions, "pcmb200_aggregator_push: session id out of range");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaEventSynchronize(a->uploaded));   // the previous push's index upload has left the pinned staging
+
+    // ---- plan on the host: where every quantum goes, which sessions flush, in how many rounds ----
+    std::vector<AggFrame> frames;
+    std::vector<AggRound> rounds;
+    std::vector<AggUndo> undo;
+    std::vector<uint8_t> touched(0);
+    AggRound cur{0, 0, 0, 0};
+    a->round_id++;
+    unsigned long long off = 0;
+    int status = PCMB200_OK;
+    std::string why;
+    auto close_round = [&](uint32_t q_end) {
+        cur.q1 = q_end; cur.f1 = (uint32_t)frames.size();
+        if (cur.q1 > cur.q0 || cur.f1 > cur.f0) rounds.push_back(cur);
+        cur.q0 = q_end; cur.f0 = (uint32_t)frames.size();
+        a->round_id++;
+    };
+    for (uint32_t i = 0; i < n_quanta; i++) {
+        const uint32_t s = sessions[i];
+        undo.push_back({s, a->fill[s], a->half[s], a->last_send[s], a->pending[0][s], a->pending[1][s]});
+        uint8_t h = a->half[s];
+        if (a->pending[h][s] == a->round_id) close_round(i);   // that half still holds an unlaunched frame
+        if (a->fill[s] >= a->half_quanta) { status = PCMB200_ERR_CAPACITY; why = "a session's buffer exceeds max_frame_quanta (no flush arrived)"; break; }
+        a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
+        a->fill[s]++;
+        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+        const double elapsed = arrival_ms[i] - a->last_send[s];
+        if (elapsed >= a->desired_ms) {
+            size_t n_out = 0;
+            resample_len((size_t)a->fill[s] * a->quantum, a->rate, &n_out);
+            if (frames.size() >= max_frames) { status = PCMB200_ERR_CAPACITY; why = "more flushed frames than max_frames"; break; }
+            if (off + n_out > out_capacity || (out_mem == PCMB200_MEM_HOST && off + n_out > a->out_cap)) {
+                status = PCMB200_ERR_CAPACITY; why = "flushed frames exceed the output capacity"; break;
+            }
+            frames.push_back({s * 2u + h, a->fill[s], s, off, (uint32_t)n_out});
+            off += (n_out + 7u) & ~(size_t)7u;                  // frames start on 16-byte boundaries
+            a->pending[h][s] = a->round_id;
+            a->half[s] = h ^ 1u;
+            a->fill[s] = 0;
+            a->last_send[s] = arrival_ms[i];                    // App.tsx:287
+        }
+    }
+    if (status != PCMB200_OK) {   // roll the sessions back: the push is rejected as a whole
+        for (size_t k = undo.size(); k-- > 0;) {
+            const AggUndo &u = undo[k];
+            a->fill[u.s] = u.fill; a->half[u.s] = u.half; a->last_send[u.s] = u.last;
+            a->pending[0][u.s] = u.p0; a->pending[1][u.s] = u.p1;
+        }
+        return fail(ctx, status, "pcmb200_aggregator_push: " + why);
+    }
+    close_round(n_quanta);
+
+    // frames of a round are launched per length class: order each round's frames by nq (stable)
+    std::vector<uint32_t> order(frames.size());
+    for (uint32_t r = 0; r < rounds.size(); r++) {
+        uint32_t k = rounds[r].f0;
+        std::vector<uint32_t> idx;
+        for (uint32_t f = rounds[r].f0; f < rounds[r].f1; f++) idx.push_back(f);
+        std::stable_sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return frames[x].nq < frames[y].nq; });
+        for (uint32_t f : idx) order[k++] = f;
+    }
+    for (size_t k = 0; k < order.size(); k++) {
+        a->h_src_row[k] = frames[order[k]].src_row;
+        a->h_dst_off[k] = frames[order[k]].off;
+    }
+
+    // ---- enqueue: uploads, then per round append + one pick/encode launch per length class ----
+    cudaStream_t st = ctx->stream;
+    const float *d_samples = samples;
+    if (samples_mem == PCMB200_MEM_HOST) {
+        CU(cudaMemcpyAsync(a->d_stage, samples, (size_t)n_quanta * a->quantum * sizeof(float), cudaMemcpyHostToDevice, st));
+        d_samples = a->d_stage;
+    }
+    CU(cudaMemcpyAsync(a->d_slot, a->h_slot, (size_t)n_quanta * 4, cudaMemcpyHostToDevice, st));
+    if (!frames.empty()) {
+        CU(cudaMemcpyAsync(a->d_src_row, a->h_src_row, frames.size() * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(a->d_dst_off, a->h_dst_off, frames.size() * 8, cudaMemcpyHostToDevice, st));
+    }
+    CU(cudaEventRecord(a->uploaded, st));
+    int16_t *d_out = out_mem == PCMB200_MEM_DEVICE ? out : a->d_out;
+    const size_t half_floats = (size_t)a->half_quanta * a->quantum;
+    uint32_t R = 0;
+    const bool is_int = integer_ratio(a->rate, &R);
+    for (const AggRound &r : rounds) {
+        if (r.q1 > r.q0) {
+            const uint32_t nq = r.q1 - r.q0;
+            const int grid = grid_for(ctx, (nq + 7) / 8, 8);
+            k_append_quanta<<<grid, 256, 0, st>>>(d_samples + (size_t)r.q0 * a->quantum, a->d_slot + r.q0, a->ring, nq, a->quantum);
+            ctx->launches++;
+        }
+        for (uint32_t k = r.f0; k < r.f1;) {
+            uint32_t k1 = k;
+            const uint32_t nq = frames[order[k]].nq;
+            while (k1 < r.f1 && frames[order[k1]].nq == nq) k1++;
+            const uint32_t n_in = nq * a->quantum, n_out = frames[order[k]].n_out;
+            if (n_out > 0) {
+                const uint32_t *lut = nullptr;
+                if (!is_int && a->rate != 16000.0) {
+                    int s2 = get_lut(ctx, n_in, a->rate, n_out, &lut);
+                    if (s2) return s2;
+                }
+                const unsigned long long n_pairs = (unsigned long long)(k1 - k) * ((n_out + 1u) / 2u);
+                const unsigned long long tiles = (n_pairs + 1023) / 1024;
+                const int grid = grid_for(ctx, tiles, resident_blocks(k_rows_pick_encode<4>, 256));
+                k_rows_pick_encode<4><<<grid, 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, d_out, a->d_dst_off + k, n_in,
+                                                            n_out, lut, is_int ? R : 1u, n_pairs);
+                ctx->launches++;
+            }
+            k = k1;
+        }
+    }
+    CU(cudaGetLastError());
+    for (size_t f = 0; f < frames.size(); f++) {
+        if (frame_session) frame_session[f] = frames[f].session;
+        if (frame_len) frame_len[f] = frames[f].n_out;
+        if (frame_offset) frame_offset[f] = frames[f].off;
+    }
+    *n_frames = (uint32_t)frames.size();
+    if (out_mem == PCMB200_MEM_HOST) {
+        if (off) CU(cudaMemcpyAsync(out, a->d_out, off * sizeof(int16_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    } else if (samples_mem == PCMB200_MEM_HOST) {
+        CU(cudaEventSynchronize(a->uploaded));   // the caller's sample buffer is free again
+    }
     return PCMB200_OK;
 }
 

@@ -570,6 +570,84 @@ k_pick_f32(const uint32_t *__restrict__ in, size_t pitch_in, uint32_t *__restric
     }
 }
 
+// ---- kernels 5/6: device-side aggregator (App.tsx:273-288) ---------------------------------------------
+// The reference grows a Float32Array by one 128-sample quantum per worklet message (re-allocating
+// and re-copying it every time) and, once >= desiredMs have passed, converts the whole buffer.  On
+// the device each session owns two fixed half-buffers ("ring"); a quantum is appended in place and a
+// flush is a pick+encode over the rows of the sessions that flushed.
+//
+// k_append_quanta: quantum i of the push (512 contiguous bytes at src + i*quantum) goes to
+// ring + dst_slot[i]*quantum.  One warp per quantum, 128-bit loads/stores.
+__global__ void __launch_bounds__(256)
+k_append_quanta(const float *__restrict__ src, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
+                uint32_t n_quanta, uint32_t quantum)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n_quanta; i += warps) {
+        const float *s = src + (size_t)i * quantum;
+        float *d = ring + (size_t)__ldg(dst_slot + i) * quantum;
+        if ((quantum & 3u) == 0u) {
+            for (uint32_t k = lane; k < (quantum >> 2); k += 32u)
+                reinterpret_cast<float4 *>(d)[k] = __ldg(reinterpret_cast<const float4 *>(s) + k);
+        } else {
+            for (uint32_t k = lane; k < quantum; k += 32u) d[k] = __ldg(s + k);
+        }
+    }
+}
+
+// k_rows_pick_encode: kernel 2 with indirect rows -- frame r reads the ring row src_row[r]
+// (row pitch `pitch_in` floats) and writes n_out int16 at out + dst_off[r] (offsets are multiples
+// of 8 samples, so pairs are 4-byte aligned).
+template <int U>
+__global__ void __launch_bounds__(512)
+k_rows_pick_encode(const float *__restrict__ ring, size_t pitch_in, const uint32_t *__restrict__ src_row,
+                   int16_t *__restrict__ out, const unsigned long long *__restrict__ dst_off, uint32_t n_in,
+                   uint32_t n_out, const uint32_t *__restrict__ lut, uint32_t stride, unsigned long long n_pairs)
+{
+    const uint32_t ppr = (n_out + 1u) >> 1;
+    const unsigned long long tile_pairs = (unsigned long long)blockDim.x * U;
+    const unsigned long long n_tiles = (n_pairs + tile_pairs - 1) / tile_pairs;
+    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const unsigned long long w0 = tile * tile_pairs + threadIdx.x;
+        float a[U], b[U];
+        int16_t *dst[U];
+        bool two[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const unsigned long long w = w0 + (unsigned long long)u * blockDim.x;
+            dst[u] = nullptr;
+            two[u] = false;
+            a[u] = b[u] = 0.0f;
+            if (w < n_pairs) {
+                const uint32_t r = (uint32_t)(w / ppr);
+                const uint32_t o = (uint32_t)(w - (unsigned long long)r * ppr) * 2u;
+                const float *row = ring + (size_t)__ldg(src_row + r) * pitch_in;
+                dst[u] = out + __ldg(dst_off + r) + o;
+                two[u] = (o + 1u < n_out);
+                uint32_t i0, i1 = 0xFFFFFFFFu;
+                if (lut) {
+                    i0 = __ldg(lut + o);
+                    if (two[u]) i1 = __ldg(lut + o + 1);
+                } else {
+                    i0 = o * stride;
+                    i1 = i0 + stride;
+                }
+                a[u] = (i0 < n_in) ? __ldg(row + i0) : __int_as_float(0x7FC00000);
+                b[u] = (two[u] && i1 < n_in) ? __ldg(row + i1) : __int_as_float(0x7FC00000);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (dst[u] != nullptr) {
+                const uint32_t p = pack_s16x2_sat(enc_s32(a[u]), enc_s32(b[u]));
+                if (two[u]) *reinterpret_cast<uint32_t *>(dst[u]) = p;
+                else dst[u][0] = (int16_t)(p & 0xFFFFu);
+            }
+        }
+    }
+}
+
 // ---- kernel 4: level meter alone (any layout; one thread per session, sequential) ----------------------
 // Fallback for batches kernel 2b cannot take (pitched rows, long frames).  Correct, not fast.
 __global__ void __launch_bounds__(128)

@@ -22,6 +22,7 @@ from ._capi import (  # noqa: F401
     load,
 )
 from .api import (  # noqa: F401
+    Aggregator,
     Context,
     DeviceBuffer,
     PinnedBuffer,
@@ -36,7 +37,7 @@ from .api import (  # noqa: F401
 )
 
 __all__ = [
-    "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
+    "Aggregator", "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
     "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",
 ]

@@ -53,6 +53,10 @@ SYMBOLS = {
     "pcmb200_timer_stop": (_int, [_vp, _P(C.c_float)]),
     "pcmb200_tune": (_int, [_vp, C.c_char_p, C.c_longlong]),
     "pcmb200_frames_encode_meter": (_int, [_vp, _vp, _sz, _vp, _sz, _u32, _u32, _dbl, _u32, _vp, _vp, _P(_sz)]),
+    "pcmb200_aggregator_create": (_int, [_vp, _u32, _dbl, _u32, _dbl, _u32, _u32, _sz, _P(_vp)]),
+    "pcmb200_aggregator_destroy": (_int, [_vp, _vp]),
+    "pcmb200_aggregator_reset_session": (_int, [_vp, _vp, _u32, _dbl]),
+    "pcmb200_aggregator_push": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _int, _vp, _sz, _int, _vp, _vp, _vp, _u32, _P(_u32)]),
     "pcmb200_tick_graph_create": (_int, [_vp, _vp, _sz, _vp, _sz, _u32, _u32, _dbl, _P(_vp)]),
     "pcmb200_tick_graph_launch": (_int, [_vp, _vp]),
     "pcmb200_tick_graph_destroy": (_int, [_vp, _vp]),

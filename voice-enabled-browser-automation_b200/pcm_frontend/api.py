@@ -273,6 +273,49 @@ class TickGraph:
         self.handle = None
 
 
+class Aggregator:
+    """The reference's capture aggregator (App.tsx:148-157, :273-288) for many sessions on the device:
+    push() takes 128-sample quanta with their arrival times and returns the frames that flushed."""
+
+    def __init__(self, ctx: Context, max_sessions: int, rate: float, quantum: int = 128, desired_ms: float = 60.0,
+                 max_frame_quanta: int = 64, max_push_quanta: int = 1 << 16, max_out_samples: int = 1 << 24):
+        self.ctx, self.quantum, self.max_push, self.max_out = ctx, quantum, max_push_quanta, max_out_samples
+        h = C.c_void_p()
+        check(ctx._L.pcmb200_aggregator_create(ctx.handle, int(max_sessions), float(rate), int(quantum), float(desired_ms),
+                                               int(max_frame_quanta), int(max_push_quanta), int(max_out_samples),
+                                               C.byref(h)), ctx.handle)
+        self.handle = h.value
+        self._out = np.empty(max_out_samples, dtype=np.int16)
+        self._fs = np.empty(max_push_quanta, dtype=np.uint32)
+        self._fl = np.empty(max_push_quanta, dtype=np.uint32)
+        self._fo = np.empty(max_push_quanta, dtype=np.uint64)
+
+    def reset_session(self, session: int, now_ms: float):
+        check(self.ctx._L.pcmb200_aggregator_reset_session(self.ctx.handle, self.handle, int(session), float(now_ms)),
+              self.ctx.handle)
+
+    def push(self, sessions: np.ndarray, arrival_ms: np.ndarray, samples: np.ndarray):
+        """sessions[n] uint32, arrival_ms[n] float64, samples[n, quantum] float32 (arrival order).
+        Returns [(session, int16 frame), ...] in flush order."""
+        sessions = np.ascontiguousarray(sessions, dtype=np.uint32)
+        arrival_ms = np.ascontiguousarray(arrival_ms, dtype=np.float64)
+        samples = np.ascontiguousarray(samples, dtype=np.float32)
+        n = sessions.size
+        assert arrival_ms.size == n and samples.size == n * self.quantum
+        nf = C.c_uint32(0)
+        check(self.ctx._L.pcmb200_aggregator_push(self.ctx.handle, self.handle, n, sessions.ctypes.data, arrival_ms.ctypes.data,
+                                                  samples.ctypes.data, MEM_HOST, self._out.ctypes.data, self._out.size, MEM_HOST,
+                                                  self._fs.ctypes.data, self._fl.ctypes.data, self._fo.ctypes.data,
+                                                  self._fs.size, C.byref(nf)), self.ctx.handle)
+        return [(int(self._fs[f]), self._out[int(self._fo[f]): int(self._fo[f]) + int(self._fl[f])].copy())
+                for f in range(nf.value)]
+
+    def close(self):
+        if self.handle and self.ctx.handle:
+            check(self.ctx._L.pcmb200_aggregator_destroy(self.ctx.handle, self.handle), self.ctx.handle)
+        self.handle = None
+
+
 def _as_f32_1d(a) -> np.ndarray:
     x = np.asarray(a)
     if x.dtype != np.float32:

@@ -201,6 +201,32 @@ def meter(ctx, n_in, S):
             "in_samples_per_s": S * n_in / (ms_fused * 1e-3)}
 
 
+def aggregator(ctx, S=65536, rate=48000):
+    """8f next-2: S sessions, every push carries 23 quanta per session (61.3 ms of 48 kHz audio), so
+    every session flushes one 2944-sample frame per push.  Host-resident quanta and frames."""
+    nq = 23
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=S * nq, max_out_samples=S * 984)
+    for s in range(0, S):
+        agg.reset_session(s, 0.0)
+    rng = np.random.RandomState(1)
+    sessions = np.tile(np.arange(S, dtype=np.uint32), nq)                  # quantum-major arrival order
+    samples = rng.uniform(-1, 1, size=(S * nq, 128)).astype(np.float32)
+    base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
+    times = []
+    for p in range(4):
+        t0 = time.perf_counter()
+        frames = agg.push(sessions, base + p * nq * (128e3 / rate), samples)
+        times.append(time.perf_counter() - t0)
+    assert len(frames) == S and frames[0][1].size == 981
+    want = oracle.frames(samples[0::S][:nq].reshape(1, -1), nq * 128, rate)[0]
+    assert np.array_equal(frames[0][1], want)
+    agg.close()
+    dt = min(times[1:])
+    return {"config": "next-2 device aggregator (host scheduler, host-resident quanta)", "sessions": S, "quanta_per_push": S * nq,
+            "push_ms_incl_python_wrapper": dt * 1e3, "in_samples_per_s": S * nq * 128 / dt,
+            "note": "the per-quantum flush plan runs on one host thread; the python wrapper also copies every frame out"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
@@ -222,10 +248,10 @@ def main():
                         print("skip", kb, stg, bps, e)
         return
     if args.only_meter:
-        for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18)):
+        for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)
