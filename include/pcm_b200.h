@@ -162,6 +162,19 @@ PCMB200_API int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *ag
                                         uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
                                         uint32_t max_frames, uint32_t *n_frames);
 
+/* ---- wire egress helpers ------------------------------------------------------------------------ */
+
+/* The reference's keep-alive (App.tsx:291-296): every PCMB200_KEEPALIVE_PERIOD_MS while the socket
+ * is open it sends `new Int16Array(1600)` -- 100 ms of silence at 16 kHz.  Writes the 1600 zero
+ * samples to `out` (host memory, capacity in samples) and sets *n; PCMB200_ERR_CAPACITY if too small.
+ * The wire format of every frame this library produces is the reference's: raw native-endian
+ * (little-endian on x86-64 / aarch64) int16 mono 16 kHz, no header (App.tsx:284, deepgram.ts:36-45);
+ * pcmb200_wire_is_little_endian() returns 1 on such hosts. */
+#define PCMB200_KEEPALIVE_SAMPLES 1600u
+#define PCMB200_KEEPALIVE_PERIOD_MS 2000u
+PCMB200_API int pcmb200_keepalive_frame(int16_t *out, size_t capacity, size_t *n);
+PCMB200_API int pcmb200_wire_is_little_endian(void);
+
 /* ---- per-tick replay --------------------------------------------------------------------------- */
 
 /* A tick whose buffers, shape and rate do not change (the steady state of a fleet: same sessions,

@@ -89,3 +89,13 @@ def test_shard_sessions_is_a_partition():
             assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
     with pytest.raises(ValueError):
         pcm_frontend.shard_sessions(10, 2, 2)
+
+
+def test_keepalive_frame_and_wire_endianness():
+    ka = pcm_frontend.keepalive_frame()
+    assert ka.dtype == np.int16 and ka.size == 1600 and not ka.any()
+    assert ka.tobytes() == oracle.keepalive_frame().tobytes()          # App.tsx:291-296
+    assert pcm_frontend.load().pcmb200_wire_is_little_endian() == 1
+    n = C.c_size_t(0)
+    small = np.empty(10, np.int16)
+    assert pcm_frontend.load().pcmb200_keepalive_frame(small.ctypes.data, small.size, C.byref(n)) == _capi.ERR_CAPACITY

@@ -915,6 +915,26 @@ extern "C" int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in, si
     return PCMB200_OK;
 }
 
+// ================================= wire egress helpers ================================================
+extern "C" int pcmb200_keepalive_frame(int16_t *out, size_t capacity, size_t *n)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(out && n, "pcmb200_keepalive_frame: NULL argument");
+    *n = 0;
+    if (capacity < PCMB200_KEEPALIVE_SAMPLES) return fail(nullptr, PCMB200_ERR_CAPACITY, "pcmb200_keepalive_frame: capacity < 1600 samples");
+    std::memset(out, 0, PCMB200_KEEPALIVE_SAMPLES * sizeof(int16_t));   // new Int16Array(1600), App.tsx:294
+    *n = PCMB200_KEEPALIVE_SAMPLES;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_wire_is_little_endian(void)
+{
+    const uint16_t probe = 1;
+    unsigned char b;
+    std::memcpy(&b, &probe, 1);
+    return b == 1;
+}
+
 // ================================= per-tick CUDA graph ================================================
 struct pcmb200_tick_graph {
     cudaGraph_t graph = nullptr;

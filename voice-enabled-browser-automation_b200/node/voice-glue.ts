@@ -42,6 +42,11 @@ export class FrameBatcher {
     this.groups.clear();
   }
 
+  /** The reference's keep-alive (App.tsx:291-296): 100 ms of silence every 2 s per open session. */
+  startKeepAlive(sink: Sink): NodeJS.Timeout {
+    return setInterval(() => sink(Buffer.alloc(1600 * 2)), 2000);
+  }
+
   close(): void {
     clearInterval(this.timer);
     this.flush();

@@ -31,6 +31,7 @@ from .api import (  # noqa: F401
     floatTo16BitPCM,
     frames_encode,
     index_table,
+    keepalive_frame,
     resample_len,
     resampleTo16k,
     shard_sessions,
@@ -38,6 +39,6 @@ from .api import (  # noqa: F401
 
 __all__ = [
     "Aggregator", "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
-    "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table",
+    "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table", "keepalive_frame",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",
 ]

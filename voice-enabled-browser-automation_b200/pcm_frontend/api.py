@@ -26,6 +26,14 @@ def index_table(n_in: int, rate: float, n_out: Optional[int] = None) -> np.ndarr
     return idx
 
 
+def keepalive_frame() -> np.ndarray:
+    """The reference's keep-alive payload (App.tsx:291-296): 1600 zero samples, sent every 2 s."""
+    out = np.empty(1600, dtype=np.int16)
+    n = C.c_size_t(0)
+    check(load().pcmb200_keepalive_frame(out.ctypes.data, out.size, C.byref(n)))
+    return out[: n.value]
+
+
 def shard_sessions(n_sessions: int, world_size: int, rank: int) -> Tuple[int, int]:
     """Session-affine sharding: contiguous blocks, the first n % world ranks get one
     extra session.  Returns (first_session, count).  Sessions never migrate and never exchange
