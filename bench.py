@@ -116,6 +116,26 @@ def sessions_for_rank(args, rank, world):
     return pcm_frontend.shard_sessions(args.sessions, world, rank)
 
 
+def bind_to_gpu_numa(index):
+    """Pin this rank to the CPUs NVML reports as local to GPU `index`, so that its pinned host ring is
+    allocated on (and fed from) the GPU's own NUMA node.  Returns (cpus bound, previous affinity)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = ((os.cpu_count() or 64) + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
+        prev = os.sched_getaffinity(0)
+        cpus = sorted(set(cpus) & prev)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus), prev
+    except Exception:
+        pass
+    return 0, None
+
+
 # ---- clocks ----------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
     """Samples SM clock / throttle reasons with NVML while the timed regions run."""
@@ -274,6 +294,7 @@ def run_b200(args):
     import pcm_frontend
     from pcm_frontend import MEM_DEVICE, MEM_HOST
 
+    bound_cpus, prev_affinity = bind_to_gpu_numa(local_rank) if world > 1 else (0, None)
     ctx = pcm_frontend.Context(local_rank)          # raises if the CUDA library / device is missing
     dist = Dist(world, True, local_rank)
     if args.tune:
@@ -383,6 +404,7 @@ def run_b200(args):
                            "sessions_total": int(units / (n_in * args.steps)), "rate_hz": RATE,
                            "frame_ms": args.frame_ms, "n_in": n_in, "n_out": n_out,
                            "parallelism": f"session-affine shards x{world}, no collectives",
+                           "numa": f"each rank bound to its GPU's {bound_cpus} local CPUs" if bound_cpus else "no CPU binding",
                            "l2": f"inputs larger than L2: {n_buf} alternating tick buffers of {algo_bytes / 1e9:.2f} GB each",
                            "tune": args.tune or "defaults"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all,
