@@ -14,6 +14,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 using namespace pcmb200;
@@ -1026,13 +1027,14 @@ struct pcmb200_aggregator {
     std::vector<uint32_t> fill;
     std::vector<uint8_t> half;
     std::vector<double> last_send;
-    std::vector<uint32_t> pending[2];      // round id (+1) in which that half was flushed
-    uint32_t round_id = 0;
+    std::vector<uint8_t> q_round, flushes_of;          // plan scratch: round of every quantum / flushes per session
+    std::vector<uint32_t> flush_nq, flush_row, touched;
+    uint32_t push_epoch = 0;
+    uint8_t *h_round = nullptr, *d_round = nullptr;    // pinned / device copy of q_round
 };
 
 namespace {
-struct AggFrame { uint32_t src_row, nq, session; unsigned long long off; uint32_t n_out; };
-struct AggRound { uint32_t q0, q1, f0, f1; };
+struct AggFrame { uint32_t src_row, nq, session; unsigned long long off; uint32_t n_out; uint32_t round; };
 struct AggUndo { uint32_t s, fill; uint8_t half; double last; uint32_t p0, p1; };
 }  // namespace
 
@@ -1056,7 +1058,6 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     cudaError_t e = cudaSuccess;
     try {
         a->fill.assign(max_sessions, 0); a->half.assign(max_sessions, 0); a->last_send.assign(max_sessions, 0.0);
-        a->pending[0].assign(max_sessions, 0); a->pending[1].assign(max_sessions, 0);
     } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
     const size_t ring_bytes = (size_t)max_sessions * 2 * max_frame_quanta * quantum * sizeof(float);
 #define AGG_STEP(call) if (e == cudaSuccess) e = (call)
@@ -1069,6 +1070,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(cudaHostAlloc((void **)&a->h_slot, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
     AGG_STEP(cudaHostAlloc((void **)&a->h_src_row, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
     AGG_STEP(cudaHostAlloc((void **)&a->h_dst_off, (size_t)max_push_quanta * 8, cudaHostAllocDefault));
+    AGG_STEP(cudaHostAlloc((void **)&a->h_round, (size_t)max_push_quanta, cudaHostAllocDefault));
+    AGG_STEP(cudaMalloc((void **)&a->d_round, (size_t)max_push_quanta));
     AGG_STEP(cudaEventCreateWithFlags(&a->uploaded, cudaEventDisableTiming));
     AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_bytes, ctx->stream));
 #undef AGG_STEP
@@ -1092,6 +1095,8 @@ extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *
     if (a->h_slot) cudaFreeHost(a->h_slot);
     if (a->h_src_row) cudaFreeHost(a->h_src_row);
     if (a->h_dst_off) cudaFreeHost(a->h_dst_off);
+    if (a->h_round) cudaFreeHost(a->h_round);
+    cudaFree(a->d_round);
     if (a->uploaded) cudaEventDestroy(a->uploaded);
     cudaGetLastError();
     delete a;
@@ -1108,6 +1113,54 @@ extern "C" int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggreg
     return PCMB200_OK;
 }
 
+// The flush plan.  Every session is a little sequential state machine (fill, half, lastSend), and
+// sessions are independent, so the plan is computed by T host threads that each own the sessions
+// in a contiguous block of session ids and scan the quanta list for them.  A session's j-th flush inside one push is
+// "round" j: the quanta of the frame that follows it are written into the half-buffer that held
+// frame j-1, which was converted at the end of round j-1 -- so appending round by round and
+// converting each round's frames before the next append never overwrites an unconverted frame.
+// A typical push has at most one flush per session: two append launches and one batch of frames.
+namespace {
+struct AggPlanShared {
+    pcmb200_aggregator *a; uint32_t n; const uint32_t *sessions; const double *arrival;
+    uint8_t *q_round;        // [n] round of every quantum
+    uint32_t *flush_nq;      // [n] 0, or the frame length in quanta if quantum i flushes
+    uint32_t *flush_row;     // [n] ring row of that frame
+};
+struct AggPlanThread { std::vector<AggUndo> undo; int status = PCMB200_OK; uint32_t max_round = 0; };
+
+void agg_plan_worker(const AggPlanShared &sh, uint32_t t, uint32_t own_shift, AggPlanThread &out, std::vector<uint8_t> &flushes_of)
+{
+    pcmb200_aggregator *a = sh.a;
+    for (uint32_t i = 0; i < sh.n; i++) {
+        const uint32_t s = sh.sessions[i];
+        if ((s >> own_shift) != t) continue;   // contiguous session blocks: no cache line is shared by two threads
+        if (a->touched[s] != a->push_epoch) {   // first quantum of this session in this push: remember its state
+            a->touched[s] = a->push_epoch;
+            out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s], 0, 0});
+        }
+        const uint8_t h = a->half[s];
+        if (a->fill[s] >= a->half_quanta) { out.status = PCMB200_ERR_CAPACITY; return; }
+        const uint8_t round = flushes_of[s];
+        a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
+        sh.q_round[i] = round;
+        a->fill[s]++;
+        sh.flush_nq[i] = 0;
+        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+        if (sh.arrival[i] - a->last_send[s] >= a->desired_ms) {
+            if (round == 255) { out.status = PCMB200_ERR_CAPACITY; return; }
+            sh.flush_nq[i] = a->fill[s];
+            sh.flush_row[i] = s * 2u + h;
+            a->half[s] = h ^ 1u;
+            a->fill[s] = 0;
+            a->last_send[s] = sh.arrival[i];                     // App.tsx:287
+            flushes_of[s] = round + 1;
+        }
+        if (round > out.max_round) out.max_round = round;
+    }
+}
+}  // namespace
+
 extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n_quanta,
                                        const uint32_t *sessions, const double *arrival_ms, const float *samples,
                                        int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
@@ -1121,70 +1174,80 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     NEED((samples_mem == PCMB200_MEM_HOST || samples_mem == PCMB200_MEM_DEVICE) &&
          (out_mem == PCMB200_MEM_HOST || out_mem == PCMB200_MEM_DEVICE), "pcmb200_aggregator_push: bad mem kind");
     NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push: more quanta than max_push_quanta");
-    for (uint32_t i = 0; i < n_quanta; i++)
-        NEED(sessions[i] < a->max_sessions, "pcmb200_aggregator_push: session id out of range");
+    {
+        uint32_t worst = 0;
+        for (uint32_t i = 0; i < n_quanta; i++) worst = sessions[i] > worst ? sessions[i] : worst;
+        NEED(worst < a->max_sessions, "pcmb200_aggregator_push: session id out of range");
+    }
     CU(cudaSetDevice(ctx->device));
     CU(cudaEventSynchronize(a->uploaded));   // the previous push's index upload has left the pinned staging
 
-    // ---- plan on the host: where every quantum goes, which sessions flush, in how many rounds ----
-    std::vector<AggFrame> frames;
-    std::vector<AggRound> rounds;
-    std::vector<AggUndo> undo;
-    std::vector<uint8_t> touched(0);
-    AggRound cur{0, 0, 0, 0};
-    a->round_id++;
-    unsigned long long off = 0;
+    // ---- plan on the host ----
+    try {
+        a->flush_nq.resize(n_quanta); a->flush_row.resize(n_quanta);
+        a->flushes_of.assign(a->max_sessions, 0);
+        if (a->touched.size() != a->max_sessions) a->touched.assign(a->max_sessions, 0);
+        a->push_epoch++;
+    } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_push: host allocation failed"); }
+    AggPlanShared sh{a, n_quanta, sessions, arrival_ms, a->h_round, a->flush_nq.data(), a->flush_row.data()};
+    uint32_t T = 1;
+    if (n_quanta >= 65536) {
+        const uint32_t hw = std::thread::hardware_concurrency();
+        while (T * 2 <= hw && T < 16) T *= 2;
+    }
+    uint32_t own_shift = 0;   // a thread owns sessions [t << own_shift, (t + 1) << own_shift)
+    while (((unsigned long long)T << own_shift) < a->max_sessions) own_shift++;
+    std::vector<AggPlanThread> th(T);
+    if (T == 1) {
+        agg_plan_worker(sh, 0, own_shift, th[0], a->flushes_of);
+    } else {
+        std::vector<std::thread> pool;
+        for (uint32_t t = 0; t < T; t++)
+            pool.emplace_back([&, t] { agg_plan_worker(sh, t, own_shift, th[t], a->flushes_of); });
+        for (auto &p : pool) p.join();
+    }
     int status = PCMB200_OK;
     std::string why;
-    auto close_round = [&](uint32_t q_end) {
-        cur.q1 = q_end; cur.f1 = (uint32_t)frames.size();
-        if (cur.q1 > cur.q0 || cur.f1 > cur.f0) rounds.push_back(cur);
-        cur.q0 = q_end; cur.f0 = (uint32_t)frames.size();
-        a->round_id++;
-    };
-    for (uint32_t i = 0; i < n_quanta; i++) {
-        const uint32_t s = sessions[i];
-        undo.push_back({s, a->fill[s], a->half[s], a->last_send[s], a->pending[0][s], a->pending[1][s]});
-        uint8_t h = a->half[s];
-        if (a->pending[h][s] == a->round_id) close_round(i);   // that half still holds an unlaunched frame
-        if (a->fill[s] >= a->half_quanta) { status = PCMB200_ERR_CAPACITY; why = "a session's buffer exceeds max_frame_quanta (no flush arrived)"; break; }
-        a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
-        a->fill[s]++;
-        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
-        const double elapsed = arrival_ms[i] - a->last_send[s];
-        if (elapsed >= a->desired_ms) {
-            size_t n_out = 0;
-            resample_len((size_t)a->fill[s] * a->quantum, a->rate, &n_out);
+    uint32_t max_round = 0;
+    for (auto &t : th) {
+        if (t.status) { status = t.status; why = "a session's buffer exceeds max_frame_quanta (no flush arrived), or it flushed > 255 times"; }
+        if (t.max_round > max_round) max_round = t.max_round;
+    }
+    // frames in flush (= quantum) order; output offsets are assigned in that order
+    std::vector<AggFrame> frames;
+    unsigned long long off = 0;
+    if (status == PCMB200_OK) {
+        std::vector<size_t> len_of(a->half_quanta + 1, (size_t)-1);   // output length per frame length (in quanta)
+        for (uint32_t i = 0; i < n_quanta; i++) {
+            if (!a->flush_nq[i]) continue;
+            size_t &n_out_c = len_of[a->flush_nq[i]];
+            if (n_out_c == (size_t)-1) resample_len((size_t)a->flush_nq[i] * a->quantum, a->rate, &n_out_c);
+            const size_t n_out = n_out_c;
             if (frames.size() >= max_frames) { status = PCMB200_ERR_CAPACITY; why = "more flushed frames than max_frames"; break; }
             if (off + n_out > out_capacity || (out_mem == PCMB200_MEM_HOST && off + n_out > a->out_cap)) {
                 status = PCMB200_ERR_CAPACITY; why = "flushed frames exceed the output capacity"; break;
             }
-            frames.push_back({s * 2u + h, a->fill[s], s, off, (uint32_t)n_out});
+            frames.push_back({a->flush_row[i], a->flush_nq[i], sessions[i], off, (uint32_t)n_out, a->h_round[i]});
             off += (n_out + 7u) & ~(size_t)7u;                  // frames start on 16-byte boundaries
-            a->pending[h][s] = a->round_id;
-            a->half[s] = h ^ 1u;
-            a->fill[s] = 0;
-            a->last_send[s] = arrival_ms[i];                    // App.tsx:287
         }
     }
     if (status != PCMB200_OK) {   // roll the sessions back: the push is rejected as a whole
-        for (size_t k = undo.size(); k-- > 0;) {
-            const AggUndo &u = undo[k];
-            a->fill[u.s] = u.fill; a->half[u.s] = u.half; a->last_send[u.s] = u.last;
-            a->pending[0][u.s] = u.p0; a->pending[1][u.s] = u.p1;
-        }
+        for (auto &t : th)
+            for (size_t k = t.undo.size(); k-- > 0;) {
+                const AggUndo &u = t.undo[k];
+                a->fill[u.s] = u.fill; a->half[u.s] = u.half; a->last_send[u.s] = u.last;
+            }
         return fail(ctx, status, "pcmb200_aggregator_push: " + why);
     }
-    close_round(n_quanta);
-
-    // frames of a round are launched per length class: order each round's frames by nq (stable)
+    // launch order of the frames: by round, then by length class (stable)
     std::vector<uint32_t> order(frames.size());
-    for (uint32_t r = 0; r < rounds.size(); r++) {
-        uint32_t k = rounds[r].f0;
-        std::vector<uint32_t> idx;
-        for (uint32_t f = rounds[r].f0; f < rounds[r].f1; f++) idx.push_back(f);
-        std::stable_sort(idx.begin(), idx.end(), [&](uint32_t x, uint32_t y) { return frames[x].nq < frames[y].nq; });
-        for (uint32_t f : idx) order[k++] = f;
+    {   // counting sort by (round, frame length): stable, O(frames)
+        const size_t classes = (size_t)(max_round + 1) * (a->half_quanta + 1);
+        std::vector<uint32_t> start(classes + 1, 0);
+        for (const AggFrame &f : frames) start[(size_t)f.round * (a->half_quanta + 1) + f.nq + 1]++;
+        for (size_t c = 0; c < classes; c++) start[c + 1] += start[c];
+        for (uint32_t f = 0; f < frames.size(); f++)
+            order[start[(size_t)frames[f].round * (a->half_quanta + 1) + frames[f].nq]++] = f;
     }
     for (size_t k = 0; k < order.size(); k++) {
         a->h_src_row[k] = frames[order[k]].src_row;
@@ -1199,6 +1262,7 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
         d_samples = a->d_stage;
     }
     CU(cudaMemcpyAsync(a->d_slot, a->h_slot, (size_t)n_quanta * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(a->d_round, a->h_round, (size_t)n_quanta, cudaMemcpyHostToDevice, st));
     if (!frames.empty()) {
         CU(cudaMemcpyAsync(a->d_src_row, a->h_src_row, frames.size() * 4, cudaMemcpyHostToDevice, st));
         CU(cudaMemcpyAsync(a->d_dst_off, a->h_dst_off, frames.size() * 8, cudaMemcpyHostToDevice, st));
@@ -1208,17 +1272,18 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     const size_t half_floats = (size_t)a->half_quanta * a->quantum;
     uint32_t R = 0;
     const bool is_int = integer_ratio(a->rate, &R);
-    for (const AggRound &r : rounds) {
-        if (r.q1 > r.q0) {
-            const uint32_t nq = r.q1 - r.q0;
-            const int grid = grid_for(ctx, (nq + 7) / 8, 8);
-            k_append_quanta<<<grid, 256, 0, st>>>(d_samples + (size_t)r.q0 * a->quantum, a->d_slot + r.q0, a->ring, nq, a->quantum);
+    size_t k = 0;
+    for (uint32_t round = 0; round <= max_round; round++) {
+        {
+            const int grid = grid_for(ctx, (n_quanta + 7) / 8, 8);
+            k_append_quanta<<<grid, 256, 0, st>>>(d_samples, a->d_slot, a->ring, n_quanta, a->quantum,
+                                                  max_round ? a->d_round : nullptr, (uint8_t)round);
             ctx->launches++;
         }
-        for (uint32_t k = r.f0; k < r.f1;) {
-            uint32_t k1 = k;
+        while (k < order.size() && frames[order[k]].round == round) {
+            size_t k1 = k;
             const uint32_t nq = frames[order[k]].nq;
-            while (k1 < r.f1 && frames[order[k1]].nq == nq) k1++;
+            while (k1 < order.size() && frames[order[k1]].round == round && frames[order[k1]].nq == nq) k1++;
             const uint32_t n_in = nq * a->quantum, n_out = frames[order[k]].n_out;
             if (n_out > 0) {
                 const uint32_t *lut = nullptr;

@@ -577,14 +577,16 @@ k_pick_f32(const uint32_t *__restrict__ in, size_t pitch_in, uint32_t *__restric
 // flush is a pick+encode over the rows of the sessions that flushed.
 //
 // k_append_quanta: quantum i of the push (512 contiguous bytes at src + i*quantum) goes to
-// ring + dst_slot[i]*quantum.  One warp per quantum, 128-bit loads/stores.
+// ring + dst_slot[i]*quantum.  One warp per quantum, 128-bit loads/stores.  When a push holds
+// several flushes of one session it is appended in rounds (q_round[i] == round).
 __global__ void __launch_bounds__(256)
 k_append_quanta(const float *__restrict__ src, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
-                uint32_t n_quanta, uint32_t quantum)
+                uint32_t n_quanta, uint32_t quantum, const uint8_t *__restrict__ q_round, uint8_t round)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n_quanta; i += warps) {
+        if (q_round && __ldg(q_round + i) != round) continue;   // this launch appends one round only
         const float *s = src + (size_t)i * quantum;
         float *d = ring + (size_t)__ldg(dst_slot + i) * quantum;
         if ((quantum & 3u) == 0u) {

@@ -203,28 +203,44 @@ def meter(ctx, n_in, S):
 
 def aggregator(ctx, S=65536, rate=48000):
     """8f next-2: S sessions, every push carries 23 quanta per session (61.3 ms of 48 kHz audio), so
-    every session flushes one 2944-sample frame per push.  Host-resident quanta and frames."""
-    nq = 23
-    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=S * nq, max_out_samples=S * 984)
-    for s in range(0, S):
-        agg.reset_session(s, 0.0)
-    rng = np.random.RandomState(1)
+    every session flushes one 2944-sample frame per push.  Device-resident quanta and frames, C ABI
+    called directly: `host_ms` is the scheduler + enqueue time of the call, `total_ms` includes the GPU."""
+    L = pcm_frontend.load()
+    from pcm_frontend._capi import check
+    nq, n = 23, S * 23
+    h = C.c_void_p()
+    check(L.pcmb200_aggregator_create(ctx.handle, S, float(rate), 128, 60.0, 32, n, S * 984, C.byref(h)), ctx.handle)
+    for s in range(S):
+        L.pcmb200_aggregator_reset_session(ctx.handle, h, s, 0.0)
     sessions = np.tile(np.arange(S, dtype=np.uint32), nq)                  # quantum-major arrival order
-    samples = rng.uniform(-1, 1, size=(S * nq, 128)).astype(np.float32)
     base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
-    times = []
-    for p in range(4):
+    d_samples = ctx.device_buffer(n * 128 * 4)
+    ctx.synth_fill(d_samples.ptr, 128, n, 128, rate)
+    d_out = ctx.device_buffer(S * 984 * 2)
+    fs, fl, fo = np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(n, np.uint64)
+    nf = C.c_uint32(0)
+    host, total = [], []
+    for p in range(5):
+        arr = base + p * nq * (128e3 / rate)
+        ctx.sync()
         t0 = time.perf_counter()
-        frames = agg.push(sessions, base + p * nq * (128e3 / rate), samples)
-        times.append(time.perf_counter() - t0)
-    assert len(frames) == S and frames[0][1].size == 981
-    want = oracle.frames(samples[0::S][:nq].reshape(1, -1), nq * 128, rate)[0]
-    assert np.array_equal(frames[0][1], want)
-    agg.close()
-    dt = min(times[1:])
-    return {"config": "next-2 device aggregator (host scheduler, host-resident quanta)", "sessions": S, "quanta_per_push": S * nq,
-            "push_ms_incl_python_wrapper": dt * 1e3, "in_samples_per_s": S * nq * 128 / dt,
-            "note": "the per-quantum flush plan runs on one host thread; the python wrapper also copies every frame out"}
+        check(L.pcmb200_aggregator_push(ctx.handle, h, n, sessions.ctypes.data, arr.ctypes.data, d_samples.ptr, MEM_DEVICE,
+                                        d_out.ptr, S * 984, MEM_DEVICE, fs.ctypes.data, fl.ctypes.data, fo.ctypes.data, n,
+                                        C.byref(nf)), ctx.handle)
+        t1 = time.perf_counter()
+        ctx.sync()
+        t2 = time.perf_counter()
+        host.append(t1 - t0); total.append(t2 - t0)
+    assert nf.value == S and fl[0] == 981
+    x = d_samples.download(np.float32, n * 128).reshape(n, 128)
+    want = oracle.frames(x[0::S][:nq].reshape(1, -1), nq * 128, rate)[0]
+    assert np.array_equal(d_out.download(np.int16, 981, int(fo[0]) * 2), want)
+    L.pcmb200_aggregator_destroy(ctx.handle, h)
+    d_samples.free(); d_out.free()
+    return {"config": "next-2 device aggregator (device-resident quanta and frames)", "sessions": S, "quanta_per_push": n,
+            "host_ms": min(host[1:]) * 1e3, "total_ms": min(total[1:]) * 1e3, "in_samples_per_s": n * 128 / min(total[1:]),
+            "realtime_sessions_at_48k": n * 128 / min(total[1:]) / rate,
+            "note": "the per-quantum flush plan runs on up to 16 host threads (contiguous session blocks)"}
 
 
 def main():
