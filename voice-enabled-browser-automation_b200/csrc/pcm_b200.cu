@@ -42,14 +42,15 @@ struct Slot {
 
 struct Tuning {
     int block = 256;
-    int blocks_per_sm = 0;   // 0 = fill the SM (2048 / block)
+    int blocks_per_sm = 0;   // 0 = one tile per block (non-persistent grid); > 0 caps the grid at SMs x this
     int unroll = 0;          // 0 = per-ratio default
     int path = 0;            // 1 = force the general pick kernel
     int store_hint = 1;      // st.global.cs: output frames are written once and not re-read
+    int occupancy = 0;       // kernel 1b: resident blocks per SM cap (0 = no cap), see launch_coal
     int coalesced = 1;       // dense integer-ratio batches: warp-coalesced kernel (1b) instead of kernel 1
     int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
     int tile_kb = 28;        // target tile size of kernel 2b
-    int stages = 2;          // tiles in flight per CTA in kernel 2b
+    int stages = 1;          // tiles in flight per CTA in kernel 2b (1: one tile per block, overlap comes from co-resident blocks)
     int meter_tile_kb = 56;  // kernel 2b with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
     size_t slice_bytes = 32u << 20;
@@ -159,17 +160,17 @@ int get_lut(pcmb200_ctx *ctx, uint32_t n_in, double rate, uint32_t n_out, const 
     return PCMB200_OK;
 }
 
-// Persistent grid: one wave of resident blocks (SM count x blocks that fit per SM), fewer if
-// there is less work.  `resident` comes from the occupancy calculator for the kernel at hand.
-int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int resident, int preferred = 0)
+// Grid sizing.  Measured on B200 (profiles/r01_grid_sweep.jsonl): for these streaming kernels a grid
+// with ONE tile per block (or per warp), left to the hardware block scheduler, beats a persistent
+// grid of 148 x k resident blocks walking the tiles in a grid-stride loop by 6-10 % at every size
+// (48 kHz, 2^20 frames: 7.24 vs 6.66-6.85 TB/s; 65 536 frames: 45.1 vs 48.3 us).  A fresh block
+// issues all its loads at once, whereas a looping block serialises load -> encode -> store per
+// iteration, and the tail is balanced at tile granularity for free.  So the default grid is simply
+// the number of tiles; `blocks_per_sm` (tuning) restores a capped, looping grid for comparison.
+int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int /*resident*/, int /*preferred*/ = 0)
 {
-    // `preferred` (blocks per SM) is the measured sweet spot of a kernel: on B200 these streaming
-    // kernels peak with roughly 100 KB of loads in flight per SM and lose a few percent with more
-    // (profiles/sweep_r1.md), so the default grid is smaller than what would fit.
-    int bps = ctx->tune.blocks_per_sm > 0 ? ctx->tune.blocks_per_sm
-                                          : (preferred > 0 && preferred < resident ? preferred : resident);
-    if (bps < 1) bps = 1;
-    unsigned long long cap = (unsigned long long)ctx->sm_count * (unsigned long long)bps;
+    unsigned long long cap = 0x7FFFFFFFull;
+    if (ctx->tune.blocks_per_sm > 0) cap = (unsigned long long)ctx->sm_count * (unsigned long long)ctx->tune.blocks_per_sm;
     unsigned long long g = tiles < cap ? tiles : cap;
     return g < 1 ? 1 : (int)g;
 }
@@ -210,7 +211,15 @@ void launch_coal(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *ou
 {
     const int block = ctx->tune.block;
     const int warps = block / 32;
-    const size_t smem = (size_t)warps * U * 256 * sizeof(int16_t);
+    size_t smem = (size_t)warps * U * 256 * sizeof(int16_t);
+    if (ctx->tune.occupancy > 0) {
+        // Cap the blocks RESIDENT per SM with unused dynamic shared memory, so the grid itself can be
+        // large (hardware block scheduling balances the tail) without putting more loads in flight
+        // per SM than the measured sweet spot.
+        const size_t per_block = (227u * 1024u) / (size_t)ctx->tune.occupancy - 1024u;
+        if (per_block > smem) smem = per_block;
+        cudaFuncSetAttribute(k_decim_coal<R, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
     int resident = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_decim_coal<R, U>, block, smem) != cudaSuccess || resident < 1) {
         cudaGetLastError();
@@ -242,9 +251,9 @@ void launch_decim_u(pcmb200_ctx *ctx, cudaStream_t st, int U, bool dense, const 
     }
 }
 
-int default_unroll(uint32_t R)
+int default_unroll(uint32_t)
 {
-    return R == 1 ? 2 : 1;   // measured: 64-96 bytes of loads in flight per thread are enough
+    return 1;   // measured: with one tile per block, 32*R bytes of loads in flight per thread are enough
 }
 
 // Kernel 2b (TMA tile-staged picks) for dense batches of short frames.  Returns the number of rows it
@@ -260,11 +269,7 @@ cudaError_t launch_tile_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, in
     int resident = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_tile_pick<STAGES, METER>, 256, smem);
     if (e != cudaSuccess || resident < 1) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;
-    // measured sweet spot: about 112 KB of tiles in flight per SM (profiles/r01_sweep_tile.json)
-    int preferred = (int)((112u * 1024u) / ((size_t)STAGES * tile_stride));
-    if (preferred < 1) preferred = 1;
-    if (METER) preferred = 0;   // the meter's 128-step binary64 chains are latency-bound: fill the SM
-    const int grid = grid_for(ctx, n_tiles, resident, preferred);
+    const int grid = grid_for(ctx, n_tiles, resident);
     k_tile_pick<STAGES, METER><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride,
                                                       ctx->tune.store_hint, meter);
     return cudaGetLastError();
@@ -831,7 +836,7 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
         NEED(value >= 32 && value <= 512 && value % 32 == 0, "pcmb200_tune: block must be a multiple of 32 in [32, 512]");
         ctx->tune.block = (int)value;
     } else if (k == "blocks_per_sm") {
-        NEED(value >= 0 && value <= 32, "pcmb200_tune: blocks_per_sm must be in [0, 32]");
+        NEED(value >= 0 && value <= 65536, "pcmb200_tune: blocks_per_sm must be in [0, 65536]");
         ctx->tune.blocks_per_sm = (int)value;
     } else if (k == "unroll") {
         NEED(value >= 0 && value <= 4, "pcmb200_tune: unroll must be 0 (default), 1, 2 or 4");
@@ -845,6 +850,9 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "coalesced") {
         NEED(value == 0 || value == 1, "pcmb200_tune: coalesced must be 0 or 1");
         ctx->tune.coalesced = (int)value;
+    } else if (k == "occupancy") {
+        NEED(value >= 0 && value <= 16, "pcmb200_tune: occupancy must be in [0, 16]");
+        ctx->tune.occupancy = (int)value;
     } else if (k == "tile") {
         NEED(value == 0 || value == 1, "pcmb200_tune: tile must be 0 or 1");
         ctx->tune.tile = (int)value;
