@@ -200,8 +200,11 @@ PCMB200_API int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out_device, size_t p
  * stop (the pipelined host path included) is inside the measured interval. */
 PCMB200_API int pcmb200_timer_start(pcmb200_ctx *ctx);
 PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
-/* Tuning knobs for sweeps: "block" (threads per block), "blocks_per_sm", "unroll",
- * "path" (0 auto, 1 force the gather kernel), "slice_bytes" (host pipeline slice), "store_hint". */
+/* Tuning knobs for sweeps (defaults are the measured best): "block" (threads per
+ * block), "blocks_per_sm" (0 = one tile per block; > 0 = capped, looping grid), "unroll", "path"
+ * (0 auto, 1 general kernel only, 2 general path with the tile-staged kernel), "coalesced", "tile",
+ * "tile_kb", "stages", "meter_tile_kb", "meter_stages", "occupancy", "store_hint",
+ * "slice_bytes" (host pipeline slice). */
 PCMB200_API int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value);
 
 /* ---- allocation-free variant ------------------------------------------------------------------ */

@@ -198,10 +198,10 @@ void launch_decim(pcmb200_ctx *ctx, cudaStream_t st, bool dense, const float *in
         if (t > tiles) tiles = t;
     }
     if (dense) {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block), 768 / block);
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block));
         k_decim_int<R, U, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
     } else {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block), 768 / block);
+        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block));
         k_decim_int<R, U, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
     }
 }
@@ -226,7 +226,7 @@ void launch_coal(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *ou
         resident = 2048 / block;
     }
     const unsigned long long blocks_needed = (n_tiles + (unsigned long long)warps * U - 1) / ((unsigned long long)warps * U);
-    const int grid = grid_for(ctx, blocks_needed, resident, 1024 / (block * U));
+    const int grid = grid_for(ctx, blocks_needed, resident);
     k_decim_coal<R, U><<<grid, block, smem, st>>>(in, out, n_tiles, ctx->tune.store_hint);
 }
 
@@ -1043,7 +1043,7 @@ struct pcmb200_aggregator {
 
 namespace {
 struct AggFrame { uint32_t src_row, nq, session; unsigned long long off; uint32_t n_out; uint32_t round; };
-struct AggUndo { uint32_t s, fill; uint8_t half; double last; uint32_t p0, p1; };
+struct AggUndo { uint32_t s, fill; uint8_t half; double last; };
 }  // namespace
 
 extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
@@ -1145,7 +1145,7 @@ void agg_plan_worker(const AggPlanShared &sh, uint32_t t, uint32_t own_shift, Ag
         if ((s >> own_shift) != t) continue;   // contiguous session blocks: no cache line is shared by two threads
         if (a->touched[s] != a->push_epoch) {   // first quantum of this session in this push: remember its state
             a->touched[s] = a->push_epoch;
-            out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s], 0, 0});
+            out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s]});
         }
         const uint8_t h = a->half[s];
         if (a->fill[s] >= a->half_quanta) { out.status = PCMB200_ERR_CAPACITY; return; }

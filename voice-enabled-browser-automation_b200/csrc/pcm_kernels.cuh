@@ -5,7 +5,9 @@
 // tensor cores, no shared-memory reuse (the reference's decimator has zero taps: it PICKS
 // samples, App.tsx:27-30), so the design rules are: 256-bit / 128-bit fully coalesced global
 // accesses, enough independent loads in flight per SM to cover HBM latency, streaming cache
-// hints so 4.7 GB ticks do not thrash L2, and persistent grids sized in multiples of the SM count.
+// hints so 4.7 GB ticks do not thrash L2, and (measured, see grid_for in pcm_b200.cu) one tile per
+// block handed out by the hardware scheduler rather than a persistent grid-stride loop -- the
+// loops below remain so that a capped grid still covers all tiles.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
