@@ -275,7 +275,7 @@ def run_reference(args):
               f"oracle/pcm_oracle.c port of App.tsx:7-32,281-282, {cores} host threads")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
-            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32->s16 (binary64 intermediate)",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
             "data": "synthetic sine+noise (host numpy, same recipe as the GPU arm)",
             "config": {"workload": workload_name(args, n_in, n_out), "reference_runtime":
                        "Node unavailable on this image: C port of the reference's JS (kind=port)"},
@@ -398,7 +398,7 @@ def run_b200(args):
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
-                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32->s16 (fp32 RZ product, exact)",
+                "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic sine+noise generated on device (pcmb200_synth_fill, seed 0x5EED)",
                 "config": {"workload": workload_name(args, n_in, n_out), "sessions_per_gpu": S,
                            "sessions_total": int(units / (n_in * args.steps)), "rate_hz": RATE,
@@ -406,7 +406,8 @@ def run_b200(args):
                            "parallelism": f"session-affine shards x{world}, no collectives",
                            "numa": f"each rank bound to its GPU's {bound_cpus} local CPUs" if bound_cpus else "no CPU binding",
                            "l2": f"inputs larger than L2: {n_buf} alternating tick buffers of {algo_bytes / 1e9:.2f} GB each",
-                           "tune": args.tune or "defaults"},
+                           "tune": args.tune or "defaults",
+                           "arithmetic": "f32 in, round-toward-zero fp32 product (exact), saturating s16 out; bit-exact vs the f64 reference"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all,
                 "clocks": sampler.summary(),
                 "output_samples_per_s": value * n_out / n_in, "device": ctx.device_info()["name"]}
