@@ -26,6 +26,14 @@ def test_fused_meter_bitwise(ctx, rate, n_in, rows):
     if nq:
         x[0, 5] = np.float32(np.nan)            # NaN poisons that session's level for good (Math.max semantics)
         x[1, 3] = np.float32(np.inf)
+        if rows > 4:
+            # a quantum of denormals, zeros and the smallest normals: the sums stay near 2^-250, where
+            # a wrong widening of a denormal would change the rounded result
+            x[3, :128] = (rng.randint(0, 3, 128) * rng.uniform(0, 1.2e-38, 128)).astype(np.float32)
+            x[3, 7] = np.float32(1e-40)
+            x[4, :128] = 0.0                        # digital silence -> exactly 0
+            if n_in > 130:
+                x[4, 130] = np.float32(-1e-45)
     state = rng.uniform(0, 1, rows)
     state[2 % rows] = 0.0
     d_in = ctx.device_buffer(x.nbytes)

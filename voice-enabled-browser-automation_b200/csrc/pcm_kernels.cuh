@@ -348,13 +348,15 @@ __device__ __forceinline__ double rms_of(double sum, uint32_t quantum)
     return __dsqrt_rn(mean);
 }
 
-// The cheap form used in the meter's inner loop: exact for zeros and normal floats.  `odd` collects
-// a flag for the rare inputs it gets wrong (denormal, Inf, NaN); the caller then redoes that
-// quantum with widen_abs.
+// The cheap form used in the meter's inner loop: exact for zeros and normal floats.  What it gets
+// wrong is caught without per-sample cost where possible: Inf and NaN come out as finite values
+// >= 2^128, so their squares push the quantum's sum to >= 2^250, which the caller tests ONCE per
+// quantum; only denormals (0 < |x| < 2^-126) need a per-sample test, folded into `odd`.  A flagged
+// quantum is redone with widen_abs.
 __device__ __forceinline__ double widen_abs_fast(float x, bool &odd)
 {
     const uint32_t a = __float_as_uint(x) & 0x7FFFFFFFu;
-    odd |= (a - 0x00800000u >= 0x7F000000u) && a != 0u;
+    odd |= (a - 1u) < 0x007FFFFFu;
     const uint32_t hi = a ? (a >> 3) + 0x38000000u : 0u;
     return __hiloint2double((int)hi, (int)(a << 29));
 }
@@ -495,6 +497,8 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
                         sum = __fma_rn(x3, x3, sum);
                         cur = nxt;
                     }
+                    // Inf / NaN inputs show up as an impossible sum (see widen_abs_fast)
+                    odd |= !(sum < __hiloint2double(0x4F900000, 0));   // 2^250; also true for NaN
                     if (odd) {   // rare: the quantum holds a denormal, Inf or NaN -> redo it exactly
                         sum = 0.0;
                         const float *src = reinterpret_cast<const float *>(src4);
