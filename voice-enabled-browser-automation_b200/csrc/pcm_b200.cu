@@ -167,23 +167,12 @@ int get_lut(pcmb200_ctx *ctx, uint32_t n_in, double rate, uint32_t n_out, const 
 // issues all its loads at once, whereas a looping block serialises load -> encode -> store per
 // iteration, and the tail is balanced at tile granularity for free.  So the default grid is simply
 // the number of tiles; `blocks_per_sm` (tuning) restores a capped, looping grid for comparison.
-int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles, int /*resident*/, int /*preferred*/ = 0)
+int grid_for(const pcmb200_ctx *ctx, unsigned long long tiles)
 {
     unsigned long long cap = 0x7FFFFFFFull;
     if (ctx->tune.blocks_per_sm > 0) cap = (unsigned long long)ctx->sm_count * (unsigned long long)ctx->tune.blocks_per_sm;
     unsigned long long g = tiles < cap ? tiles : cap;
     return g < 1 ? 1 : (int)g;
-}
-
-template <typename K>
-int resident_blocks(K kernel, int block)
-{
-    int n = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, block, 0) != cudaSuccess || n < 1) {
-        cudaGetLastError();
-        n = 2048 / block;
-    }
-    return n;
 }
 
 template <int R, int U>
@@ -198,10 +187,10 @@ void launch_decim(pcmb200_ctx *ctx, cudaStream_t st, bool dense, const float *in
         if (t > tiles) tiles = t;
     }
     if (dense) {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, true>, block));
+        const int grid = grid_for(ctx, tiles);
         k_decim_int<R, U, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
     } else {
-        const int grid = grid_for(ctx, tiles, resident_blocks(k_decim_int<R, U, false>, block));
+        const int grid = grid_for(ctx, tiles);
         k_decim_int<R, U, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, rows, cpr, tail, n_chunks, ctx->tune.store_hint);
     }
 }
@@ -220,13 +209,8 @@ void launch_coal(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *ou
         if (per_block > smem) smem = per_block;
         cudaFuncSetAttribute(k_decim_coal<R, U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     }
-    int resident = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_decim_coal<R, U>, block, smem) != cudaSuccess || resident < 1) {
-        cudaGetLastError();
-        resident = 2048 / block;
-    }
     const unsigned long long blocks_needed = (n_tiles + (unsigned long long)warps * U - 1) / ((unsigned long long)warps * U);
-    const int grid = grid_for(ctx, blocks_needed, resident);
+    const int grid = grid_for(ctx, blocks_needed);
     k_decim_coal<R, U><<<grid, block, smem, st>>>(in, out, n_tiles, ctx->tune.store_hint);
 }
 
@@ -264,12 +248,15 @@ cudaError_t launch_tile_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, in
                           uint32_t n_out, uint32_t K, unsigned long long n_tiles, const uint32_t *lut, uint32_t R,
                           uint32_t tile_stride, size_t smem, const MeterArgs &meter)
 {
-    cudaError_t e = cudaFuncSetAttribute(k_tile_pick<STAGES, METER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    int resident = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, k_tile_pick<STAGES, METER>, 256, smem);
-    if (e != cudaSuccess || resident < 1) return e != cudaSuccess ? e : cudaErrorInvalidConfiguration;
-    const int grid = grid_for(ctx, n_tiles, resident);
+    // opt in to > 48 KB of dynamic shared memory once per (kernel instance, device, size high-water mark)
+    static size_t granted[64] = {0};
+    const int dev = ctx->device & 63;
+    if (smem > granted[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(k_tile_pick<STAGES, METER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        granted[dev] = smem;
+    }
+    const int grid = grid_for(ctx, n_tiles);
     k_tile_pick<STAGES, METER><<<grid, 256, smem, st>>>(in, out, n_in, n_out, K, n_tiles, lut, R, tile_stride,
                                                       ctx->tune.store_hint, meter);
     return cudaGetLastError();
@@ -408,10 +395,10 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
 #define PICK(UU)                                                                                                      \
     do {                                                                                                              \
         if (pair32) {                                                                                                 \
-            const int grid = grid_for(ctx, tiles, resident_blocks(k_pick_encode<UU, true>, block));                   \
+            const int grid = grid_for(ctx, tiles);                   \
             k_pick_encode<UU, true><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, n_out, lut, R, n_pairs); \
         } else {                                                                                                      \
-            const int grid = grid_for(ctx, tiles, resident_blocks(k_pick_encode<UU, false>, block));                  \
+            const int grid = grid_for(ctx, tiles);                  \
             k_pick_encode<UU, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, n_out, lut, R, n_pairs); \
         }                                                                                                             \
     } while (0)
@@ -781,7 +768,7 @@ int pcmb200_resample_to_16k(pcmb200_ctx *ctx, const float *in, size_t n_in, doub
         dout = (float *)sl.d_out;
     }
     const int block = 256;
-    const int grid = grid_for(ctx, (n_out + block - 1) / block, 2048 / block);
+    const int grid = grid_for(ctx, (n_out + block - 1) / block);
     k_pick_f32<<<grid, block, 0, ctx->stream>>>((const uint32_t *)din, n_in, (uint32_t *)dout, n_out, (uint32_t)n_in,
                                                (uint32_t)n_out, lut, R, n_out);
     ctx->launches++;
@@ -801,7 +788,7 @@ int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out, size_t pitch, uint32_t rows
     NEED(out && pitch >= n && rate > 0, "pcmb200_synth_fill: bad argument");
     CU(cudaSetDevice(ctx->device));
     const unsigned long long total = (unsigned long long)rows * n;
-    const int grid = grid_for(ctx, (total + 255) / 256, 8);
+    const int grid = grid_for(ctx, (total + 255) / 256);
     k_synth<<<grid, 256, 0, ctx->stream>>>(out, pitch, rows, n, (float)(1.0 / rate), seed, row0);
     CU(cudaGetLastError());
     return PCMB200_OK;
@@ -915,7 +902,7 @@ extern "C" int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in, si
         }
         if (m.nq > 0) {
             MeterArgs mr{quantum, m.nq, level_state + took, levels ? levels + (size_t)took * m.nq : nullptr};
-            const int grid = grid_for(ctx, (rest + 127) / 128, 16);
+            const int grid = grid_for(ctx, (rest + 127) / 128);
             k_level_meter<<<grid, 128, 0, ctx->stream>>>(in + (size_t)took * pitch_in, pitch_in, rest, mr);
             ctx->launches++;
             CU(cudaGetLastError());
@@ -1283,7 +1270,7 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     size_t k = 0;
     for (uint32_t round = 0; round <= max_round; round++) {
         {
-            const int grid = grid_for(ctx, (n_quanta + 7) / 8, 8);
+            const int grid = grid_for(ctx, (n_quanta + 7) / 8);
             k_append_quanta<<<grid, 256, 0, st>>>(d_samples, a->d_slot, a->ring, n_quanta, a->quantum,
                                                   max_round ? a->d_round : nullptr, (uint8_t)round);
             ctx->launches++;
@@ -1301,7 +1288,7 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
                 }
                 const unsigned long long n_pairs = (unsigned long long)(k1 - k) * ((n_out + 1u) / 2u);
                 const unsigned long long tiles = (n_pairs + 1023) / 1024;
-                const int grid = grid_for(ctx, tiles, resident_blocks(k_rows_pick_encode<4>, 256));
+                const int grid = grid_for(ctx, tiles);
                 k_rows_pick_encode<4><<<grid, 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, d_out, a->d_dst_off + k, n_in,
                                                             n_out, lut, is_int ? R : 1u, n_pairs);
                 ctx->launches++;
