@@ -519,7 +519,9 @@ int pcmb200_device_count(int *count)
     if (e != cudaSuccess || *count <= 0) {
         *count = 0;
         cudaGetLastError();
-        return fail(nullptr, PCMB200_ERR_NO_DEVICE, std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+        return fail(nullptr, PCMB200_ERR_NO_DEVICE,
+                    std::string("no usable CUDA device (cudaGetDeviceCount: ") + cudaGetErrorString(e) +
+                        "); this library has no CPU fallback");
     }
     return PCMB200_OK;
 }
