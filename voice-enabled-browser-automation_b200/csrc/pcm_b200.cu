@@ -461,11 +461,18 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
         int s = slot_reserve(ctx, ctx->slots[i], rps * dpi * 4, rps * dpo * 2);
         if (s) return s;
     }
-    CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
-    for (int i = 0; i < used; i++) CU(cudaStreamWaitEvent(ctx->slots[i].st, ctx->ev_fork, 0));
+    // A single slice (a small call: one frame, one short batch) runs on the context's own stream and
+    // skips the fork/join events -- they cost more than the copies at that size.  Earlier pipelined
+    // calls were joined into this stream, so slot 0's buffers are free in stream order.
+    const bool single = n_slices == 1;
+    if (!single) {
+        CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
+        for (int i = 0; i < used; i++) CU(cudaStreamWaitEvent(ctx->slots[i].st, ctx->ev_fork, 0));
+    }
 
     for (size_t k = 0; k < n_slices; k++) {
-        Slot &s = ctx->slots[k % kSlots];
+        Slot s = ctx->slots[k % kSlots];
+        if (single) s.st = ctx->stream;
         const size_t r0 = k * rps;
         const uint32_t nr = (uint32_t)((rows - r0 < rps) ? rows - r0 : rps);
         const float *hin = in + r0 * pitch_in;
@@ -481,7 +488,7 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
         else
             CU(cudaMemcpy2DAsync(hout, pitch_out * 2, s.d_out, dpo * 2, (size_t)n_out * 2, nr, cudaMemcpyDeviceToHost, s.st));
     }
-    for (int i = 0; i < used; i++) {
+    for (int i = 0; i < used && !single; i++) {
         CU(cudaEventRecord(ctx->slots[i].done, ctx->slots[i].st));
         CU(cudaStreamWaitEvent(ctx->stream, ctx->slots[i].done, 0));
     }

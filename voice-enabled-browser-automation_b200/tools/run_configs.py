@@ -74,7 +74,7 @@ def config1(ctx):
     return {"config": 1, "n_in": n, "n_out": 16000, "node": "Node unavailable on this box",
             "cpu_oracle_1thread_ns_per_in_sample": cpu_ns / n, "cpu_oracle_us_per_call": cpu_ns / 1e3,
             "gpu_host_call_fused_us": gpu_fused_ns / 1e3, "gpu_host_call_two_functions_us": gpu_two_ns / 1e3,
-            "note": "single stream: H2D + launch + D2H latency dominates, the GPU does not beat one CPU core"}
+            "note": "single stream: fixed costs (pageable H2D staging, launch, D2H, sync) dominate; on a par with one CPU core, no speed-up to be had"}
 
 
 def config2(ctx):
