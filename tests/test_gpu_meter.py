@@ -26,11 +26,18 @@ def test_fused_meter_bitwise(ctx, rate, n_in, rows):
     if nq:
         x[0, 5] = np.float32(np.nan)            # NaN poisons that session's level for good (Math.max semantics)
         x[1, 3] = np.float32(np.inf)
-        if rows > 4:
+        if rows > 8:
             # a quantum of denormals, zeros and the smallest normals: the sums stay near 2^-250, where
             # a wrong widening of a denormal would change the rounded result
             x[3, :128] = (rng.randint(0, 3, 128) * rng.uniform(0, 1.2e-38, 128)).astype(np.float32)
             x[3, 7] = np.float32(1e-40)
+            # around the 2^-60 threshold of the fast widening, with zeros before / between / after
+            x[5, :128] = 0.0
+            x[5, 17] = np.float32(2.0 ** -60)
+            x[5, 90] = np.float32(-(2.0 ** -60) * 1.0000001)
+            x[6, :128] = (rng.randint(0, 2, 128) * 2.0 ** rng.uniform(-63, -57, 128)).astype(np.float32)
+            x[7, :128] = 0.0
+            x[7, 127] = np.float32(3.0e-19)        # first nonzero sample is the last of the quantum
             x[4, :128] = 0.0                        # digital silence -> exactly 0
             if n_in > 130:
                 x[4, 130] = np.float32(-1e-45)

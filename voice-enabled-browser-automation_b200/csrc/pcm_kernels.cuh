@@ -348,17 +348,23 @@ __device__ __forceinline__ double rms_of(double sum, uint32_t quantum)
     return __dsqrt_rn(mean);
 }
 
-// The cheap form used in the meter's inner loop: exact for zeros and normal floats.  What it gets
-// wrong is caught without per-sample cost where possible: Inf and NaN come out as finite values
-// >= 2^128, so their squares push the quantum's sum to >= 2^250, which the caller tests ONCE per
-// quantum; only denormals (0 < |x| < 2^-126) need a per-sample test, folded into `odd`.  A flagged
-// quantum is redone with widen_abs.
+// The cheap form used in the meter's inner loop (the loop is issue-bound on the ALU pipe, so every
+// instruction counts, and the shifts are written so that they land on the FMA pipe as IMADs):
+//   * normal |x| >= 2^-60: exact re-packing;
+//   * zero: comes out as 2^-127, i.e. adds 2^-254 to the sum instead of 0.  That cannot change a
+//     correctly rounded sum that already holds a term >= 2^-120 (2^-254 is far below half an ulp),
+//     and before the first such term the polluted partial sum (< 2^-246) is absorbed the same way
+//     when the term arrives; a quantum of nothing but zeros ends below 2^-200 and is set to 0;
+//   * 0 < |x| < 2^-60 (denormals included) would break that argument: flagged in `odd`;
+//   * Inf / NaN come out finite but >= 2^128, pushing the sum to >= 2^250: tested once per quantum.
+// A flagged quantum is redone with widen_abs.
 __device__ __forceinline__ double widen_abs_fast(float x, bool &odd)
 {
-    const uint32_t a = __float_as_uint(x) & 0x7FFFFFFFu;
-    odd |= (a - 1u) < 0x007FFFFFu;
-    const uint32_t hi = a ? (a >> 3) + 0x38000000u : 0u;
-    return __hiloint2double((int)hi, (int)(a << 29));
+    const uint32_t b = __float_as_uint(x);
+    const uint32_t t = b << 1;                                   // 2 * |x| bits: the sign is gone
+    odd |= (t - 2u) < (2u * 0x21800000u - 2u);                   // 0 < |x| < 2^-60
+    const uint32_t hi = __umulhi(t, 0x10000000u) + 0x38000000u;  // (|x| bits >> 3) + re-bias
+    return __hiloint2double((int)hi, (int)(b << 29));
 }
 
 __device__ __forceinline__ double js_max(double a, double b)
@@ -497,8 +503,9 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
                         sum = __fma_rn(x3, x3, sum);
                         cur = nxt;
                     }
-                    // Inf / NaN inputs show up as an impossible sum (see widen_abs_fast)
+                    // see widen_abs_fast: Inf / NaN inputs show up as an impossible sum; silence as ~0
                     odd |= !(sum < __hiloint2double(0x4F900000, 0));   // 2^250; also true for NaN
+                    if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;   // < 2^-200: every sample was zero
                     if (odd) {   // rare: the quantum holds a denormal, Inf or NaN -> redo it exactly
                         sum = 0.0;
                         const float *src = reinterpret_cast<const float *>(src4);
