@@ -273,9 +273,6 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
     if (!aligned(in, 16) || !aligned(out, 16)) return 0;
     uint32_t k0 = 4;                                   // smallest row group whose bytes are a multiple of 16
     if (n_in % 4 == 0) k0 = 1; else if (n_in % 2 == 0) k0 = 2;
-    // ... and whose outputs are a whole number of 8-sample (16-byte) chunks
-    const uint32_t ko = n_out % 8 == 0 ? 1 : (n_out % 4 == 0 ? 2 : (n_out % 2 == 0 ? 4 : 8));
-    if (ko > k0) k0 = ko;
     const size_t group_bytes = (size_t)k0 * n_in * 4;
     const size_t target = (size_t)(meter ? ctx->tune.meter_tile_kb : ctx->tune.tile_kb) * 1024;
     if (group_bytes > 96 * 1024) return 0;             // frames too long to stage whole: other kernels handle them

@@ -276,7 +276,7 @@ k_pick_encode(const float *__restrict__ in, size_t pitch_in, int16_t *__restrict
 // memory through a copy of the pick table (also in shared memory), encode, and write one 128-bit
 // streaming store per 8 outputs; consecutive lanes write consecutive 16-byte chunks.
 // Requirements (launcher): in and out 16-byte aligned, rows dense (pitch_in == n_in, pitch_out ==
-// n_out), K * n_in % 4 == 0 and K * n_out % 8 == 0, tile + table fit in shared memory.
+// n_out), K * n_in % 4 == 0, tile + table fit in shared memory.
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
@@ -389,7 +389,7 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
     const uint32_t tile_bytes = rows_per_tile * n_in * 4u;
     const uint32_t cpr = n_out >> 3;                             // 8-output chunks per row (rows_aligned)
     const bool rows_aligned = (n_out & 7u) == 0u;
-    const uint32_t chunks_per_tile = (rows_per_tile * n_out) >> 3;   // launcher: rows_per_tile * n_out % 8 == 0
+    const uint32_t outs_per_tile = rows_per_tile * n_out;
 
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -419,8 +419,16 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
         const uint32_t parity = (it / STAGES) & 1u;
         mbar_wait(&bars[s], parity);
         const float *tile = reinterpret_cast<const float *>(reinterpret_cast<const unsigned char *>(tiles) + (size_t)s * tile_stride_bytes);
-        int16_t *dst_tile = out + t * (unsigned long long)chunks_per_tile * 8ull;
-        for (uint32_t g = threadIdx.x; g < chunks_per_tile; g += blockDim.x) {
+        // Output of this tile: outs_per_tile consecutive int16 starting at `first`.  When frames are
+        // a whole number of 8-sample chunks the tile starts 16-byte aligned; otherwise (the
+        // reference's real frames: 23 quanta at 48 kHz -> 981 outputs) the aligned body is written
+        // with 128-bit stores and the few samples before / after it one by one.
+        const unsigned long long first = t * (unsigned long long)outs_per_tile;
+        const unsigned long long body0 = (first + 7ull) & ~7ull;
+        const unsigned long long body1 = (first + outs_per_tile) & ~7ull;
+        const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
+        const uint32_t head = (uint32_t)(body0 - first);
+        for (uint32_t g = threadIdx.x; g < n_body; g += blockDim.x) {
             uint32_t idx[8];     // offset of each pick inside the tile (0xFFFFFFFF: outside its frame)
             if (rows_aligned) {
                 const uint32_t rr = g / cpr, c = g - rr * cpr;
@@ -437,10 +445,9 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
 #pragma unroll
                 for (int j = 0; j < 8; j++) idx[j] = idx[j] < n_in ? base + idx[j] : 0xFFFFFFFFu;
             } else {
-                // frames whose length is not a multiple of 8 outputs (the reference's real frames:
-                // 23 quanta at 48 kHz -> 981 outputs): a chunk is 8 consecutive outputs of the tile's
-                // flat output and may run over a frame boundary
-                uint32_t rr = (8u * g) / n_out, o = 8u * g - rr * n_out;
+                // a chunk is 8 consecutive outputs of the tile's flat output; it may run over a frame boundary
+                const uint32_t f = head + 8u * g;
+                uint32_t rr = f / n_out, o = f - rr * n_out;
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
                     const uint32_t i = lut ? tab[o] : o * stride;
@@ -455,12 +462,27 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
                 const float x = (idx[j] != 0xFFFFFFFFu) ? tile[idx[j]] : __int_as_float(0x7FC00000);
                 e[j] = enc_s32(x);
             }
-            uint4 o;
-            o.x = pack_s16x2_sat(e[0], e[1]);
-            o.y = pack_s16x2_sat(e[2], e[3]);
-            o.z = pack_s16x2_sat(e[4], e[5]);
-            o.w = pack_s16x2_sat(e[6], e[7]);
-            st_128(dst_tile + (size_t)g * 8u, o, hint);
+            uint4 o4;
+            o4.x = pack_s16x2_sat(e[0], e[1]);
+            o4.y = pack_s16x2_sat(e[2], e[3]);
+            o4.z = pack_s16x2_sat(e[4], e[5]);
+            o4.w = pack_s16x2_sat(e[6], e[7]);
+            st_128(out + body0 + (size_t)g * 8u, o4, hint);
+        }
+        if (!rows_aligned) {   // the < 8 + < 8 samples around the aligned body
+            const uint32_t tail0 = (uint32_t)(body1 > body0 ? body1 - first : head), n_edge = head + (outs_per_tile - tail0);
+            for (uint32_t k = threadIdx.x; k < n_edge && body1 > body0; k += blockDim.x) {
+                const uint32_t f = k < head ? k : tail0 + (k - head);
+                const uint32_t rr = f / n_out, o = f - rr * n_out;
+                const uint32_t i = lut ? tab[o] : o * stride;
+                out[first + f] = enc_s16(i < n_in ? tile[rr * n_in + i] : __int_as_float(0x7FC00000));
+            }
+            if (body1 <= body0)   // degenerate: the whole tile is shorter than one aligned chunk
+                for (uint32_t f = threadIdx.x; f < outs_per_tile; f += blockDim.x) {
+                    const uint32_t rr = f / n_out, o = f - rr * n_out;
+                    const uint32_t i = lut ? tab[o] : o * stride;
+                    out[first + f] = enc_s16(i < n_in ? tile[rr * n_in + i] : __int_as_float(0x7FC00000));
+                }
         }
         if (METER) {
             // the session levels are needed only after the meter: fetch them now so the global-memory
