@@ -51,7 +51,7 @@ struct Tuning {
     int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
     int tile_kb = 28;        // target tile size of kernel 2b
     int stages = 1;          // tiles in flight per CTA in kernel 2b (1: one tile per block, overlap comes from co-resident blocks)
-    int meter_tile_kb = 56;  // kernel 2b with the fused level meter: tile size ...
+    int meter_tile_kb = 64;  // kernel 2b with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
     size_t slice_bytes = 32u << 20;
 };
@@ -278,6 +278,21 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
     if (group_bytes > 96 * 1024) return 0;             // frames too long to stage whole: other kernels handle them
     uint32_t K = (uint32_t)(target / group_bytes) * k0;
     if (K < k0) K = k0;
+    if (meter && meter->nq > 0) {
+        // The meter works one lane per quantum and is issue-bound, so a tile whose quanta fill whole
+        // warps (K * nq close to a multiple of 32 from below) wastes the fewest issue slots: pick
+        // the best-filling tile height between 24 KB and the target size.
+        double best = -1.0;
+        for (uint32_t k = k0; (size_t)k * n_in * 4 <= target || k == k0; k += k0) {
+            const size_t bytes = (size_t)k * n_in * 4;
+            const uint32_t q = k * meter->nq;
+            const double fill = (double)q / (32.0 * ((q + 31) / 32));
+            if (bytes >= 24 * 1024 || bytes + group_bytes > target) {
+                if (fill > best + 1e-9) { best = fill; K = k; }
+            }
+            if (bytes > target) break;
+        }
+    }
     if (rows < K) return 0;
     const unsigned long long n_tiles = rows / K;
     const uint32_t tile_bytes = K * n_in * 4;
