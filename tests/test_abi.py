@@ -99,3 +99,17 @@ def test_keepalive_frame_and_wire_endianness():
     n = C.c_size_t(0)
     small = np.empty(10, np.int16)
     assert pcm_frontend.load().pcmb200_keepalive_frame(small.ctypes.data, small.size, C.byref(n)) == _capi.ERR_CAPACITY
+
+
+def test_header_is_plain_c_and_links(tmp_path):
+    """include/pcm_b200.h compiles as C11 and the example program links against the library and
+    runs (without a GPU it stops at context creation, loudly, with exit code 0 by design)."""
+    import subprocess
+    src = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "examples", "frames_c_abi.c")
+    lib = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "lib")
+    exe = str(tmp_path / "frames_c_abi")
+    subprocess.run(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), src,
+                    "-L", lib, "-lpcm_b200", f"-Wl,-rpath,{lib}", "-lm", "-o", exe], check=True)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "libpcm_b200 ABI" in out.stdout and ("frames of 320 samples" in out.stdout or "no device" in out.stdout)
