@@ -49,6 +49,7 @@ def parse_args(argv=None):
     ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
                     help="weak: every GPU holds --sessions sessions; strong: --sessions are sharded over the GPUs")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--wc", type=int, default=0, help="1: e2e input ring in write-combined pinned memory")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
     ap.add_argument("--ref-sessions", type=int, default=1 << 16, help="sessions per step of --impl reference")
@@ -356,7 +357,7 @@ def run_b200(args):
     # ---- end to end: pinned host buffers through the C-ABI call, H2D + kernel + D2H per step ----
     e2e = None
     if not args.no_e2e:
-        h_in = ctx.pinned((S, n_in), np.float32)
+        h_in = ctx.pinned((S, n_in), np.float32, write_combined=bool(args.wc))
         h_out = ctx.pinned((S, n_out), np.int16)
         ctx.memcpy_d2h(h_in.ptr, d_in[0].ptr, in_bytes)
         for _ in range(2):

@@ -93,6 +93,10 @@ PCMB200_API int pcmb200_device_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr)
 PCMB200_API int pcmb200_device_free(pcmb200_ctx *ctx, void *ptr);
 /* Page-locked host memory: H2D/D2H of pinned buffers runs at PCIe speed and overlaps compute. */
 PCMB200_API int pcmb200_pinned_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr);
+/* Same, write-combined (cudaHostAllocWriteCombined): for buffers the host only WRITES (input
+ * samples on their way to the GPU).  The device reads them without snooping the CPU caches; host
+ * reads of such memory are very slow.  Free with pcmb200_pinned_free. */
+PCMB200_API int pcmb200_pinned_alloc_write_combined(pcmb200_ctx *ctx, size_t bytes, void **ptr);
 PCMB200_API int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr);
 /* Blocking copies on the context's stream. */
 PCMB200_API int pcmb200_memcpy_h2d(pcmb200_ctx *ctx, void *dst_device, const void *src_host, size_t bytes);

@@ -673,6 +673,15 @@ int pcmb200_pinned_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr)
     return PCMB200_OK;
 }
 
+int pcmb200_pinned_alloc_write_combined(pcmb200_ctx *ctx, size_t bytes, void **ptr)
+{
+    NEED(ctx && ptr, "pcmb200_pinned_alloc_write_combined: NULL argument");
+    *ptr = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocWriteCombined));
+    return PCMB200_OK;
+}
+
 int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr)
 {
     NEED(ctx, "pcmb200_pinned_free: ctx is NULL");

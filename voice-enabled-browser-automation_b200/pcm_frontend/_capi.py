@@ -41,6 +41,7 @@ SYMBOLS = {
     "pcmb200_device_alloc": (_int, [_vp, _sz, _P(_vp)]),
     "pcmb200_device_free": (_int, [_vp, _vp]),
     "pcmb200_pinned_alloc": (_int, [_vp, _sz, _P(_vp)]),
+    "pcmb200_pinned_alloc_write_combined": (_int, [_vp, _sz, _P(_vp)]),
     "pcmb200_pinned_free": (_int, [_vp, _vp]),
     "pcmb200_memcpy_h2d": (_int, [_vp, _vp, _vp, _sz]),
     "pcmb200_memcpy_d2h": (_int, [_vp, _vp, _vp, _sz]),

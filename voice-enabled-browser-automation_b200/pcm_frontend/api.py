@@ -90,13 +90,14 @@ class DeviceBuffer:
 class PinnedBuffer:
     """Page-locked host memory (pcmb200_pinned_alloc) exposed as a numpy array."""
 
-    def __init__(self, ctx: "Context", shape, dtype):
+    def __init__(self, ctx: "Context", shape, dtype, write_combined: bool = False):
         self.ctx = ctx
         dtype = np.dtype(dtype)
         n = int(np.prod(shape)) if np.ndim(shape) else int(shape)
         self.nbytes = n * dtype.itemsize
         p = C.c_void_p()
-        check(load().pcmb200_pinned_alloc(ctx.handle, self.nbytes, C.byref(p)), ctx.handle)
+        alloc = load().pcmb200_pinned_alloc_write_combined if write_combined else load().pcmb200_pinned_alloc
+        check(alloc(ctx.handle, self.nbytes, C.byref(p)), ctx.handle)
         self.ptr = p.value
         raw = (C.c_char * max(self.nbytes, 1)).from_address(self.ptr)
         self.array = np.frombuffer(raw, dtype=dtype, count=n).reshape(shape)
@@ -168,8 +169,8 @@ class Context:
     def device_buffer(self, nbytes: int) -> DeviceBuffer:
         return DeviceBuffer(self, nbytes)
 
-    def pinned(self, shape, dtype) -> PinnedBuffer:
-        return PinnedBuffer(self, shape, dtype)
+    def pinned(self, shape, dtype, write_combined: bool = False) -> PinnedBuffer:
+        return PinnedBuffer(self, shape, dtype, write_combined)
 
     def memcpy_h2d(self, dst_device: int, src_host: int, nbytes: int):
         check(self._L.pcmb200_memcpy_h2d(self.handle, dst_device, src_host, int(nbytes)), self.handle)
