@@ -10,12 +10,15 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "../../include/pcm_b200.h"
 
 namespace {
 
 pcmb200_ctx *g_ctx = nullptr;
+std::mutex g_ctx_mutex;   // a context is not thread-safe: the async worker and the main thread take turns
 
 bool throw_status(napi_env env, int status)
 {
@@ -66,6 +69,7 @@ napi_value FloatTo16BitPCM(napi_env env, napi_callback_info info)
     void *out = nullptr;
     napi_value res = make_typed(env, napi_int16_array, n, 2, &out);   // a fresh array, like `new Int16Array(len)`
     if (!res) return nullptr;
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
     if (throw_status(env, pcmb200_encode_f32_s16(g_ctx, in, static_cast<int16_t *>(out), n, PCMB200_MEM_HOST))) return nullptr;
     return res;
 }
@@ -91,6 +95,7 @@ napi_value ResampleTo16k(napi_env env, napi_callback_info info)
     napi_value res = make_typed(env, napi_float32_array, n_out, 4, &out);
     if (!res) return nullptr;
     size_t got = 0;
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
     if (throw_status(env, pcmb200_resample_to_16k(g_ctx, in, n, rate, static_cast<float *>(out), n_out, &got, PCMB200_MEM_HOST)))
         return nullptr;
     return res;
@@ -132,10 +137,98 @@ napi_value FramesEncode(napi_env env, napi_callback_info info)
         res = make_typed(env, napi_int16_array, (size_t)rows * n_out, 2, &out);
         if (!res) return nullptr;
     }
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
     if (throw_status(env, pcmb200_frames_encode(g_ctx, in, n_in, static_cast<int16_t *>(out), n_out, rows, n_in, rate,
                                                 PCMB200_MEM_HOST, nullptr)))
         return nullptr;
     return res;
+}
+
+// framesEncodeAsync(batch, rows, nIn, rate, out): Promise<Int16Array>
+// The many-session path: the conversion (H2D, kernel, D2H and the wait for them) runs on a libuv
+// worker thread, so the event loop that owns the WebSockets is never blocked on a CUDA sync.
+// `batch` and `out` must stay untouched until the promise settles (use the pinned allocators).
+struct AsyncJob {
+    napi_async_work work = nullptr;
+    napi_deferred deferred = nullptr;
+    napi_ref batch_ref = nullptr, out_ref = nullptr;
+    const float *in = nullptr;
+    int16_t *out = nullptr;
+    uint32_t rows = 0, n_in = 0;
+    size_t n_out = 0;
+    double rate = 0;
+    int status = PCMB200_OK;
+    std::string error;
+};
+
+void async_execute(napi_env, void *data)
+{
+    AsyncJob *j = static_cast<AsyncJob *>(data);
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    j->status = pcmb200_frames_encode(g_ctx, j->in, j->n_in, j->out, j->n_out, j->rows, j->n_in, j->rate, PCMB200_MEM_HOST, nullptr);
+    if (j->status != PCMB200_OK) j->error = pcmb200_last_error(g_ctx);
+}
+
+void async_complete(napi_env env, napi_status, void *data)
+{
+    AsyncJob *j = static_cast<AsyncJob *>(data);
+    napi_value out_arr = nullptr;
+    napi_get_reference_value(env, j->out_ref, &out_arr);
+    if (j->status == PCMB200_OK) {
+        napi_resolve_deferred(env, j->deferred, out_arr);
+    } else {
+        napi_value msg = nullptr, err = nullptr;
+        napi_create_string_utf8(env, j->error.c_str(), NAPI_AUTO_LENGTH, &msg);
+        if (j->status == PCMB200_ERR_RANGE) napi_create_range_error(env, nullptr, msg, &err);
+        else napi_create_error(env, nullptr, msg, &err);
+        napi_reject_deferred(env, j->deferred, err);
+    }
+    napi_delete_reference(env, j->batch_ref);
+    napi_delete_reference(env, j->out_ref);
+    napi_delete_async_work(env, j->work);
+    delete j;
+}
+
+napi_value FramesEncodeAsync(napi_env env, napi_callback_info info)
+{
+    size_t argc = 5;
+    napi_value argv[5];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    const float *in;
+    size_t n;
+    uint32_t rows = 0, n_in = 0;
+    double rate = 0;
+    if (argc < 5 || !get_f32(env, argv[0], &in, &n)) {
+        if (argc < 5) napi_throw_type_error(env, "PCMB200_TYPE", "framesEncodeAsync(batch, rows, nIn, rate, out)");
+        return nullptr;
+    }
+    if (napi_get_value_uint32(env, argv[1], &rows) != napi_ok || napi_get_value_uint32(env, argv[2], &n_in) != napi_ok ||
+        napi_get_value_double(env, argv[3], &rate) != napi_ok || (size_t)rows * n_in > n) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "framesEncodeAsync: rows * nIn exceeds batch.length");
+        return nullptr;
+    }
+    size_t n_out = 0;
+    if (throw_status(env, pcmb200_resample_len(n_in, rate, &n_out))) return nullptr;
+    bool is_ta = false;
+    napi_typedarray_type t;
+    size_t len = 0;
+    void *out = nullptr;
+    if (napi_is_typedarray(env, argv[4], &is_ta) != napi_ok || !is_ta ||
+        napi_get_typedarray_info(env, argv[4], &t, &len, &out, nullptr, nullptr) != napi_ok || t != napi_int16_array ||
+        len < (size_t)rows * n_out) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "out must be an Int16Array of at least rows * resampleLen(nIn, rate)");
+        return nullptr;
+    }
+    AsyncJob *j = new AsyncJob();
+    j->in = in; j->out = static_cast<int16_t *>(out); j->rows = rows; j->n_in = n_in; j->n_out = n_out; j->rate = rate;
+    napi_value promise = nullptr, name = nullptr;
+    napi_create_promise(env, &j->deferred, &promise);
+    napi_create_reference(env, argv[0], 1, &j->batch_ref);   // keep both arrays alive until the job is done
+    napi_create_reference(env, argv[4], 1, &j->out_ref);
+    napi_create_string_utf8(env, "pcm_b200.framesEncodeAsync", NAPI_AUTO_LENGTH, &name);
+    napi_create_async_work(env, nullptr, name, async_execute, async_complete, j, &j->work);
+    napi_queue_async_work(env, j->work);
+    return promise;
 }
 
 // resampleLen(n: number, rate: number): number                   App.tsx:23-24
@@ -200,6 +293,7 @@ napi_value Init(napi_env env, napi_value exports)
         {"floatTo16BitPCM", nullptr, FloatTo16BitPCM, nullptr, nullptr, nullptr, 0, nullptr},
         {"resampleTo16k", nullptr, ResampleTo16k, nullptr, nullptr, nullptr, 0, nullptr},
         {"framesEncode", nullptr, FramesEncode, nullptr, nullptr, nullptr, 0, nullptr},
+        {"framesEncodeAsync", nullptr, FramesEncodeAsync, nullptr, nullptr, nullptr, 0, nullptr},
         {"resampleLen", nullptr, ResampleLen, nullptr, nullptr, nullptr, 0, nullptr},
         {"allocPinnedFloat32", nullptr, AllocPinnedFloat32, nullptr, nullptr, nullptr, 0, nullptr},
         {"allocPinnedInt16", nullptr, AllocPinnedInt16, nullptr, nullptr, nullptr, 0, nullptr},

@@ -4,6 +4,8 @@ export function floatTo16BitPCM(float32: Float32Array): Int16Array;
 export function resampleTo16k(input: Float32Array, inputSampleRate: number): Float32Array;
 /** floatTo16BitPCM(resampleTo16k(row, rate)) for `rows` dense rows of `nIn` samples (App.tsx:281-282), fused on the GPU. */
 export function framesEncode(batch: Float32Array, rows: number, nIn: number, rate: number, out?: Int16Array): Int16Array;
+/** Same on a worker thread: the event loop is not blocked; `batch` and `out` must not be touched until the promise settles. */
+export function framesEncodeAsync(batch: Float32Array, rows: number, nIn: number, rate: number, out: Int16Array): Promise<Int16Array>;
 /** Math.floor(n / (rate / 16000)) as the reference computes it (App.tsx:23-24); throws RangeError where `new Float32Array` would. */
 export function resampleLen(n: number, rate: number): number;
 /** Typed arrays over page-locked host memory (no staging copy on H2D / D2H). */

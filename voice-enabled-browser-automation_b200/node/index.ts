@@ -9,6 +9,8 @@ export const floatTo16BitPCM: (float32: Float32Array) => Int16Array = native.flo
 export const resampleTo16k: (input: Float32Array, inputSampleRate: number) => Float32Array = native.resampleTo16k;
 export const framesEncode: (batch: Float32Array, rows: number, nIn: number, rate: number, out?: Int16Array) => Int16Array =
   native.framesEncode;
+export const framesEncodeAsync: (batch: Float32Array, rows: number, nIn: number, rate: number, out: Int16Array) => Promise<Int16Array> =
+  native.framesEncodeAsync;
 export const resampleLen: (n: number, rate: number) => number = native.resampleLen;
 export const allocPinnedFloat32: (length: number) => Float32Array = native.allocPinnedFloat32;
 export const allocPinnedInt16: (length: number) => Int16Array = native.allocPinnedInt16;

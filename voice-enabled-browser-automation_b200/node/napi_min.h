@@ -48,6 +48,22 @@ napi_status napi_throw_type_error(napi_env, const char *code, const char *msg);
 napi_status napi_throw_range_error(napi_env, const char *code, const char *msg);
 napi_status napi_define_properties(napi_env, napi_value object, size_t property_count, const napi_property_descriptor *properties);
 napi_status napi_add_env_cleanup_hook(napi_env, void (*fun)(void *arg), void *arg);
+typedef struct napi_deferred__ *napi_deferred;
+typedef struct napi_async_work__ *napi_async_work;
+typedef struct napi_ref__ *napi_ref;
+typedef void (*napi_async_execute_callback)(napi_env env, void *data);
+typedef void (*napi_async_complete_callback)(napi_env env, napi_status status, void *data);
+napi_status napi_create_promise(napi_env, napi_deferred *deferred, napi_value *promise);
+napi_status napi_resolve_deferred(napi_env, napi_deferred deferred, napi_value resolution);
+napi_status napi_reject_deferred(napi_env, napi_deferred deferred, napi_value rejection);
+napi_status napi_create_async_work(napi_env, napi_value async_resource, napi_value async_resource_name,
+                                   napi_async_execute_callback execute, napi_async_complete_callback complete, void *data,
+                                   napi_async_work *result);
+napi_status napi_queue_async_work(napi_env, napi_async_work work);
+napi_status napi_delete_async_work(napi_env, napi_async_work work);
+napi_status napi_create_reference(napi_env, napi_value value, uint32_t initial_refcount, napi_ref *result);
+napi_status napi_delete_reference(napi_env, napi_ref ref);
+napi_status napi_get_reference_value(napi_env, napi_ref ref, napi_value *result);
 void napi_module_register(napi_module *mod);
 }
 #define NAPI_AUTO_LENGTH ((size_t)-1)

@@ -2,7 +2,7 @@
 // Frames that arrive within one tick are grouped by (rate, length), converted with ONE framesEncode
 // call per group, and each session's slice is passed to the unchanged DeepgramClient.sendAudio
 // (apps/voice/src/deepgram.ts:55-58).  New glue, not a behaviour of the reference.
-import { allocPinnedFloat32, allocPinnedInt16, framesEncode, resampleLen } from "./index";
+import { allocPinnedFloat32, allocPinnedInt16, framesEncodeAsync, resampleLen } from "./index";
 
 type Sink = (pcm16: Buffer) => void;
 type Group = { rate: number; nIn: number; frames: Float32Array[]; sinks: Sink[] };
@@ -14,7 +14,7 @@ export class FrameBatcher {
   private timer: NodeJS.Timeout;
 
   constructor(opts: { tickMs?: number } = {}) {
-    this.timer = setInterval(() => this.flush(), opts.tickMs ?? 20);
+    this.timer = setInterval(() => void this.flush(), opts.tickMs ?? 20);
   }
 
   /** One Float32 frame of one session (the bytes of a WS binary message). */
@@ -27,19 +27,21 @@ export class FrameBatcher {
     g.sinks.push(sink);
   }
 
-  flush(): void {
-    for (const g of this.groups.values()) {
+  /** Converts everything that arrived during the tick; the CUDA work runs off the event loop. */
+  async flush(): Promise<void> {
+    const groups = [...this.groups.values()];
+    this.groups.clear();
+    for (const g of groups) {
       const rows = g.frames.length;
       const nOut = resampleLen(g.nIn, g.rate);
       if (rows * g.nIn > this.pinIn.length) this.pinIn = allocPinnedFloat32(2 * rows * g.nIn);
       if (rows * nOut > this.pinOut.length) this.pinOut = allocPinnedInt16(2 * rows * nOut);
       g.frames.forEach((f, r) => this.pinIn.set(f, r * g.nIn));
-      framesEncode(this.pinIn, rows, g.nIn, g.rate, this.pinOut);
+      const out = await framesEncodeAsync(this.pinIn, rows, g.nIn, g.rate, this.pinOut);
       g.sinks.forEach((sink, r) =>
         // copy out of the shared pinned block: sendAudio may keep the Buffer beyond this tick
-        sink(Buffer.from(Buffer.from(this.pinOut.buffer, this.pinOut.byteOffset + r * nOut * 2, nOut * 2))));
+        sink(Buffer.from(Buffer.from(out.buffer, out.byteOffset + r * nOut * 2, nOut * 2))));
     }
-    this.groups.clear();
   }
 
   /** The reference's keep-alive (App.tsx:291-296): 100 ms of silence every 2 s per open session. */
@@ -49,6 +51,6 @@ export class FrameBatcher {
 
   close(): void {
     clearInterval(this.timer);
-    this.flush();
+    void this.flush();
   }
 }
