@@ -12,6 +12,7 @@ export class FrameBatcher {
   private pinIn = allocPinnedFloat32(1 << 20);
   private pinOut = allocPinnedInt16(1 << 19);
   private timer: NodeJS.Timeout;
+  private busy = false;
 
   constructor(opts: { tickMs?: number } = {}) {
     this.timer = setInterval(() => void this.flush(), opts.tickMs ?? 20);
@@ -29,6 +30,8 @@ export class FrameBatcher {
 
   /** Converts everything that arrived during the tick; the CUDA work runs off the event loop. */
   async flush(): Promise<void> {
+    if (this.busy) return;              // the pinned blocks are still in use: keep collecting, flush next tick
+    this.busy = true;
     const groups = [...this.groups.values()];
     this.groups.clear();
     for (const g of groups) {
@@ -42,6 +45,7 @@ export class FrameBatcher {
         // copy out of the shared pinned block: sendAudio may keep the Buffer beyond this tick
         sink(Buffer.from(Buffer.from(out.buffer, out.byteOffset + r * nOut * 2, nOut * 2))));
     }
+    this.busy = false;
   }
 
   /** The reference's keep-alive (App.tsx:291-296): 100 ms of silence every 2 s per open session. */
