@@ -156,6 +156,14 @@ PCMB200_API int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_session
 PCMB200_API int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *agg);
 /* Initial state / stop() of the reference (App.tsx:148-157, :325-330): empty buffer, lastSend = now. */
 PCMB200_API int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t session, double now_ms);
+/* Level meter of the aggregated sessions (App.tsx:267-271): when enabled, the quanta of every
+ * flushed frame go through rms = sqrt(sum(x*x)/quantum), level = Math.max(rms, level * 0.85) in
+ * arrival order (binary64, bit-identical to the reference's arithmetic).  get_levels copies the
+ * current level of `count` sessions to the host (waits for the pushes enqueued so far).  The level
+ * lags the reference's by the quanta still waiting in a session's buffer. */
+PCMB200_API int pcmb200_aggregator_set_meter(pcmb200_ctx *ctx, pcmb200_aggregator *agg, int enabled);
+PCMB200_API int pcmb200_aggregator_get_levels(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t first_session,
+                                              uint32_t count, double *levels_host);
 /* Append n_quanta quanta, in arrival order (quantum i belongs to sessions[i], samples + i*quantum),
  * and convert every frame that flushes.  Frame f (in flush order) is frame_len[f] int16 samples of
  * session frame_session[f] at out + frame_offset[f] (offsets are multiples of 8 samples).

@@ -22,7 +22,12 @@ def test_aggregator_matches_oracle(ctx, rate):
         nq = int(seconds * 1e3 / q_ms)
         t = 5.0 * rng.rand() + np.cumsum(q_ms + rng.uniform(-0.4, 0.4, nq))
         x = (rng.uniform(-1.1, 1.1, size=(nq, 128)) * rng.uniform(0.05, 1)).astype(np.float32)
-        x[0, :3] = [np.nan, np.inf, -0.0]
+        if s == 0:
+            x[0, :3] = [np.nan, np.inf, -0.0]       # poisons session 0's level for good (Math.max NaN rule)
+        elif s == 1:
+            x[2, 5] = np.float32(np.inf)
+        elif s == 2:
+            x[:4] = 0.0                              # starts with silence
         audio[s], times[s] = x, t
         flush, _ = oracle.aggregator_plan(t, 60.0, 0.0)
         frames, start = [], 0
@@ -34,6 +39,7 @@ def test_aggregator_matches_oracle(ctx, rate):
         events += [(t[q], s, q) for q in range(nq)]
     events.sort()
     agg = pcm_frontend.Aggregator(ctx, n_sessions, rate, max_frame_quanta=96, max_push_quanta=4096, max_out_samples=1 << 20)
+    agg.set_meter(True)
     for s in range(n_sessions):
         agg.reset_session(s, 0.0)
     got = {s: [] for s in range(n_sessions)}
@@ -50,6 +56,13 @@ def test_aggregator_matches_oracle(ctx, rate):
                           np.stack([audio[e[1]][e[2]] for e in chunk]))
         for s, pcm in frames:
             got[s].append(pcm)
+    # level meter (App.tsx:267-271): binary64 level after the last FLUSHED quantum of every session
+    levels = agg.levels(0, n_sessions)
+    for s in range(n_sessions):
+        flush, _ = oracle.aggregator_plan(times[s], 60.0, 0.0)
+        last = np.nonzero(flush)[0][-1] + 1
+        want_lv = oracle.level_meter(audio[s][:last].reshape(-1))[-1]
+        assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], (s, levels[s], want_lv)
     agg.close()
     n_frames = 0
     for s in range(n_sessions):

@@ -1056,6 +1056,8 @@ struct pcmb200_aggregator {
     std::vector<uint32_t> flush_nq, flush_row, touched;
     uint32_t push_epoch = 0;
     uint8_t *h_round = nullptr, *d_round = nullptr;    // pinned / device copy of q_round
+    double *d_level = nullptr;                         // [max_sessions] level of every session (meter)
+    bool meter = false;
 };
 
 namespace {
@@ -1097,6 +1099,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(cudaHostAlloc((void **)&a->h_dst_off, (size_t)max_push_quanta * 8, cudaHostAllocDefault));
     AGG_STEP(cudaHostAlloc((void **)&a->h_round, (size_t)max_push_quanta, cudaHostAllocDefault));
     AGG_STEP(cudaMalloc((void **)&a->d_round, (size_t)max_push_quanta));
+    AGG_STEP(cudaMalloc((void **)&a->d_level, (size_t)max_sessions * sizeof(double)));
+    AGG_STEP(cudaMemsetAsync(a->d_level, 0, (size_t)max_sessions * sizeof(double), ctx->stream));
     AGG_STEP(cudaEventCreateWithFlags(&a->uploaded, cudaEventDisableTiming));
     AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_bytes, ctx->stream));
 #undef AGG_STEP
@@ -1122,6 +1126,7 @@ extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *
     if (a->h_dst_off) cudaFreeHost(a->h_dst_off);
     if (a->h_round) cudaFreeHost(a->h_round);
     cudaFree(a->d_round);
+    cudaFree(a->d_level);
     if (a->uploaded) cudaEventDestroy(a->uploaded);
     cudaGetLastError();
     delete a;
@@ -1135,6 +1140,27 @@ extern "C" int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggreg
     NEED(session < a->max_sessions, "pcmb200_aggregator_reset_session: session out of range");
     a->fill[session] = 0;
     a->last_send[session] = now_ms;
+    return PCMB200_OK;
+}
+
+// Level meter of the aggregated sessions (App.tsx:267-271).  When enabled, every flushed frame's
+// quanta run through rms / max(rms, level * 0.85) in arrival order; the level of a session therefore
+// lags the reference's by the quanta still waiting in its buffer (it is a UI-only value there).
+extern "C" int pcmb200_aggregator_set_meter(pcmb200_ctx *ctx, pcmb200_aggregator *a, int enabled)
+{
+    NEED(ctx && a, "pcmb200_aggregator_set_meter: NULL argument");
+    a->meter = enabled != 0;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_get_levels(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t first_session, uint32_t count,
+                                             double *levels_host)
+{
+    NEED(ctx && a && (levels_host || count == 0), "pcmb200_aggregator_get_levels: NULL argument");
+    NEED((unsigned long long)first_session + count <= a->max_sessions, "pcmb200_aggregator_get_levels: session range out of bounds");
+    CU(cudaSetDevice(ctx->device));
+    if (count) CU(cudaMemcpyAsync(levels_host, a->d_level + first_session, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
     return PCMB200_OK;
 }
 
@@ -1321,6 +1347,12 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
                 const int grid = grid_for(ctx, tiles);
                 k_rows_pick_encode<4><<<grid, 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, d_out, a->d_dst_off + k, n_in,
                                                             n_out, lut, is_int ? R : 1u, n_pairs);
+                ctx->launches++;
+            }
+            if (a->meter) {   // App.tsx:267-271 over the quanta of these frames, in session order
+                const uint32_t nf = (uint32_t)(k1 - k);
+                k_rows_meter<<<grid_for(ctx, (nf + 7) / 8), 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, nf, nq, a->quantum,
+                                                                        a->d_level);
                 ctx->launches++;
             }
             k = k1;

@@ -685,6 +685,44 @@ k_rows_pick_encode(const float *__restrict__ ring, size_t pitch_in, const uint32
     }
 }
 
+// k_rows_meter: the level meter (App.tsx:267-271) over the frames an aggregator push flushed.  One
+// warp per frame; lane l accumulates quantum l of the frame in sample order (exact widening), then
+// the session's level runs through the frame's quanta in order.  session = src_row >> 1.
+__global__ void __launch_bounds__(256)
+k_rows_meter(const float *__restrict__ ring, size_t pitch_in, const uint32_t *__restrict__ src_row, uint32_t n_frames,
+             uint32_t nq, uint32_t quantum, double *__restrict__ level)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; f < n_frames; f += warps) {
+        const uint32_t row = __ldg(src_row + f);
+        const float *base = ring + (size_t)row * pitch_in;
+        double lv = level[row >> 1];
+        bool poisoned = lv != lv;
+        for (uint32_t q0 = 0; q0 < nq; q0 += 32u) {
+            const uint32_t q = q0 + lane;
+            double sum = 0.0;
+            if (q < nq) {
+                const float *src = base + (size_t)q * quantum;
+                for (uint32_t k = 0; k < quantum; k++) {
+                    const double x = widen_abs(__ldg(src + k));
+                    sum = __fma_rn(x, x, sum);
+                }
+            }
+            const double rms = rms_of(sum, quantum);
+            const uint32_t cnt = nq - q0 < 32u ? nq - q0 : 32u;
+            for (uint32_t j = 0; j < cnt; j++) {          // every lane runs the same chain; lane 0 stores it
+                const double r = __shfl_sync(0xFFFFFFFFu, rms, j);
+                poisoned |= r != r;
+                const double dec = __dmul_rn(lv, 0.85);
+                lv = r > dec ? r : dec;
+                if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
+            }
+        }
+        if (lane == 0) level[row >> 1] = lv;
+    }
+}
+
 // ---- kernel 4: level meter alone (any layout; one thread per session, sequential) ----------------------
 // Fallback for batches kernel 2b cannot take (pitched rows, long frames).  Correct, not fast.
 __global__ void __launch_bounds__(128)

@@ -299,6 +299,16 @@ class Aggregator:
         self._fl = np.empty(max_push_quanta, dtype=np.uint32)
         self._fo = np.empty(max_push_quanta, dtype=np.uint64)
 
+    def set_meter(self, enabled: bool = True):
+        check(self.ctx._L.pcmb200_aggregator_set_meter(self.ctx.handle, self.handle, int(enabled)), self.ctx.handle)
+
+    def levels(self, first_session: int, count: int) -> np.ndarray:
+        """Current meter level (App.tsx:267-271) of `count` sessions, as of their last flushed frame."""
+        out = np.empty(count, dtype=np.float64)
+        check(self.ctx._L.pcmb200_aggregator_get_levels(self.ctx.handle, self.handle, int(first_session), int(count),
+                                                        out.ctypes.data), self.ctx.handle)
+        return out
+
     def reset_session(self, session: int, now_ms: float):
         check(self.ctx._L.pcmb200_aggregator_reset_session(self.ctx.handle, self.handle, int(session), float(now_ms)),
               self.ctx.handle)
