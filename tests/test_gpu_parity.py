@@ -351,3 +351,43 @@ def test_tile_staged_kernel_matches_general_kernel(ctx, rate, n_in):
             assert np.array_equal(raw[: rows * n_out].reshape(rows, n_out), want), (rate, rows, tune)
             assert (raw[rows * n_out:] == 0x5555).all()
         d_in.free(); d_out.free()
+
+
+def test_frame_batcher_groups_mixed_rates(ctx):
+    """Tick batching across sessions with different capture rates and frame lengths (8f next-4)."""
+    import pcm_frontend
+    rng = np.random.RandomState(77)
+    fb = pcm_frontend.FrameBatcher(ctx)
+    sent, want = {}, {}
+    for sid in range(200):
+        rate, n_in = [(48000, 960), (44100, 882), (16000, 320), (48000, 2944), (8000, 160)][sid % 5]
+        x = rng.uniform(-1.1, 1.1, n_in).astype(np.float32)
+        want[sid] = oracle.frames(x.reshape(1, -1), n_in, rate)[0].astype("<i2").tobytes()
+        fb.push(sid, rate, x, sink=lambda b, sid=sid: sent.__setitem__(sid, b))
+    out = dict(fb.flush())
+    assert out == want and sent == want
+    assert fb.flush() == []
+
+
+def test_two_contexts_from_two_threads(ctx):
+    """A context is not thread-safe, but two contexts on one device used from two threads are fine."""
+    import threading
+
+    import pcm_frontend
+    rng = np.random.RandomState(5)
+    x = _audio(rng, 2048, 960)
+    want = oracle.frames(x, 960, 48000)
+    errors = []
+
+    def work():
+        try:
+            with pcm_frontend.Context(0) as c:
+                for _ in range(20):
+                    if not np.array_equal(c.frames_encode(x, 48000), want):
+                        errors.append("mismatch")
+        except Exception as e:   # noqa: BLE001
+            errors.append(repr(e))
+    ts = [threading.Thread(target=work) for _ in range(2)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    assert not errors, errors

@@ -25,6 +25,7 @@ from .api import (  # noqa: F401
     Aggregator,
     Context,
     DeviceBuffer,
+    FrameBatcher,
     PinnedBuffer,
     TickGraph,
     default_context,
@@ -38,7 +39,7 @@ from .api import (  # noqa: F401
 )
 
 __all__ = [
-    "Aggregator", "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
+    "Aggregator", "Context", "DeviceBuffer", "FrameBatcher", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
     "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table", "keepalive_frame",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",
 ]
