@@ -86,3 +86,14 @@ def test_aggregator_rejects_overlong_buffer_and_rolls_back(ctx):
     frames = agg.push(np.zeros(4, np.uint32), np.array([1.0, 2.0, 3.0, 61.0]), x[:4])
     assert len(frames) == 1 and frames[0][0] == 0 and frames[0][1].size == 170 and (frames[0][1] == 8191).all()
     agg.close()
+
+
+def test_aggregator_rejects_out_of_range_session(ctx):
+    agg = pcm_frontend.Aggregator(ctx, 37, 48000, max_frame_quanta=8, max_push_quanta=64, max_out_samples=4096)
+    x = np.zeros((3, 128), np.float32)
+    with pytest.raises(pcm_frontend.PcmError):
+        agg.push(np.array([1, 40, 2], np.uint32), np.array([1.0, 2.0, 3.0]), x)
+    # the valid sessions of the rejected push were rolled back: session 1 still flushes a 1-quantum frame
+    frames = agg.push(np.array([1], np.uint32), np.array([70.0]), x[:1])
+    assert len(frames) == 1 and frames[0][1].size == 42
+    agg.close()

@@ -8,6 +8,7 @@
 #include "pcm_kernels.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -1054,6 +1055,8 @@ struct pcmb200_aggregator {
     std::vector<double> last_send;
     std::vector<uint8_t> q_round, flushes_of;          // plan scratch: round of every quantum / flushes per session
     std::vector<uint32_t> flush_nq, flush_row, touched;
+    std::vector<unsigned long long> flush_bits;
+    std::vector<std::vector<uint32_t>> buckets;        // [producer thread][owner thread] quantum indices
     uint32_t push_epoch = 0;
     uint8_t *h_round = nullptr, *d_round = nullptr;    // pinned / device copy of q_round
     double *d_level = nullptr;                         // [max_sessions] level of every session (meter)
@@ -1175,39 +1178,55 @@ namespace {
 struct AggPlanShared {
     pcmb200_aggregator *a; uint32_t n; const uint32_t *sessions; const double *arrival;
     uint8_t *q_round;        // [n] round of every quantum
-    uint32_t *flush_nq;      // [n] 0, or the frame length in quanta if quantum i flushes
+    uint32_t *flush_nq;      // [n] the frame length in quanta, valid where quantum i flushes
     uint32_t *flush_row;     // [n] ring row of that frame
+    unsigned long long *flush_bits;   // [(n + 63) / 64] bit i set <=> quantum i flushes
 };
-struct AggPlanThread { std::vector<AggUndo> undo; int status = PCMB200_OK; uint32_t max_round = 0; };
+struct AggPlanThread { std::vector<AggUndo> undo; int status = PCMB200_OK; uint32_t max_round = 0, worst_session = 0; };
 
-void agg_plan_worker(const AggPlanShared &sh, uint32_t t, uint32_t own_shift, AggPlanThread &out, std::vector<uint8_t> &flushes_of)
+// Phase 1: thread t looks at its share of the quanta list and sorts the indices into one bucket per
+// owner thread (so nobody scans the whole list).  Phase 2: the owner walks the buckets addressed to
+// it, producer by producer, which is ascending index order, and runs the session state machines.
+void agg_plan_worker(const AggPlanShared &sh, uint32_t t, uint32_t T, uint32_t own_shift, AggPlanThread &out,
+                     std::vector<uint8_t> &flushes_of, std::vector<std::vector<uint32_t>> &buckets, std::atomic<uint32_t> &arrived)
 {
     pcmb200_aggregator *a = sh.a;
-    for (uint32_t i = 0; i < sh.n; i++) {
+    const uint32_t i0 = (uint32_t)((unsigned long long)sh.n * t / T), i1 = (uint32_t)((unsigned long long)sh.n * (t + 1) / T);
+    for (uint32_t o = 0; o < T; o++) buckets[(size_t)t * T + o].clear();
+    for (uint32_t i = i0; i < i1; i++) {
         const uint32_t s = sh.sessions[i];
-        if ((s >> own_shift) != t) continue;   // contiguous session blocks: no cache line is shared by two threads
-        if (a->touched[s] != a->push_epoch) {   // first quantum of this session in this push: remember its state
-            a->touched[s] = a->push_epoch;
-            out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s]});
+        if (s > out.worst_session) out.worst_session = s;
+        if (s < a->max_sessions) buckets[(size_t)t * T + (s >> own_shift)].push_back(i);   // ids out of range: nobody's
+    }
+    arrived.fetch_add(1, std::memory_order_acq_rel);          // barrier between the phases
+    while (arrived.load(std::memory_order_acquire) < T) std::this_thread::yield();
+
+    for (uint32_t p = 0; p < T; p++) {
+        for (const uint32_t i : buckets[(size_t)p * T + t]) {
+            const uint32_t s = sh.sessions[i];
+            if (a->touched[s] != a->push_epoch) {   // first quantum of this session in this push: remember its state
+                a->touched[s] = a->push_epoch;
+                out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s]});
+            }
+            const uint8_t h = a->half[s];
+            if (a->fill[s] >= a->half_quanta) { out.status = PCMB200_ERR_CAPACITY; return; }
+            const uint8_t round = flushes_of[s];
+            a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
+            sh.q_round[i] = round;
+            a->fill[s]++;
+            // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+            if (sh.arrival[i] - a->last_send[s] >= a->desired_ms) {
+                if (round == 255) { out.status = PCMB200_ERR_CAPACITY; return; }
+                sh.flush_nq[i] = a->fill[s];
+                sh.flush_row[i] = s * 2u + h;
+                __atomic_fetch_or(&sh.flush_bits[i >> 6], 1ull << (i & 63u), __ATOMIC_RELAXED);
+                a->half[s] = h ^ 1u;
+                a->fill[s] = 0;
+                a->last_send[s] = sh.arrival[i];                     // App.tsx:287
+                flushes_of[s] = round + 1;
+            }
+            if (round > out.max_round) out.max_round = round;
         }
-        const uint8_t h = a->half[s];
-        if (a->fill[s] >= a->half_quanta) { out.status = PCMB200_ERR_CAPACITY; return; }
-        const uint8_t round = flushes_of[s];
-        a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
-        sh.q_round[i] = round;
-        a->fill[s]++;
-        sh.flush_nq[i] = 0;
-        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
-        if (sh.arrival[i] - a->last_send[s] >= a->desired_ms) {
-            if (round == 255) { out.status = PCMB200_ERR_CAPACITY; return; }
-            sh.flush_nq[i] = a->fill[s];
-            sh.flush_row[i] = s * 2u + h;
-            a->half[s] = h ^ 1u;
-            a->fill[s] = 0;
-            a->last_send[s] = sh.arrival[i];                     // App.tsx:287
-            flushes_of[s] = round + 1;
-        }
-        if (round > out.max_round) out.max_round = round;
     }
 }
 }  // namespace
@@ -1225,22 +1244,18 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     NEED((samples_mem == PCMB200_MEM_HOST || samples_mem == PCMB200_MEM_DEVICE) &&
          (out_mem == PCMB200_MEM_HOST || out_mem == PCMB200_MEM_DEVICE), "pcmb200_aggregator_push: bad mem kind");
     NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push: more quanta than max_push_quanta");
-    {
-        uint32_t worst = 0;
-        for (uint32_t i = 0; i < n_quanta; i++) worst = sessions[i] > worst ? sessions[i] : worst;
-        NEED(worst < a->max_sessions, "pcmb200_aggregator_push: session id out of range");
-    }
     CU(cudaSetDevice(ctx->device));
     CU(cudaEventSynchronize(a->uploaded));   // the previous push's index upload has left the pinned staging
 
     // ---- plan on the host ----
     try {
         a->flush_nq.resize(n_quanta); a->flush_row.resize(n_quanta);
+        a->flush_bits.assign((n_quanta + 63) / 64, 0ull);
         a->flushes_of.assign(a->max_sessions, 0);
         if (a->touched.size() != a->max_sessions) a->touched.assign(a->max_sessions, 0);
         a->push_epoch++;
     } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_push: host allocation failed"); }
-    AggPlanShared sh{a, n_quanta, sessions, arrival_ms, a->h_round, a->flush_nq.data(), a->flush_row.data()};
+    AggPlanShared sh{a, n_quanta, sessions, arrival_ms, a->h_round, a->flush_nq.data(), a->flush_row.data(), a->flush_bits.data()};
     uint32_t T = 1;
     if (n_quanta >= 65536) {
         const uint32_t hw = std::thread::hardware_concurrency();
@@ -1249,12 +1264,14 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     uint32_t own_shift = 0;   // a thread owns sessions [t << own_shift, (t + 1) << own_shift)
     while (((unsigned long long)T << own_shift) < a->max_sessions) own_shift++;
     std::vector<AggPlanThread> th(T);
+    if (a->buckets.size() < (size_t)T * T) a->buckets.resize((size_t)T * T);
+    std::atomic<uint32_t> arrived{0};
     if (T == 1) {
-        agg_plan_worker(sh, 0, own_shift, th[0], a->flushes_of);
+        agg_plan_worker(sh, 0, 1, own_shift, th[0], a->flushes_of, a->buckets, arrived);
     } else {
         std::vector<std::thread> pool;
         for (uint32_t t = 0; t < T; t++)
-            pool.emplace_back([&, t] { agg_plan_worker(sh, t, own_shift, th[t], a->flushes_of); });
+            pool.emplace_back([&, t] { agg_plan_worker(sh, t, T, own_shift, th[t], a->flushes_of, a->buckets, arrived); });
         for (auto &p : pool) p.join();
     }
     int status = PCMB200_OK;
@@ -1263,14 +1280,18 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
     for (auto &t : th) {
         if (t.status) { status = t.status; why = "a session's buffer exceeds max_frame_quanta (no flush arrived), or it flushed > 255 times"; }
         if (t.max_round > max_round) max_round = t.max_round;
+        if (t.worst_session >= a->max_sessions) {   // such ids belong to no thread: no state was touched for them
+            status = PCMB200_ERR_INVALID; why = "session id out of range";
+        }
     }
     // frames in flush (= quantum) order; output offsets are assigned in that order
     std::vector<AggFrame> frames;
     unsigned long long off = 0;
     if (status == PCMB200_OK) {
         std::vector<size_t> len_of(a->half_quanta + 1, (size_t)-1);   // output length per frame length (in quanta)
-        for (uint32_t i = 0; i < n_quanta; i++) {
-            if (!a->flush_nq[i]) continue;
+        for (size_t w = 0; w < a->flush_bits.size() && status == PCMB200_OK; w++)
+          for (unsigned long long bits = a->flush_bits[w]; bits; bits &= bits - 1) {
+            const uint32_t i = (uint32_t)(w * 64 + (size_t)__builtin_ctzll(bits));
             size_t &n_out_c = len_of[a->flush_nq[i]];
             if (n_out_c == (size_t)-1) resample_len((size_t)a->flush_nq[i] * a->quantum, a->rate, &n_out_c);
             const size_t n_out = n_out_c;
