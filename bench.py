@@ -10,7 +10,8 @@ Workload (config.workload): BASELINE.json configs[3] -- 2^20 concurrent 48 kHz m
 framing, i.e. floatTo16BitPCM(resampleTo16k(frame, 48000)) of App.tsx:281-282 for every session.
 One STEP = one tick = one frame of every session of the rank's shard = one kernel launch.
 Sessions are independent: multi-GPU is session-affine sharding, no collective on the data path
-(torch.distributed is used only for the start barrier and the max-over-ranks of the timings).
+(torch.distributed, gloo backend, is used only for the start barrier and the max-over-ranks of the
+timings; no NCCL communicator is ever created).
 
 Prints ONE JSON line (rank 0).  `value` = input PCM samples/s, device-resident;
 `e2e` = the same through pcmb200_frames_encode with pinned HOST buffers (H2D + kernel + D2H).
@@ -76,13 +77,11 @@ class Dist:
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             os.environ.setdefault("MASTER_PORT", "29511")
             self.torch = torch
-            if use_cuda and torch.cuda.is_available():
-                torch.cuda.set_device(local_rank)
-                self.device = torch.device("cuda", local_rank)
-                dist.init_process_group("nccl", device_id=self.device)
-            else:
-                self.device = torch.device("cpu")
-                dist.init_process_group("gloo")
+            # Control plane only (start barrier, MAX / SUM of a few doubles): gloo on CPU tensors.  The
+            # data path has no exchange step, so no NCCL communicator is created -- which also keeps
+            # stdout to the one JSON line (NCCL announces its version there).
+            self.device = torch.device("cpu")
+            dist.init_process_group("gloo")
             self.dist = dist
 
     def barrier(self):
