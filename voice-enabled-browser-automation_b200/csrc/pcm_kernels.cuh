@@ -391,10 +391,12 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
     const bool rows_aligned = (n_out & 7u) == 0u;
     const uint32_t outs_per_tile = rows_per_tile * n_out;
 
+    __shared__ float4 zero_granule;   // METER: what a lane reads before it starts / after it finishes
     if (threadIdx.x == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; s++) mbar_init(&bars[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        zero_granule = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     if (lut)
         for (uint32_t i = threadIdx.x; i < n_out; i += blockDim.x) tab[i] = __ldg(lut + i);
@@ -507,16 +509,14 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
                     const bool valid = qg < quanta;
                     const uint32_t rr = valid ? qg / meter.nq : 0u, q = valid ? qg - rr * meter.nq : 0u;
                     const float4 *src4 = reinterpret_cast<const float4 *>(tile + rr * n_in + q * meter.quantum);
-                    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                    float4 cur = (valid && sub == 0u) ? src4[0] : zero4;
+                    float4 cur = *((valid && sub == 0u) ? src4 : &zero_granule);
                     double sum = 0.0;
                     bool odd = false;
-                    // No branches inside: a lane that has not started or has finished feeds zeros
-                    // (sum + 0*0 leaves sum unchanged, NaN and Inf included).
+                    // No branches inside: a lane that has not started or has finished reads a granule
+                    // of zeros instead (one address select per step, not four value selects).
                     for (uint32_t i = 0; i < G + 7u; i++) {
                         const uint32_t gn = i - sub + 1u;     // next granule; wraps to 0 one step before the start
-                        const float4 v = src4[gn < G ? gn : G - 1u];
-                        const float4 nxt = (valid && gn < G) ? v : zero4;
+                        const float4 nxt = *((valid && gn < G) ? src4 + gn : &zero_granule);
                         const double x0 = widen_abs_fast(cur.x, odd), x1 = widen_abs_fast(cur.y, odd),
                                      x2 = widen_abs_fast(cur.z, odd), x3 = widen_abs_fast(cur.w, odd);
                         sum = __fma_rn(x0, x0, sum);
