@@ -87,3 +87,14 @@ def test_meter_fallback_kernel_on_pitched_rows(ctx):
     want = _oracle_levels(x, n_in, state)
     assert np.array_equal(d_lv.download(np.float64, rows * 7).reshape(rows, 7).view(np.uint64), want.view(np.uint64))
     assert np.array_equal(d_out.download(np.int16, rows * 320).reshape(rows, 320), oracle.frames(x, n_in, 48000))
+
+
+def test_host_array_convenience(ctx):
+    rng = np.random.RandomState(3)
+    x = rng.uniform(-1, 1, size=(50, 2944)).astype(np.float32)
+    state = rng.uniform(0, 1, 50)
+    pcm, levels, new_state = ctx.frames_encode_meter(x, 48000, state)
+    assert np.array_equal(pcm, oracle.frames(x, 2944, 48000))
+    want = _oracle_levels(x, 2944, state)
+    assert np.array_equal(levels.view(np.uint64), want.view(np.uint64))
+    assert np.array_equal(new_state.view(np.uint64), want[:, -1].view(np.uint64))

@@ -254,6 +254,34 @@ class Context:
                                                   int(levels_ptr) if levels_ptr else None, C.byref(got)), self.handle)
         return int(got.value)
 
+    def frames_encode_meter(self, batch: np.ndarray, rate: float, level_state: np.ndarray, quantum: int = 128):
+        """Host-array convenience over frames_encode_meter_ptr: returns (pcm16 [rows, n_out],
+        levels [rows, n_in // quantum], new level_state [rows]).  Stages through device buffers."""
+        if batch.ndim != 2 or batch.dtype != np.float32:
+            raise TypeError("expected a 2-D float32 batch [rows, samples]")
+        batch = np.ascontiguousarray(batch)
+        rows, n_in = batch.shape
+        n_out, nq = resample_len(n_in, rate), n_in // quantum
+        state = np.ascontiguousarray(level_state, dtype=np.float64)
+        assert state.size == rows
+        d_in, d_out = self.device_buffer(max(batch.nbytes, 16)), self.device_buffer(max(rows * n_out * 2, 16))
+        d_state, d_lv = self.device_buffer(max(rows * 8, 16)), self.device_buffer(max(rows * nq * 8, 16))
+        try:
+            if batch.size:
+                d_in.upload(batch)
+            if rows:
+                d_state.upload(state)
+            self.frames_encode_meter_ptr(d_in.ptr, max(n_in, 1), d_out.ptr, max(n_out, 1), rows, n_in, rate, d_state.ptr,
+                                         d_lv.ptr, quantum)
+            self.sync()
+            pcm = d_out.download(np.int16, rows * n_out).reshape(rows, n_out)
+            levels = d_lv.download(np.float64, rows * nq).reshape(rows, nq)
+            new_state = d_state.download(np.float64, rows)
+        finally:
+            for d in (d_in, d_out, d_state, d_lv):
+                d.free()
+        return pcm, levels, new_state
+
     def tick_graph(self, in_ptr: int, pitch_in: int, out_ptr: int, pitch_out: int, rows: int, n_in: int,
                    rate: float) -> "TickGraph":
         """Record one device-resident tick as a CUDA graph (pcmb200_tick_graph_create)."""
