@@ -9,6 +9,8 @@ Workload (config.workload): BASELINE.json configs[3] -- 2^20 concurrent 48 kHz m
 20 ms frames (960 in -> 320 out per frame), nearest-sample decimation to 16 kHz + Int16 encode +
 framing, i.e. floatTo16BitPCM(resampleTo16k(frame, 48000)) of App.tsx:281-282 for every session.
 One STEP = one tick = one frame of every session of the rank's shard = one kernel launch.
+Default `--scaling strong`: the 2^20 sessions are sharded over the N ranks (2^20 / N per GPU), which is
+what BASELINE configs[3] states; `--scaling weak` gives every GPU 2^20 sessions instead.
 Sessions are independent: multi-GPU is session-affine sharding, no collective on the data path
 (torch.distributed, gloo backend, is used only for the start barrier and the max-over-ranks of the
 timings; no NCCL communicator is ever created).
@@ -47,13 +49,17 @@ def parse_args(argv=None):
     ap.add_argument("--sessions", type=int, default=1 << 20, help="concurrent sessions (per GPU when --scaling weak)")
     ap.add_argument("--frame-ms", type=int, default=20)
     ap.add_argument("--rate", type=float, default=48000.0, help="capture rate of every session (Hz); BASELINE uses 48000")
-    ap.add_argument("--scaling", choices=["weak", "strong"], default="weak",
-                    help="weak: every GPU holds --sessions sessions; strong: --sessions are sharded over the GPUs")
+    ap.add_argument("--scaling", choices=["weak", "strong"], default="strong",
+                    help="strong (default, BASELINE configs[3]): --sessions are sharded over the GPUs; "
+                         "weak: every GPU holds --sessions sessions")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--wc", type=int, default=0, help="1: e2e input ring in write-combined pinned memory")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
-    ap.add_argument("--ref-sessions", type=int, default=1 << 16, help="sessions per step of --impl reference")
+    ap.add_argument("--ref-sessions", type=int, default=0,
+                    help="sessions per step of --impl reference (0 = all --sessions: the full tick, like the CUDA arm)")
+    ap.add_argument("--sustained-seconds", type=float, default=2.5,
+                    help="length of the back-to-back `sustained` leg (0 = skip)")
     ap.add_argument("--tune", default="", help="comma list key=value passed to pcmb200_tune (sweeps)")
     args = ap.parse_args(argv)
     global RATE
@@ -95,6 +101,15 @@ class Dist:
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
         return float(t.item())
 
+    def gather(self, x: float):
+        """Every rank's value, in rank order (used to separate per-rank time from the max over ranks)."""
+        if not self.dist:
+            return [float(x)]
+        t = self.torch.tensor([float(x)], dtype=self.torch.float64, device=self.device)
+        out = [self.torch.zeros_like(t) for _ in range(self.world)]
+        self.dist.all_gather(out, t)
+        return [float(o.item()) for o in out]
+
     def close(self):
         if self.dist:
             self.dist.barrier()
@@ -117,23 +132,28 @@ def sessions_for_rank(args, rank, world):
 
 
 def bind_to_gpu_numa(index):
-    """Pin this rank to the CPUs NVML reports as local to GPU `index`, so that its pinned host ring is
-    allocated on (and fed from) the GPU's own NUMA node.  Returns (cpus bound, previous affinity)."""
+    """Bind this rank to the CPUs NVML reports as local to GPU `index` -- but only when that is a real
+    choice.  On a box whose GPUs all report the same affinity (one NUMA node; every 8-GPU box of this
+    pool so far) the "local" set is every CPU, binding would do nothing, and the note says so.
+    Returns (number of CPUs bound to or 0, note for the JSON line)."""
     try:
         import pynvml
         pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(index)
         words = ((os.cpu_count() or 64) + 63) // 64
-        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
-        cpus = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1]
         prev = os.sched_getaffinity(0)
-        cpus = sorted(set(cpus) & prev)
-        if cpus:
-            os.sched_setaffinity(0, cpus)
-            return len(cpus), prev
-    except Exception:
-        pass
-    return 0, None
+
+        def local(i):
+            mask = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(i), words)
+            return {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1} & prev
+        mine = local(index)
+        if not mine:
+            return 0, "NVML reports no local CPUs: no CPU binding"
+        if len(mine) == len(prev):
+            return 0, f"GPU {index} is local to all {len(prev)} CPUs of this process (single NUMA node): no CPU binding"
+        os.sched_setaffinity(0, sorted(mine))
+        return len(mine), f"rank bound to its GPU's {len(mine)} local CPUs (of {len(prev)})"
+    except Exception as e:
+        return 0, f"no CPU binding (NVML affinity unavailable: {type(e).__name__})"
 
 
 # ---- clocks ----------------------------------------------------------------------------------
@@ -146,7 +166,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.stop_flag, self.in_region = index, [], False, False
+        self.index, self.samples, self.stop_flag, self.in_region = index, [], False, None
         self.ok, self.max_mhz = False, None
         try:
             import pynvml
@@ -168,35 +188,30 @@ class ClockSampler(threading.Thread):
                     rs = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     rs = self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                self.samples.append((self.in_region, mhz, rs))
+                try:
+                    pw = self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                except Exception:
+                    pw = None
+                self.samples.append((self.in_region, mhz, rs, pw))
             except Exception:
                 pass
             time.sleep(0.004)
 
-    def summary(self):
+    def mark(self, region):
+        """Name of the region the following samples belong to (None = outside every timed region)."""
+        self.in_region = region
+
+    def summary(self, region="timed"):
         if not self.ok or not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "NVML unavailable"}
-        timed = [s for s in self.samples if s[0]] or self.samples
+        timed = [s for s in self.samples if s[0] == region] or self.samples
         mask = 0
-        for _, _, rs in timed:
+        for _, _, rs, _ in timed:
             mask |= rs
         reasons = sorted(name for bit, name in self.REASONS.items() if mask & bit)
-        return {"sm_mhz": float(np.median([m for _, m, _ in timed])), "sm_max_mhz": self.max_mhz,
-                "reasons": reasons, "samples_in_timed_regions": len([s for s in self.samples if s[0]])}
-
-
-# ---- synthetic audio on the host (reference arm; same recipe as pcmb200_synth_fill) --------------
-def host_synth(rows, n, rate, seed=0x5EED, row0=0):
-    rng = np.random.RandomState(seed & 0xFFFFFFFF)
-    out = np.empty((rows, n), dtype=np.float32)
-    k = np.arange(n, dtype=np.float64)[None, :]
-    for a in range(0, rows, 8192):
-        b = min(rows, a + 8192)
-        s = (row0 + np.arange(a, b))[:, None]
-        f = 110.0 + 7.0 * (s % 512)
-        amp = np.where((s % 8) == 7, 1.2, 0.5)
-        out[a:b] = (amp * np.sin(2 * np.pi * f * k / rate) + 0.05 * rng.uniform(-1, 1, size=(b - a, n))).astype(np.float32)
-    return out
+        return {"sm_mhz": float(np.median([m for _, m, _, _ in timed])), "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "power_w_max": max((p for _, _, _, p in timed if p is not None), default=None),
+                "samples_in_region": len([s for s in self.samples if s[0] == region])}
 
 
 def hbm_peak():
@@ -224,14 +239,26 @@ def workload_name(args, n_in, n_out):
             f"({n_in} in -> {n_out} out), decimate to 16 kHz + int16 encode + framing")
 
 
+def config_dict(args, world, n_in, n_out, sessions_per_gpu, sessions_total):
+    """The `config` object: IDENTICAL for the CUDA arm and the reference arm at the same flags (what is
+    run).  How an arm runs it (buffers, tuning, host threads ...) goes in the line's `arm` object."""
+    return {"workload": workload_name(args, n_in, n_out), "sessions_total": int(sessions_total),
+            "sessions_per_gpu": int(sessions_per_gpu), "rate_hz": RATE, "frame_ms": args.frame_ms,
+            "n_in": n_in, "n_out": n_out, "scaling": args.scaling,
+            "parallelism": f"session-affine shards x{world}, no collectives",
+            "l2": "inputs larger than L2, no flush: the CUDA arm rotates >= 3 distinct tick buffers with a working set "
+                  ">= 2 GB per GPU (L2 is 126 MB); the CPU arm's tick is far larger than the host's last-level cache"}
+
+
 # ---- CPU legs (oracle = the reference's algorithm restated; kind 'port') ---------------------------
-def cpu_time_frames(x, n_in, rate, threads, reps):
+def cpu_time_frames(x, n_in, rate, threads, reps, out=None):
     import ctypes as C
     import oracle
     L = oracle.lib()
     rows = x.shape[0]
     n_out = oracle.resample_len(n_in, rate)
-    out = np.empty((rows, n_out), dtype=np.int16)
+    if out is None:
+        out = np.empty((rows, n_out), dtype=np.int16)
     pi, po = x.ctypes.data_as(C.POINTER(C.c_float)), out.ctypes.data_as(C.POINTER(C.c_int16))
     t0 = time.perf_counter()
     for _ in range(reps):
@@ -241,44 +268,54 @@ def cpu_time_frames(x, n_in, rate, threads, reps):
 
 
 def cpu_baseline_leg(x, n_in, rate, cpu_seconds):
-    """Oracle on this box's host cores over a bounded sample of the workload."""
+    """Oracle on this box's host cores over the WHOLE tick (all rows of x), repeated until about
+    `cpu_seconds` of CPU work are spent.  Returns (record, oracle output of every row)."""
     cores = os.cpu_count() or 1
     rows = x.shape[0]
-    dt1, _ = cpu_time_frames(x[: max(1, rows // 16)], n_in, rate, 1, 1)          # calibrate, 1 thread
-    per_sample_1t = dt1 / (max(1, rows // 16) * n_in)
+    cal = max(1, rows // 64)
+    dt1, _ = cpu_time_frames(x[:cal], n_in, rate, 1, 1)                           # calibrate, 1 thread
+    per_sample_1t = dt1 / (cal * n_in)
     work_one_pass = per_sample_1t * rows * n_in                                   # CPU-seconds per pass
     reps = int(max(1, min(200, round(cpu_seconds / max(work_one_pass, 1e-9)))))
+    cpu_time_frames(x, n_in, rate, cores, 1)                                      # warm (first touch of `out`)
     dt, out = cpu_time_frames(x, n_in, rate, cores, reps)
     return {"value": rows * n_in * reps / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "value_1thread": 1.0 / per_sample_1t,
-            "sample": f"{rows} sessions x {n_in} samples x {reps} passes, oracle/pcm_oracle.c (C restatement of "
-                      f"App.tsx:7-32,281-282; the reference is TypeScript and no JS engine exists on this image), "
-                      f"{cores} threads, same input bits as the GPU run"}, out
+            "sample": f"{rows} sessions x {n_in} samples (the whole tick) x {reps} passes, oracle/pcm_oracle.c (C "
+                      f"restatement of App.tsx:7-32,281-282; the reference is TypeScript and no JS engine exists on "
+                      f"this image), {cores} threads, same input bits as the GPU run"}, out
 
 
 def run_reference(args):
+    """The reference's own CPU path for the same workload: every step converts the full tick (all
+    --sessions sessions) with the C port of App.tsx:7-32,281-282 on all host threads.  Rank 0 only."""
     rank, _, world = dist_env()
     if rank != 0:
         return 0
     import oracle
     oracle.build()
+    world = max(world, args.gpus, 1)
     n_in = int(RATE * args.frame_ms // 1000)
     n_out = oracle.resample_len(n_in, RATE)
-    rows = args.ref_sessions
+    rows = args.ref_sessions or args.sessions
     cores = os.cpu_count() or 1
-    x = host_synth(rows, n_in, RATE)
-    for _ in range(args.warmup):
-        cpu_time_frames(x, n_in, RATE, cores, 1)
-    dt, _ = cpu_time_frames(x, n_in, RATE, cores, args.steps)
+    x = oracle.synth_fill(rows, n_in, RATE, 0x5EED, 0, cores)
+    out = np.empty((rows, n_out), dtype=np.int16)
+    for _ in range(max(args.warmup, 1)):
+        cpu_time_frames(x, n_in, RATE, cores, 1, out)
+    dt, _ = cpu_time_frames(x, n_in, RATE, cores, args.steps, out)
     value = rows * n_in * args.steps / dt
-    sample = (f"each step = {rows} sessions x {n_in} samples (a bounded sample of the 2^20-session tick), "
-              f"oracle/pcm_oracle.c port of App.tsx:7-32,281-282, {cores} host threads")
+    whole = "the whole tick" if rows == args.sessions else f"a bounded sample of the {args.sessions}-session tick"
+    sample = (f"each step = {rows} sessions x {n_in} samples ({whole}), oracle/pcm_oracle.c port of "
+              f"App.tsx:7-32,281-282, {cores} host threads")
+    per_gpu = args.sessions if args.scaling == "weak" else -(-args.sessions // world)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
-            "data": "synthetic sine+noise (host numpy, same recipe as the GPU arm)",
-            "config": {"workload": workload_name(args, n_in, n_out), "reference_runtime":
-                       "Node unavailable on this image: C port of the reference's JS (kind=port)"},
+            "data": "synthetic sine+noise (oracle_synth_fill: the device generator's recipe and noise bits, host libm sine)",
+            "config": config_dict(args, world, n_in, n_out, per_gpu, args.sessions),
+            "arm": {"runtime": "Node unavailable on this image: C port of the reference's JS (kind=port)",
+                    "sessions_per_step": rows, "host_threads": cores},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -294,7 +331,7 @@ def run_b200(args):
     import pcm_frontend
     from pcm_frontend import MEM_DEVICE, MEM_HOST
 
-    bound_cpus, prev_affinity = bind_to_gpu_numa(local_rank) if world > 1 else (0, None)
+    bound_cpus, numa_note = bind_to_gpu_numa(local_rank) if world > 1 else (0, "single rank: no CPU binding")
     ctx = pcm_frontend.Context(local_rank)          # raises if the CUDA library / device is missing
     dist = Dist(world, True, local_rank)
     if args.tune:
@@ -306,8 +343,9 @@ def run_b200(args):
     in_bytes, out_bytes = S * n_in * 4, S * n_out * 2
     algo_bytes = in_bytes + out_bytes                  # 4*N_in + 2*N_out per frame, FIR reads = 0
 
-    # two distinct tick buffers, alternated; each tick (4.7 GB at 2^20 sessions) is >> the 126 MB L2
-    n_buf = 2
+    # distinct tick buffers, rotated; the working set is kept >> the 126 MB L2 (a 2^20-session tick is
+    # 4.7 GB; a 131 072-session shard is 0.59 GB, so small shards rotate more buffers)
+    n_buf = int(min(8, max(3, -(-2_000_000_000 // max(algo_bytes, 1)))))
     d_in = [ctx.device_buffer(in_bytes) for _ in range(n_buf)]
     d_out = [ctx.device_buffer(out_bytes) for _ in range(n_buf)]
     for b in range(n_buf):
@@ -327,21 +365,22 @@ def run_b200(args):
     ctx.sync()
     dist.barrier()
     l0 = ctx.launches
-    sampler.in_region = True
+    sampler.mark("timed")
     ctx.timer_start()
     for i in range(args.steps):
         step(i)
     ms = ctx.timer_stop()
-    sampler.in_region = False
+    sampler.mark(None)
     launches = ctx.launches - l0
     dist.barrier()
     launches_all = int(dist.reduce(float(launches), "sum"))
+    per_rank_ms = dist.gather(ms)
     units, ms_max, value = aggregate(dist, float(S) * n_in * args.steps, ms)
     kernel_ms = ms / max(launches, 1)                  # the timed region holds nothing but these launches
     peak, peak_src = hbm_peak()
     achieved = algo_bytes * (args.steps / max(launches, 1)) / (kernel_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": peak_src,
+                "traffic": None, "traffic_source": None, "peak_source": peak_src,
                 "kernel": kernel_name(args),
                 "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": kernel_ms}
     tr = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu capture
@@ -350,11 +389,32 @@ def run_b200(args):
             t = json.load(open(tr))
             if t.get("sessions") == S and t.get("n_in") == n_in:
                 roofline["traffic"] = t["dram_bytes_per_launch"]
+                roofline["traffic_source"] = ("NOT measured in this run: dram__bytes_read.sum + dram__bytes_write.sum of "
+                                              "the same kernel and shape from the committed ncu capture "
+                                              "(profiles/traffic.json: " + str(t.get("source", "ncu --set full")) + ")")
         except Exception:
             pass
 
+    # ---- sustained: >= 2 s of back-to-back ticks with their own clock record ---------------------
+    sustained = None
+    if args.sustained_seconds > 0:
+        n_s = int(max(args.steps, args.sustained_seconds * 1e3 / max(ms / args.steps, 1e-6)))
+        dist.barrier()
+        sampler.mark("sustained")
+        ctx.timer_start()
+        for i in range(n_s):
+            step(i)
+        ms_s = ctx.timer_stop()
+        sampler.mark(None)
+        _, ms_s_max, v_s = aggregate(dist, float(S) * n_in * n_s, ms_s)
+        gbs = algo_bytes * n_s / (ms_s * 1e-3) / 1e9
+        sustained = {"seconds": ms_s_max * 1e-3, "steps": n_s, "ms_per_step": ms_s_max / n_s, "value": v_s,
+                     "unit": UNIT, "achieved_gbs_rank0": gbs, "frac_rank0": gbs / peak,
+                     "clocks": sampler.summary("sustained")}
+
     # ---- end to end: pinned host buffers through the C-ABI call, H2D + kernel + D2H per step ----
     e2e = None
+    h_in = h_out = None
     if not args.no_e2e:
         h_in = ctx.pinned((S, n_in), np.float32, write_combined=bool(args.wc))
         h_out = ctx.pinned((S, n_out), np.int16)
@@ -363,53 +423,65 @@ def run_b200(args):
             ctx.frames_encode_ptr(h_in.ptr, n_in, h_out.ptr, n_out, S, n_in, RATE, MEM_HOST)
         dist.barrier()
         e2e_steps = args.steps
-        sampler.in_region = True
+        sampler.mark("timed")
         ctx.timer_start()
         for _ in range(e2e_steps):
             ctx.frames_encode_ptr(h_in.ptr, n_in, h_out.ptr, n_out, S, n_in, RATE, MEM_HOST)   # returns when out is on the host
         ms_e = ctx.timer_stop()
-        sampler.in_region = False
+        sampler.mark(None)
         dist.barrier()
         _, ms_e_max, e_val = aggregate(dist, float(S) * n_in * e2e_steps, ms_e)
         e2e = {"value": e_val, "unit": UNIT, "h2d_bytes_per_step": in_bytes, "d2h_bytes_per_step": out_bytes,
                "ms_per_step": ms_e_max / e2e_steps, "steps": e2e_steps,
                "pcie_gbs": (in_bytes + out_bytes) * e2e_steps / (ms_e * 1e-3) / 1e9,
-               "h2d_gbs": in_bytes * e2e_steps / (ms_e * 1e-3) / 1e9}
-        # the device result of tick buffer 0 and the host-path result must be the same bytes
-        chk = d_out[0].download(np.int16, min(S, 4096) * n_out)
-        if not np.array_equal(chk, h_out.array[: min(S, 4096)].reshape(-1)):
-            raise SystemExit("e2e output differs from the device-resident output")
+               "h2d_gbs": in_bytes * e2e_steps / (ms_e * 1e-3) / 1e9,
+               "per_rank_ms": dist.gather(ms_e)}
+        # the device result of tick buffer 0 and the host-path result must be the same bytes (all rows)
+        step(0)
+        ctx.sync()
+        for r0 in range(0, S, 1 << 17):
+            nr = min(1 << 17, S - r0)
+            chk = d_out[0].download(np.int16, nr * n_out, r0 * n_out * 2)
+            if not np.array_equal(chk, h_out.array[r0:r0 + nr].reshape(-1)):
+                raise SystemExit("e2e output differs from the device-resident output")
 
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    # ---- CPU baseline on this box's host cores (rank 0, N=1 only) ----------------------------------
+    # ---- CPU baseline on this box's host cores (rank 0, N=1 only): the whole tick, every row checked
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         import oracle
-        rows = min(S, 1 << 16)
-        x = d_in[0].download(np.float32, rows * n_in).reshape(rows, n_in)
+        if h_in is not None:
+            x = h_in.array                                          # the tick's input bits, already on the host
+        else:
+            x = d_in[0].download(np.float32, S * n_in).reshape(S, n_in)
         cpu, want = cpu_baseline_leg(x, n_in, RATE, args.cpu_seconds)
-        got = d_out[0].download(np.int16, rows * n_out).reshape(rows, n_out)
-        if not np.array_equal(got, want):
-            raise SystemExit("GPU output differs from the oracle on the cpu_baseline sample")
-        cpu["parity_checked_rows"] = rows
+        step(0)
+        ctx.sync()
+        for r0 in range(0, S, 1 << 17):
+            nr = min(1 << 17, S - r0)
+            got = d_out[0].download(np.int16, nr * n_out, r0 * n_out * 2).reshape(nr, n_out)
+            if not np.array_equal(got, want[r0:r0 + nr]):
+                raise SystemExit(f"GPU output differs from the oracle (rows {r0}..{r0 + nr})")
+        if h_out is not None and not np.array_equal(h_out.array, want):
+            raise SystemExit("e2e (host-resident) output differs from the oracle")
+        cpu["parity_checked_rows"] = S
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
                 "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic sine+noise generated on device (pcmb200_synth_fill, seed 0x5EED)",
-                "config": {"workload": workload_name(args, n_in, n_out), "sessions_per_gpu": S,
-                           "sessions_total": int(units / (n_in * args.steps)), "rate_hz": RATE,
-                           "frame_ms": args.frame_ms, "n_in": n_in, "n_out": n_out,
-                           "parallelism": f"session-affine shards x{world}, no collectives",
-                           "numa": f"each rank bound to its GPU's {bound_cpus} local CPUs" if bound_cpus else "no CPU binding",
-                           "l2": f"inputs larger than L2: {n_buf} alternating tick buffers of {algo_bytes / 1e9:.2f} GB each",
-                           "tune": args.tune or "defaults",
-                           "arithmetic": "f32 in, round-toward-zero fp32 product (exact), saturating s16 out; bit-exact vs the f64 reference"},
+                "config": config_dict(args, world, n_in, n_out, S if args.scaling == "weak" else -(-args.sessions // world),
+                                      int(units / (n_in * args.steps))),
+                "arm": {"numa": numa_note,
+                        "l2": f"inputs larger than L2: {n_buf} rotating tick buffers of {algo_bytes / 1e9:.2f} GB each",
+                        "tune": args.tune or "defaults", "sessions_rank0": S,
+                        "arithmetic": "f32 in, round-toward-zero fp32 product (exact), saturating s16 out; bit-exact vs the f64 reference"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all,
-                "clocks": sampler.summary(),
+                "per_rank_ms": per_rank_ms, "sustained": sustained,
+                "clocks": sampler.summary("timed"),
                 "output_samples_per_s": value * n_out / n_in, "device": ctx.device_info()["name"]}
         print(json.dumps(line), flush=True)
     dist.close()

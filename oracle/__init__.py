@@ -55,6 +55,8 @@ def lib() -> C.CDLL:
         L.oracle_aggregator_plan.argtypes = [f64p, C.c_size_t, C.c_double, f64p, u8p]
         L.oracle_keepalive_frame.restype = C.c_size_t
         L.oracle_keepalive_frame.argtypes = [i16p]
+        L.oracle_synth_fill.restype = None
+        L.oracle_synth_fill.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_double, C.c_uint64, C.c_uint64, C.c_int]
         _lib = L
     return _lib
 
@@ -134,4 +136,13 @@ def aggregator_plan(arrival_ms: np.ndarray, desired_ms: float = 60.0, last_send:
 def keepalive_frame() -> np.ndarray:
     out = np.empty(1600, dtype=np.int16)
     lib().oracle_keepalive_frame(_p(out, C.c_int16))
+    return out
+
+
+def synth_fill(rows: int, n: int, rate: float, seed: int = 0x5EED, row0: int = 0, threads: int = 1) -> np.ndarray:
+    """The benchmark's synthetic audio generated on the host: same counter hash as
+    the device generator (identical noise bits), host libm sine (last-bit differences possible)."""
+    out = np.empty((rows, n), dtype=np.float32)
+    if rows and n:
+        lib().oracle_synth_fill(_p(out, C.c_float), n, rows, n, float(rate), seed, row0, threads)
     return out

@@ -255,3 +255,55 @@ ORACLE_API size_t oracle_keepalive_frame(int16_t *out)
     memset(out, 0, 1600 * sizeof(int16_t));
     return 1600;
 }
+
+/* ---- synthetic benchmark input on the host (SURVEY.md 8d recipe) --------------------------------
+ * The same generator as the CUDA library's pcmb200_synth_fill, restated for the host so that
+ * `bench.py --impl reference` can build its 2^20-session tick without touching the GPU library:
+ *   x[n] = A*sin(2*pi*f*n/rate) + 0.05*u,  f = 110 + 7*(session mod 512) Hz,
+ *   A = 1.2 for every 8th session else 0.5,  u ~ U[-1,1) from a counter hash of (seed, session, n).
+ * The hash (and therefore u) is bit-identical to the device's; the sine goes through the host
+ * libm instead of the device's sinpif, so samples can differ from the device's in the last bit.
+ * Not part of the reference: test / measurement infrastructure only. */
+static uint64_t synth_mix64(uint64_t z)
+{
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+struct synth_job { float *out; size_t pitch, r0, r1, n; double rate; uint64_t seed, row0; };
+static void *synth_worker(void *p)
+{
+    struct synth_job *j = (struct synth_job *)p;
+    const float inv_rate = (float)(1.0 / j->rate);
+    for (size_t r = j->r0; r < j->r1; r++) {
+        const uint64_t session = j->row0 + r;
+        const float f = 110.0f + 7.0f * (float)(session & 511u);
+        const float amp = ((session & 7u) == 7u) ? 1.2f : 0.5f;
+        const uint64_t key = synth_mix64(j->seed ^ (session * 0xD1342543DE82EF95ull));
+        float *row = j->out + r * j->pitch;
+        for (size_t k = 0; k < j->n; k++) {
+            const uint64_t h = synth_mix64(key + k);
+            const float u = (float)(uint32_t)(h >> 40) * (1.0f / 8388608.0f) - 1.0f;
+            const float ph = 2.0f * f * (float)k * inv_rate;
+            row[k] = amp * (float)sin(3.14159265358979323846 * (double)ph) + 0.05f * u;
+        }
+    }
+    return NULL;
+}
+ORACLE_API void oracle_synth_fill(float *out, size_t pitch, size_t rows, size_t n, double rate,
+                                  uint64_t seed, uint64_t row0, int threads)
+{
+    if (threads < 1) threads = 1;
+    if ((size_t)threads > rows) threads = rows ? (int)rows : 1;
+    pthread_t *tid = (pthread_t *)malloc(sizeof(pthread_t) * (size_t)threads);
+    struct synth_job *jobs = (struct synth_job *)malloc(sizeof(struct synth_job) * (size_t)threads);
+    for (int t = 0; t < threads; t++) {
+        jobs[t] = (struct synth_job){ out, pitch, rows * (size_t)t / (size_t)threads,
+                                      rows * (size_t)(t + 1) / (size_t)threads, n, rate, seed, row0 };
+        pthread_create(&tid[t], NULL, synth_worker, &jobs[t]);
+    }
+    for (int t = 0; t < threads; t++) pthread_join(tid[t], NULL);
+    free(jobs);
+    free(tid);
+}
