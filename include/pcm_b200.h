@@ -73,6 +73,19 @@ PCMB200_API const char *pcmb200_last_error(const pcmb200_ctx *ctx);
 PCMB200_API int pcmb200_sync(pcmb200_ctx *ctx);
 /* Number of this library's kernels launched through the context so far. */
 PCMB200_API int pcmb200_launch_count(const pcmb200_ctx *ctx, uint64_t *launches);
+/* Capacity up front (ctx_create(device, max_sessions, max_frame_in, ...)).  Sizes the three
+ * staging slots of the host-resident pipeline for batches of up to max_rows frames of up to max_n_in
+ * input / max_n_out output samples, and sets aside max_rate_classes (<= 32) pick-index tables of
+ * max_n_out entries (one per distinct non-integer (rate, frame length) in use, e.g. the 44.1 kHz
+ * family).  After it, pcmb200_frames_encode / _encode_f32_s16 / _resample_to_16k within those limits
+ * call no cudaMalloc, cudaFree or device-wide synchronisation: larger batches are cut into more
+ * slices instead of growing the slots.  Without it the library grows on demand (the first large
+ * batch of a live server then pays an allocation stall).  pcmb200_alloc_stats reports how often the
+ * library allocated / freed device memory and synchronised a stream on its own behalf. */
+PCMB200_API int pcmb200_ctx_reserve(pcmb200_ctx *ctx, uint32_t max_rows, uint32_t max_n_in, uint32_t max_n_out,
+                                    uint32_t max_rate_classes);
+PCMB200_API int pcmb200_alloc_stats(const pcmb200_ctx *ctx, uint64_t *device_mallocs, uint64_t *device_frees,
+                                    uint64_t *stream_syncs);
 /* Name, SM count and total memory of the context's device. */
 PCMB200_API int pcmb200_device_info(const pcmb200_ctx *ctx, char *name, size_t name_cap,
                                     int *sm_count, size_t *total_mem);
@@ -97,6 +110,7 @@ PCMB200_API int pcmb200_pinned_alloc(pcmb200_ctx *ctx, size_t bytes, void **ptr)
  * samples on their way to the GPU).  The device reads them without snooping the CPU caches; host
  * reads of such memory are very slow.  Free with pcmb200_pinned_free. */
 PCMB200_API int pcmb200_pinned_alloc_write_combined(pcmb200_ctx *ctx, size_t bytes, void **ptr);
+/* ctx may be NULL here (page-locked host memory is not tied to a device). */
 PCMB200_API int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr);
 /* Blocking copies on the context's stream. */
 PCMB200_API int pcmb200_memcpy_h2d(pcmb200_ctx *ctx, void *dst_device, const void *src_host, size_t bytes);
@@ -189,7 +203,9 @@ PCMB200_API int pcmb200_wire_is_little_endian(void);
 
 /* ---- per-tick replay --------------------------------------------------------------------------- */
 
-/* A tick whose buffers, shape and rate do not change (the steady state of a fleet: same sessions,
+/* (The graph owns a private copy of its pick table, so it stays valid whatever the context's table
+ * cache does afterwards.)
+ * A tick whose buffers, shape and rate do not change (the steady state of a fleet: same sessions,
  * same frame length every 20 ms) can be recorded once as a CUDA graph and replayed, which removes
  * the per-launch CPU cost that dominates small ticks (config 2: 1.97 MB per tick is 0.3 us of HBM
  * time).  Device-resident buffers only.  The graph is replayed on the context's stream. */
@@ -237,8 +253,10 @@ PCMB200_API int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
  *   - the first call on a device resolves the array's address: make it at start-up, before any
  *     stream capture;
  *   - all calls on a device share the array and it keeps the last call's table: calls whose GPU work
- *     may overlap (issued on different streams) race and must be serialised by the caller; calls on
- *     one stream are ordered by the stream and are safe. */
+ *     may overlap (issued on different streams) race and must be serialised by the caller ON THE GPU:
+ *     the later stream has to wait (cudaStreamWaitEvent) on an event recorded in the earlier stream
+ *     after the earlier call -- calling later on the host is not enough, even for the same frame shape;
+ *     calls on one stream are ordered by the stream and are safe. */
 #define PCMB200_NOALLOC_MAX_OUT 16384u
 PCMB200_API int pcmb200_frames_encode_noalloc(const float *in_device, size_t pitch_in, int16_t *out_device,
                                               size_t pitch_out, uint32_t rows, uint32_t n_in, double in_rate,

@@ -19,10 +19,11 @@ WORKER = textwrap.dedent("""
     args = bench.parse_args(["--gpus", str(world), "--sessions", "1001", "--scaling", sys.argv[1]])
     first, count = bench.sessions_for_rank(args, rank, world)
     # every rank converts ITS sessions only (oracle stands in for the device here) ...
-    x = bench.host_synth(count, 96, 48000.0, row0=first)
+    x = oracle.synth_fill(count, 96, 48000.0, row0=first)
     y = oracle.frames(x, 96, 48000.0)
     # ... and the job-level numbers come from a SUM of units and a MAX of times
     units, ms, value = bench.aggregate(d, float(count) * 96, 10.0 * (rank + 1))
+    assert d.gather(10.0 * (rank + 1)) == [10.0, 20.0]           # per-rank times, in rank order
     cover = d.reduce(float(count), "sum")
     chk = d.reduce(float(np.int64(y.astype(np.int64).sum())), "sum")
     if rank == 0:
@@ -58,9 +59,10 @@ def test_strong_scaling_shards_cover_all_sessions_once():
     assert r["cover"] == 1001 and r["first"] == 0 and r["count"] == 501
     assert r["units"] == 1001 * 96 and r["ms"] == 20.0           # MAX over ranks, not the mean
     assert abs(r["value"] - 1001 * 96 / 0.020) < 1e-6
-    whole = oracle.frames(bench.host_synth(501, 96, 48000.0, row0=0), 96, 48000.0).astype(np.int64).sum() + \
-        oracle.frames(bench.host_synth(500, 96, 48000.0, row0=501), 96, 48000.0).astype(np.int64).sum()
-    assert r["chk"] == float(whole)                               # sharded result == per-shard oracle
+    # the generator is keyed on the global session id, so the two shards are exactly the rows of the
+    # unsharded batch: sharded result == whole-batch oracle
+    whole = oracle.frames(oracle.synth_fill(1001, 96, 48000.0, row0=0), 96, 48000.0).astype(np.int64).sum()
+    assert r["chk"] == float(whole)
 
 
 def test_weak_scaling_gives_every_rank_the_full_session_count():

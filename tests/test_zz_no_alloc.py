@@ -3,7 +3,8 @@ device memory while running (a real-time tick thread that cannot afford cudaMall
 stall; a process whose GPU memory already belongs to another framework's allocator).
 
 It is called through the C ABI on device buffers and must produce exactly the bytes of the existing
-pcmb200_frames_encode (tolerance 0: integer output), on two calls in a row -- the second call reuses
+pcmb200_frames_encode and of the CPU oracle (tolerance 0: integer output), on two calls in a row --
+the second call reuses
 the library's built-in table that the first one filled, then a different frame shape overwrites it.
 The file sorts last so that a run stopped at the first failure has already run every other test; it
 also passes alone in a fresh process (it sets up everything it needs itself)."""
@@ -12,6 +13,7 @@ import ctypes as C
 import numpy as np
 import pytest
 
+import oracle
 import pcm_frontend
 from pcm_frontend import MEM_DEVICE, _capi
 
@@ -46,6 +48,11 @@ def _both(ctx, rng, rows, n_in, rate, pitch_pad=0):
     new = d_new.download(np.int16, rows * pitch_out)
     for d in (d_in, d_ref, d_new):
         d.free()
+    # and against the CPU oracle, not only against the other CUDA entry point: the frames must be the
+    # oracle's bytes and the padding between rows must still hold the 0x11 fill
+    want = np.full((rows, pitch_out), 0x1111, dtype=np.int16)
+    want[:, :n_out] = oracle.frames(x, n_in, rate)
+    assert np.array_equal(new.reshape(rows, pitch_out), want), (rows, n_in, rate, pitch_pad)
     return ref, new
 
 

@@ -29,8 +29,14 @@ struct Lut {
     uint64_t rate_bits = 0;
     uint32_t n_in = 0, n_out = 0;
     uint32_t *dev = nullptr;
+    size_t cap = 0;            // entries `dev` can hold (tables from pcmb200_ctx_reserve are sized up front)
+    bool used = false;         // false: a reserved, still empty table
     std::vector<uint32_t> host;
 };
+
+// How often the library itself allocated, freed or device-synchronised on behalf of a context
+// (pcmb200_alloc_stats): after pcmb200_ctx_reserve these must stand still on the frame path.
+struct AllocStats { uint64_t mallocs = 0, frees = 0, syncs = 0; };
 
 struct Slot {
     cudaStream_t st = nullptr;
@@ -71,6 +77,8 @@ struct pcmb200_ctx {
     Slot slots[kSlots];
     std::vector<Lut> luts;
     Tuning tune;
+    AllocStats stats;
+    bool reserved = false;     // pcmb200_ctx_reserve was called: slices are cut to fit the staging slots
     std::string err;
 };
 
@@ -135,29 +143,66 @@ bool integer_ratio(double rate, uint32_t *R)
     return true;
 }
 
+// Wait for everything this context may have in flight (its stream and the three pipeline streams).
+int ctx_quiesce(pcmb200_ctx *ctx)
+{
+    ctx->stats.syncs++;
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < kSlots; i++) CU(cudaStreamSynchronize(ctx->slots[i].st));
+    return PCMB200_OK;
+}
+
 int get_lut(pcmb200_ctx *ctx, uint32_t n_in, double rate, uint32_t n_out, const uint32_t **dev)
 {
     uint64_t bits;
     std::memcpy(&bits, &rate, 8);
     for (auto &l : ctx->luts)
-        if (l.rate_bits == bits && l.n_in == n_in && l.n_out == n_out) { *dev = l.dev; return PCMB200_OK; }
-    if (ctx->luts.size() >= kMaxLuts) {   // evict the oldest; make sure nothing in flight reads it
-        CU(cudaDeviceSynchronize());
-        CU(cudaFree(ctx->luts.front().dev));
-        ctx->luts.erase(ctx->luts.begin());
+        if (l.used && l.rate_bits == bits && l.n_in == n_in && l.n_out == n_out) { *dev = l.dev; return PCMB200_OK; }
+    // a free table from pcmb200_ctx_reserve that is large enough?
+    Lut *slot = nullptr;
+    for (auto &l : ctx->luts)
+        if (!l.used && l.cap >= n_out) { slot = &l; break; }
+    if (!slot && ctx->luts.size() >= kMaxLuts) {
+        // evict the oldest table in use; nothing of this context may still be reading it.  (Tick graphs
+        // own private copies of their tables, so replays are not affected.)
+        int s = ctx_quiesce(ctx);
+        if (s) return s;
+        size_t victim = 0;
+        while (victim < ctx->luts.size() && !ctx->luts[victim].used) victim++;
+        if (victim == ctx->luts.size()) victim = 0;
+        Lut v = std::move(ctx->luts[victim]);
+        ctx->luts.erase(ctx->luts.begin() + (long)victim);
+        if (v.cap >= n_out) {            // reuse its memory
+            v.used = false;
+            ctx->luts.push_back(std::move(v));
+            slot = &ctx->luts.back();
+        } else {
+            ctx->stats.frees++;
+            CU(cudaFree(v.dev));
+        }
     }
-    Lut l;
-    l.rate_bits = bits;
-    l.n_in = n_in;
-    l.n_out = n_out;
-    try { l.host.resize(n_out); } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "index table: host allocation failed"); }
-    build_index_table(n_in, rate, n_out, l.host.data());
-    CU(cudaMalloc((void **)&l.dev, (size_t)n_out * 4));
-    // synchronous upload: the table is tiny and is built once per (rate, frame length)
-    cudaError_t e = cudaMemcpy(l.dev, l.host.data(), (size_t)n_out * 4, cudaMemcpyHostToDevice);
-    if (e != cudaSuccess) { cudaFree(l.dev); return fail(ctx, PCMB200_ERR_CUDA, std::string("index table upload: ") + cudaGetErrorString(e)); }
-    *dev = l.dev;
-    ctx->luts.push_back(std::move(l));
+    if (!slot) {
+        Lut l;
+        ctx->stats.mallocs++;
+        CU(cudaMalloc((void **)&l.dev, (size_t)(n_out ? n_out : 1) * 4));
+        l.cap = n_out ? n_out : 1;
+        try { ctx->luts.push_back(std::move(l)); } catch (const std::bad_alloc &) { cudaFree(l.dev); return fail(ctx, PCMB200_ERR_NOMEM, "index table: host allocation failed"); }
+        slot = &ctx->luts.back();
+    }
+    try { slot->host.resize(n_out); } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "index table: host allocation failed"); }
+    build_index_table(n_in, rate, n_out, slot->host.data());
+    // synchronous upload (the table is tiny and is built once per (rate, frame length)); complete when
+    // the call returns, so every later launch on any stream sees it
+    cudaError_t e = cudaMemcpy(slot->dev, slot->host.data(), (size_t)n_out * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) return fail(ctx, PCMB200_ERR_CUDA, std::string("index table upload: ") + cudaGetErrorString(e));
+    slot->rate_bits = bits;
+    slot->n_in = n_in;
+    slot->n_out = n_out;
+    slot->used = true;
+    *dev = slot->dev;
+    // keep tables in use ordered oldest-first for eviction: move this one to the back
+    const size_t at = (size_t)(slot - ctx->luts.data());
+    if (at + 1 != ctx->luts.size()) std::rotate(ctx->luts.begin() + (long)at, ctx->luts.begin() + (long)at + 1, ctx->luts.end());
     return PCMB200_OK;
 }
 
@@ -322,7 +367,8 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
 
 // Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
 int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
-                  size_t pitch_out, uint32_t rows, uint32_t n_in, double rate, uint32_t n_out)
+                  size_t pitch_out, uint32_t rows, uint32_t n_in, double rate, uint32_t n_out,
+                  const uint32_t *lut_override = nullptr)
 {
     if (rows == 0 || n_out == 0) return PCMB200_OK;
     uint32_t R = 0;
@@ -387,8 +433,8 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
         return PCMB200_OK;
     }
 
-    const uint32_t *lut = nullptr;
-    if (!is_int) {
+    const uint32_t *lut = lut_override;
+    if (!is_int && !lut) {
         int s = get_lut(ctx, n_in, rate, n_out, &lut);
         if (s) return s;
     }
@@ -425,16 +471,20 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
 int slot_reserve(pcmb200_ctx *ctx, Slot &s, size_t in_bytes, size_t out_bytes)
 {
     if (s.in_cap < in_bytes) {
+        ctx->stats.syncs++;
         CU(cudaStreamSynchronize(s.st));
-        if (s.d_in) CU(cudaFree(s.d_in));
+        if (s.d_in) { ctx->stats.frees++; CU(cudaFree(s.d_in)); }
         s.d_in = nullptr; s.in_cap = 0;
+        ctx->stats.mallocs++;
         CU(cudaMalloc(&s.d_in, in_bytes));
         s.in_cap = in_bytes;
     }
     if (s.out_cap < out_bytes) {
+        ctx->stats.syncs++;
         CU(cudaStreamSynchronize(s.st));
-        if (s.d_out) CU(cudaFree(s.d_out));
+        if (s.d_out) { ctx->stats.frees++; CU(cudaFree(s.d_out)); }
         s.d_out = nullptr; s.out_cap = 0;
+        ctx->stats.mallocs++;
         CU(cudaMalloc(&s.d_out, out_bytes));
         s.out_cap = out_bytes;
     }
@@ -464,6 +514,16 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
     // keep every slice a whole number of 256-output warp tiles so it needs one launch, not two
     size_t tile_rows = 256;
     for (size_t a = n_out, b = 256; b;) { size_t t = a % b; a = b; b = t; tile_rows = 256 / a; }
+    if (ctx->reserved) {
+        // capacity was fixed up front (pcmb200_ctx_reserve): cut slices to fit the staging slots instead
+        // of growing them; only a single row larger than a slot still grows it (and is counted)
+        size_t cap_rows = rps;
+        for (int i = 0; i < kSlots; i++) {
+            const size_t fit_in = ctx->slots[i].in_cap / (dpi * 4), fit_out = dpo ? ctx->slots[i].out_cap / (dpo * 2) : cap_rows;
+            cap_rows = std::min(cap_rows, std::min(fit_in, fit_out));
+        }
+        if (cap_rows >= 1) rps = cap_rows;
+    }
     if (rps > tile_rows) rps -= rps % tile_rows;
     if (rps < 1) rps = 1;
     if (rps > rows) rps = rows;
@@ -483,28 +543,44 @@ int frames_host(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out
         for (int i = 0; i < used; i++) CU(cudaStreamWaitEvent(ctx->slots[i].st, ctx->ev_fork, 0));
     }
 
-    for (size_t k = 0; k < n_slices; k++) {
+    // A failure in the middle of the pipeline must not leave the slot streams detached from the
+    // context's stream (a later pcmb200_sync would then miss their work): remember the first error,
+    // stop issuing, and always run the join below.
+    int status = PCMB200_OK;
+    std::string why;
+    auto step_failed = [&](cudaError_t e, const char *what) {
+        if (e == cudaSuccess) return false;
+        status = e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA;
+        why = std::string(what) + ": " + cudaGetErrorString(e);
+        return true;
+    };
+    for (size_t k = 0; k < n_slices && status == PCMB200_OK; k++) {
         Slot s = ctx->slots[k % kSlots];
         if (single) s.st = ctx->stream;
         const size_t r0 = k * rps;
         const uint32_t nr = (uint32_t)((rows - r0 < rps) ? rows - r0 : rps);
         const float *hin = in + r0 * pitch_in;
         int16_t *hout = out + r0 * pitch_out;
+        cudaError_t e;
         if (pitch_in == dpi || nr == 1)
-            CU(cudaMemcpyAsync(s.d_in, hin, ((size_t)(nr - 1) * dpi + n_in) * 4, cudaMemcpyHostToDevice, s.st));
+            e = cudaMemcpyAsync(s.d_in, hin, ((size_t)(nr - 1) * dpi + n_in) * 4, cudaMemcpyHostToDevice, s.st);
         else
-            CU(cudaMemcpy2DAsync(s.d_in, dpi * 4, hin, pitch_in * 4, (size_t)n_in * 4, nr, cudaMemcpyHostToDevice, s.st));
-        int st = launch_frames(ctx, s.st, (const float *)s.d_in, dpi, (int16_t *)s.d_out, dpo, nr, n_in, rate, n_out);
-        if (st) return st;
+            e = cudaMemcpy2DAsync(s.d_in, dpi * 4, hin, pitch_in * 4, (size_t)n_in * 4, nr, cudaMemcpyHostToDevice, s.st);
+        if (step_failed(e, "frames_host: upload")) break;
+        status = launch_frames(ctx, s.st, (const float *)s.d_in, dpi, (int16_t *)s.d_out, dpo, nr, n_in, rate, n_out);
+        if (status) { why = ctx->err; break; }
         if (pitch_out == dpo || nr == 1)
-            CU(cudaMemcpyAsync(hout, s.d_out, ((size_t)(nr - 1) * dpo + n_out) * 2, cudaMemcpyDeviceToHost, s.st));
+            e = cudaMemcpyAsync(hout, s.d_out, ((size_t)(nr - 1) * dpo + n_out) * 2, cudaMemcpyDeviceToHost, s.st);
         else
-            CU(cudaMemcpy2DAsync(hout, pitch_out * 2, s.d_out, dpo * 2, (size_t)n_out * 2, nr, cudaMemcpyDeviceToHost, s.st));
+            e = cudaMemcpy2DAsync(hout, pitch_out * 2, s.d_out, dpo * 2, (size_t)n_out * 2, nr, cudaMemcpyDeviceToHost, s.st);
+        if (step_failed(e, "frames_host: download")) break;
     }
     for (int i = 0; i < used && !single; i++) {
-        CU(cudaEventRecord(ctx->slots[i].done, ctx->slots[i].st));
-        CU(cudaStreamWaitEvent(ctx->stream, ctx->slots[i].done, 0));
+        cudaError_t e = cudaEventRecord(ctx->slots[i].done, ctx->slots[i].st);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->slots[i].done, 0);
+        if (status == PCMB200_OK) step_failed(e, "frames_host: join");
     }
+    if (status != PCMB200_OK) return fail(ctx, status, why);
     return PCMB200_OK;
 }
 
@@ -631,6 +707,50 @@ int pcmb200_device_info(const pcmb200_ctx *c, char *name, size_t name_cap, int *
     return PCMB200_OK;
 }
 
+int pcmb200_ctx_reserve(pcmb200_ctx *ctx, uint32_t max_rows, uint32_t max_n_in, uint32_t max_n_out, uint32_t max_rate_classes)
+{
+    NEED(ctx, "pcmb200_ctx_reserve: ctx is NULL");
+    NEED(max_rows > 0 && max_n_in > 0 && max_n_out > 0, "pcmb200_ctx_reserve: sizes must be positive");
+    NEED(max_rate_classes <= kMaxLuts, "pcmb200_ctx_reserve: at most 32 rate classes");
+    CU(cudaSetDevice(ctx->device));
+    // staging slots of the host-resident pipeline: one slice each, the slice being the tuned slice
+    // size or the whole batch if that is smaller (same arithmetic as frames_host)
+    const size_t dpi = round_up(max_n_in, 8), dpo = round_up(max_n_out, 8);
+    size_t rps = ctx->tune.slice_bytes / (dpi * 4);
+    if (rps < 1) rps = 1;
+    if (rps > max_rows) rps = max_rows;
+    size_t in_bytes = rps * dpi * 4, out_bytes = rps * dpo * 2;
+    // slot 0 also stages the stand-alone resampleTo16k (Float32 out)
+    const size_t out0 = std::max(out_bytes, (size_t)max_n_out * 4);
+    for (int i = 0; i < kSlots; i++) {
+        int s = slot_reserve(ctx, ctx->slots[i], in_bytes, i == 0 ? out0 : out_bytes);
+        if (s) return s;
+    }
+    // pick-index tables: max_rate_classes tables of max_n_out entries, filled on first use
+    size_t have = 0;
+    for (auto &l : ctx->luts) if (l.cap >= max_n_out) have++;
+    for (; have < max_rate_classes && ctx->luts.size() < kMaxLuts; have++) {
+        Lut l;
+        ctx->stats.mallocs++;
+        CU(cudaMalloc((void **)&l.dev, (size_t)max_n_out * 4));
+        l.cap = max_n_out;
+        try { l.host.reserve(max_n_out); ctx->luts.insert(ctx->luts.begin(), std::move(l)); }
+        catch (const std::bad_alloc &) { cudaFree(l.dev); return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_ctx_reserve: host allocation failed"); }
+    }
+    ctx->reserved = true;
+    return PCMB200_OK;
+}
+
+int pcmb200_alloc_stats(const pcmb200_ctx *c, uint64_t *device_mallocs, uint64_t *device_frees, uint64_t *stream_syncs)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(c, "pcmb200_alloc_stats: ctx is NULL");
+    if (device_mallocs) *device_mallocs = c->stats.mallocs;
+    if (device_frees) *device_frees = c->stats.frees;
+    if (stream_syncs) *stream_syncs = c->stats.syncs;
+    return PCMB200_OK;
+}
+
 int pcmb200_resample_len(size_t n_in, double in_rate, size_t *n_out)
 {
     pcmb200_ctx *ctx = nullptr;
@@ -685,8 +805,9 @@ int pcmb200_pinned_alloc_write_combined(pcmb200_ctx *ctx, size_t bytes, void **p
 
 int pcmb200_pinned_free(pcmb200_ctx *ctx, void *ptr)
 {
-    NEED(ctx, "pcmb200_pinned_free: ctx is NULL");
-    CU(cudaSetDevice(ctx->device));
+    // ctx may be NULL: page-locked host memory is not tied to a device, and a finalizer may run
+    // after its context is gone (node/addon.cc free_pinned)
+    if (ctx) CU(cudaSetDevice(ctx->device));
     if (ptr) CU(cudaFreeHost(ptr));
     return PCMB200_OK;
 }
@@ -967,6 +1088,8 @@ struct pcmb200_tick_graph {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     uint64_t kernels = 0;
+    uint32_t *table = nullptr;   // the graph's OWN copy of the pick table (non-integer ratios): the context's
+                                 // table cache may evict and free its copy while the graph is still alive
 };
 
 extern "C" int pcmb200_tick_graph_create(pcmb200_ctx *ctx, const float *in, size_t pitch_in, int16_t *out,
@@ -981,31 +1104,43 @@ extern "C" int pcmb200_tick_graph_create(pcmb200_ctx *ctx, const float *in, size
     NEED(rows > 0 && n_out > 0 && in && out, "pcmb200_tick_graph_create: empty tick or NULL buffer");
     NEED((pitch_in >= n_in && pitch_out >= n_out) || rows == 1, "pcmb200_tick_graph_create: pitch too small");
     CU(cudaSetDevice(ctx->device));
-    uint32_t R;
-    if (!integer_ratio(in_rate, &R)) {   // the table upload must not happen inside the capture
-        const uint32_t *lut;
-        s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
-        if (s) return s;
-    }
     pcmb200_tick_graph *g = new (std::nothrow) pcmb200_tick_graph();
     if (!g) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_tick_graph_create: host allocation failed");
+    uint32_t R;
+    if (!integer_ratio(in_rate, &R)) {
+        // The recorded kernels keep a raw pointer to the pick table, so the graph gets a private copy
+        // that lives exactly as long as the graph (allocated and uploaded before the capture starts).
+        std::vector<uint32_t> host;
+        try { host.resize(n_out); } catch (const std::bad_alloc &) { delete g; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_tick_graph_create: host allocation failed"); }
+        build_index_table(n_in, in_rate, n_out, host.data());
+        cudaError_t e = cudaMalloc((void **)&g->table, n_out * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMemcpy(g->table, host.data(), n_out * sizeof(uint32_t), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) {
+            if (g->table) cudaFree(g->table);
+            delete g;
+            cudaGetLastError();
+            return fail(ctx, e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA,
+                        std::string("pcmb200_tick_graph_create: pick table: ") + cudaGetErrorString(e));
+        }
+    }
     const uint64_t before = ctx->launches;
-    CU(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
-    s = launch_frames(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, in_rate, (uint32_t)n_out);
-    cudaError_t e = cudaStreamEndCapture(ctx->stream, &g->graph);
+    cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) {
+        if (g->table) cudaFree(g->table);
+        delete g;
+        return fail(ctx, PCMB200_ERR_CUDA, std::string("cudaStreamBeginCapture: ") + cudaGetErrorString(e));
+    }
+    s = launch_frames(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, in_rate, (uint32_t)n_out, g->table);
+    e = cudaStreamEndCapture(ctx->stream, &g->graph);
     g->kernels = ctx->launches - before;
     ctx->launches = before;   // recorded, not run
+    if (s == PCMB200_OK && e == cudaSuccess && g->graph) e = cudaGraphInstantiate(&g->exec, g->graph, 0);
     if (s || e != cudaSuccess || !g->graph) {
         if (g->graph) cudaGraphDestroy(g->graph);
+        if (g->table) cudaFree(g->table);
         delete g;
         cudaGetLastError();
-        return s ? s : fail(ctx, PCMB200_ERR_CUDA, std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
-    }
-    e = cudaGraphInstantiate(&g->exec, g->graph, 0);
-    if (e != cudaSuccess) {
-        cudaGraphDestroy(g->graph);
-        delete g;
-        return fail(ctx, PCMB200_ERR_CUDA, std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        return s ? s : fail(ctx, PCMB200_ERR_CUDA, std::string("pcmb200_tick_graph_create: capture/instantiate: ") + cudaGetErrorString(e));
     }
     *graph = g;
     return PCMB200_OK;
@@ -1028,6 +1163,7 @@ extern "C" int pcmb200_tick_graph_destroy(pcmb200_ctx *ctx, pcmb200_tick_graph *
     CU(cudaStreamSynchronize(ctx->stream));
     if (graph->exec) cudaGraphExecDestroy(graph->exec);
     if (graph->graph) cudaGraphDestroy(graph->graph);
+    if (graph->table) cudaFree(graph->table);
     delete graph;
     return PCMB200_OK;
 }
@@ -1419,8 +1555,11 @@ extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, 
 //     (entries past the current frame's length are stale and are never read; nothing in it has to
 //     start at zero, every entry a launch reads is rewritten first when the frame shape changes).
 //     Two calls whose GPU work can overlap (issued on different streams) race on it: serialise
-//     them.  Calls on one stream are ordered by the stream (the table upload of the second waits
-//     for the kernel of the first) and are safe.
+//     them ON THE GPU -- the later stream must wait (cudaStreamWaitEvent) on an event recorded in
+//     the earlier stream after the earlier call; merely calling later is not enough, also when both
+//     calls use the same frame shape (the second then skips the upload and would read the table
+//     while the first stream's upload may still be in flight).  Calls on one stream are ordered by
+//     the stream (the table upload of the second waits for the kernel of the first) and are safe.
 //   * The device that holds `in` and `out` must be the calling thread's current device.
 namespace {
 
@@ -1467,7 +1606,7 @@ extern "C" int pcmb200_frames_encode_noalloc(const float *in, size_t pitch_in, i
     CU(cudaGetDevice(&dev));
     NEED(dev >= 0 && dev < kNoallocMaxDevices, "pcmb200_frames_encode_noalloc: device ordinal above 63");
 
-    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    std::unique_lock<std::mutex> lock(g_noalloc_mutex);
     NoallocDevice &d = g_noalloc_dev[dev];
     if (!d.table) {   // once per device, with that device current
         uint32_t *p = nullptr;
@@ -1502,6 +1641,7 @@ extern "C" int pcmb200_frames_encode_noalloc(const float *in, size_t pitch_in, i
     else
         k_pick_encode<4, false><<<grid, block, 0, st>>>(in, pitch_in, out, pitch_out, n_in, (uint32_t)n_out, d.table, 0, n_pairs);
     CU(cudaGetLastError());
+    lock.unlock();   // the wait below concerns this device only: do not hold up callers on other devices
     if (wait) CU(cudaStreamSynchronize(st));
     return PCMB200_OK;
 }

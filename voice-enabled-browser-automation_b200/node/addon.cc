@@ -165,6 +165,11 @@ void async_execute(napi_env, void *data)
 {
     AsyncJob *j = static_cast<AsyncJob *>(data);
     std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    if (!g_ctx) {   // the environment is shutting down (cleanup ran first): fail the job, touch nothing
+        j->status = PCMB200_ERR_INVALID;
+        j->error = "pcm_b200: the addon's context was destroyed (environment shutting down)";
+        return;
+    }
     j->status = pcmb200_frames_encode(g_ctx, j->in, j->n_in, j->out, j->n_out, j->rows, j->n_in, j->rate, PCMB200_MEM_HOST, nullptr);
     if (j->status != PCMB200_OK) j->error = pcmb200_last_error(g_ctx);
 }
@@ -249,7 +254,15 @@ napi_value ResampleLen(napi_env env, napi_callback_info info)
     return r;
 }
 
-void free_pinned(napi_env, void *data, void *) { pcmb200_pinned_free(g_ctx, data); }
+// GC finalizer of a pinned ArrayBuffer.  It can run on the main thread while a worker is inside the
+// context (which records errors in it), and after cleanup() has destroyed the context: take the same
+// lock as every other user, and let the library free without a context then (ctx == NULL is allowed
+// for pcmb200_pinned_free: page-locked host memory does not belong to a device).
+void free_pinned(napi_env, void *data, void *)
+{
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    pcmb200_pinned_free(g_ctx, data);
+}
 
 // allocPinnedFloat32(n) / allocPinnedInt16(n): typed arrays over page-locked memory, so JS fills
 // H2D-ready buffers and receives D2H results without a staging copy.
@@ -264,11 +277,14 @@ napi_value alloc_pinned(napi_env env, napi_callback_info info, napi_typedarray_t
         return nullptr;
     }
     void *p = nullptr;
-    if (throw_status(env, pcmb200_pinned_alloc(g_ctx, (size_t)n * elem, &p))) return nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_ctx_mutex);
+        if (throw_status(env, pcmb200_pinned_alloc(g_ctx, (size_t)n * elem, &p))) return nullptr;
+    }
     napi_value ab = nullptr, ta = nullptr;
     if (napi_create_external_arraybuffer(env, p, (size_t)n * elem, free_pinned, nullptr, &ab) != napi_ok ||
         napi_create_typedarray(env, t, (size_t)n, ab, 0, &ta) != napi_ok) {
-        pcmb200_pinned_free(g_ctx, p);
+        free_pinned(env, p, nullptr);
         napi_throw_error(env, "PCMB200_NAPI", "could not wrap pinned memory");
         return nullptr;
     }
@@ -277,8 +293,11 @@ napi_value alloc_pinned(napi_env env, napi_callback_info info, napi_typedarray_t
 napi_value AllocPinnedFloat32(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_float32_array, 4); }
 napi_value AllocPinnedInt16(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_int16_array, 2); }
 
+// Environment teardown.  Waits (on the lock) for a conversion that is still running on a worker
+// thread, then destroys the context; jobs that start later see g_ctx == NULL and reject.
 void cleanup(void *)
 {
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
     pcmb200_ctx_destroy(g_ctx);
     g_ctx = nullptr;
 }

@@ -36,6 +36,8 @@ SYMBOLS = {
     "pcmb200_sync": (_int, [_vp]),
     "pcmb200_launch_count": (_int, [_vp, _P(_u64)]),
     "pcmb200_device_info": (_int, [_vp, C.c_char_p, _sz, _P(_int), _P(_sz)]),
+    "pcmb200_ctx_reserve": (_int, [_vp, _u32, _u32, _u32, _u32]),
+    "pcmb200_alloc_stats": (_int, [_vp, _P(_u64), _P(_u64), _P(_u64)]),
     "pcmb200_resample_len": (_int, [_sz, _dbl, _P(_sz)]),
     "pcmb200_index_table": (_int, [_sz, _dbl, _sz, _vp]),
     "pcmb200_device_alloc": (_int, [_vp, _sz, _P(_vp)]),

@@ -155,6 +155,20 @@ class Context:
         check(self._L.pcmb200_launch_count(self.handle, C.byref(n)), self.handle)
         return int(n.value)
 
+    def reserve(self, max_rows: int, max_n_in: int, max_n_out: Optional[int] = None, max_rate_classes: int = 4):
+        """Capacity up front (pcmb200_ctx_reserve): after this, host-resident calls within the limits
+        neither allocate nor free device memory."""
+        if max_n_out is None:
+            max_n_out = max_n_in
+        check(self._L.pcmb200_ctx_reserve(self.handle, int(max_rows), int(max_n_in), int(max_n_out), int(max_rate_classes)),
+              self.handle)
+
+    @property
+    def alloc_stats(self) -> dict:
+        m, f, s = C.c_uint64(0), C.c_uint64(0), C.c_uint64(0)
+        check(self._L.pcmb200_alloc_stats(self.handle, C.byref(m), C.byref(f), C.byref(s)), self.handle)
+        return {"device_mallocs": int(m.value), "device_frees": int(f.value), "stream_syncs": int(s.value)}
+
     def device_info(self) -> dict:
         name = C.create_string_buffer(256)
         sm, mem = C.c_int(0), C.c_size_t(0)
