@@ -161,18 +161,26 @@ PCMB200_API int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in_de
  * flushes the session's WHOLE buffer as one frame, pcm16 = floatTo16BitPCM(resampleTo16k(buf, rate))
  * (:281-282), and resets buffer and lastSend (:286-287).  The wall clock is injected: arrival_ms[i]
  * is performance.now() at quantum i.  Sessions of one aggregator share the capture rate.
- *   max_frame_quanta  longest frame, in quanta (a push that would exceed it is rejected whole)
- *   max_push_quanta   most quanta in one push;   max_out_samples_per_push  output arena (host path) */
+ * Session state, buffers and the flush plan of every push live on the GPU (no host threads).
+ *   quantum           samples per quantum, a multiple of 4 (the AudioWorklet quantum is 128)
+ *   max_frame_quanta  longest frame, in quanta (a push that would exceed it is rejected whole); one frame
+ *                     must fit on chip: max_frame_quanta * (quantum + 4) * 4 bytes <= 200 KB
+ *   max_push_quanta   most quanta in one push;   max_out_samples_per_push  output arena (host path)
+ * A rejected push (unknown session id, over-long buffer, more frames than max_frames, output too small)
+ * returns an error and leaves every session exactly as it was. */
 typedef struct pcmb200_aggregator pcmb200_aggregator;
 PCMB200_API int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
                                           double desired_ms, uint32_t max_frame_quanta, uint32_t max_push_quanta,
                                           size_t max_out_samples_per_push, pcmb200_aggregator **agg);
 PCMB200_API int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *agg);
-/* Initial state / stop() of the reference (App.tsx:148-157, :325-330): empty buffer, lastSend = now. */
+/* Initial state / stop() of the reference (App.tsx:148-157, :325-330): empty buffer, lastSend = now.
+ * Enqueued on the context's stream (ordered with the pushes); _range resets `count` sessions at once. */
 PCMB200_API int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t session, double now_ms);
-/* Level meter of the aggregated sessions (App.tsx:267-271): when enabled, the quanta of every
- * flushed frame go through rms = sqrt(sum(x*x)/quantum), level = Math.max(rms, level * 0.85) in
- * arrival order (binary64, bit-identical to the reference's arithmetic).  get_levels copies the
+PCMB200_API int pcmb200_aggregator_reset_range(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t first_session,
+                                               uint32_t count, double now_ms);
+/* Level meter of the aggregated sessions (App.tsx:267-271): when enabled (before the first push), the
+ * quanta of every flushed frame go through rms = sqrt(sum(x*x)/quantum), level = Math.max(rms, level * 0.85)
+ * in arrival order (binary64, bit-identical to the reference's arithmetic).  get_levels copies the
  * current level of `count` sessions to the host (waits for the pushes enqueued so far).  The level
  * lags the reference's by the quanta still waiting in a session's buffer. */
 PCMB200_API int pcmb200_aggregator_set_meter(pcmb200_ctx *ctx, pcmb200_aggregator *agg, int enabled);
@@ -180,13 +188,25 @@ PCMB200_API int pcmb200_aggregator_get_levels(pcmb200_ctx *ctx, pcmb200_aggregat
                                               uint32_t count, double *levels_host);
 /* Append n_quanta quanta, in arrival order (quantum i belongs to sessions[i], samples + i*quantum),
  * and convert every frame that flushes.  Frame f (in flush order) is frame_len[f] int16 samples of
- * session frame_session[f] at out + frame_offset[f] (offsets are multiples of 8 samples).
- * Host `out`: returns when the frames are on the host.  Device `out`: asynchronous (pcmb200_sync). */
+ * session frame_session[f] at out + frame_offset[f]; offsets are multiples of 8 samples, so
+ * out_capacity must hold every frame rounded up to a multiple of 8 samples.
+ * sessions / arrival_ms / the frame arrays are HOST arrays here; samples and out are host or device
+ * memory (samples_mem / out_mem).  Returns when the frames and the frame arrays are complete. */
 PCMB200_API int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t n_quanta,
                                         const uint32_t *sessions, const double *arrival_ms, const float *samples,
                                         int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
                                         uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
                                         uint32_t max_frames, uint32_t *n_frames);
+/* The same with EVERYTHING in device memory (a producer on the GPU: a decoder, a mixer): nothing
+ * crosses PCIe but the 24-byte outcome.  Asynchronous on the context's stream; the frame arrays may
+ * be NULL.  pcmb200_aggregator_wait waits for the push, returns its status and the number of frames /
+ * output samples (padded total); one push may be pending per aggregator. */
+PCMB200_API int pcmb200_aggregator_push_device(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t n_quanta,
+                                               const uint32_t *sessions_device, const double *arrival_ms_device,
+                                               const float *samples_device, int16_t *out_device, size_t out_capacity,
+                                               uint32_t *frame_session_device, uint32_t *frame_len_device,
+                                               unsigned long long *frame_offset_device, uint32_t max_frames);
+PCMB200_API int pcmb200_aggregator_wait(pcmb200_ctx *ctx, pcmb200_aggregator *agg, uint32_t *n_frames, size_t *out_samples);
 
 /* ---- wire egress helpers ------------------------------------------------------------------------ */
 

@@ -97,3 +97,144 @@ def test_aggregator_rejects_out_of_range_session(ctx):
     frames = agg.push(np.array([1], np.uint32), np.array([70.0]), x[:1])
     assert len(frames) == 1 and frames[0][1].size == 42
     agg.close()
+
+
+def _session_frames(x, t, rate, last0=0.0):
+    """Oracle frames of one session: x [nq, 128] quanta, t [nq] arrival times."""
+    flush, last = oracle.aggregator_plan(t, 60.0, last0)
+    frames, start = [], 0
+    for q in np.nonzero(flush)[0]:
+        buf = x[start:q + 1].reshape(1, -1)
+        frames.append(oracle.frames(buf, buf.shape[1], rate)[0])
+        start = q + 1
+    return frames, start, last
+
+
+@pytest.mark.parametrize("rate", [48000, 44100])
+def test_aggregator_65536_sessions_vs_oracle(ctx, rate):
+    """The device-side planner at scale: 65 536 sessions, three pushes of jittered quanta (sessions
+    interleaved at random inside a push, some sessions skipping a push, buffers carried from push to
+    push), every flushed frame and every level compared with the oracle."""
+    rng = np.random.RandomState(int(rate) // 100)
+    S, q_ms = 65536, 128e3 / rate
+    per_push = (9, 11, 8)                                  # quanta per session per push (~60 ms flushes span pushes)
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=40, max_push_quanta=S * 11, max_out_samples=S * 1100)
+    agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
+    start_t = 5.0 * rng.rand(S)
+    period = q_ms + rng.uniform(-0.3, 0.3, S)             # each session's own quantum period
+    audio, times, got = [], [], {}
+    done = np.zeros(S, np.int64)                           # quanta sent so far per session
+    for p, m in enumerate(per_push):
+        active = rng.rand(S) > (0.02 if p else 0.0)       # a few sessions skip later pushes
+        sess = np.repeat(np.nonzero(active)[0].astype(np.uint32), m)
+        k = np.tile(np.arange(m), int(active.sum())) + done[sess]
+        t = start_t[sess] + (k + 1) * period[sess]
+        order = np.lexsort((sess, t))                      # arrival order: by time, sessions interleaved
+        sess, t, k = sess[order], t[order], k[order]
+        x = (rng.uniform(-1.1, 1.1, size=(sess.size, 128)) * rng.uniform(0.05, 1, size=(sess.size, 1))).astype(np.float32)
+        audio.append((sess, k, x)); times.append(t)
+        done[active] += m
+        for s, pcm in agg.push(sess, t, x):
+            got.setdefault(s, []).append(pcm)
+    levels = agg.levels(0, S)
+    agg.close()
+    # regroup the audio per session in arrival order
+    all_s = np.concatenate([a[0] for a in audio]); all_k = np.concatenate([a[1] for a in audio])
+    all_x = np.concatenate([a[2] for a in audio]); all_t = np.concatenate(times)
+    order = np.lexsort((all_k, all_s))
+    all_s, all_x, all_t = all_s[order], all_x[order], all_t[order]
+    bounds = np.searchsorted(all_s, np.arange(S + 1))
+    n_frames = 0
+    for s in range(S):
+        a, b = bounds[s], bounds[s + 1]
+        want, flushed_q, _ = _session_frames(all_x[a:b], all_t[a:b], rate)
+        have = got.get(s, [])
+        assert len(have) == len(want), (s, len(have), len(want))
+        for u, v in zip(have, want):
+            assert u.size == v.size and np.array_equal(u, v), s
+        n_frames += len(want)
+        if s % 16 == 0:                                    # levels: every 16th session (the oracle loop is Python)
+            want_lv = oracle.level_meter(all_x[a:a + flushed_q].reshape(-1))[-1] if flushed_q else 0.0
+            assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], (s, levels[s], want_lv)
+    assert n_frames >= 0.9 * S                            # ~75 ms of audio per session: one flush each, a few skipped
+
+
+def test_aggregator_capacity_is_checked_on_the_padded_total(ctx):
+    """frames start on 8-sample boundaries, so the output must hold every frame rounded up to
+    8 samples.  A capacity equal to the exact, unpadded total is refused cleanly (nothing is written
+    past it, the session is untouched); the padded total is accepted."""
+    import ctypes as C
+    from pcm_frontend._capi import check, MEM_HOST
+    L = pcm_frontend.load()
+    agg = pcm_frontend.Aggregator(ctx, 4, 48000, max_frame_quanta=32, max_push_quanta=64, max_out_samples=4096)
+    agg.reset_range(0, 4, 0.0)
+    x = (np.arange(23 * 128, dtype=np.float32).reshape(23, 128) % 97) / 97.0
+    t = (np.arange(23) + 1) * (128e3 / 48000)             # the 23rd quantum arrives at 61.3 ms -> 981 outputs
+    sess = np.zeros(23, np.uint32)
+    out = np.full(984 + 64, 0x1111, np.int16)
+    fs, fl, fo = np.empty(8, np.uint32), np.empty(8, np.uint32), np.empty(8, np.uint64)
+    nf = C.c_uint32(0)
+
+    def push(cap):
+        return L.pcmb200_aggregator_push(ctx.handle, agg.handle, 23, sess.ctypes.data, t.ctypes.data, x.ctypes.data, MEM_HOST,
+                                         out.ctypes.data, cap, MEM_HOST, fs.ctypes.data, fl.ctypes.data, fo.ctypes.data, 8, C.byref(nf))
+    assert push(981) == pcm_frontend._capi.ERR_CAPACITY
+    assert (out == 0x1111).all()
+    check(push(984), ctx.handle)
+    assert nf.value == 1 and fl[0] == 981 and fo[0] == 0
+    assert np.array_equal(out[:981], oracle.frames(x.reshape(1, -1), 23 * 128, 48000)[0]) and (out[984:] == 0x1111).all()
+    agg.close()
+
+
+def test_aggregator_device_resident_push_and_wait(ctx):
+    """pcmb200_aggregator_push_device: ids, times, quanta, frames and frame arrays all in device memory."""
+    rng = np.random.RandomState(77)
+    S, nq, rate = 1000, 25, 48000
+    n = S * nq
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=n, max_out_samples=16)
+    agg.reset_range(0, S, 0.0)
+    sess = np.tile(np.arange(S, dtype=np.uint32), nq)
+    t = np.repeat((np.arange(nq) + 1) * (128e3 / rate), S)
+    x = rng.uniform(-1, 1, size=(n, 128)).astype(np.float32)
+    d = {k: ctx.device_buffer(v) for k, v in dict(s=n * 4, t=n * 8, x=n * 512, o=S * 984 * 2, fs=n * 4, fl=n * 4, fo=n * 8).items()}
+    d["s"].upload(sess); d["t"].upload(t); d["x"].upload(x)
+    agg.push_device(n, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984, d["fs"].ptr, d["fl"].ptr, d["fo"].ptr, n)
+    with pytest.raises(pcm_frontend.PcmError):            # one push may be pending
+        agg.push_device(n, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984)
+    nf, ns = agg.wait()
+    assert nf == S and ns == S * 984                       # 23 quanta flush (61.3 ms), quanta 24 and 25 stay buffered
+    fs, fl, fo = d["fs"].download(np.uint32, S), d["fl"].download(np.uint32, S), d["fo"].download(np.uint64, S)
+    assert (fs == np.arange(S)).all() and (fl == 981).all() and (fo == np.arange(S) * 984).all()
+    got = d["o"].download(np.int16, S * 984).reshape(S, 984)[:, :981]
+    xs = x.reshape(nq, S, 128).transpose(1, 0, 2)
+    want = oracle.frames(np.ascontiguousarray(xs[:, :23].reshape(S, 23 * 128)), 23 * 128, rate, threads=4)
+    assert np.array_equal(got, want)
+    # second push: 21 more quanta per session -> the 2 buffered quanta + 21 new ones flush as 23 again
+    t2 = np.repeat((np.arange(nq, nq + 21) + 1) * (128e3 / rate), S)
+    x2 = rng.uniform(-1, 1, size=(S * 21, 128)).astype(np.float32)
+    d["t"].upload(t2); d["x"].upload(x2)
+    agg.push_device(S * 21, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984, None, None, None, n)
+    nf, ns = agg.wait()
+    assert nf == S
+    got = d["o"].download(np.int16, S * 984).reshape(S, 984)[:, :981]
+    x2s = x2.reshape(21, S, 128).transpose(1, 0, 2)
+    frame = np.concatenate([xs[:, 23:25], x2s], axis=1).reshape(S, 23 * 128)
+    assert np.array_equal(got, oracle.frames(np.ascontiguousarray(frame), 23 * 128, rate, threads=4))
+    # too small an output: rejected, and the state is unchanged (the same push then succeeds)
+    t3 = np.repeat((np.arange(nq + 21, nq + 44) + 1) * (128e3 / rate), S)
+    d["t"].upload(t3)
+    x3 = rng.uniform(-1, 1, size=(S * 23, 128)).astype(np.float32)
+    d["x"].upload(x3)
+    agg.push_device(S * 23, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984 - 1)
+    with pytest.raises(pcm_frontend.PcmError) as ei:
+        agg.wait()
+    assert ei.value.status == pcm_frontend._capi.ERR_CAPACITY
+    agg.push_device(S * 23, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984)
+    assert agg.wait() == (S, S * 984)
+    got = d["o"].download(np.int16, S * 984).reshape(S, 984)[:, :981]
+    x3s = x3.reshape(23, S, 128).transpose(1, 0, 2).reshape(S, 23 * 128)
+    assert np.array_equal(got, oracle.frames(np.ascontiguousarray(x3s), 23 * 128, rate, threads=4))
+    agg.close()
+    for b in d.values():
+        b.free()

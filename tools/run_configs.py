@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Measures BASELINE.json configs 1, 2, 3 and 5 on one B200 (config 4 is bench.py itself).
 
-    python voice-enabled-browser-automation_b200/tools/run_configs.py --out gpurun_out/configs.json
+    python tools/run_configs.py --out gpurun_out/configs.json
 
 Every GPU figure is timed with CUDA events on the context's stream after warm-up; CPU figures are
 the oracle port (oracle/pcm_oracle.c) on this box's host cores, on the same input bits.
@@ -17,8 +17,8 @@ import time
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-ROOT = os.path.dirname(os.path.dirname(HERE))
-sys.path.insert(0, os.path.dirname(HERE))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, os.path.join(ROOT, "voice-enabled-browser-automation_b200"))
 sys.path.insert(0, ROOT)
 import oracle  # noqa: E402  (measurement baseline + checker only)
 import pcm_frontend  # noqa: E402
@@ -168,7 +168,7 @@ def config5(ctx):
     return res
 
 
-def meter(ctx, n_in, S):
+def meter(ctx, n_in, S, reps=20):
     """8f next-1: frames + fused level meter vs frames alone on the same dense batch."""
     n_out = n_in // 3
     nq = n_in // 128
@@ -187,8 +187,8 @@ def meter(ctx, n_in, S):
     def fused():
         di, do = bufs[k["i"] % 2]; k["i"] += 1
         ctx.frames_encode_meter_ptr(di.ptr, n_in, do.ptr, n_out, S, n_in, 48000, st.ptr, None)
-    ms_plain = timed(ctx, plain, 20)
-    ms_fused = timed(ctx, fused, 20)
+    ms_plain = timed(ctx, plain, reps)
+    ms_fused = timed(ctx, fused, reps)
     algo = S * (n_in * 4 + n_out * 2)
     algo_m = algo + S * 16          # + level state read and written
     for di, do in bufs:
@@ -201,46 +201,70 @@ def meter(ctx, n_in, S):
             "in_samples_per_s": S * n_in / (ms_fused * 1e-3)}
 
 
-def aggregator(ctx, S=65536, rate=48000):
+def aggregator(ctx, S=65536, rate=48000, meter=False):
     """8f next-2: S sessions, every push carries 23 quanta per session (61.3 ms of 48 kHz audio), so
-    every session flushes one 2944-sample frame per push.  Device-resident quanta and frames, C ABI
-    called directly: `host_ms` is the scheduler + enqueue time of the call, `total_ms` includes the GPU."""
-    L = pcm_frontend.load()
-    from pcm_frontend._capi import check
+    every session flushes one 2944-sample frame per push.  Everything device-resident
+    (pcmb200_aggregator_push_device): `enqueue_ms` is the host time of the call, `total_ms` runs from
+    the call to the end of pcmb200_aggregator_wait (plan + convert on the GPU, 24 bytes read back).
+    Also timed: the same push through pcmb200_aggregator_push with HOST session/arrival arrays."""
     nq, n = 23, S * 23
-    h = C.c_void_p()
-    check(L.pcmb200_aggregator_create(ctx.handle, S, float(rate), 128, 60.0, 32, n, S * 984, C.byref(h)), ctx.handle)
-    for s in range(S):
-        L.pcmb200_aggregator_reset_session(ctx.handle, h, s, 0.0)
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=n, max_out_samples=S * 984)
+    if meter:
+        agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
     sessions = np.tile(np.arange(S, dtype=np.uint32), nq)                  # quantum-major arrival order
     base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
     d_samples = ctx.device_buffer(n * 128 * 4)
     ctx.synth_fill(d_samples.ptr, 128, n, 128, rate)
     d_out = ctx.device_buffer(S * 984 * 2)
-    fs, fl, fo = np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(n, np.uint64)
-    nf = C.c_uint32(0)
-    host, total = [], []
-    for p in range(5):
+    d_sess, d_arr = ctx.device_buffer(n * 4), ctx.device_buffer(n * 8)
+    d_fs, d_fl, d_fo = ctx.device_buffer(n * 4), ctx.device_buffer(n * 4), ctx.device_buffer(n * 8)
+    d_sess.upload(sessions)
+    enq, total = [], []
+    for p in range(6):
+        d_arr.upload(base + p * nq * (128e3 / rate))
+        ctx.sync()
+        t0 = time.perf_counter()
+        agg.push_device(n, d_sess.ptr, d_arr.ptr, d_samples.ptr, d_out.ptr, S * 984, d_fs.ptr, d_fl.ptr, d_fo.ptr, n)
+        t1 = time.perf_counter()
+        nf, ns = agg.wait()
+        t2 = time.perf_counter()
+        enq.append(t1 - t0); total.append(t2 - t0)
+        assert nf == S and ns == S * 984, (nf, ns)
+    fl, fo, fs = d_fl.download(np.uint32, S), d_fo.download(np.uint64, S), d_fs.download(np.uint32, S)
+    assert (fl == 981).all() and (fs == np.arange(S)).all()
+    # every frame against the oracle: session s holds quanta s, s+S, ... of the push
+    x = d_samples.download(np.float32, n * 128).reshape(nq, S, 128).transpose(1, 0, 2).reshape(S, nq * 128)
+    want = oracle.frames(np.ascontiguousarray(x), nq * 128, rate, threads=os.cpu_count() or 1)
+    got = d_out.download(np.int16, S * 984).reshape(S, 984)[:, :981]
+    assert np.array_equal(got, want)
+    # the same push with host metadata arrays (pageable numpy): pcmb200_aggregator_push
+    L = pcm_frontend.load()
+    from pcm_frontend._capi import check
+    fs_h, fl_h, fo_h = np.empty(n, np.uint32), np.empty(n, np.uint32), np.empty(n, np.uint64)
+    nf_c = C.c_uint32(0)
+    host_meta = []
+    for p in range(6, 9):
         arr = base + p * nq * (128e3 / rate)
         ctx.sync()
         t0 = time.perf_counter()
-        check(L.pcmb200_aggregator_push(ctx.handle, h, n, sessions.ctypes.data, arr.ctypes.data, d_samples.ptr, MEM_DEVICE,
-                                        d_out.ptr, S * 984, MEM_DEVICE, fs.ctypes.data, fl.ctypes.data, fo.ctypes.data, n,
-                                        C.byref(nf)), ctx.handle)
-        t1 = time.perf_counter()
-        ctx.sync()
-        t2 = time.perf_counter()
-        host.append(t1 - t0); total.append(t2 - t0)
-    assert nf.value == S and fl[0] == 981
-    x = d_samples.download(np.float32, n * 128).reshape(n, 128)
-    want = oracle.frames(x[0::S][:nq].reshape(1, -1), nq * 128, rate)[0]
-    assert np.array_equal(d_out.download(np.int16, 981, int(fo[0]) * 2), want)
-    L.pcmb200_aggregator_destroy(ctx.handle, h)
-    d_samples.free(); d_out.free()
-    return {"config": "next-2 device aggregator (device-resident quanta and frames)", "sessions": S, "quanta_per_push": n,
-            "host_ms": min(host[1:]) * 1e3, "total_ms": min(total[1:]) * 1e3, "in_samples_per_s": n * 128 / min(total[1:]),
-            "realtime_sessions_at_48k": n * 128 / min(total[1:]) / rate,
-            "note": "the per-quantum flush plan runs on up to 16 host threads (contiguous session blocks)"}
+        check(L.pcmb200_aggregator_push(ctx.handle, agg.handle, n, sessions.ctypes.data, arr.ctypes.data, d_samples.ptr, MEM_DEVICE,
+                                        d_out.ptr, S * 984, MEM_DEVICE, fs_h.ctypes.data, fl_h.ctypes.data, fo_h.ctypes.data, n,
+                                        C.byref(nf_c)), ctx.handle)
+        host_meta.append(time.perf_counter() - t0)
+        assert nf_c.value == S
+    agg.close()
+    for d in (d_samples, d_out, d_sess, d_arr, d_fs, d_fl, d_fo):
+        d.free()
+    t = min(total[1:])
+    # bytes the push has to move: every quantum read once (512 B), every frame written once
+    algo = n * 512 + S * 981 * 2
+    return {"config": "next-2 device aggregator (device-resident quanta, ids, times and frames)", "meter": meter, "sessions": S,
+            "quanta_per_push": n, "enqueue_ms": min(enq[1:]) * 1e3, "total_ms": t * 1e3, "in_samples_per_s": n * 128 / t,
+            "realtime_sessions_at_48k": n * 128 / t / rate, "algorithmic_gbs": algo / t / 1e9, "frac_of_measured_peak": algo / t / 1e9 / PEAK,
+            "host_metadata_push_ms": min(host_meta) * 1e3, "frames_checked_against_oracle": S,
+            "note": "flush plan, frame list and conversion all on the GPU (agg_kernels.cuh); total_ms is host wall clock from "
+                    "the call to the end of pcmb200_aggregator_wait"}
 
 
 def main():
@@ -249,25 +273,39 @@ def main():
     ctx = pcm_frontend.Context(0)
     results = {"device": ctx.device_info(), "host_cores": os.cpu_count(), "hbm_peak_gbs": PEAK, "configs": []}
     ap.add_argument("--only-meter", action="store_true")
+    ap.add_argument("--meter-once", type=int, default=0, help="n_in: a short frames+meter run of that frame length (for ncu)")
+    ap.add_argument("--tune", default="", help="comma list key=value for pcmb200_tune")
     ap.add_argument("--sweep-meter", action="store_true")
     args = ap.parse_args()
+    if args.tune:
+        ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
+    if args.meter_once:
+        print(json.dumps(meter(ctx, args.meter_once, (1 << 19) if args.meter_once < 2000 else (1 << 17), reps=3)), flush=True)
+        return
     if args.sweep_meter:
-        for kb in (12, 20, 28, 40, 56, 80, 104):
+        # kernel 2c: tile height (via meter_tile_kb: 32/64/96/128 KB = 8/16/24/32 rows of 960 samples),
+        # stages and grid cap; meter_kernel=0 is the old kernel 2b for comparison
+        pts = [dict(meter_kernel=0, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0)]
+        for kb in (32, 64, 96, 128):
             for stg in (1, 2):
-                for bps in (0, 1, 2, 3, 4, 6):
-                    try:
-                        ctx.tune(meter_tile_kb=kb, meter_stages=stg, blocks_per_sm=bps)
-                        for n_in, S in ((960, 1 << 19), (2944, 1 << 17)):
-                            r = meter(ctx, n_in, S)
-                            print(json.dumps(dict(kb=kb, stages=stg, bps=bps, n_in=n_in, ms=r["frames_plus_meter_ms"], frac=r["frac_of_measured_peak"])), flush=True)
-                    except Exception as e:
-                        print("skip", kb, stg, bps, e)
+                for bps in (0, 1, 2, 3, 4):
+                    if kb * stg > 200 or (bps and bps * kb * stg > 220):
+                        continue
+                    pts.append(dict(meter_kernel=1, meter_tile_kb=kb, meter_stages=stg, blocks_per_sm=bps))
+        for pt in pts:
+            try:
+                ctx.tune(**pt)
+                for n_in, S in ((960, 1 << 19), (2944, 1 << 17)):
+                    r = meter(ctx, n_in, S)
+                    print(json.dumps(dict(pt, n_in=n_in, ms=r["frames_plus_meter_ms"], frac=r["frac_of_measured_peak"])), flush=True)
+            except Exception as e:
+                print("skip", pt, e, flush=True)
         return
     if args.only_meter:
-        for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx)):
+        for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)

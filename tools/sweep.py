@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Tuning sweep of the device-resident frame kernels (one process, buffers allocated once).
 
-    python voice-enabled-browser-automation_b200/tools/sweep.py [--sessions N] [--out file.json]
+    python tools/sweep.py [--sessions N] [--out file.json]
 
 For every (rate, frame) workload and every tuning point it times K launches with CUDA events on
 the context's stream and reports algorithmic GB/s (4*N_in + 2*N_out bytes per frame) and the
@@ -14,7 +14,7 @@ import os
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.join(os.path.dirname(HERE), "voice-enabled-browser-automation_b200"))
 import pcm_frontend  # noqa: E402
 
 
@@ -25,7 +25,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--quick", action="store_true")
     args = ap.parse_args()
-    root = os.path.dirname(os.path.dirname(HERE))
+    root = os.path.dirname(HERE)
     try:
         peak = json.load(open(os.path.join(root, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:

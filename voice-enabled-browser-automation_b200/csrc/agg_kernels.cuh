@@ -1,0 +1,628 @@
+// agg_kernels.cuh -- device-side capture aggregator (App.tsx:148-157, :273-288), sm_100a.
+//
+// The reference appends 128-sample quanta to a per-session buffer and, when a quantum arrives with
+// now - lastSend >= desiredMs, converts the whole buffer and resets it.  Round 1 ran that per-session
+// state machine on host threads (5.2 of 5.7 ms per 65 536-session push).  Here the whole push is
+// planned on the GPU; the host only enqueues a fixed sequence of kernels and reads three numbers back.
+//
+// One push of n quanta (quantum i belongs to sessions[i], arrived at arrival[i]):
+//   1 k_agg_count    count[s]++ per quantum; the first toucher of a session appends it to `touched`
+//   2 scan A         exclusive scan of count[touched[k]] -> where each touched session's index list starts
+//   3 k_agg_scatter  sorted[cursor[s]++] = i   (atomic, so the order inside a session is arbitrary ...)
+//   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
+//                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
+//                    writes scratch (the session's new state, per-quantum flush marks and ring slots).
+//   5 scan B         over quanta: frame index and output offset of every flush, in flush order
+//                    (= ascending i); its apply pass also emits the caller's frame arrays.
+//   6 k_agg_convert  every flushed frame: its quanta are staged into shared memory with one bulk copy
+//                    each -- from the session's ring (quanta carried over from earlier pushes) or
+//                    straight from the push (never written to the ring at all) -- then picked, encoded,
+//                    stored; with the meter on, each quantum's rms is computed from the staged copy.
+//   7 k_agg_levels   level = max(rms, level * 0.85) along each session's flushed quanta, in order
+//   8 k_agg_append   quanta that did not flush go to their session's ring (with their rms)
+//   9 k_agg_commit   fill / lastSend take their new values; per-push counters are cleared
+// Steps 6-9 look at the push's status word first: if any check failed (unknown session, a buffer
+// longer than max_frame_quanta, too many frames, output too small) they change nothing, which IS the
+// rollback -- the plan so far lives only in scratch.
+#pragma once
+#include "pcm_kernels.cuh"
+
+namespace pcmb200 {
+
+enum : uint32_t {
+    AGG_ST_BAD_SESSION = 1u,     // a session id >= max_sessions
+    AGG_ST_FRAME_TOO_LONG = 2u,  // a session's buffer would exceed max_frame_quanta
+    AGG_ST_TOO_MANY_FRAMES = 4u, // more flushed frames than max_frames
+    AGG_ST_OUT_TOO_SMALL = 8u    // flushed frames exceed the output capacity
+};
+
+struct AggCtl {                  // lives in device memory; copied to the host after every push
+    uint32_t status;
+    uint32_t n_touched;
+    uint32_t n_frames;
+    uint32_t n_leftover;         // quanta of this push that went to a ring
+    unsigned long long out_total;   // output samples incl. the padding of every frame to 8 samples
+};
+
+struct AggFrameDesc {
+    uint32_t session;
+    uint32_t nq;                 // quanta in the frame
+    uint32_t ring_count;         // of which the first ring_count come from the session's ring
+    uint32_t pos;                // the rest: sorted[pos], sorted[pos + 1], ...
+};
+
+struct AggGeom {
+    uint32_t max_sessions, quantum, half_quanta;
+    uint32_t stride;             // integer ratio R, or 0 when picks come from the table
+    double desired_ms;
+};
+
+// ---- 1: count ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sessions, uint32_t *__restrict__ count,
+            uint32_t *__restrict__ touched, AggCtl *__restrict__ ctl)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t s = __ldg(sessions + i);
+    if (s >= max_sessions) { atomicOr(&ctl->status, AGG_ST_BAD_SESSION); return; }
+    if (atomicAdd(count + s, 1u) == 0u) touched[atomicAdd(&ctl->n_touched, 1u)] = s;
+}
+
+// ---- scans (two u32 channels, 2048 items per block) --------------------------------------------------------
+// A three-pass scan: per-block totals, one block scans the totals, per-block rescan + apply.  The
+// length is read on the device (n_touched is not known to the host); blocks past it do nothing.
+constexpr int kScanThreads = 256, kScanItems = 8, kScanBlock = kScanThreads * kScanItems;
+
+struct ScanArgs {
+    // mode 0 (scan A): item k < ctl->n_touched, a = count[touched[k]]
+    // mode 1 (scan B): item i < n, a = fl_nq[i] != 0, b = padded output length of that frame
+    uint32_t n;
+    const uint32_t *touched, *count;
+    const uint32_t *fl_nq, *nout_of;
+    const AggCtl *ctl;
+};
+
+template <int MODE>
+__device__ __forceinline__ void scan_load(const ScanArgs &a, uint32_t idx, uint32_t len, uint32_t &va, uint32_t &vb)
+{
+    va = 0; vb = 0;
+    if (idx >= len) return;
+    if (MODE == 0) {
+        va = a.count[a.touched[idx]];
+    } else {
+        // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
+        if (a.ctl->status != 0u) return;
+        const uint32_t nq = a.fl_nq[idx];
+        if (nq) { va = 1u; vb = (__ldg(a.nout_of + nq) + 7u) & ~7u; }
+    }
+}
+template <int MODE>
+__device__ __forceinline__ uint32_t scan_len(const ScanArgs &a) { return MODE == 0 ? a.ctl->n_touched : a.n; }
+
+// exclusive block scan of one value per thread (256 threads); returns the block total in `total`
+__device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_sums, uint32_t &total)
+{
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= (uint32_t)d) inc += o;
+    }
+    if (lane == 31u) warp_sums[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; w++) {
+        const uint32_t ws = warp_sums[w];
+        if ((uint32_t)w < warp) base += ws;
+        tot += ws;
+    }
+    __syncthreads();
+    total = tot;
+    return base + inc - v;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kScanThreads)
+k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b)
+{
+    __shared__ uint32_t ws[kScanThreads / 32];
+    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t base = blockIdx.x * kScanBlock;
+    if (base >= len) return;
+    uint32_t sa = 0, sb = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        uint32_t va, vb;
+        scan_load<MODE>(a, base + threadIdx.x * kScanItems + k, len, va, vb);
+        sa += va; sb += vb;
+    }
+    uint32_t ta, tb;
+    block_exscan(sa, ws, ta);
+    block_exscan(sb, ws, tb);
+    if (threadIdx.x == 0) { sums_a[blockIdx.x] = ta; sums_b[blockIdx.x] = tb; }
+}
+
+// One block turns the per-block totals into exclusive offsets (64-bit for channel b: sample counts).
+// MODE 1 also checks the two capacities and publishes n_frames / out_total.
+template <int MODE>
+__global__ void __launch_bounds__(1024)
+k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b, unsigned long long *__restrict__ offs_b,
+            AggCtl *__restrict__ ctl, uint32_t max_frames, unsigned long long out_capacity)
+{
+    __shared__ unsigned long long carry_a, carry_b;
+    __shared__ unsigned long long wsum_a[32], wsum_b[32];
+    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t nb = (len + kScanBlock - 1) / kScanBlock;
+    if (threadIdx.x == 0) { carry_a = 0; carry_b = 0; }
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (uint32_t b0 = 0; b0 < nb; b0 += 1024u) {
+        const uint32_t b = b0 + threadIdx.x;
+        unsigned long long va = b < nb ? sums_a[b] : 0ull, vb = b < nb ? sums_b[b] : 0ull;
+        unsigned long long ia = va, ib = vb;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long oa = __shfl_up_sync(0xFFFFFFFFu, ia, d), ob = __shfl_up_sync(0xFFFFFFFFu, ib, d);
+            if (lane >= (uint32_t)d) { ia += oa; ib += ob; }
+        }
+        if (lane == 31u) { wsum_a[warp] = ia; wsum_b[warp] = ib; }
+        __syncthreads();
+        unsigned long long ba = carry_a, bb = carry_b, ta = 0, tb = 0;
+        for (uint32_t w = 0; w < 32u; w++) {
+            if (w < warp) { ba += wsum_a[w]; bb += wsum_b[w]; }
+            ta += wsum_a[w]; tb += wsum_b[w];
+        }
+        if (b < nb) { sums_a[b] = (uint32_t)(ba + ia - va); offs_b[b] = bb + ib - vb; }
+        __syncthreads();
+        if (threadIdx.x == 0) { carry_a += ta; carry_b += tb; }
+        __syncthreads();
+    }
+    if (MODE == 1 && threadIdx.x == 0) {
+        ctl->n_frames = (uint32_t)carry_a;
+        ctl->out_total = carry_b;
+        uint32_t st = 0;
+        if (carry_a > max_frames) st |= AGG_ST_TOO_MANY_FRAMES;
+        if (carry_b > out_capacity) st |= AGG_ST_OUT_TOO_SMALL;
+        if (st) atomicOr(&ctl->status, st);
+    }
+}
+
+struct ScanApplyA { uint32_t *cursor; };
+struct ScanApplyB {
+    const uint32_t *sessions, *fl_ring, *fl_pos;
+    uint32_t *frame_session, *frame_len;
+    unsigned long long *frame_offset;
+    AggFrameDesc *fdesc;
+    unsigned long long *fdesc_off;
+    uint32_t max_frames;
+};
+
+template <int MODE, typename Apply>
+__global__ void __launch_bounds__(kScanThreads)
+k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, Apply ap)
+{
+    __shared__ uint32_t ws[kScanThreads / 32];
+    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t base = blockIdx.x * kScanBlock;
+    if (base >= len) return;
+    if (MODE == 1 && a.ctl->status != 0u) return;      // rejected push: nothing to emit
+    uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        scan_load<MODE>(a, base + threadIdx.x * kScanItems + k, len, va[k], vb[k]);
+        sa += va[k]; sb += vb[k];
+    }
+    uint32_t ta, tb;
+    uint32_t ea = block_exscan(sa, ws, ta) + sums_a[blockIdx.x];
+    unsigned long long eb = (unsigned long long)block_exscan(sb, ws, tb) + offs_b[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        const uint32_t idx = base + threadIdx.x * kScanItems + k;
+        if (idx < len) {
+            if constexpr (MODE == 0) {
+                ap.cursor[a.touched[idx]] = ea;          // where this session's index list starts
+            } else {
+                if (va[k] && ea < ap.max_frames) {        // quantum idx flushes frame number ea
+                    const uint32_t nq = a.fl_nq[idx], s = ap.sessions[idx];
+                    if (ap.frame_session) ap.frame_session[ea] = s;
+                    if (ap.frame_len) ap.frame_len[ea] = __ldg(a.nout_of + nq);
+                    if (ap.frame_offset) ap.frame_offset[ea] = eb;
+                    ap.fdesc[ea] = AggFrameDesc{s, nq, ap.fl_ring[idx], ap.fl_pos[idx]};
+                    ap.fdesc_off[ea] = eb;
+                }
+            }
+        }
+        ea += va[k]; eb += vb[k];
+    }
+}
+
+// ---- 3: scatter --------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted,
+              const AggCtl *__restrict__ ctl)
+{
+    if (ctl->status != 0u) return;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    sorted[atomicAdd(cursor + __ldg(sessions + i), 1u)] = i;
+}
+
+// ---- 4: walk -------------------------------------------------------------------------------------------------
+// In-place heap sort for the rare session with a long list in one push (short lists use insertion sort).
+__device__ inline void sift_down(uint32_t *a, uint32_t start, uint32_t end)
+{
+    uint32_t root = start;
+    while (2u * root + 1u < end) {
+        uint32_t child = 2u * root + 1u;
+        if (child + 1u < end && a[child] < a[child + 1u]) child++;
+        if (a[root] >= a[child]) return;
+        const uint32_t t = a[root]; a[root] = a[child]; a[child] = t;
+        root = child;
+    }
+}
+__device__ inline void sort_indices(uint32_t *a, uint32_t m)
+{
+    if (m <= 48u) {
+        for (uint32_t i = 1; i < m; i++) {
+            const uint32_t v = a[i];
+            uint32_t j = i;
+            while (j > 0 && a[j - 1] > v) { a[j] = a[j - 1]; j--; }
+            a[j] = v;
+        }
+        return;
+    }
+    for (uint32_t s = m / 2; s-- > 0;) sift_down(a, s, m);
+    for (uint32_t e = m; e-- > 1;) {
+        const uint32_t t = a[0]; a[0] = a[e]; a[e] = t;
+        sift_down(a, 0, e);
+    }
+}
+
+struct AggWalkOut {
+    uint32_t *fl_nq, *fl_ring, *fl_pos;   // [n] per quantum: frame length in quanta if it flushes (else 0), ...
+    uint32_t *dst_slot;                   // [n] ring slot of a quantum that does not flush, else 0xFFFFFFFF
+    uint32_t *new_fill, *flushed;         // [touched] new fill; push quanta of the session that flushed
+    double *new_last;                     // [touched] new lastSend
+};
+
+__global__ void __launch_bounds__(128)
+k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count,
+           const uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted, const uint32_t *__restrict__ fill,
+           const double *__restrict__ last_send, AggWalkOut o, AggCtl *__restrict__ ctl)
+{
+    if (ctl->status != 0u) return;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= ctl->n_touched) return;
+    const uint32_t s = touched[k], m = count[s], base = cursor[s] - m;
+    uint32_t *list = sorted + base;
+    sort_indices(list, m);
+    const uint32_t c0 = fill[s];
+    uint32_t f = c0, ring_cnt = c0, frame_start = 0;
+    double last = last_send[s];
+    for (uint32_t j = 0; j < m; j++) {
+        const uint32_t i = list[j];
+        if (f >= g.half_quanta) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
+        f++;
+        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+        const double now = arrival[i];
+        if (now - last >= g.desired_ms) {
+            o.fl_nq[i] = f; o.fl_ring[i] = ring_cnt; o.fl_pos[i] = base + frame_start;
+            f = 0; ring_cnt = 0; frame_start = j + 1u;
+            last = now;                                                    // App.tsx:287
+        } else {
+            o.fl_nq[i] = 0u;
+        }
+    }
+    // quanta after the last flush stay in the session's buffer: behind what was there if nothing flushed
+    const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
+    for (uint32_t j = 0; j < m; j++) o.dst_slot[list[j]] = j >= frame_start ? first_slot + (j - frame_start) : 0xFFFFFFFFu;
+    o.new_fill[k] = f;
+    o.new_last[k] = last;
+    o.flushed[k] = frame_start;
+    if (m > frame_start) atomicAdd(&ctl->n_leftover, m - frame_start);
+}
+
+// ---- 6: convert -------------------------------------------------------------------------------------------------
+// A CTA takes G consecutive frames at a time.  Their quanta are packed into `slots` of shared memory
+// (slot pitch = quantum + 4 floats: 33 sixteen-byte units for the 128-sample quantum, odd, so that the
+// eight lanes of an LDS.128 phase -- eight consecutive quanta -- hit eight different bank groups), one
+// bulk copy per quantum.  Then all threads pick + encode + store; with METER each of the first T lanes
+// accumulates its quantum's sum of squares in sample order (same arithmetic as kernel 2c).
+struct AggConvertArgs {
+    const float *samples;            // the push's quanta
+    const float *ring;               // [max_sessions][half_quanta][quantum]
+    const uint32_t *sorted;
+    const AggFrameDesc *fdesc;
+    const unsigned long long *fdesc_off;
+    const uint32_t *nout_of;         // [half_quanta + 1] output length of a frame of nq quanta
+    const uint32_t *lut;             // pick table shared by every frame length (prefix property), or null
+    int16_t *out;
+    double *rms_at;                  // [n] rms of push quantum sorted[p] at rms_at[p] (METER)
+    const AggCtl *ctl;
+    uint32_t G;                      // frames per CTA step
+    uint32_t magic_q;                // ceil(2^32 / quantum), 0 for quantum == 1
+    int out_aligned16;               // `out` is 16-byte aligned: 128-bit stores
+    int hint;
+};
+
+template <bool METER>
+__global__ void __launch_bounds__(256)
+k_agg_convert(AggGeom g, AggConvertArgs a)
+{
+    if (a.ctl->status != 0u) return;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t Q = g.quantum, pitch = Q + 4u;
+    const uint32_t max_slots = a.G * g.half_quanta;
+    float *arena = reinterpret_cast<float *>(smem_raw);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (((size_t)max_slots * pitch * 4u + 127u) & ~(size_t)127u));
+    uint32_t *qstart = reinterpret_cast<uint32_t *>(bar + 2);        // [G + 1] first slot of each frame
+    uint32_t *cstart = qstart + (a.G + 1u);                           // [G + 1] first 8-output chunk of each frame
+    AggFrameDesc *fd = reinterpret_cast<AggFrameDesc *>(cstart + (a.G + 1u) + ((2u * a.G + 2u) & 1u));   // [G], 8-byte aligned
+    unsigned long long *foff = reinterpret_cast<unsigned long long *>(fd + a.G);                          // [G]
+
+    const uint32_t n_frames = a.ctl->n_frames;
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t it = 0;
+    for (uint32_t f0 = blockIdx.x * a.G; f0 < n_frames; f0 += gridDim.x * a.G, it++) {
+        const uint32_t nf = min(a.G, n_frames - f0);
+        __syncthreads();                                   // previous step's readers are done with the arena
+        if (threadIdx.x < nf) {
+            fd[threadIdx.x] = a.fdesc[f0 + threadIdx.x];
+            foff[threadIdx.x] = a.fdesc_off[f0 + threadIdx.x];
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t qs = 0, cs = 0;
+            for (uint32_t k = 0; k < nf; k++) {
+                qstart[k] = qs; cstart[k] = cs;
+                qs += fd[k].nq;
+                cs += (__ldg(a.nout_of + fd[k].nq) + 7u) >> 3;
+            }
+            qstart[nf] = qs; cstart[nf] = cs;
+            mbar_expect_tx(bar, qs * Q * 4u);
+        }
+        __syncthreads();
+        const uint32_t T = qstart[nf];
+        for (uint32_t sl = threadIdx.x; sl < T; sl += blockDim.x) {
+            uint32_t k = 0;
+            while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
+            const uint32_t j = sl - qstart[k];
+            const AggFrameDesc d = fd[k];
+            const float *src = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
+                                                : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
+            bulk_g2s(arena + (size_t)sl * pitch, src, Q * 4u, bar);
+        }
+        mbar_wait(bar, it & 1u);
+
+        // ---- pick + encode + store: work item = 8 consecutive outputs of one frame ----------------------
+        const uint32_t n_chunks = cstart[nf];
+        for (uint32_t c = threadIdx.x; c < n_chunks; c += blockDim.x) {
+            uint32_t k = 0;
+            while (k + 1u < nf && c >= cstart[k + 1u]) k++;
+            const uint32_t nq = fd[k].nq, n_in = nq * Q, n_out = __ldg(a.nout_of + nq);
+            const uint32_t o0 = (c - cstart[k]) * 8u;
+            const float *fr = arena + (size_t)qstart[k] * pitch;
+            int e[8];
+#pragma unroll
+            for (int jj = 0; jj < 8; jj++) {
+                const uint32_t o = o0 + jj;
+                uint32_t i = 0xFFFFFFFFu;
+                if (o < n_out) i = a.lut ? __ldg(a.lut + o) : o * g.stride;
+                float x = __int_as_float(0x7FC00000);                    // outside the frame: undefined -> NaN -> 0
+                if (i < n_in) {
+                    const uint32_t qi = div_magic(i, a.magic_q);
+                    x = fr[qi * pitch + (i - qi * Q)];
+                }
+                e[jj] = enc_s32(x);
+            }
+            int16_t *dst = a.out + foff[k] + o0;
+            if (o0 + 8u <= n_out && a.out_aligned16) {
+                uint4 o4;
+                o4.x = pack_s16x2_sat(e[0], e[1]);
+                o4.y = pack_s16x2_sat(e[2], e[3]);
+                o4.z = pack_s16x2_sat(e[4], e[5]);
+                o4.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(dst, o4, a.hint);
+            } else {
+#pragma unroll
+                for (int jj = 0; jj < 8; jj++)
+                    if (o0 + jj < n_out) dst[jj] = (int16_t)(pack_s16x2_sat(e[jj], 0) & 0xFFFFu);
+            }
+        }
+
+        if (METER) {
+            // lane <-> slot; ring-carried quanta were metered when they were appended
+            const uint32_t m_warps = (T + 31u) >> 5;
+            const uint32_t rot = m_warps < 8u ? (it * m_warps) & 7u : 0u;
+            const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+            for (uint32_t sl = (((warp + 8u - rot) & 7u) << 5) + lane; sl < T; sl += blockDim.x) {
+                uint32_t k = 0;
+                while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
+                const uint32_t j = sl - qstart[k];
+                if (j < fd[k].ring_count) continue;
+                const float4 *src4 = reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch);
+                double sum = 0.0;
+                uint32_t lowest = 0xFFFFFFFFu;
+                auto four = [&](const float4 v) {
+                    const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int jj = 0; jj < 4; jj++) {
+                        const uint32_t b = __float_as_uint(xs[jj]);
+                        const uint32_t t2 = b << 1;
+                        lowest = min(lowest, t2 - 2u);
+                        const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;
+                        const double x = __hiloint2double((int)hi, (int)(b << 29));
+                        sum = __fma_rn(x, x, sum);
+                    }
+                };
+                if (Q == 128u) {
+#pragma unroll 8
+                    for (uint32_t gq = 0; gq < 32u; gq++) four(src4[gq]);
+                } else {
+                    for (uint32_t gq = 0; gq < (Q >> 2); gq++) four(src4[gq]);
+                }
+                bool odd = lowest < (2u * 0x21800000u - 2u);
+                odd |= !(sum < __hiloint2double(0x4F900000, 0));
+                if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;
+                if (odd) {
+                    sum = 0.0;
+                    const float *src = reinterpret_cast<const float *>(src4);
+                    for (uint32_t q = 0; q < Q; q++) {
+                        const double x = widen_abs(src[q]);
+                        sum = __fma_rn(x, x, sum);
+                    }
+                }
+                a.rms_at[fd[k].pos + (j - fd[k].ring_count)] = rms_of(sum, Q);
+            }
+        }
+    }
+}
+
+// ---- 7: levels ---------------------------------------------------------------------------------------------------
+// App.tsx:271 along every touched session's FLUSHED quanta, in arrival order: first the quanta that were
+// waiting in its ring (their rms was stored when they were appended), then this push's.
+__global__ void __launch_bounds__(128)
+k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, const uint32_t *__restrict__ cursor,
+             const uint32_t *__restrict__ fill, const uint32_t *__restrict__ flushed, const double *__restrict__ ring_rms,
+             const double *__restrict__ rms_at, double *__restrict__ level, const AggCtl *__restrict__ ctl)
+{
+    if (ctl->status != 0u) return;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= ctl->n_touched) return;
+    const uint32_t nfl = flushed[k];
+    if (nfl == 0u) return;
+    const uint32_t s = touched[k], base = cursor[s] - count[s], c0 = fill[s];
+    double lv = level[s];
+    bool poisoned = lv != lv;
+    auto step = [&](double rms) {
+        poisoned |= rms != rms;
+        const double dec = __dmul_rn(lv, 0.85);
+        lv = rms > dec ? rms : dec;
+        if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
+    };
+    for (uint32_t j = 0; j < c0; j++) step(ring_rms[(size_t)s * g.half_quanta + j]);
+    for (uint32_t j = 0; j < nfl; j++) step(rms_at[base + j]);
+    level[s] = lv;
+}
+
+// ---- 8: append ------------------------------------------------------------------------------------------------------
+// Quanta that did not flush go to their ring slot.  Without the meter: one warp per quantum, 128-bit
+// copies, nothing else.  With the meter the quantum's rms must be accumulated in sample order by ONE
+// lane (handing a running sum from lane to lane costs ~15 warp-instructions per sample), so a CTA stages
+// 64 consecutive quanta of the push in shared memory (bulk copies, slot pitch quantum + 4 floats), lane t
+// meters slot t exactly like kernel 2c, and the warps then copy the slots out to the rings.
+template <bool METER>
+__global__ void __launch_bounds__(256)
+k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
+             double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl)
+{
+    if (ctl->status != 0u || ctl->n_leftover == 0u) return;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t granules = quantum >> 2;
+    if (!METER) {
+        const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+        for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
+            const uint32_t slot = __ldg(dst_slot + i);
+            if (slot == 0xFFFFFFFFu) continue;
+            const float4 *s4 = reinterpret_cast<const float4 *>(samples + (size_t)i * quantum);
+            float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)slot * quantum);
+            for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = __ldg(s4 + gi);
+        }
+        return;
+    }
+    constexpr uint32_t TILE = 64;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t pitch = quantum + 4u;
+    float *arena = reinterpret_cast<float *>(smem_raw);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (((size_t)TILE * pitch * 4u + 127u) & ~(size_t)127u));
+    __shared__ uint32_t slot_s[TILE];
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t it = 0;
+    for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
+        __syncthreads();
+        uint32_t slot = 0xFFFFFFFFu;
+        if (threadIdx.x < TILE && i0 + threadIdx.x < n) slot = __ldg(dst_slot + i0 + threadIdx.x);
+        if (threadIdx.x < TILE) slot_s[threadIdx.x] = slot;
+        const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
+        if (live == 0) continue;
+        if (threadIdx.x == 0) mbar_expect_tx(bar, (uint32_t)live * quantum * 4u);
+        __syncthreads();
+        if (slot != 0xFFFFFFFFu)
+            bulk_g2s(arena + (size_t)threadIdx.x * pitch, samples + (size_t)(i0 + threadIdx.x) * quantum, quantum * 4u, bar);
+        mbar_wait(bar, it & 1u);
+        it++;
+        if (slot != 0xFFFFFFFFu) {                        // threads 0..63: the meter of slot t
+            const float4 *src4 = reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch);
+            double sum = 0.0;
+            uint32_t lowest = 0xFFFFFFFFu;
+            auto four = [&](const float4 v) {
+                const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int jj = 0; jj < 4; jj++) {
+                    const uint32_t b = __float_as_uint(xs[jj]);
+                    const uint32_t t2 = b << 1;
+                    lowest = min(lowest, t2 - 2u);
+                    const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;
+                    const double x = __hiloint2double((int)hi, (int)(b << 29));
+                    sum = __fma_rn(x, x, sum);
+                }
+            };
+            if (quantum == 128u) {
+#pragma unroll 8
+                for (uint32_t gq = 0; gq < 32u; gq++) four(src4[gq]);
+            } else {
+                for (uint32_t gq = 0; gq < granules; gq++) four(src4[gq]);
+            }
+            bool odd = lowest < (2u * 0x21800000u - 2u);
+            odd |= !(sum < __hiloint2double(0x4F900000, 0));
+            if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;
+            if (odd) {
+                sum = 0.0;
+                const float *src = reinterpret_cast<const float *>(src4);
+                for (uint32_t q = 0; q < quantum; q++) {
+                    const double x = widen_abs(src[q]);
+                    sum = __fma_rn(x, x, sum);
+                }
+            }
+            ring_rms[slot] = rms_of(sum, quantum);
+        }
+        // copy out: warps 2..7 start at once, warps 0 and 1 join when their meter lanes are done
+        for (uint32_t t = (warp + 6u) & 7u; t < TILE; t += 8u) {
+            const uint32_t sl = slot_s[t];
+            if (sl == 0xFFFFFFFFu) continue;
+            const float4 *s4 = reinterpret_cast<const float4 *>(arena + (size_t)t * pitch);
+            float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)sl * quantum);
+            for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = s4[gi];
+        }
+    }
+}
+
+// ---- 9: commit ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_agg_commit(const uint32_t *__restrict__ touched, uint32_t *__restrict__ count, uint32_t *__restrict__ fill,
+             double *__restrict__ last_send, const uint32_t *__restrict__ new_fill, const double *__restrict__ new_last,
+             const AggCtl *__restrict__ ctl)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= ctl->n_touched) return;
+    const uint32_t s = touched[k];
+    count[s] = 0u;                                        // always: the next push starts from clean counters
+    if (ctl->status == 0u) { fill[s] = new_fill[k]; last_send[s] = new_last[k]; }
+}
+
+__global__ void k_agg_reset(uint32_t *__restrict__ fill, double *__restrict__ last_send, uint32_t first, uint32_t n, double now_ms)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n) { fill[first + k] = 0u; last_send[first + k] = now_ms; }
+}
+
+}  // namespace pcmb200

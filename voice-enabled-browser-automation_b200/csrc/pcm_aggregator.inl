@@ -1,0 +1,386 @@
+// pcm_aggregator.inl -- host side of the device-side capture aggregator (included by pcm_b200.cu).
+//
+// Restates the reference's aggregator (App.tsx:148-157, :273-288) for many sessions: per session,
+// 128-sample quanta are appended to a buffer; the quantum that arrives with now - lastSend >= desiredMs
+// flushes the WHOLE buffer (a multiple of 128 samples, e.g. 23 quanta = 2944 samples -> 981 outputs at
+// 48 kHz) through floatTo16BitPCM(resampleTo16k(buf, rate)) and resets buffer and lastSend.  The wall
+// clock is injected: every quantum carries its arrival time.
+//
+// All per-session state (fill, lastSend, level, the buffer itself) lives in HBM, and the flush plan of
+// a push is computed by kernels (agg_kernels.cuh): the host enqueues a fixed sequence of launches and
+// reads back {status, n_frames, out_total}.  A rejected push changes nothing (the plan is scratch until
+// the commit kernel runs).
+#include "agg_kernels.cuh"
+
+struct pcmb200_aggregator {
+    AggGeom geo{};
+    uint32_t max_push = 0, nout_max = 0;
+    size_t out_cap = 0;
+    double rate = 0;
+    bool meter = false;
+    // persistent device state
+    float *ring = nullptr;                 // [max_sessions][half_quanta][quantum]
+    double *ring_rms = nullptr;            // [max_sessions][half_quanta] rms of every waiting quantum (meter)
+    uint32_t *fill = nullptr, *count = nullptr, *cursor = nullptr;   // [max_sessions]
+    double *last_send = nullptr, *level = nullptr;                   // [max_sessions]
+    uint32_t *nout_of = nullptr;           // [half_quanta + 1] output length of a frame of nq quanta
+    uint32_t *lut = nullptr;               // one pick table for every frame length (see create)
+    // per-push scratch, sized for max_push quanta
+    uint32_t *d_sessions = nullptr;        // staging when the caller's arrays are host memory
+    double *d_arrival = nullptr;
+    float *d_stage = nullptr;
+    uint32_t *touched = nullptr, *sorted = nullptr, *fl_nq = nullptr, *fl_ring = nullptr, *fl_pos = nullptr,
+             *dst_slot = nullptr, *new_fill = nullptr, *flushed = nullptr;
+    double *new_last = nullptr, *rms_at = nullptr;
+    uint32_t *sums_a = nullptr, *sums_b = nullptr;
+    unsigned long long *offs_b = nullptr;
+    AggFrameDesc *fdesc = nullptr;
+    unsigned long long *fdesc_off = nullptr;
+    uint32_t *f_session = nullptr, *f_len = nullptr;     // frame arrays when the caller's are host memory
+    unsigned long long *f_off = nullptr;
+    int16_t *d_out = nullptr;              // [out_cap] when the caller's output is host memory
+    AggCtl *ctl = nullptr;                 // device
+    AggCtl *h_ctl = nullptr;               // pinned copy
+    // convert kernel geometry
+    uint32_t G = 1;
+    size_t convert_smem = 0, append_smem = 0;
+    bool pending = false;                  // a push was enqueued and its result not yet collected
+};
+
+namespace {
+
+int agg_status_to_error(pcmb200_ctx *ctx, uint32_t st)
+{
+    if (st == 0) return PCMB200_OK;
+    if (st & AGG_ST_BAD_SESSION) return fail(ctx, PCMB200_ERR_INVALID, "pcmb200_aggregator_push: session id out of range (push rejected, nothing changed)");
+    if (st & AGG_ST_FRAME_TOO_LONG)
+        return fail(ctx, PCMB200_ERR_CAPACITY, "pcmb200_aggregator_push: a session's buffer exceeds max_frame_quanta (no flush arrived); push rejected, nothing changed");
+    if (st & AGG_ST_TOO_MANY_FRAMES) return fail(ctx, PCMB200_ERR_CAPACITY, "pcmb200_aggregator_push: more flushed frames than max_frames; push rejected, nothing changed");
+    return fail(ctx, PCMB200_ERR_CAPACITY, "pcmb200_aggregator_push: flushed frames exceed the output capacity; push rejected, nothing changed");
+}
+
+template <typename T>
+cudaError_t agg_alloc(T **p, size_t count)
+{
+    return cudaMalloc((void **)p, (count ? count : 1) * sizeof(T));
+}
+
+// Enqueue the whole push on the context's stream.  Every pointer is device memory.
+int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint32_t *sessions, const double *arrival,
+                const float *samples, int16_t *out, size_t out_capacity, uint32_t *frame_session, uint32_t *frame_len,
+                unsigned long long *frame_offset, uint32_t max_frames)
+{
+    cudaStream_t st = ctx->stream;
+    CU(cudaMemsetAsync(a->ctl, 0, sizeof(AggCtl), st));
+    const int blocks_n = (int)((n + 255u) / 256u);
+    const int scan_blocks = (int)((n + kScanBlock - 1) / kScanBlock);
+    k_agg_count<<<blocks_n, 256, 0, st>>>(sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
+    ScanArgs sa{n, a->touched, a->count, a->fl_nq, a->nout_of, a->ctl};
+    k_scan_reduce<0><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
+    k_scan_sums<0><<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, 0u, 0ull);
+    k_scan_apply<0, ScanApplyA><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ScanApplyA{a->cursor});
+    k_agg_scatter<<<blocks_n, 256, 0, st>>>(sessions, n, a->cursor, a->sorted, a->ctl);
+    AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
+    k_agg_walk<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill,
+                                                         a->last_send, wo, a->ctl);
+    k_scan_reduce<1><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
+    k_scan_sums<1><<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
+    ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
+    k_scan_apply<1, ScanApplyB><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ab);
+    ctx->launches += 9;
+
+    AggConvertArgs ca{};
+    ca.samples = samples; ca.ring = a->ring; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
+    ca.nout_of = a->nout_of; ca.lut = a->lut; ca.out = out; ca.rms_at = a->rms_at; ca.ctl = a->ctl; ca.G = a->G;
+    ca.magic_q = magic_for(a->geo.quantum); ca.out_aligned16 = aligned(out, 16) ? 1 : 0; ca.hint = ctx->tune.store_hint;
+    // frames <= quanta; a frame has about desired_ms worth of quanta, so n / G blocks is an upper bound
+    // that is far too generous: cap the grid and let the blocks loop
+    unsigned long long conv_blocks = ((unsigned long long)n + a->G - 1) / a->G;
+    const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
+    if (conv_blocks > cap) conv_blocks = cap;
+    if (a->meter) k_agg_convert<true><<<(int)conv_blocks, 256, a->convert_smem, st>>>(a->geo, ca);
+    else k_agg_convert<false><<<(int)conv_blocks, 256, a->convert_smem, st>>>(a->geo, ca);
+    if (a->meter) {
+        k_agg_levels<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms,
+                                                             a->rms_at, a->level, a->ctl);
+        const unsigned long long tiles = ((unsigned long long)n + 63ull) / 64ull;
+        const int grid = (int)(tiles < cap ? tiles : cap);
+        k_agg_append<true><<<grid, 256, a->append_smem, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
+        ctx->launches += 1;
+    } else {
+        const unsigned long long warps_blocks = ((unsigned long long)n + 7ull) / 8ull;
+        const int grid = (int)(warps_blocks < cap ? warps_blocks : cap);
+        k_agg_append<false><<<grid, 256, 0, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
+    }
+    k_agg_commit<<<blocks_n, 256, 0, st>>>(a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
+    ctx->launches += 3;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(a->h_ctl, a->ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
+    a->pending = true;
+    return PCMB200_OK;
+}
+
+}  // namespace
+
+extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
+                                         double desired_ms, uint32_t max_frame_quanta, uint32_t max_push_quanta,
+                                         size_t max_out_samples_per_push, pcmb200_aggregator **out)
+{
+    NEED(ctx && out, "pcmb200_aggregator_create: NULL argument");
+    *out = nullptr;
+    NEED(max_sessions > 0 && quantum > 0 && max_frame_quanta > 0 && max_push_quanta > 0 && max_out_samples_per_push > 0,
+         "pcmb200_aggregator_create: sizes must be positive");
+    NEED(in_rate > 0 && desired_ms == desired_ms, "pcmb200_aggregator_create: bad rate / desired_ms");
+    NEED(quantum % 4 == 0, "pcmb200_aggregator_create: quantum must be a multiple of 4 samples (the AudioWorklet quantum is 128)");
+    NEED((unsigned long long)max_sessions * max_frame_quanta < 0xFFFFFFFFull, "pcmb200_aggregator_create: max_sessions * max_frame_quanta must be below 2^32");
+    NEED((unsigned long long)max_frame_quanta * quantum * quantum < 0xF0000000ull, "pcmb200_aggregator_create: frame too long");
+    size_t probe = 0;
+    int s = resample_len((size_t)max_frame_quanta * quantum, in_rate, &probe);
+    if (s) return fail(ctx, s, "pcmb200_aggregator_create: RangeError: invalid typed array length");
+    NEED(probe <= 0x7FFFFFFFull, "pcmb200_aggregator_create: frame too long");
+    // one frame (max_frame_quanta quanta at a pitch of quantum + 4 floats) must fit in shared memory
+    const size_t slot_bytes = (size_t)(quantum + 4) * 4;
+    NEED((size_t)max_frame_quanta * slot_bytes <= 200 * 1024,
+         "pcmb200_aggregator_create: max_frame_quanta * quantum is too long to stage one frame on chip (limit ~200 KB, "
+         "e.g. 387 quanta of 128 samples = 1 s at 48 kHz)");
+    CU(cudaSetDevice(ctx->device));
+    pcmb200_aggregator *a = new (std::nothrow) pcmb200_aggregator();
+    if (!a) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed");
+    a->geo.max_sessions = max_sessions; a->geo.quantum = quantum; a->geo.half_quanta = max_frame_quanta;
+    a->geo.desired_ms = desired_ms;
+    a->max_push = max_push_quanta; a->out_cap = max_out_samples_per_push; a->rate = in_rate;
+    uint32_t R = 0;
+    a->geo.stride = (in_rate == 16000.0) ? 1u : (integer_ratio(in_rate, &R) ? R : 0u);
+    a->nout_max = (uint32_t)probe;
+
+    // Frame arithmetic for every possible frame length, once.  The pick sequence floor(idx), idx += ratio
+    // (App.tsx:26-30) does not depend on the input length -- a shorter frame uses a prefix of it -- so ONE
+    // table serves every frame length; the per-length part is only the output length (App.tsx:24).
+    std::vector<uint32_t> h_nout, h_lut;
+    try {
+        h_nout.assign(max_frame_quanta + 1, 0);
+        for (uint32_t nq = 1; nq <= max_frame_quanta; nq++) {
+            size_t no = 0;
+            resample_len((size_t)nq * quantum, in_rate, &no);
+            h_nout[nq] = (uint32_t)no;
+        }
+        if (a->geo.stride == 0) {
+            h_lut.resize(a->nout_max ? a->nout_max : 1);
+            build_index_table((size_t)max_frame_quanta * quantum, in_rate, a->nout_max, h_lut.data());
+        }
+    } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
+
+    // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
+    a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (64 * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
+    a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 16 + 8 * (a->G + 1) + 24 * a->G;
+    a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127) + 16;
+
+    cudaError_t e = cudaSuccess;
+    const size_t S = max_sessions, P = max_push_quanta;
+    const size_t ring_floats = S * max_frame_quanta * quantum;
+#define AGG_STEP(call) if (e == cudaSuccess) e = (call)
+    AGG_STEP(agg_alloc(&a->ring, ring_floats));
+    AGG_STEP(agg_alloc(&a->ring_rms, S * max_frame_quanta));
+    AGG_STEP(agg_alloc(&a->fill, S));
+    AGG_STEP(agg_alloc(&a->count, S));
+    AGG_STEP(agg_alloc(&a->cursor, S));
+    AGG_STEP(agg_alloc(&a->last_send, S));
+    AGG_STEP(agg_alloc(&a->level, S));
+    AGG_STEP(agg_alloc(&a->nout_of, (size_t)max_frame_quanta + 1));
+    if (a->geo.stride == 0) AGG_STEP(agg_alloc(&a->lut, h_lut.size()));
+    AGG_STEP(agg_alloc(&a->d_sessions, P));
+    AGG_STEP(agg_alloc(&a->d_arrival, P));
+    // d_stage (a whole push of samples) is allocated on the first push whose samples are host memory
+    AGG_STEP(agg_alloc(&a->touched, P));
+    AGG_STEP(agg_alloc(&a->sorted, P));
+    AGG_STEP(agg_alloc(&a->fl_nq, P));
+    AGG_STEP(agg_alloc(&a->fl_ring, P));
+    AGG_STEP(agg_alloc(&a->fl_pos, P));
+    AGG_STEP(agg_alloc(&a->dst_slot, P));
+    AGG_STEP(agg_alloc(&a->new_fill, P));
+    AGG_STEP(agg_alloc(&a->flushed, P));
+    AGG_STEP(agg_alloc(&a->new_last, P));
+    AGG_STEP(agg_alloc(&a->rms_at, P));
+    const size_t nb = (P + kScanBlock - 1) / kScanBlock;
+    AGG_STEP(agg_alloc(&a->sums_a, nb));
+    AGG_STEP(agg_alloc(&a->sums_b, nb));
+    AGG_STEP(agg_alloc(&a->offs_b, nb));
+    AGG_STEP(agg_alloc(&a->fdesc, P));
+    AGG_STEP(agg_alloc(&a->fdesc_off, P));
+    AGG_STEP(agg_alloc(&a->f_session, P));
+    AGG_STEP(agg_alloc(&a->f_len, P));
+    AGG_STEP(agg_alloc(&a->f_off, P));
+    AGG_STEP(agg_alloc(&a->d_out, max_out_samples_per_push));
+    AGG_STEP(agg_alloc(&a->ctl, 1));
+    AGG_STEP(cudaHostAlloc((void **)&a->h_ctl, sizeof(AggCtl), cudaHostAllocDefault));
+    AGG_STEP(cudaMemsetAsync(a->fill, 0, S * 4, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->count, 0, S * 4, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->last_send, 0, S * 8, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->level, 0, S * 8, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_floats * 4, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->ring_rms, 0, S * max_frame_quanta * 8, ctx->stream));
+    AGG_STEP(cudaMemcpyAsync(a->nout_of, h_nout.data(), h_nout.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (a->geo.stride == 0) AGG_STEP(cudaMemcpyAsync(a->lut, h_lut.data(), h_lut.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
+#undef AGG_STEP
+    if (e != cudaSuccess) {
+        std::string m = std::string("pcmb200_aggregator_create: ") + cudaGetErrorString(e);
+        pcmb200_aggregator_destroy(ctx, a);
+        cudaGetLastError();
+        return fail(ctx, e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA, m);
+    }
+    if (a->h_ctl) std::memset(a->h_ctl, 0, sizeof(AggCtl));
+    *out = a;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *a)
+{
+    NEED(ctx, "pcmb200_aggregator_destroy: ctx is NULL");
+    if (!a) return PCMB200_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    void *dev[] = {a->ring, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
+                   a->d_arrival, a->d_stage, a->touched, a->sorted, a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill,
+                   a->flushed, a->new_last, a->rms_at, a->sums_a, a->sums_b, a->offs_b, a->fdesc, a->fdesc_off, a->f_session,
+                   a->f_len, a->f_off, a->d_out, a->ctl};
+    for (void *p : dev) if (p) cudaFree(p);
+    if (a->h_ctl) cudaFreeHost(a->h_ctl);
+    cudaGetLastError();
+    delete a;
+    return PCMB200_OK;
+}
+
+// App.tsx:325-330 (stop) / :148-157 (initial state): empty buffer, lastSend = now.  Enqueued on the
+// context's stream, so it is ordered with the pushes.
+extern "C" int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t session, double now_ms)
+{
+    NEED(ctx && a, "pcmb200_aggregator_reset_session: NULL argument");
+    NEED(session < a->geo.max_sessions, "pcmb200_aggregator_reset_session: session out of range");
+    CU(cudaSetDevice(ctx->device));
+    k_agg_reset<<<1, 32, 0, ctx->stream>>>(a->fill, a->last_send, session, 1u, now_ms);
+    CU(cudaGetLastError());
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_reset_range(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t first_session, uint32_t count,
+                                              double now_ms)
+{
+    NEED(ctx && a, "pcmb200_aggregator_reset_range: NULL argument");
+    NEED((unsigned long long)first_session + count <= a->geo.max_sessions, "pcmb200_aggregator_reset_range: session range out of bounds");
+    if (count == 0) return PCMB200_OK;
+    CU(cudaSetDevice(ctx->device));
+    k_agg_reset<<<(int)((count + 255u) / 256u), 256, 0, ctx->stream>>>(a->fill, a->last_send, first_session, count, now_ms);
+    CU(cudaGetLastError());
+    return PCMB200_OK;
+}
+
+// Level meter of the aggregated sessions (App.tsx:267-271).  When enabled, every quantum's rms is taken
+// as the quantum passes through the chip, and the level runs through the quanta of every flushed frame
+// in arrival order; the level of a session therefore lags the reference's by the quanta still waiting
+// in its buffer (it is a UI-only value there).  Switch it on before the first push: quanta appended
+// while it was off have no rms on record.
+extern "C" int pcmb200_aggregator_set_meter(pcmb200_ctx *ctx, pcmb200_aggregator *a, int enabled)
+{
+    NEED(ctx && a, "pcmb200_aggregator_set_meter: NULL argument");
+    a->meter = enabled != 0;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_get_levels(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t first_session, uint32_t count,
+                                             double *levels_host)
+{
+    NEED(ctx && a && (levels_host || count == 0), "pcmb200_aggregator_get_levels: NULL argument");
+    NEED((unsigned long long)first_session + count <= a->geo.max_sessions, "pcmb200_aggregator_get_levels: session range out of bounds");
+    CU(cudaSetDevice(ctx->device));
+    if (count) CU(cudaMemcpyAsync(levels_host, a->level + first_session, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCMB200_OK;
+}
+
+// Everything on the device: quanta, their session ids and arrival times, the frames and the frame
+// arrays.  Asynchronous; pcmb200_aggregator_wait collects the outcome.
+extern "C" int pcmb200_aggregator_push_device(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n_quanta,
+                                              const uint32_t *sessions_device, const double *arrival_ms_device,
+                                              const float *samples_device, int16_t *out_device, size_t out_capacity,
+                                              uint32_t *frame_session_device, uint32_t *frame_len_device,
+                                              unsigned long long *frame_offset_device, uint32_t max_frames)
+{
+    NEED(ctx && a, "pcmb200_aggregator_push_device: NULL argument");
+    NEED(!a->pending, "pcmb200_aggregator_push_device: collect the previous push with pcmb200_aggregator_wait first");
+    if (n_quanta == 0) { std::memset(a->h_ctl, 0, sizeof(AggCtl)); a->pending = true; return PCMB200_OK; }
+    NEED(sessions_device && arrival_ms_device && samples_device && out_device, "pcmb200_aggregator_push_device: NULL buffer");
+    NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push_device: more quanta than max_push_quanta");
+    NEED(aligned(samples_device, 16), "pcmb200_aggregator_push_device: samples must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    return agg_enqueue(ctx, a, n_quanta, sessions_device, arrival_ms_device, samples_device, out_device, out_capacity,
+                       frame_session_device, frame_len_device, frame_offset_device, max_frames);
+}
+
+extern "C" int pcmb200_aggregator_wait(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t *n_frames, size_t *out_samples)
+{
+    NEED(ctx && a, "pcmb200_aggregator_wait: NULL argument");
+    if (n_frames) *n_frames = 0;
+    if (out_samples) *out_samples = 0;
+    NEED(a->pending, "pcmb200_aggregator_wait: no push is pending");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    a->pending = false;
+    if (a->h_ctl->status) return agg_status_to_error(ctx, a->h_ctl->status);
+    if (n_frames) *n_frames = a->h_ctl->n_frames;
+    if (out_samples) *out_samples = (size_t)a->h_ctl->out_total;
+    return PCMB200_OK;
+}
+
+extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n_quanta,
+                                       const uint32_t *sessions, const double *arrival_ms, const float *samples,
+                                       int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
+                                       uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
+                                       uint32_t max_frames, uint32_t *n_frames)
+{
+    NEED(ctx && a && n_frames, "pcmb200_aggregator_push: NULL argument");
+    *n_frames = 0;
+    NEED(!a->pending, "pcmb200_aggregator_push: collect the previous asynchronous push with pcmb200_aggregator_wait first");
+    if (n_quanta == 0) return PCMB200_OK;
+    NEED(sessions && arrival_ms && samples && out, "pcmb200_aggregator_push: NULL buffer");
+    NEED((samples_mem == PCMB200_MEM_HOST || samples_mem == PCMB200_MEM_DEVICE) &&
+         (out_mem == PCMB200_MEM_HOST || out_mem == PCMB200_MEM_DEVICE), "pcmb200_aggregator_push: bad mem kind");
+    NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push: more quanta than max_push_quanta");
+    NEED(samples_mem == PCMB200_MEM_HOST || aligned(samples, 16), "pcmb200_aggregator_push: device samples must be 16-byte aligned");
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    // the session ids and arrival times are host arrays in this entry point: stage them (pinned caller
+    // memory goes at PCIe speed, pageable memory through the driver's bounce buffer)
+    CU(cudaMemcpyAsync(a->d_sessions, sessions, (size_t)n_quanta * 4, cudaMemcpyHostToDevice, st));
+    CU(cudaMemcpyAsync(a->d_arrival, arrival_ms, (size_t)n_quanta * 8, cudaMemcpyHostToDevice, st));
+    const float *d_samples = samples;
+    if (samples_mem == PCMB200_MEM_HOST) {
+        if (!a->d_stage) CU(agg_alloc(&a->d_stage, (size_t)a->max_push * a->geo.quantum));
+        CU(cudaMemcpyAsync(a->d_stage, samples, (size_t)n_quanta * a->geo.quantum * sizeof(float), cudaMemcpyHostToDevice, st));
+        d_samples = a->d_stage;
+    }
+    int16_t *d_out = out_mem == PCMB200_MEM_DEVICE ? out : a->d_out;
+    const size_t cap = out_mem == PCMB200_MEM_DEVICE ? out_capacity : std::min(out_capacity, a->out_cap);
+    if (max_frames > a->max_push) max_frames = a->max_push;       // frames <= quanta; the internal arrays hold max_push
+    int s = agg_enqueue(ctx, a, n_quanta, a->d_sessions, a->d_arrival, d_samples, d_out, cap, a->f_session, a->f_len, a->f_off, max_frames);
+    if (s) return s;
+    CU(cudaStreamSynchronize(st));
+    a->pending = false;
+    if (a->h_ctl->status) return agg_status_to_error(ctx, a->h_ctl->status);
+    const uint32_t nf = a->h_ctl->n_frames;
+    if (nf) {
+        if (frame_session) CU(cudaMemcpyAsync(frame_session, a->f_session, (size_t)nf * 4, cudaMemcpyDeviceToHost, st));
+        if (frame_len) CU(cudaMemcpyAsync(frame_len, a->f_len, (size_t)nf * 4, cudaMemcpyDeviceToHost, st));
+        if (frame_offset) CU(cudaMemcpyAsync(frame_offset, a->f_off, (size_t)nf * 8, cudaMemcpyDeviceToHost, st));
+        // the frames themselves: out_total counts every frame padded to 8 samples, and the capacity check
+        // was made on that padded total, so this copy stays inside both buffers
+        if (out_mem == PCMB200_MEM_HOST && a->h_ctl->out_total)
+            CU(cudaMemcpyAsync(out, a->d_out, (size_t)a->h_ctl->out_total * sizeof(int16_t), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    *n_frames = nf;
+    return PCMB200_OK;
+}

@@ -58,8 +58,9 @@ struct Tuning {
     int tile = 1;            // dense short-frame batches on the general path: TMA tile-staged kernel (2b)
     int tile_kb = 28;        // target tile size of kernel 2b
     int stages = 1;          // tiles in flight per CTA in kernel 2b (1: one tile per block, overlap comes from co-resident blocks)
-    int meter_tile_kb = 64;  // kernel 2b with the fused level meter: tile size ...
+    int meter_tile_kb = 64;  // kernels 2b/2c with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
+    int meter_kernel = 1;    // 1: kernel 2c (padded-row tiles) where it applies; 0: kernel 2b only
     size_t slice_bytes = 32u << 20;
 };
 
@@ -363,6 +364,82 @@ uint32_t launch_tile(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t 
     if (e != cudaSuccess) { cudaGetLastError(); return 0; }   // fall back to the other kernels for the whole batch
     ctx->launches++;
     return (uint32_t)(n_tiles * K);
+}
+
+// Kernel 2c (frames + fused level meter on padded-row tiles).  Takes the whole batch or nothing:
+// returns true when it was launched.
+template <int RT, int STAGES>
+cudaError_t launch_meter_k(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *out, const TileMeterGeom &geo,
+                           unsigned long long n_tiles, const uint32_t *lut, size_t smem, const MeterArgs &meter)
+{
+    static size_t granted[64] = {0};
+    const int dev = ctx->device & 63;
+    if (smem > granted[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(k_frames_meter<RT, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        granted[dev] = smem;
+    }
+    const int grid = grid_for(ctx, n_tiles);
+    k_frames_meter<RT, STAGES><<<grid, 256, smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
+    return cudaGetLastError();
+}
+
+uint32_t magic_for(uint32_t d) { return d <= 1 ? 0u : (uint32_t)((0x100000000ull + d - 1) / d); }
+
+bool launch_frames_meter(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
+                         uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R, const MeterArgs &meter)
+{
+    if (!ctx->tune.tile || ctx->tune.meter_kernel == 0) return false;
+    if (pitch_in != n_in || pitch_out != n_out || n_out == 0 || n_out > 8192 || rows == 0) return false;
+    if ((n_in & 3u) || (meter.quantum & 3u) || meter.nq == 0) return false;
+    if (!aligned(in, 16) || !aligned(out, 16)) return false;
+    // row pitch: an odd number of 16-byte units, at least one unit of padding (it holds the NaN slot)
+    const uint32_t units = n_in / 4;
+    const uint32_t pitch = (units + ((units & 1u) ? 2u : 1u)) * 4u;
+    const size_t row_bytes = (size_t)pitch * 4;
+    const size_t target = (size_t)ctx->tune.meter_tile_kb * 1024;
+    const int stages = ctx->tune.meter_stages;
+    // rows per tile: multiples of 8 (8 consecutive rows = 8 different bank groups) up to the target size,
+    // preferring the height whose quanta fill whole warps; fewer than 8 only when 8 rows do not fit
+    uint32_t K = 0;
+    double best = -1.0;
+    for (uint32_t k = 8; (size_t)k * row_bytes <= target; k += 8) {
+        const uint32_t q = k * meter.nq;
+        const double fill = (double)q / (32.0 * ((q + 31) / 32));
+        if (fill > best - 1e-9) { best = fill; K = k; }   // ties go to the taller tile (fewer blocks, same fill)
+    }
+    if (K == 0) {
+        K = 8;
+        while (K > 1 && (size_t)K * row_bytes * stages > 200 * 1024) K >>= 1;
+    }
+    if (K > rows) K = rows >= 8 ? (rows & ~7u) : rows;
+    const uint32_t tile_stride = (uint32_t)(((size_t)K * row_bytes + 127) & ~(size_t)127);
+    size_t smem = (size_t)stages * tile_stride + (lut ? ((n_out * 4u + 15u) & ~15u) : 0u) + (size_t)((stages + 1) & ~1) * 8 +
+                  (size_t)K * meter.nq * sizeof(double);
+    if (smem > 220 * 1024) return false;
+    if ((unsigned long long)K * n_out * n_out >= 0xF0000000ull) return false;     // keeps div_magic exact
+    TileMeterGeom geo;
+    geo.n_in = n_in; geo.n_out = n_out; geo.K = K; geo.rows = rows; geo.pitch = pitch; geo.stride = R ? R : 1u;
+    geo.magic_cpr = magic_for(n_out / 8); geo.magic_nout = magic_for(n_out); geo.magic_K = magic_for(K);
+    geo.tile_stride_bytes = tile_stride;
+    const unsigned long long n_tiles = ((unsigned long long)rows + K - 1) / K;
+    cudaError_t e;
+    const int rt = (!lut && (n_out % 8 == 0) && (R == 1 || R == 2 || R == 3 || R == 4 || R == 6)) ? (int)R : 0;
+#define METER_K(RT_)                                                                                               \
+    (stages == 1 ? launch_meter_k<RT_, 1>(ctx, st, in, out, geo, n_tiles, lut, smem, meter)                          \
+                 : launch_meter_k<RT_, 2>(ctx, st, in, out, geo, n_tiles, lut, smem, meter))
+    switch (rt) {
+    case 1: e = METER_K(1); break;
+    case 2: e = METER_K(2); break;
+    case 3: e = METER_K(3); break;
+    case 4: e = METER_K(4); break;
+    case 6: e = METER_K(6); break;
+    default: e = METER_K(0); break;
+    }
+#undef METER_K
+    if (e != cudaSuccess) { cudaGetLastError(); return false; }
+    ctx->launches++;
+    return true;
 }
 
 // Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
@@ -1001,6 +1078,9 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "meter_tile_kb") {
         NEED(value >= 4 && value <= 160, "pcmb200_tune: meter_tile_kb must be in [4, 160]");
         ctx->tune.meter_tile_kb = (int)value;
+    } else if (k == "meter_kernel") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: meter_kernel must be 0 or 1");
+        ctx->tune.meter_kernel = (int)value;
     } else if (k == "meter_stages") {
         NEED(value == 1 || value == 2, "pcmb200_tune: meter_stages must be 1 or 2");
         ctx->tune.meter_stages = (int)value;
@@ -1043,7 +1123,10 @@ extern "C" int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in, si
             s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
             if (s) return s;
         }
-        took = launch_tile(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, &m);
+        if (launch_frames_meter(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, m))
+            took = rows;
+        else
+            took = launch_tile(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, &m);
     }
     if (took < rows) {   // rows the fused kernel did not take: the plain frame path + the stand-alone meter
         const uint32_t rest = rows - took;
@@ -1169,367 +1252,9 @@ extern "C" int pcmb200_tick_graph_destroy(pcmb200_ctx *ctx, pcmb200_tick_graph *
 }
 
 // ================================= device-side aggregator ======================
-// Host scheduler + device rings restating the reference's capture aggregator (App.tsx:148-157,
-// :273-288): per session, 128-sample quanta are appended to a buffer; when a quantum arrives with
-// now - lastSend >= desiredMs the WHOLE buffer (a multiple of 128 samples, e.g. 23 quanta = 2944
-// samples at 48 kHz) is converted with floatTo16BitPCM(resampleTo16k(buf, rate)) and the buffer and
-// lastSend are reset.  The wall clock is injected: every quantum carries its arrival time.
-struct pcmb200_aggregator {
-    uint32_t max_sessions = 0, quantum = 128, half_quanta = 0, max_push = 0;
-    size_t out_cap = 0;
-    double rate = 0, desired_ms = 60;
-    float *ring = nullptr;                 // [max_sessions][2][half_quanta * quantum]
-    float *d_stage = nullptr;              // [max_push][quantum] upload area for host-resident quanta
-    int16_t *d_out = nullptr;              // [out_cap] when the caller's output is host memory
-    uint32_t *d_slot = nullptr, *d_src_row = nullptr;
-    unsigned long long *d_dst_off = nullptr;
-    uint32_t *h_slot = nullptr, *h_src_row = nullptr;   // pinned staging of the three index arrays
-    unsigned long long *h_dst_off = nullptr;
-    cudaEvent_t uploaded = nullptr;
-    std::vector<uint32_t> fill;
-    std::vector<uint8_t> half;
-    std::vector<double> last_send;
-    std::vector<uint8_t> q_round, flushes_of;          // plan scratch: round of every quantum / flushes per session
-    std::vector<uint32_t> flush_nq, flush_row, touched;
-    std::vector<unsigned long long> flush_bits;
-    std::vector<std::vector<uint32_t>> buckets;        // [producer thread][owner thread] quantum indices
-    uint32_t push_epoch = 0;
-    uint8_t *h_round = nullptr, *d_round = nullptr;    // pinned / device copy of q_round
-    double *d_level = nullptr;                         // [max_sessions] level of every session (meter)
-    bool meter = false;
-};
-
-namespace {
-struct AggFrame { uint32_t src_row, nq, session; unsigned long long off; uint32_t n_out; uint32_t round; };
-struct AggUndo { uint32_t s, fill; uint8_t half; double last; };
-}  // namespace
-
-extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions, double in_rate, uint32_t quantum,
-                                         double desired_ms, uint32_t max_frame_quanta, uint32_t max_push_quanta,
-                                         size_t max_out_samples_per_push, pcmb200_aggregator **out)
-{
-    NEED(ctx && out, "pcmb200_aggregator_create: NULL argument");
-    *out = nullptr;
-    NEED(max_sessions > 0 && quantum > 0 && max_frame_quanta > 0 && max_push_quanta > 0 && max_out_samples_per_push > 0,
-         "pcmb200_aggregator_create: sizes must be positive");
-    NEED(in_rate > 0 && desired_ms == desired_ms, "pcmb200_aggregator_create: bad rate / desired_ms");
-    size_t probe = 0;
-    int s = resample_len((size_t)max_frame_quanta * quantum, in_rate, &probe);
-    if (s) return fail(ctx, s, "pcmb200_aggregator_create: RangeError: invalid typed array length");
-    CU(cudaSetDevice(ctx->device));
-    pcmb200_aggregator *a = new (std::nothrow) pcmb200_aggregator();
-    if (!a) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed");
-    a->max_sessions = max_sessions; a->quantum = quantum; a->half_quanta = max_frame_quanta; a->max_push = max_push_quanta;
-    a->out_cap = max_out_samples_per_push; a->rate = in_rate; a->desired_ms = desired_ms;
-    cudaError_t e = cudaSuccess;
-    try {
-        a->fill.assign(max_sessions, 0); a->half.assign(max_sessions, 0); a->last_send.assign(max_sessions, 0.0);
-    } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
-    const size_t ring_bytes = (size_t)max_sessions * 2 * max_frame_quanta * quantum * sizeof(float);
-#define AGG_STEP(call) if (e == cudaSuccess) e = (call)
-    AGG_STEP(cudaMalloc((void **)&a->ring, ring_bytes));
-    AGG_STEP(cudaMalloc((void **)&a->d_stage, (size_t)max_push_quanta * quantum * sizeof(float)));
-    AGG_STEP(cudaMalloc((void **)&a->d_out, max_out_samples_per_push * sizeof(int16_t)));
-    AGG_STEP(cudaMalloc((void **)&a->d_slot, (size_t)max_push_quanta * 4));
-    AGG_STEP(cudaMalloc((void **)&a->d_src_row, (size_t)max_push_quanta * 4));
-    AGG_STEP(cudaMalloc((void **)&a->d_dst_off, (size_t)max_push_quanta * 8));
-    AGG_STEP(cudaHostAlloc((void **)&a->h_slot, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
-    AGG_STEP(cudaHostAlloc((void **)&a->h_src_row, (size_t)max_push_quanta * 4, cudaHostAllocDefault));
-    AGG_STEP(cudaHostAlloc((void **)&a->h_dst_off, (size_t)max_push_quanta * 8, cudaHostAllocDefault));
-    AGG_STEP(cudaHostAlloc((void **)&a->h_round, (size_t)max_push_quanta, cudaHostAllocDefault));
-    AGG_STEP(cudaMalloc((void **)&a->d_round, (size_t)max_push_quanta));
-    AGG_STEP(cudaMalloc((void **)&a->d_level, (size_t)max_sessions * sizeof(double)));
-    AGG_STEP(cudaMemsetAsync(a->d_level, 0, (size_t)max_sessions * sizeof(double), ctx->stream));
-    AGG_STEP(cudaEventCreateWithFlags(&a->uploaded, cudaEventDisableTiming));
-    AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_bytes, ctx->stream));
-#undef AGG_STEP
-    if (e != cudaSuccess) {
-        std::string m = std::string("pcmb200_aggregator_create: ") + cudaGetErrorString(e);
-        pcmb200_aggregator_destroy(ctx, a);
-        cudaGetLastError();
-        return fail(ctx, e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA, m);
-    }
-    *out = a;
-    return PCMB200_OK;
-}
-
-extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *a)
-{
-    NEED(ctx, "pcmb200_aggregator_destroy: ctx is NULL");
-    if (!a) return PCMB200_OK;
-    cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
-    cudaFree(a->ring); cudaFree(a->d_stage); cudaFree(a->d_out); cudaFree(a->d_slot); cudaFree(a->d_src_row); cudaFree(a->d_dst_off);
-    if (a->h_slot) cudaFreeHost(a->h_slot);
-    if (a->h_src_row) cudaFreeHost(a->h_src_row);
-    if (a->h_dst_off) cudaFreeHost(a->h_dst_off);
-    if (a->h_round) cudaFreeHost(a->h_round);
-    cudaFree(a->d_round);
-    cudaFree(a->d_level);
-    if (a->uploaded) cudaEventDestroy(a->uploaded);
-    cudaGetLastError();
-    delete a;
-    return PCMB200_OK;
-}
-
-// App.tsx:325-330 (stop) / :148-157 (initial state): empty buffer, lastSend = now.
-extern "C" int pcmb200_aggregator_reset_session(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t session, double now_ms)
-{
-    NEED(ctx && a, "pcmb200_aggregator_reset_session: NULL argument");
-    NEED(session < a->max_sessions, "pcmb200_aggregator_reset_session: session out of range");
-    a->fill[session] = 0;
-    a->last_send[session] = now_ms;
-    return PCMB200_OK;
-}
-
-// Level meter of the aggregated sessions (App.tsx:267-271).  When enabled, every flushed frame's
-// quanta run through rms / max(rms, level * 0.85) in arrival order; the level of a session therefore
-// lags the reference's by the quanta still waiting in its buffer (it is a UI-only value there).
-extern "C" int pcmb200_aggregator_set_meter(pcmb200_ctx *ctx, pcmb200_aggregator *a, int enabled)
-{
-    NEED(ctx && a, "pcmb200_aggregator_set_meter: NULL argument");
-    a->meter = enabled != 0;
-    return PCMB200_OK;
-}
-
-extern "C" int pcmb200_aggregator_get_levels(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t first_session, uint32_t count,
-                                             double *levels_host)
-{
-    NEED(ctx && a && (levels_host || count == 0), "pcmb200_aggregator_get_levels: NULL argument");
-    NEED((unsigned long long)first_session + count <= a->max_sessions, "pcmb200_aggregator_get_levels: session range out of bounds");
-    CU(cudaSetDevice(ctx->device));
-    if (count) CU(cudaMemcpyAsync(levels_host, a->d_level + first_session, (size_t)count * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    CU(cudaStreamSynchronize(ctx->stream));
-    return PCMB200_OK;
-}
-
-// The flush plan.  Every session is a little sequential state machine (fill, half, lastSend), and
-// sessions are independent, so the plan is computed by T host threads that each own the sessions
-// in a contiguous block of session ids and scan the quanta list for them.  A session's j-th flush inside one push is
-// "round" j: the quanta of the frame that follows it are written into the half-buffer that held
-// frame j-1, which was converted at the end of round j-1 -- so appending round by round and
-// converting each round's frames before the next append never overwrites an unconverted frame.
-// A typical push has at most one flush per session: two append launches and one batch of frames.
-namespace {
-struct AggPlanShared {
-    pcmb200_aggregator *a; uint32_t n; const uint32_t *sessions; const double *arrival;
-    uint8_t *q_round;        // [n] round of every quantum
-    uint32_t *flush_nq;      // [n] the frame length in quanta, valid where quantum i flushes
-    uint32_t *flush_row;     // [n] ring row of that frame
-    unsigned long long *flush_bits;   // [(n + 63) / 64] bit i set <=> quantum i flushes
-};
-struct AggPlanThread { std::vector<AggUndo> undo; int status = PCMB200_OK; uint32_t max_round = 0, worst_session = 0; };
-
-// Phase 1: thread t looks at its share of the quanta list and sorts the indices into one bucket per
-// owner thread (so nobody scans the whole list).  Phase 2: the owner walks the buckets addressed to
-// it, producer by producer, which is ascending index order, and runs the session state machines.
-void agg_plan_worker(const AggPlanShared &sh, uint32_t t, uint32_t T, uint32_t own_shift, AggPlanThread &out,
-                     std::vector<uint8_t> &flushes_of, std::vector<std::vector<uint32_t>> &buckets, std::atomic<uint32_t> &arrived)
-{
-    pcmb200_aggregator *a = sh.a;
-    const uint32_t i0 = (uint32_t)((unsigned long long)sh.n * t / T), i1 = (uint32_t)((unsigned long long)sh.n * (t + 1) / T);
-    for (uint32_t o = 0; o < T; o++) buckets[(size_t)t * T + o].clear();
-    for (uint32_t i = i0; i < i1; i++) {
-        const uint32_t s = sh.sessions[i];
-        if (s > out.worst_session) out.worst_session = s;
-        if (s < a->max_sessions) buckets[(size_t)t * T + (s >> own_shift)].push_back(i);   // ids out of range: nobody's
-    }
-    arrived.fetch_add(1, std::memory_order_acq_rel);          // barrier between the phases
-    while (arrived.load(std::memory_order_acquire) < T) std::this_thread::yield();
-
-    for (uint32_t p = 0; p < T; p++) {
-        for (const uint32_t i : buckets[(size_t)p * T + t]) {
-            const uint32_t s = sh.sessions[i];
-            if (a->touched[s] != a->push_epoch) {   // first quantum of this session in this push: remember its state
-                a->touched[s] = a->push_epoch;
-                out.undo.push_back({s, a->fill[s], a->half[s], a->last_send[s]});
-            }
-            const uint8_t h = a->half[s];
-            if (a->fill[s] >= a->half_quanta) { out.status = PCMB200_ERR_CAPACITY; return; }
-            const uint8_t round = flushes_of[s];
-            a->h_slot[i] = (s * 2u + h) * a->half_quanta + a->fill[s];
-            sh.q_round[i] = round;
-            a->fill[s]++;
-            // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
-            if (sh.arrival[i] - a->last_send[s] >= a->desired_ms) {
-                if (round == 255) { out.status = PCMB200_ERR_CAPACITY; return; }
-                sh.flush_nq[i] = a->fill[s];
-                sh.flush_row[i] = s * 2u + h;
-                __atomic_fetch_or(&sh.flush_bits[i >> 6], 1ull << (i & 63u), __ATOMIC_RELAXED);
-                a->half[s] = h ^ 1u;
-                a->fill[s] = 0;
-                a->last_send[s] = sh.arrival[i];                     // App.tsx:287
-                flushes_of[s] = round + 1;
-            }
-            if (round > out.max_round) out.max_round = round;
-        }
-    }
-}
-}  // namespace
-
-extern "C" int pcmb200_aggregator_push(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n_quanta,
-                                       const uint32_t *sessions, const double *arrival_ms, const float *samples,
-                                       int samples_mem, int16_t *out, size_t out_capacity, int out_mem,
-                                       uint32_t *frame_session, uint32_t *frame_len, unsigned long long *frame_offset,
-                                       uint32_t max_frames, uint32_t *n_frames)
-{
-    NEED(ctx && a && n_frames, "pcmb200_aggregator_push: NULL argument");
-    *n_frames = 0;
-    if (n_quanta == 0) return PCMB200_OK;
-    NEED(sessions && arrival_ms && samples && out, "pcmb200_aggregator_push: NULL buffer");
-    NEED((samples_mem == PCMB200_MEM_HOST || samples_mem == PCMB200_MEM_DEVICE) &&
-         (out_mem == PCMB200_MEM_HOST || out_mem == PCMB200_MEM_DEVICE), "pcmb200_aggregator_push: bad mem kind");
-    NEED(n_quanta <= a->max_push, "pcmb200_aggregator_push: more quanta than max_push_quanta");
-    CU(cudaSetDevice(ctx->device));
-    CU(cudaEventSynchronize(a->uploaded));   // the previous push's index upload has left the pinned staging
-
-    // ---- plan on the host ----
-    try {
-        a->flush_nq.resize(n_quanta); a->flush_row.resize(n_quanta);
-        a->flush_bits.assign((n_quanta + 63) / 64, 0ull);
-        a->flushes_of.assign(a->max_sessions, 0);
-        if (a->touched.size() != a->max_sessions) a->touched.assign(a->max_sessions, 0);
-        a->push_epoch++;
-    } catch (const std::bad_alloc &) { return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_push: host allocation failed"); }
-    AggPlanShared sh{a, n_quanta, sessions, arrival_ms, a->h_round, a->flush_nq.data(), a->flush_row.data(), a->flush_bits.data()};
-    uint32_t T = 1;
-    if (n_quanta >= 65536) {
-        const uint32_t hw = std::thread::hardware_concurrency();
-        while (T * 2 <= hw && T < 16) T *= 2;
-    }
-    uint32_t own_shift = 0;   // a thread owns sessions [t << own_shift, (t + 1) << own_shift)
-    while (((unsigned long long)T << own_shift) < a->max_sessions) own_shift++;
-    std::vector<AggPlanThread> th(T);
-    if (a->buckets.size() < (size_t)T * T) a->buckets.resize((size_t)T * T);
-    std::atomic<uint32_t> arrived{0};
-    if (T == 1) {
-        agg_plan_worker(sh, 0, 1, own_shift, th[0], a->flushes_of, a->buckets, arrived);
-    } else {
-        std::vector<std::thread> pool;
-        for (uint32_t t = 0; t < T; t++)
-            pool.emplace_back([&, t] { agg_plan_worker(sh, t, T, own_shift, th[t], a->flushes_of, a->buckets, arrived); });
-        for (auto &p : pool) p.join();
-    }
-    int status = PCMB200_OK;
-    std::string why;
-    uint32_t max_round = 0;
-    for (auto &t : th) {
-        if (t.status) { status = t.status; why = "a session's buffer exceeds max_frame_quanta (no flush arrived), or it flushed > 255 times"; }
-        if (t.max_round > max_round) max_round = t.max_round;
-        if (t.worst_session >= a->max_sessions) {   // such ids belong to no thread: no state was touched for them
-            status = PCMB200_ERR_INVALID; why = "session id out of range";
-        }
-    }
-    // frames in flush (= quantum) order; output offsets are assigned in that order
-    std::vector<AggFrame> frames;
-    unsigned long long off = 0;
-    if (status == PCMB200_OK) {
-        std::vector<size_t> len_of(a->half_quanta + 1, (size_t)-1);   // output length per frame length (in quanta)
-        for (size_t w = 0; w < a->flush_bits.size() && status == PCMB200_OK; w++)
-          for (unsigned long long bits = a->flush_bits[w]; bits; bits &= bits - 1) {
-            const uint32_t i = (uint32_t)(w * 64 + (size_t)__builtin_ctzll(bits));
-            size_t &n_out_c = len_of[a->flush_nq[i]];
-            if (n_out_c == (size_t)-1) resample_len((size_t)a->flush_nq[i] * a->quantum, a->rate, &n_out_c);
-            const size_t n_out = n_out_c;
-            if (frames.size() >= max_frames) { status = PCMB200_ERR_CAPACITY; why = "more flushed frames than max_frames"; break; }
-            if (off + n_out > out_capacity || (out_mem == PCMB200_MEM_HOST && off + n_out > a->out_cap)) {
-                status = PCMB200_ERR_CAPACITY; why = "flushed frames exceed the output capacity"; break;
-            }
-            frames.push_back({a->flush_row[i], a->flush_nq[i], sessions[i], off, (uint32_t)n_out, a->h_round[i]});
-            off += (n_out + 7u) & ~(size_t)7u;                  // frames start on 16-byte boundaries
-        }
-    }
-    if (status != PCMB200_OK) {   // roll the sessions back: the push is rejected as a whole
-        for (auto &t : th)
-            for (size_t k = t.undo.size(); k-- > 0;) {
-                const AggUndo &u = t.undo[k];
-                a->fill[u.s] = u.fill; a->half[u.s] = u.half; a->last_send[u.s] = u.last;
-            }
-        return fail(ctx, status, "pcmb200_aggregator_push: " + why);
-    }
-    // launch order of the frames: by round, then by length class (stable)
-    std::vector<uint32_t> order(frames.size());
-    {   // counting sort by (round, frame length): stable, O(frames)
-        const size_t classes = (size_t)(max_round + 1) * (a->half_quanta + 1);
-        std::vector<uint32_t> start(classes + 1, 0);
-        for (const AggFrame &f : frames) start[(size_t)f.round * (a->half_quanta + 1) + f.nq + 1]++;
-        for (size_t c = 0; c < classes; c++) start[c + 1] += start[c];
-        for (uint32_t f = 0; f < frames.size(); f++)
-            order[start[(size_t)frames[f].round * (a->half_quanta + 1) + frames[f].nq]++] = f;
-    }
-    for (size_t k = 0; k < order.size(); k++) {
-        a->h_src_row[k] = frames[order[k]].src_row;
-        a->h_dst_off[k] = frames[order[k]].off;
-    }
-
-    // ---- enqueue: uploads, then per round append + one pick/encode launch per length class ----
-    cudaStream_t st = ctx->stream;
-    const float *d_samples = samples;
-    if (samples_mem == PCMB200_MEM_HOST) {
-        CU(cudaMemcpyAsync(a->d_stage, samples, (size_t)n_quanta * a->quantum * sizeof(float), cudaMemcpyHostToDevice, st));
-        d_samples = a->d_stage;
-    }
-    CU(cudaMemcpyAsync(a->d_slot, a->h_slot, (size_t)n_quanta * 4, cudaMemcpyHostToDevice, st));
-    CU(cudaMemcpyAsync(a->d_round, a->h_round, (size_t)n_quanta, cudaMemcpyHostToDevice, st));
-    if (!frames.empty()) {
-        CU(cudaMemcpyAsync(a->d_src_row, a->h_src_row, frames.size() * 4, cudaMemcpyHostToDevice, st));
-        CU(cudaMemcpyAsync(a->d_dst_off, a->h_dst_off, frames.size() * 8, cudaMemcpyHostToDevice, st));
-    }
-    CU(cudaEventRecord(a->uploaded, st));
-    int16_t *d_out = out_mem == PCMB200_MEM_DEVICE ? out : a->d_out;
-    const size_t half_floats = (size_t)a->half_quanta * a->quantum;
-    uint32_t R = 0;
-    const bool is_int = integer_ratio(a->rate, &R);
-    size_t k = 0;
-    for (uint32_t round = 0; round <= max_round; round++) {
-        {
-            const int grid = grid_for(ctx, (n_quanta + 7) / 8);
-            k_append_quanta<<<grid, 256, 0, st>>>(d_samples, a->d_slot, a->ring, n_quanta, a->quantum,
-                                                  max_round ? a->d_round : nullptr, (uint8_t)round);
-            ctx->launches++;
-        }
-        while (k < order.size() && frames[order[k]].round == round) {
-            size_t k1 = k;
-            const uint32_t nq = frames[order[k]].nq;
-            while (k1 < order.size() && frames[order[k1]].round == round && frames[order[k1]].nq == nq) k1++;
-            const uint32_t n_in = nq * a->quantum, n_out = frames[order[k]].n_out;
-            if (n_out > 0) {
-                const uint32_t *lut = nullptr;
-                if (!is_int && a->rate != 16000.0) {
-                    int s2 = get_lut(ctx, n_in, a->rate, n_out, &lut);
-                    if (s2) return s2;
-                }
-                const unsigned long long n_pairs = (unsigned long long)(k1 - k) * ((n_out + 1u) / 2u);
-                const unsigned long long tiles = (n_pairs + 1023) / 1024;
-                const int grid = grid_for(ctx, tiles);
-                k_rows_pick_encode<4><<<grid, 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, d_out, a->d_dst_off + k, n_in,
-                                                            n_out, lut, is_int ? R : 1u, n_pairs);
-                ctx->launches++;
-            }
-            if (a->meter) {   // App.tsx:267-271 over the quanta of these frames, in session order
-                const uint32_t nf = (uint32_t)(k1 - k);
-                k_rows_meter<<<grid_for(ctx, (nf + 7) / 8), 256, 0, st>>>(a->ring, half_floats, a->d_src_row + k, nf, nq, a->quantum,
-                                                                        a->d_level);
-                ctx->launches++;
-            }
-            k = k1;
-        }
-    }
-    CU(cudaGetLastError());
-    for (size_t f = 0; f < frames.size(); f++) {
-        if (frame_session) frame_session[f] = frames[f].session;
-        if (frame_len) frame_len[f] = frames[f].n_out;
-        if (frame_offset) frame_offset[f] = frames[f].off;
-    }
-    *n_frames = (uint32_t)frames.size();
-    if (out_mem == PCMB200_MEM_HOST) {
-        if (off) CU(cudaMemcpyAsync(out, a->d_out, off * sizeof(int16_t), cudaMemcpyDeviceToHost, st));
-        CU(cudaStreamSynchronize(st));
-    } else if (samples_mem == PCMB200_MEM_HOST) {
-        CU(cudaEventSynchronize(a->uploaded));   // the caller's sample buffer is free again
-    }
-    return PCMB200_OK;
-}
+// Host side in pcm_aggregator.inl (same translation unit: it uses the context and the helpers above),
+// kernels in agg_kernels.cuh.
+#include "pcm_aggregator.inl"
 
 // ================================= allocation-free entry point =====================================
 // pcmb200_frames_encode_noalloc: the general pick + encode kernel (k_pick_encode) with its pick-index

@@ -588,6 +588,238 @@ k_tile_pick(const float *__restrict__ in, int16_t *__restrict__ out, uint32_t n_
     }
 }
 
+// ---- kernel 2c: frames + level meter, padded-row tiles (the fast meter path) ----------------------
+// Same job as kernel 2b with METER (frames out, level meter of App.tsx:267-271 fused in), rebuilt
+// around what ncu showed about 2b: it was ISSUE-bound (0.84 warp-instructions per input sample, 76 %
+// of the issue slots, HBM at 58 %), and more than half of those instructions were the meter loop's
+// bookkeeping -- lane skew against shared-memory bank conflicts (G+7 steps for G of work, one
+// address select per step) -- and its partly filled warps.  Here:
+//   * rows sit in shared memory at a pitch of an ODD number of 16-byte units (one bulk copy per row
+//     instead of one per tile).  Lane l of a warp takes quantum q of row (l mod K): the 8 lanes of an
+//     LDS.128 phase read the same granule of 8 consecutive rows, which now fall into 8 different
+//     bank groups.  No skew, no selects: the inner loop is LDS.128 + 4 x (2 IMAD, LEA.HI, VIADDMNMX,
+//     DFMA), fully unrolled for the 128-sample quantum;
+//   * the pad slot after every row holds a NaN, and table entries that point outside the input are
+//     redirected to it when the table is staged, so the gather has no per-pick range test;
+//   * integer ratios are compile-time (RT), so the 8 picks of a chunk are immediate offsets from one
+//     address; row / chunk splits use a host-made reciprocal instead of a division;
+//   * a partial last tile is handled in the kernel (no remainder launches).
+// The arithmetic (widen_abs_fast and its two escape hatches, rms_of, the Math.max chain) is
+// unchanged from kernel 2b, so the results stay bit-identical to the oracle.
+// Requirements (launcher): n_in % 4 == 0, quantum % 4 == 0, dense rows (pitch_in == n_in, pitch_out ==
+// n_out), in / out 16-byte aligned, K rows + table fit in shared memory.
+struct TileMeterGeom {
+    uint32_t n_in, n_out;
+    uint32_t K;              // rows per tile
+    uint32_t rows;           // rows of the batch (the last tile may be partial)
+    uint32_t pitch;          // shared-memory row pitch in floats: n_in + 4 or n_in + 8, (pitch / 4) odd
+    uint32_t stride;         // integer ratio when RT == 0 and no table
+    uint32_t magic_cpr;      // ceil(2^32 / (n_out / 8))  (n_out % 8 == 0 only); 0 stands for a divisor of 1
+    uint32_t magic_nout;     // ceil(2^32 / n_out)
+    uint32_t magic_K;        // ceil(2^32 / K)
+    uint32_t tile_stride_bytes;
+};
+
+// x / d for the small x of one tile, d folded into magic = ceil(2^32 / d) on the host (exact while
+// x * d < 2^32, which the launcher guarantees); magic == 0 encodes d == 1.
+__device__ __forceinline__ uint32_t div_magic(uint32_t x, uint32_t magic) { return magic ? __umulhi(x, magic) : x; }
+
+template <int RT, int STAGES>
+__global__ void __launch_bounds__(256)
+k_frames_meter(const float *__restrict__ in, int16_t *__restrict__ out, TileMeterGeom geo, unsigned long long n_tiles,
+               const uint32_t *__restrict__ lut, int hint, MeterArgs meter)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // layout: [STAGES][tile_stride_bytes] | table u32[n_out] (only if lut) | mbarriers | rms double[K * nq]
+    const uint32_t n_in = geo.n_in, n_out = geo.n_out, K = geo.K, P = geo.pitch;
+    uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)STAGES * geo.tile_stride_bytes);
+    const uint32_t tab_bytes = lut ? ((n_out * 4u + 15u) & ~15u) : 0u;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw + (size_t)STAGES * geo.tile_stride_bytes + tab_bytes);
+    double *rms_s = reinterpret_cast<double *>(bars + ((STAGES + 1) & ~1));
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t stride = RT > 0 ? (uint32_t)RT : geo.stride;
+    const bool rows_aligned = (n_out & 7u) == 0u;
+    const uint32_t cpr = n_out >> 3;
+    const uint32_t nq = meter.nq, Q = meter.quantum;
+
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) mbar_init(&bars[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (lut)   // picks outside the input (JS reads `undefined` -> NaN -> 0) go to the row's NaN pad slot
+        for (uint32_t i = threadIdx.x; i < n_out; i += blockDim.x) {
+            const uint32_t v = __ldg(lut + i);
+            tab[i] = v < n_in ? v : n_in;
+        }
+    for (uint32_t i = threadIdx.x; i < K * STAGES; i += blockDim.x) {   // the pad slots (bulk copies never touch them)
+        float *row = reinterpret_cast<float *>(smem_raw + (size_t)(i / K) * geo.tile_stride_bytes) + (size_t)(i % K) * P;
+        row[n_in] = __int_as_float(0x7FC00000);
+    }
+    __syncthreads();
+
+    // one bulk copy per row; a warp issues them, lane r takes rows r, r+32, ...
+    auto issue = [&](unsigned long long t, int s) {
+        const unsigned long long row0 = t * K;
+        const uint32_t nr = (uint32_t)((geo.rows - row0 < K) ? geo.rows - row0 : K);
+        if (lane == 0) mbar_expect_tx(&bars[s], nr * n_in * 4u);
+        __syncwarp();
+        float *dst = reinterpret_cast<float *>(smem_raw + (size_t)s * geo.tile_stride_bytes);
+        for (uint32_t r = lane; r < nr; r += 32u)
+            bulk_g2s(dst + (size_t)r * P, in + (row0 + r) * n_in, n_in * 4u, &bars[s]);
+    };
+    if (warp == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) {
+            const unsigned long long t = blockIdx.x + (unsigned long long)s * gridDim.x;
+            if (t < n_tiles) issue(t, s);
+        }
+    }
+
+    uint32_t it = 0;
+    for (unsigned long long t = blockIdx.x; t < n_tiles; t += gridDim.x, it++) {
+        const int s = it % STAGES;
+        const unsigned long long row0 = t * K;
+        const uint32_t nr = (uint32_t)((geo.rows - row0 < K) ? geo.rows - row0 : K);
+        const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * geo.tile_stride_bytes);
+        // session levels are needed only after the meter: fetch them now, the latency hides behind it
+        double lv_in = 0.0;
+        if (threadIdx.x < nr) lv_in = meter.state[row0 + threadIdx.x];
+        mbar_wait(&bars[s], (it / STAGES) & 1u);
+
+        // ---- frames: pick + encode + store -------------------------------------------------------
+        const unsigned long long first = row0 * n_out;
+        const uint32_t outs = nr * n_out;
+        if (rows_aligned) {
+            // rows are whole 8-sample chunks and start 16-byte aligned: chunk g = (row rr, chunk c)
+            const uint32_t n_chunks = nr * cpr;
+            for (uint32_t g = threadIdx.x; g < n_chunks; g += blockDim.x) {
+                const uint32_t rr = div_magic(g, geo.magic_cpr), c = g - rr * cpr;
+                const float *row = tile + rr * P;
+                int e[8];
+                if (lut) {
+                    const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
+                    const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
+                    e[0] = enc_s32(row[a.x]); e[1] = enc_s32(row[a.y]); e[2] = enc_s32(row[a.z]); e[3] = enc_s32(row[a.w]);
+                    e[4] = enc_s32(row[b.x]); e[5] = enc_s32(row[b.y]); e[6] = enc_s32(row[b.z]); e[7] = enc_s32(row[b.w]);
+                } else {
+                    const float *p = row + 8u * c * stride;
+#pragma unroll
+                    for (int j = 0; j < 8; j++) e[j] = enc_s32(p[j * stride]);
+                }
+                uint4 o4;
+                o4.x = pack_s16x2_sat(e[0], e[1]);
+                o4.y = pack_s16x2_sat(e[2], e[3]);
+                o4.z = pack_s16x2_sat(e[4], e[5]);
+                o4.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(out + first + (size_t)g * 8u, o4, hint);
+            }
+        } else {
+            // the tile's output is one flat run of `outs` samples starting anywhere: an aligned body of
+            // 8-sample chunks (which may straddle frames) plus < 8 samples before and after it
+            const unsigned long long body0 = (first + 7ull) & ~7ull;
+            const unsigned long long body1 = (first + outs) & ~7ull;
+            const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
+            const uint32_t head = n_body ? (uint32_t)(body0 - first) : outs;
+            auto pick = [&](uint32_t rr, uint32_t o) -> float {
+                const uint32_t i = lut ? tab[o] : o * stride;
+                return tile[rr * P + i];
+            };
+            for (uint32_t g = threadIdx.x; g < n_body; g += blockDim.x) {
+                const uint32_t f = head + 8u * g;
+                uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                int e[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    e[j] = enc_s32(pick(rr, o));
+                    if (++o == n_out) { o = 0; rr++; }
+                }
+                uint4 o4;
+                o4.x = pack_s16x2_sat(e[0], e[1]);
+                o4.y = pack_s16x2_sat(e[2], e[3]);
+                o4.z = pack_s16x2_sat(e[4], e[5]);
+                o4.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(out + body0 + (size_t)g * 8u, o4, hint);
+            }
+            const uint32_t tail0 = head + 8u * n_body, n_edge = head + (outs - tail0);
+            for (uint32_t k = threadIdx.x; k < n_edge; k += blockDim.x) {
+                const uint32_t f = k < head ? k : tail0 + (k - head);
+                const uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                out[first + f] = enc_s16(pick(rr, o));
+            }
+        }
+
+        // ---- level meter: lane <-> (quantum q, row r), w = q * K + r -----------------------------------
+        // The meter takes ceil(items / 32) of the block's 8 warps.  Which ones rotates with the tile
+        // index: a warp's scheduler is fixed by its index (warp % 4), so always using warps 0, 1, ...
+        // would load the same schedulers in every co-resident block and leave the others idle.
+        const uint32_t items = K * nq;
+        const uint32_t m_warps = (items + 31u) >> 5;
+        const uint32_t rot = m_warps < 8u ? ((uint32_t)t * m_warps) & 7u : 0u;
+        for (uint32_t w = (((warp + 8u - rot) & 7u) << 5) + lane; w < ((items + 31u) & ~31u); w += blockDim.x) {
+            const uint32_t q = div_magic(w, geo.magic_K), r = w - q * K;
+            if (w >= items || r >= nr) continue;            // partial tile / partly filled last warp
+            const float4 *src4 = reinterpret_cast<const float4 *>(tile + r * P + q * Q);
+            double sum = 0.0;
+            uint32_t lowest = 0xFFFFFFFFu;                    // min over samples of (2|x| bits - 2), zeros wrap to the top
+            auto four = [&](const float4 v) {
+                const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const uint32_t b = __float_as_uint(xs[j]);
+                    const uint32_t t2 = b << 1;                               // sign gone
+                    lowest = min(lowest, t2 - 2u);
+                    const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;   // (|x| bits >> 3) + re-bias
+                    const double x = __hiloint2double((int)hi, (int)(b << 29));
+                    sum = __fma_rn(x, x, sum);
+                }
+            };
+            if (Q == 128u) {
+#pragma unroll 8
+                for (uint32_t g = 0; g < 32u; g++) four(src4[g]);
+            } else {
+                for (uint32_t g = 0; g < (Q >> 2); g++) four(src4[g]);
+            }
+            // widen_abs_fast's escape hatches: a nonzero sample below 2^-60 (denormals included), or an
+            // Inf / NaN (shows up as an impossible sum) -> redo the quantum with the exact widening
+            bool odd = lowest < (2u * 0x21800000u - 2u);
+            odd |= !(sum < __hiloint2double(0x4F900000, 0));                  // 2^250; also true for NaN
+            if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;             // < 2^-200: every sample was zero
+            if (odd) {
+                sum = 0.0;
+                const float *src = reinterpret_cast<const float *>(src4);
+                for (uint32_t k = 0; k < Q; k++) {
+                    const double x = widen_abs(src[k]);
+                    sum = __fma_rn(x, x, sum);
+                }
+            }
+            rms_s[w] = rms_of(sum, Q);
+        }
+        __syncthreads();
+        for (uint32_t rr = threadIdx.x; rr < nr; rr += blockDim.x) {
+            const unsigned long long row = row0 + rr;
+            double lv = rr == threadIdx.x ? lv_in : meter.state[row];
+            // Math.max(rms, level * 0.85): NaN if either is NaN, and a NaN level stays NaN
+            bool poisoned = lv != lv;
+            for (uint32_t q = 0; q < nq; q++) {
+                const double rms = rms_s[q * K + rr];
+                const uint32_t hi = (uint32_t)__double2hiint(rms) & 0x7FFFFFFFu;
+                poisoned |= hi > 0x7FF00000u || (hi == 0x7FF00000u && __double2loint(rms) != 0);
+                const double dec = __dmul_rn(lv, 0.85);
+                lv = rms > dec ? rms : dec;
+                if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
+                if (meter.levels) meter.levels[row * nq + q] = lv;
+            }
+            meter.state[row] = lv;
+        }
+        __syncthreads();   // everyone is done with stage s (tile and rms_s)
+        if (warp == 0) {
+            const unsigned long long tn = t + (unsigned long long)STAGES * gridDim.x;
+            if (tn < n_tiles) issue(tn, s);
+        }
+    }
+}
+
 // ---- kernel 3: resampleTo16k alone (Float32 -> Float32 picks; App.tsx:18-32) ------------------------
 // Only for signature parity with the reference's stand-alone function; the batched product path is
 // the fused kernels above.  Bit patterns are moved as 32-bit words so NaN payloads survive.

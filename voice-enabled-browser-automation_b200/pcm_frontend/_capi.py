@@ -59,6 +59,9 @@ SYMBOLS = {
     "pcmb200_aggregator_create": (_int, [_vp, _u32, _dbl, _u32, _dbl, _u32, _u32, _sz, _P(_vp)]),
     "pcmb200_aggregator_destroy": (_int, [_vp, _vp]),
     "pcmb200_aggregator_reset_session": (_int, [_vp, _vp, _u32, _dbl]),
+    "pcmb200_aggregator_reset_range": (_int, [_vp, _vp, _u32, _u32, _dbl]),
+    "pcmb200_aggregator_push_device": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _vp, _sz, _vp, _vp, _vp, _u32]),
+    "pcmb200_aggregator_wait": (_int, [_vp, _vp, _P(_u32), _P(_sz)]),
     "pcmb200_aggregator_set_meter": (_int, [_vp, _vp, _int]),
     "pcmb200_aggregator_get_levels": (_int, [_vp, _vp, _u32, _u32, _vp]),
     "pcmb200_aggregator_push": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _int, _vp, _sz, _int, _vp, _vp, _vp, _u32, _P(_u32)]),

@@ -355,6 +355,26 @@ class Aggregator:
         check(self.ctx._L.pcmb200_aggregator_reset_session(self.ctx.handle, self.handle, int(session), float(now_ms)),
               self.ctx.handle)
 
+    def reset_range(self, first_session: int, count: int, now_ms: float):
+        """Initial state (App.tsx:148-157) for `count` sessions at once."""
+        check(self.ctx._L.pcmb200_aggregator_reset_range(self.ctx.handle, self.handle, int(first_session), int(count),
+                                                         float(now_ms)), self.ctx.handle)
+
+    def push_device(self, n: int, sessions_ptr: int, arrival_ptr: int, samples_ptr: int, out_ptr: int, out_capacity: int,
+                    frame_session_ptr: Optional[int] = None, frame_len_ptr: Optional[int] = None,
+                    frame_offset_ptr: Optional[int] = None, max_frames: Optional[int] = None):
+        """Everything device-resident, asynchronous (pcmb200_aggregator_push_device); collect with wait()."""
+        check(self.ctx._L.pcmb200_aggregator_push_device(self.ctx.handle, self.handle, int(n), int(sessions_ptr), int(arrival_ptr),
+                                                         int(samples_ptr), int(out_ptr), int(out_capacity),
+                                                         frame_session_ptr, frame_len_ptr, frame_offset_ptr,
+                                                         int(n if max_frames is None else max_frames)), self.ctx.handle)
+
+    def wait(self) -> Tuple[int, int]:
+        """(n_frames, output samples incl. per-frame padding) of the pending push; raises if it was rejected."""
+        nf, ns = C.c_uint32(0), C.c_size_t(0)
+        check(self.ctx._L.pcmb200_aggregator_wait(self.ctx.handle, self.handle, C.byref(nf), C.byref(ns)), self.ctx.handle)
+        return int(nf.value), int(ns.value)
+
     def push(self, sessions: np.ndarray, arrival_ms: np.ndarray, samples: np.ndarray):
         """sessions[n] uint32, arrival_ms[n] float64, samples[n, quantum] float32 (arrival order).
         Returns [(session, int16 frame), ...] in flush order."""
