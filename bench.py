@@ -53,6 +53,7 @@ def parse_args(argv=None):
                     help="strong (default, BASELINE configs[3]): --sessions are sharded over the GPUs; "
                          "weak: every GPU holds --sessions sessions")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true", help="do not let consecutive ticks overlap on the GPU (overlap_ticks=0)")
     ap.add_argument("--wc", type=int, default=0, help="1: e2e input ring in write-combined pinned memory")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="CPU work budget of the cpu_baseline leg")
@@ -286,6 +287,28 @@ def cpu_baseline_leg(x, n_in, rate, cpu_seconds):
                       f"this image), {cores} threads, same input bits as the GPU run"}, out
 
 
+def node_pin():
+    """If a Node binary AND the reference's source tree are both present, run the reference's own
+    JavaScript (sliced out of App.tsx at run time, tools/pin_with_node.mjs) on the committed vectors and
+    time config 1 with it.  Neither exists on this image or on the GPU boxes so far."""
+    import shutil
+    import subprocess
+    exe = shutil.which("node")
+    ref = os.environ.get("PCMB200_REFERENCE_ROOT", "/root/reference")
+    if not exe:
+        return {"available": False, "why": "no `node` on PATH"}
+    if not os.path.exists(os.path.join(ref, "apps", "web", "src", "App.tsx")):
+        return {"available": False, "why": f"node found ({exe}) but no reference tree at {ref} (set PCMB200_REFERENCE_ROOT)"}
+    try:
+        out = subprocess.run([exe, os.path.join(ROOT, "tools", "pin_with_node.mjs"), ref, "--bench"], capture_output=True,
+                             text=True, timeout=600)
+        bench = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
+        return {"available": True, "parity_pinned": out.returncode == 0 and "PARITY PINNED" in out.stdout,
+                "config1": bench[-1] if bench else None, "stderr_tail": out.stderr[-300:]}
+    except Exception as e:  # noqa: BLE001
+        return {"available": True, "error": repr(e)}
+
+
 def run_reference(args):
     """The reference's own CPU path for the same workload: every step converts the full tick (all
     --sessions sessions) with the C port of App.tsx:7-32,281-282 on all host threads.  Rank 0 only."""
@@ -309,13 +332,15 @@ def run_reference(args):
     sample = (f"each step = {rows} sessions x {n_in} samples ({whole}), oracle/pcm_oracle.c port of "
               f"App.tsx:7-32,281-282, {cores} host threads")
     per_gpu = args.sessions if args.scaling == "weak" else -(-args.sessions // world)
+    node = node_pin()
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
             "data": "synthetic sine+noise (oracle_synth_fill: the device generator's recipe and noise bits, host libm sine)",
             "config": config_dict(args, world, n_in, n_out, per_gpu, args.sessions),
-            "arm": {"runtime": "Node unavailable on this image: C port of the reference's JS (kind=port)",
-                    "sessions_per_step": rows, "host_threads": cores},
+            "arm": {"runtime": "C port of the reference's JS (kind=port), all host threads; the reference itself is "
+                               "single-threaded TypeScript for a browser",
+                    "sessions_per_step": rows, "host_threads": cores, "node": node},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -334,6 +359,11 @@ def run_b200(args):
     bound_cpus, numa_note = bind_to_gpu_numa(local_rank) if world > 1 else (0, "single rank: no CPU binding")
     ctx = pcm_frontend.Context(local_rank)          # raises if the CUDA library / device is missing
     dist = Dist(world, True, local_rank)
+    # Ticks are independent frames in rotating buffers, so consecutive launches may overlap on the GPU
+    # (programmatic dependent launch: the next tick's blocks fill the previous tick's draining last wave).
+    # That matters for small shards (a 131 072-session tick is 85 us: +6 %), not for the 2^20-session one.
+    if not args.no_overlap:
+        ctx.tune(overlap_ticks=1)
     if args.tune:
         ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
 
@@ -478,6 +508,8 @@ def run_b200(args):
                 "arm": {"numa": numa_note,
                         "l2": f"inputs larger than L2: {n_buf} rotating tick buffers of {algo_bytes / 1e9:.2f} GB each",
                         "tune": args.tune or "defaults", "sessions_rank0": S,
+                        "tick_overlap": "off" if args.no_overlap else "on: consecutive ticks may overlap on the GPU (programmatic "
+                                        "dependent launch); kernel_ms is the timed region / launches",
                         "arithmetic": "f32 in, round-toward-zero fp32 product (exact), saturating s16 out; bit-exact vs the f64 reference"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches_all,
                 "per_rank_ms": per_rank_ms, "sustained": sustained,

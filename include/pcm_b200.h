@@ -220,6 +220,25 @@ PCMB200_API int pcmb200_aggregator_wait(pcmb200_ctx *ctx, pcmb200_aggregator *ag
 #define PCMB200_KEEPALIVE_PERIOD_MS 2000u
 PCMB200_API int pcmb200_keepalive_frame(int16_t *out, size_t capacity, size_t *n);
 PCMB200_API int pcmb200_wire_is_little_endian(void);
+/* Per-session wire payloads over a converted batch: the reference sends one WebSocket binary message
+ * per frame, payload = pcm16.buffer (App.tsx:284), relayed untouched (apps/voice/src/server.ts:260-265)
+ * into sendAudio (deepgram.ts:55-58).  Row r of a [rows][pitch_out] int16 block is the payload
+ * (byte_offset[r], byte_length[r] = 2 * n_out) of that block: hand out views, not copies.
+ * _frames does the same for an aggregator push (frame_offset / frame_len in samples). */
+PCMB200_API int pcmb200_egress_table(uint32_t rows, size_t n_out, size_t pitch_out, unsigned long long *byte_offset,
+                                     uint32_t *byte_length);
+PCMB200_API int pcmb200_egress_table_frames(uint32_t n_frames, const unsigned long long *frame_offset, const uint32_t *frame_len,
+                                            unsigned long long *byte_offset, uint32_t *byte_length);
+/* Keep-alive schedule of a fleet (App.tsx:291-296: setInterval(send 1600 zeros if the socket is open, 2000),
+ * armed by start(), cleared by stop() :309-312) on an injected clock.  start_ms[s]: when session s armed
+ * its timer (NaN = not armed); ticks_done[s] (in/out): timer ticks already served; socket_open[s]: the
+ * readyState === OPEN test.  Writes the sessions that must be sent a keep-alive frame now (each at most
+ * once per poll; elapsed ticks are marked done also for closed sockets, whose callback returns early).
+ * PCMB200_ERR_CAPACITY (and no change) if more than max_due are due.  period_ms is
+ * PCMB200_KEEPALIVE_PERIOD_MS in the reference. */
+PCMB200_API int pcmb200_keepalive_due(double now_ms, uint32_t n_sessions, const double *start_ms,
+                                      unsigned long long *ticks_done, const uint8_t *socket_open, double period_ms,
+                                      uint32_t *due_sessions, uint32_t max_due, uint32_t *n_due);
 
 /* ---- per-tick replay --------------------------------------------------------------------------- */
 
@@ -244,6 +263,10 @@ PCMB200_API int pcmb200_tick_graph_destroy(pcmb200_ctx *ctx, pcmb200_tick_graph 
  * session = row0 + row. */
 PCMB200_API int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out_device, size_t pitch, uint32_t rows,
                                    uint32_t n, double rate, uint64_t seed, uint64_t row0);
+/* Bare copy probe: `reps` rounds of one pinned H2D copy (h2d_bytes) and one pinned D2H copy (d2h_bytes)
+ * in flight together, no kernels: the platform ceiling of the host-resident path (tools/pcie_probe.py
+ * runs it from N processes at once).  *milliseconds = device time of all `reps` rounds. */
+PCMB200_API int pcmb200_pcie_probe(pcmb200_ctx *ctx, size_t h2d_bytes, size_t d2h_bytes, int reps, float *milliseconds);
 /* CUDA-event stopwatch on the context's stream: everything the context enqueues between start and
  * stop (the pipelined host path included) is inside the measured interval. */
 PCMB200_API int pcmb200_timer_start(pcmb200_ctx *ctx);
@@ -252,7 +275,12 @@ PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
  * block), "blocks_per_sm" (0 = one tile per block; > 0 = capped, looping grid), "unroll", "path"
  * (0 auto, 1 general kernel only, 2 general path with the tile-staged kernel), "coalesced", "tile",
  * "tile_kb", "stages", "meter_tile_kb", "meter_stages", "occupancy", "store_hint",
- * "slice_bytes" (host pipeline slice). */
+ * "slice_bytes" (host pipeline slice), "meter_kernel", "ws_smem_kb", "ws_consumers", "ws_depth", "ws_rows".
+ * "overlap_ticks" = 1 changes behaviour, not just speed: consecutive device-resident dense integer-ratio
+ * calls on this context may then OVERLAP on the GPU (the next tick's blocks start while the previous
+ * tick's last wave drains; programmatic dependent launch).  Only for callers whose consecutive calls
+ * are independent (different frames in different buffers); copies, pcmb200_sync and the stopwatch still
+ * wait for everything. */
 PCMB200_API int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value);
 
 /* ---- allocation-free variant ------------------------------------------------------------------ */

@@ -55,6 +55,8 @@ def lib() -> C.CDLL:
         L.oracle_aggregator_plan.argtypes = [f64p, C.c_size_t, C.c_double, f64p, u8p]
         L.oracle_keepalive_frame.restype = C.c_size_t
         L.oracle_keepalive_frame.argtypes = [i16p]
+        L.oracle_keepalive_timer.restype = C.c_size_t
+        L.oracle_keepalive_timer.argtypes = [C.c_double, C.c_double, f64p, C.c_size_t, u8p, u8p]
         L.oracle_synth_fill.restype = None
         L.oracle_synth_fill.argtypes = [f32p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_double, C.c_uint64, C.c_uint64, C.c_int]
         _lib = L
@@ -146,3 +148,12 @@ def synth_fill(rows: int, n: int, rate: float, seed: int = 0x5EED, row0: int = 0
     if rows and n:
         lib().oracle_synth_fill(_p(out, C.c_float), n, rows, n, float(rate), seed, row0, threads)
     return out
+
+
+def keepalive_timer(start_ms: float, polls: np.ndarray, socket_open: np.ndarray, period_ms: float = 2000.0) -> np.ndarray:
+    """App.tsx:291-296 for one session: which of the polls send a keep-alive frame (uint8 per poll)."""
+    polls = np.ascontiguousarray(polls, dtype=np.float64)
+    op = np.ascontiguousarray(socket_open, dtype=np.uint8)
+    sent = np.zeros(polls.size, dtype=np.uint8)
+    lib().oracle_keepalive_timer(float(start_ms), float(period_ms), _p(polls, C.c_double), polls.size, _p(op, C.c_uint8), _p(sent, C.c_uint8))
+    return sent

@@ -307,3 +307,26 @@ ORACLE_API void oracle_synth_fill(float *out, size_t pitch, size_t rows, size_t 
     free(jobs);
     free(tid);
 }
+
+/* App.tsx:291-296 keep-alive TIMER of one session on an injected clock, event by event: the timer
+ * armed at start_ms fires at start_ms + k * 2000 (k = 1, 2, ...); the host looks at its timers at the
+ * times polls[0..n_polls) (ascending).  A poll runs the callback once if at least one firing time has
+ * passed since the last poll that ran it (a blocked timer's ticks coalesce), and the callback sends
+ * only if the socket is open at that poll.  sent[p] = 1 when poll p sends a keep-alive frame.
+ * Returns the number of frames sent.  Written as a simulation of firing times, deliberately not as
+ * the closed form the library uses. */
+ORACLE_API size_t oracle_keepalive_timer(double start_ms, double period_ms, const double *polls, size_t n_polls,
+                                         const uint8_t *socket_open, uint8_t *sent)
+{
+    size_t frames = 0;
+    unsigned long long next_k = 1;                  /* the next firing not yet consumed */
+    for (size_t p = 0; p < n_polls; p++) {
+        int fired = 0;
+        /* consume every firing time that is <= this poll.  A firing is "k periods after the start"; whether
+         * it has passed is decided on the elapsed time, the way a timer counts intervals */
+        while ((polls[p] - start_ms) / period_ms >= (double)next_k) { next_k++; fired = 1; }
+        sent[p] = 0;
+        if (fired && socket_open[p]) { sent[p] = 1; frames++; }
+    }
+    return frames;
+}

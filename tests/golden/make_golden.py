@@ -73,6 +73,77 @@ def js_resample_to_16k(samples, rate):
     return [samples[i] if i < len(samples) else math.nan for i in js_pick_indices(len(samples), rate)]
 
 
+# ---- 0. a THIRD derivation, integers only (no hardware floating point anywhere) ----------------
+# js_float_to_16bit_pcm above and oracle/pcm_oracle.c both lean on the machine's IEEE-754 unit.  These
+# two functions redo the same semantics with Python integers: the float32 is taken apart into sign,
+# exponent and significand, the product with 0x7fff / 0x8000 is an exact integer times a power of two,
+# and ToInt16's truncation is a shift.  The binary64 running sum of resampleTo16k is redone with a
+# software round-to-nearest-even addition.  tests/test_golden_integer.py checks that all three agree
+# on the committed fixtures.
+def int_float_to_16bit_pcm_bits(bits: int) -> int:
+    """floatTo16BitPCM (App.tsx:7-16) of one float32 given as its bit pattern, integers only."""
+    sign, e, frac = bits >> 31, (bits >> 23) & 0xFF, bits & 0x7FFFFF
+    if e == 0xFF:
+        if frac:                       # NaN: both comparisons false, NaN * 0x7fff = NaN, ToInt16(NaN) = 0
+            return 0
+        return -32768 if sign else 32767           # +-Inf clamps to +-1
+    if e == 0:
+        m, ex = frac, -149                          # denormal: frac * 2^-149
+    else:
+        m, ex = frac | 0x800000, e - 150           # (1.frac) * 2^(e-127) = m * 2^(e-150)
+    # |s| > 1  <=>  m * 2^ex > 1: clamp (App.tsx:11-12)
+    if ex >= 0 or m > (1 << -ex):
+        return -32768 if sign else 32767
+    c = 0x8000 if (sign and m != 0) else 0x7FFF     # `s < 0` is false for -0 (App.tsx:13)
+    p = m * c                                       # exact: |v| = p * 2^ex with ex < 0
+    t = p >> -ex                                    # truncate toward zero (ToInt16 of a finite |v| <= 32768)
+    return -t if sign else t
+
+
+def soft_add_f64(a_bits: int, b_bits: int) -> int:
+    """IEEE-754 binary64 addition of two non-negative finite doubles, round to nearest even, integers only."""
+    def unpack(x):
+        e, f = (x >> 52) & 0x7FF, x & ((1 << 52) - 1)
+        return (f, -1074) if e == 0 else (f | (1 << 52), e - 1075)
+    (ma, ea), (mb, eb) = unpack(a_bits), unpack(b_bits)
+    e = min(ea, eb)
+    m = (ma << (ea - e)) + (mb << (eb - e))         # exact sum = m * 2^e
+    if m == 0:
+        return 0
+    shift = max(m.bit_length() - 53, -1074 - e if e < -1074 else 0)
+    if shift > 0:
+        rem, half = m & ((1 << shift) - 1), 1 << (shift - 1)
+        m >>= shift
+        e += shift
+        if rem > half or (rem == half and (m & 1)):
+            m += 1
+            if m.bit_length() > 53:
+                m >>= 1
+                e += 1
+    while m.bit_length() < 53 and e > -1074:        # normalise (exact)
+        m <<= 1
+        e -= 1
+    if m.bit_length() < 53:                          # subnormal result
+        return m
+    return ((e + 1075) << 52) | (m & ((1 << 52) - 1))
+
+
+def int_pick_indices(n: int, rate: int):
+    """resampleTo16k's pick indices (App.tsx:23-30) with the running sum done by soft_add_f64.  The
+    two divisions (rate / 16000 and n / ratio) are single correctly-rounded operations that Python's
+    integer-to-float true division reproduces; what accumulates -- the sum -- is done in integers."""
+    ratio = rate / 16000
+    new_len = math.floor(n / ratio)
+    rb = struct.unpack("<Q", struct.pack("<d", ratio))[0]
+    pos, idx = 0, []
+    for _ in range(new_len):
+        e, f = (pos >> 52) & 0x7FF, pos & ((1 << 52) - 1)
+        m, ex = (f, -1074) if e == 0 else (f | (1 << 52), e - 1075)
+        idx.append(m << ex if ex >= 0 else m >> -ex)           # Math.floor of a non-negative double
+        pos = soft_add_f64(pos, rb)
+    return idx
+
+
 # ---- 1. hand-stated value table (SURVEY.md 8a-1) + computed hazard cases ---------------
 VALUE_TABLE = [  # (description, float32 bit pattern, expected int16) -- expectations written by hand
     ("1.0", 0x3F800000, 32767), ("-1.0", 0xBF800000, -32768),
@@ -172,6 +243,22 @@ def make_frame_kat():
         meta.append({"key": key, "rate": rate, "n_in": n_in, "rows": rows, "n_out": js_resample_len(n_in, rate)})
     blobs["meta"] = np.frombuffer(json.dumps(meta).encode(), dtype=np.uint8)
     np.savez_compressed(os.path.join(HERE, "frames_kat.npz"), **blobs)
+    write_frames_raw(meta, blobs)
+
+
+def write_frames_raw(meta, blobs):
+    """The same frame fixtures as flat little-endian files, for tools/pin_with_node.mjs (Node has no npz
+    reader): frames_kat_in.f32 / frames_kat_out.s16 hold the rows back to back in `meta` order and
+    frames_kat_raw.json says where each case starts."""
+    index, fin, fout = [], bytearray(), bytearray()
+    for m in meta:
+        x, y = blobs[m["key"] + "_in"], blobs[m["key"] + "_out"]
+        index.append(dict(m, in_offset=len(fin) // 4, out_offset=len(fout) // 2))
+        fin += np.ascontiguousarray(x, dtype="<f4").tobytes()
+        fout += np.ascontiguousarray(y, dtype="<i2").tobytes()
+    open(os.path.join(HERE, "frames_kat_in.f32"), "wb").write(bytes(fin))
+    open(os.path.join(HERE, "frames_kat_out.s16"), "wb").write(bytes(fout))
+    json.dump({"cases": index}, open(os.path.join(HERE, "frames_kat_raw.json"), "w"), separators=(",", ":"))
 
 
 if __name__ == "__main__":

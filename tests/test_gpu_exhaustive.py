@@ -2,6 +2,9 @@
 path (C ABI, host buffers) against the oracle's binary64 arithmetic.  Closes hard part H1 of
 SURVEY.md: the device code uses a round-toward-zero fp32 product instead of binary64."""
 import ctypes as C
+import hashlib
+import json
+import os
 import threading
 
 import numpy as np
@@ -33,6 +36,7 @@ def test_all_float32_bit_patterns(ctx):
     pin_out = ctx.pinned(chunk, np.int16)
     want = np.empty(chunk, dtype=np.int16)
     base = np.arange(chunk, dtype=np.uint32)
+    digest = hashlib.sha256()
     for c in range((1 << 32) // chunk):
         np.add(base, np.uint32(c * chunk), out=pin_in.array, casting="unsafe")
         x = pin_in.array.view(np.float32)
@@ -42,4 +46,10 @@ def test_all_float32_bit_patterns(ctx):
             bad = np.nonzero(pin_out.array != want)[0][:5]
             raise AssertionError(f"chunk {c}: first mismatches at bits "
                                  f"{[hex(int(pin_in.array[i])) for i in bad]} got {pin_out.array[bad]} want {want[bad]}")
+        digest.update(pin_out.array.astype("<i2", copy=False).tobytes())
     pin_in.free(); pin_out.free()
+    # the committed digest of the whole sweep (tools/make_sweep_digest.py): the same number
+    # tools/pin_with_node.mjs expects from the reference's own JavaScript
+    here = os.path.dirname(os.path.abspath(__file__))
+    committed = json.load(open(os.path.join(here, "golden", "encode_sweep_sha256.json")))["sha256"]
+    assert digest.hexdigest() == committed

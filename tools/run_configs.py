@@ -285,19 +285,20 @@ def main():
     if args.sweep_meter:
         # kernel 2c: tile height (via meter_tile_kb: 32/64/96/128 KB = 8/16/24/32 rows of 960 samples),
         # stages and grid cap; meter_kernel=0 is the old kernel 2b for comparison
-        pts = [dict(meter_kernel=0, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0)]
-        for kb in (32, 64, 96, 128):
-            for stg in (1, 2):
-                for bps in (0, 1, 2, 3, 4):
-                    if kb * stg > 200 or (bps and bps * kb * stg > 220):
-                        continue
-                    pts.append(dict(meter_kernel=1, meter_tile_kb=kb, meter_stages=stg, blocks_per_sm=bps))
+        pts = [dict(meter_kernel=0, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0),
+               dict(meter_kernel=1, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0)]
+        # kernel 2d: stage size, ring size, CTAs per SM (2 CTAs need the ring to be <= ~110 KB each)
+        for smem_kb in (160, 212, 224):
+            for cons in (4, 6, 8, 12):
+                for depth in (1, 2, 3):
+                    for rows in (0, 2):
+                        pts.append(dict(meter_kernel=2, ws_smem_kb=smem_kb, ws_consumers=cons, ws_depth=depth, ws_rows=rows, blocks_per_sm=0))
         for pt in pts:
             try:
                 ctx.tune(**pt)
                 for n_in, S in ((960, 1 << 19), (2944, 1 << 17)):
                     r = meter(ctx, n_in, S)
-                    print(json.dumps(dict(pt, n_in=n_in, ms=r["frames_plus_meter_ms"], frac=r["frac_of_measured_peak"])), flush=True)
+                    print(json.dumps(dict(pt, n_in=n_in, ms=r["frames_plus_meter_ms"], frac=round(r["frac_of_measured_peak"], 4))), flush=True)
             except Exception as e:
                 print("skip", pt, e, flush=True)
         return

@@ -446,39 +446,7 @@ k_agg_convert(AggGeom g, AggConvertArgs a)
                 while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
                 const uint32_t j = sl - qstart[k];
                 if (j < fd[k].ring_count) continue;
-                const float4 *src4 = reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch);
-                double sum = 0.0;
-                uint32_t lowest = 0xFFFFFFFFu;
-                auto four = [&](const float4 v) {
-                    const float xs[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                    for (int jj = 0; jj < 4; jj++) {
-                        const uint32_t b = __float_as_uint(xs[jj]);
-                        const uint32_t t2 = b << 1;
-                        lowest = min(lowest, t2 - 2u);
-                        const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;
-                        const double x = __hiloint2double((int)hi, (int)(b << 29));
-                        sum = __fma_rn(x, x, sum);
-                    }
-                };
-                if (Q == 128u) {
-#pragma unroll 8
-                    for (uint32_t gq = 0; gq < 32u; gq++) four(src4[gq]);
-                } else {
-                    for (uint32_t gq = 0; gq < (Q >> 2); gq++) four(src4[gq]);
-                }
-                bool odd = lowest < (2u * 0x21800000u - 2u);
-                odd |= !(sum < __hiloint2double(0x4F900000, 0));
-                if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;
-                if (odd) {
-                    sum = 0.0;
-                    const float *src = reinterpret_cast<const float *>(src4);
-                    for (uint32_t q = 0; q < Q; q++) {
-                        const double x = widen_abs(src[q]);
-                        sum = __fma_rn(x, x, sum);
-                    }
-                }
-                a.rms_at[fd[k].pos + (j - fd[k].ring_count)] = rms_of(sum, Q);
+                a.rms_at[fd[k].pos + (j - fd[k].ring_count)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
             }
         }
     }
@@ -561,39 +529,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         mbar_wait(bar, it & 1u);
         it++;
         if (slot != 0xFFFFFFFFu) {                        // threads 0..63: the meter of slot t
-            const float4 *src4 = reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch);
-            double sum = 0.0;
-            uint32_t lowest = 0xFFFFFFFFu;
-            auto four = [&](const float4 v) {
-                const float xs[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int jj = 0; jj < 4; jj++) {
-                    const uint32_t b = __float_as_uint(xs[jj]);
-                    const uint32_t t2 = b << 1;
-                    lowest = min(lowest, t2 - 2u);
-                    const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;
-                    const double x = __hiloint2double((int)hi, (int)(b << 29));
-                    sum = __fma_rn(x, x, sum);
-                }
-            };
-            if (quantum == 128u) {
-#pragma unroll 8
-                for (uint32_t gq = 0; gq < 32u; gq++) four(src4[gq]);
-            } else {
-                for (uint32_t gq = 0; gq < granules; gq++) four(src4[gq]);
-            }
-            bool odd = lowest < (2u * 0x21800000u - 2u);
-            odd |= !(sum < __hiloint2double(0x4F900000, 0));
-            if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;
-            if (odd) {
-                sum = 0.0;
-                const float *src = reinterpret_cast<const float *>(src4);
-                for (uint32_t q = 0; q < quantum; q++) {
-                    const double x = widen_abs(src[q]);
-                    sum = __fma_rn(x, x, sum);
-                }
-            }
-            ring_rms[slot] = rms_of(sum, quantum);
+            ring_rms[slot] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
         }
         // copy out: warps 2..7 start at once, warps 0 and 1 join when their meter lanes are done
         for (uint32_t t = (warp + 6u) & 7u; t < TILE; t += 8u) {

@@ -60,7 +60,12 @@ struct Tuning {
     int stages = 1;          // tiles in flight per CTA in kernel 2b (1: one tile per block, overlap comes from co-resident blocks)
     int meter_tile_kb = 64;  // kernels 2b/2c with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
-    int meter_kernel = 1;    // 1: kernel 2c (padded-row tiles) where it applies; 0: kernel 2b only
+    int meter_kernel = 2;    // 2: kernel 2d (producer/consumer pipeline), 1: kernel 2c (padded-row tiles), 0: kernel 2b only
+    int overlap_ticks = 0;   // 1: consecutive dense integer-ratio ticks may overlap on the GPU (programmatic dependent launch)
+    int ws_smem_kb = 212;    // kernel 2d: shared memory for the ring of stages ...
+    int ws_consumers = 8;    // ... consumer warps (1..16; fewer if the ring does not fit) ...
+    int ws_depth = 2;        // ... stages per consumer warp ...
+    int ws_rows = 0;         // ... and a cap on the rows per stage (0 = as many as fill one warp with quanta)
     size_t slice_bytes = 32u << 20;
 };
 
@@ -258,16 +263,38 @@ void launch_coal(pcmb200_ctx *ctx, cudaStream_t st, const float *in, int16_t *ou
     }
     const unsigned long long blocks_needed = (n_tiles + (unsigned long long)warps * U - 1) / ((unsigned long long)warps * U);
     const int grid = grid_for(ctx, blocks_needed);
+    if (ctx->tune.overlap_ticks) {
+        // programmatic dependent launch: this grid may begin while the previous launch of the stream is
+        // still draining its last wave (see k_decim_coal); opt-in, for callers whose consecutive ticks
+        // are independent (different frames, different buffers)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)grid);
+        cfg.blockDim = dim3((unsigned)block);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, k_decim_coal<R, U>, in, out, n_tiles, ctx->tune.store_hint);
+        return;
+    }
     k_decim_coal<R, U><<<grid, block, smem, st>>>(in, out, n_tiles, ctx->tune.store_hint);
 }
 
 template <int R>
 void launch_coal_u(pcmb200_ctx *ctx, cudaStream_t st, int U, const float *in, int16_t *out, unsigned long long n_tiles)
 {
-    switch (U) {
-    case 1: launch_coal<R, 1>(ctx, st, in, out, n_tiles); break;
-    case 2: launch_coal<R, 2>(ctx, st, in, out, n_tiles); break;
-    default: launch_coal<R, 4>(ctx, st, in, out, n_tiles); break;
+    if constexpr (R == 5 || R == 8 || R == 12) {   // 80 / 128 / 192 kHz: one instance each (U = 1 is the default anyway)
+        (void)U;
+        launch_coal<R, 1>(ctx, st, in, out, n_tiles);
+    } else {
+        switch (U) {
+        case 1: launch_coal<R, 1>(ctx, st, in, out, n_tiles); break;
+        case 2: launch_coal<R, 2>(ctx, st, in, out, n_tiles); break;
+        default: launch_coal<R, 4>(ctx, st, in, out, n_tiles); break;
+        }
     }
 }
 
@@ -275,10 +302,15 @@ template <int R>
 void launch_decim_u(pcmb200_ctx *ctx, cudaStream_t st, int U, bool dense, const float *in, size_t pitch_in,
                     int16_t *out, size_t pitch_out, uint32_t rows, uint32_t cpr, uint32_t tail)
 {
-    switch (U) {
-    case 1: launch_decim<R, 1>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
-    case 2: launch_decim<R, 2>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
-    default: launch_decim<R, 4>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+    if constexpr (R == 5 || R == 8 || R == 12) {
+        (void)U;
+        launch_decim<R, 1>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail);
+    } else {
+        switch (U) {
+        case 1: launch_decim<R, 1>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+        case 2: launch_decim<R, 2>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+        default: launch_decim<R, 4>(ctx, st, dense, in, pitch_in, out, pitch_out, rows, cpr, tail); break;
+        }
     }
 }
 
@@ -389,7 +421,7 @@ uint32_t magic_for(uint32_t d) { return d <= 1 ? 0u : (uint32_t)((0x100000000ull
 bool launch_frames_meter(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
                          uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R, const MeterArgs &meter)
 {
-    if (!ctx->tune.tile || ctx->tune.meter_kernel == 0) return false;
+    if (!ctx->tune.tile || ctx->tune.meter_kernel == 0) return false;   // (meter_kernel 2 falls through to here when 2d declines)
     if (pitch_in != n_in || pitch_out != n_out || n_out == 0 || n_out > 8192 || rows == 0) return false;
     if ((n_in & 3u) || (meter.quantum & 3u) || meter.nq == 0) return false;
     if (!aligned(in, 16) || !aligned(out, 16)) return false;
@@ -442,6 +474,60 @@ bool launch_frames_meter(pcmb200_ctx *ctx, cudaStream_t st, const float *in, siz
     return true;
 }
 
+// Kernel 2d (warp-specialised producer / consumer pipeline).  Takes the whole batch or nothing.
+bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out, size_t pitch_out,
+                            uint32_t rows, uint32_t n_in, uint32_t n_out, const uint32_t *lut, uint32_t R, const MeterArgs &meter)
+{
+    if (!ctx->tune.tile || ctx->tune.meter_kernel != 2) return false;
+    if (pitch_in != n_in || pitch_out != n_out || n_out == 0 || n_out > 8192 || rows == 0) return false;
+    if ((n_in & 3u) || (meter.quantum & 3u) || meter.nq == 0 || meter.nq > 32u) return false;
+    if (!aligned(in, 16) || !aligned(out, 16)) return false;
+    const uint32_t Q = meter.quantum, spr = (n_in + Q - 1) / Q, slot_pitch = Q + 4;
+    const size_t row_bytes = (size_t)spr * slot_pitch * 4;
+    // rows per stage: as many as keep the stage's quanta within one warp (one lane per quantum)
+    uint32_t Ks = 32u / meter.nq;
+    if (ctx->tune.ws_rows > 0 && (uint32_t)ctx->tune.ws_rows < Ks) Ks = (uint32_t)ctx->tune.ws_rows;
+    if (Ks > rows) Ks = rows;
+    while (Ks > 1 && (size_t)Ks * row_bytes > 48 * 1024) Ks--;
+    if ((size_t)Ks * row_bytes > 64 * 1024) return false;
+    const uint32_t stage_bytes = (uint32_t)(((size_t)Ks * row_bytes + 127) & ~(size_t)127);
+    const size_t tab = (n_out * 4u + 15u) & ~15u;
+    const size_t per_stage = (size_t)stage_bytes + 16;
+    const size_t budget = (size_t)ctx->tune.ws_smem_kb * 1024;
+    // Consumer warps and ring size go together: n_stages = depth * NC, so that warp w owns stages
+    // w, w + NC, ... (see the kernel's header).  Two stages per warp (one loading while the other is
+    // computed on) unless the tuning says otherwise; as many warps as then fit, at most ws_consumers.
+    const uint32_t depth = (uint32_t)ctx->tune.ws_depth;
+    uint32_t NC = (uint32_t)ctx->tune.ws_consumers;
+    while (NC > 1 && tab + (size_t)NC * 32 * 8 + (size_t)depth * NC * per_stage > budget) NC--;
+    const size_t fixed = tab + (size_t)NC * 32 * 8;
+    if (fixed + (size_t)depth * NC * per_stage > budget) return false;
+    const uint32_t n_stages = depth * NC;
+    const size_t smem = (size_t)n_stages * per_stage + fixed;
+    if ((unsigned long long)Ks * n_out * n_out >= 0xF0000000ull || (unsigned long long)n_in * Q >= 0xF0000000ull) return false;
+    WsGeom geo;
+    geo.n_in = n_in; geo.n_out = n_out; geo.Ks = Ks; geo.rows = rows; geo.spr = spr; geo.slot_pitch = slot_pitch;
+    geo.stride = lut ? 0u : (R ? R : 1u);
+    geo.magic_cpr = magic_for(n_out / 8); geo.magic_nout = magic_for(n_out); geo.magic_q = magic_for(Q);
+    geo.magic_nq = magic_for(meter.nq); geo.magic_spr = magic_for(spr);
+    geo.stage_bytes = stage_bytes; geo.n_stages = n_stages; geo.NC = NC;
+    const unsigned long long n_tiles = ((unsigned long long)rows + Ks - 1) / Ks;
+    static size_t granted[64] = {0};
+    const int dev = ctx->device & 63;
+    if (smem > granted[dev]) {
+        if (cudaFuncSetAttribute(k_frames_meter_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
+        granted[dev] = smem;
+    }
+    const int grid = (int)(n_tiles < (unsigned long long)ctx->sm_count ? n_tiles : (unsigned long long)ctx->sm_count);
+    k_frames_meter_ws<<<grid, 32 * (1 + NC), smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
+    if (cudaGetLastError() != cudaSuccess) return false;
+    ctx->launches++;
+    return true;
+}
+
 // Enqueue the fused resample+encode of a DEVICE-resident batch on `st`.
 int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pitch_in, int16_t *out,
                   size_t pitch_out, uint32_t rows, uint32_t n_in, double rate, uint32_t n_out,
@@ -450,7 +536,7 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
     if (rows == 0 || n_out == 0) return PCMB200_OK;
     uint32_t R = 0;
     const bool is_int = integer_ratio(rate, &R);
-    const bool fast_ok = is_int && (R == 1 || R == 2 || R == 3 || R == 4 || R == 6) && ctx->tune.path == 0 &&
+    const bool fast_ok = is_int && (R == 1 || R == 2 || R == 3 || R == 4 || R == 5 || R == 6 || R == 8 || R == 12) && ctx->tune.path == 0 &&
                          aligned(in, 32) && aligned(out, 16) && (pitch_in % 8 == 0 || rows == 1) &&
                          (pitch_out % 8 == 0 || rows == 1);
     if (fast_ok) {
@@ -469,6 +555,9 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
                 case 2: launch_coal_u<2>(ctx, st, U, in, out, n_tiles); break;
                 case 3: launch_coal_u<3>(ctx, st, U, in, out, n_tiles); break;
                 case 4: launch_coal_u<4>(ctx, st, U, in, out, n_tiles); break;
+                case 5: launch_coal_u<5>(ctx, st, U, in, out, n_tiles); break;
+                case 8: launch_coal_u<8>(ctx, st, U, in, out, n_tiles); break;
+                case 12: launch_coal_u<12>(ctx, st, U, in, out, n_tiles); break;
                 default: launch_coal_u<6>(ctx, st, U, in, out, n_tiles); break;
                 }
                 ctx->launches++;
@@ -481,6 +570,9 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
                 case 2: launch_decim_u<2>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
                 case 3: launch_decim_u<3>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
                 case 4: launch_decim_u<4>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                case 5: launch_decim_u<5>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                case 8: launch_decim_u<8>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
+                case 12: launch_decim_u<12>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
                 default: launch_decim_u<6>(ctx, st, 1, true, pi, 0, po, 0, 1, (uint32_t)rest_chunks, 0); break;
                 }
                 ctx->launches++;
@@ -502,6 +594,9 @@ int launch_frames(pcmb200_ctx *ctx, cudaStream_t st, const float *in, size_t pit
             case 2: launch_decim_u<2>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
             case 3: launch_decim_u<3>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
             case 4: launch_decim_u<4>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 5: launch_decim_u<5>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 8: launch_decim_u<8>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
+            case 12: launch_decim_u<12>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
             default: launch_decim_u<6>(ctx, st, U, dense, pi, pitch_in, po, pitch_out, nr, cpr, tail); break;
             }
             ctx->launches++;
@@ -1023,6 +1118,58 @@ int pcmb200_synth_fill(pcmb200_ctx *ctx, float *out, size_t pitch, uint32_t rows
     return PCMB200_OK;
 }
 
+// Bare copy probe: `reps` rounds of one pinned H2D copy of h2d_bytes and one pinned D2H copy of d2h_bytes
+// issued together on two streams -- the host-resident path's traffic with every kernel removed.  What
+// this reaches is the platform's ceiling for pcmb200_frames_encode(PCMB200_MEM_HOST); run from N
+// processes at once (tools/pcie_probe.py) it shows how that ceiling is shared between GPUs.
+int pcmb200_pcie_probe(pcmb200_ctx *ctx, size_t h2d_bytes, size_t d2h_bytes, int reps, float *milliseconds)
+{
+    NEED(ctx && milliseconds && reps > 0 && (h2d_bytes || d2h_bytes), "pcmb200_pcie_probe: bad argument");
+    CU(cudaSetDevice(ctx->device));
+    void *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, ea = nullptr, eb = nullptr;
+    cudaError_t e = cudaSuccess;
+#define PROBE_STEP(call) if (e == cudaSuccess) e = (call)
+    if (h2d_bytes) { PROBE_STEP(cudaHostAlloc(&h_in, h2d_bytes, cudaHostAllocDefault)); PROBE_STEP(cudaMalloc(&d_in, h2d_bytes)); }
+    if (d2h_bytes) { PROBE_STEP(cudaHostAlloc(&h_out, d2h_bytes, cudaHostAllocDefault)); PROBE_STEP(cudaMalloc(&d_out, d2h_bytes)); }
+    if (e == cudaSuccess && h_in) std::memset(h_in, 1, h2d_bytes);       // touch the pages before timing
+    if (e == cudaSuccess && h_out) std::memset(h_out, 1, d2h_bytes);
+    PROBE_STEP(cudaEventCreate(&e0));
+    PROBE_STEP(cudaEventCreate(&e1));
+    PROBE_STEP(cudaEventCreateWithFlags(&ea, cudaEventDisableTiming));
+    PROBE_STEP(cudaEventCreateWithFlags(&eb, cudaEventDisableTiming));
+    cudaStream_t sa = ctx->slots[0].st, sb = ctx->slots[1].st;
+    for (int r = -1; r < reps && e == cudaSuccess; r++) {                // round -1 is the warm-up
+        if (r == 0) {
+            PROBE_STEP(cudaStreamSynchronize(sa));
+            PROBE_STEP(cudaStreamSynchronize(sb));
+            PROBE_STEP(cudaEventRecord(e0, ctx->stream));
+            PROBE_STEP(cudaStreamWaitEvent(sa, e0, 0));
+            PROBE_STEP(cudaStreamWaitEvent(sb, e0, 0));
+        }
+        if (h2d_bytes) PROBE_STEP(cudaMemcpyAsync(d_in, h_in, h2d_bytes, cudaMemcpyHostToDevice, sa));
+        if (d2h_bytes) PROBE_STEP(cudaMemcpyAsync(h_out, d_out, d2h_bytes, cudaMemcpyDeviceToHost, sb));
+    }
+    PROBE_STEP(cudaEventRecord(ea, sa));
+    PROBE_STEP(cudaEventRecord(eb, sb));
+    PROBE_STEP(cudaStreamWaitEvent(ctx->stream, ea, 0));
+    PROBE_STEP(cudaStreamWaitEvent(ctx->stream, eb, 0));
+    PROBE_STEP(cudaEventRecord(e1, ctx->stream));
+    PROBE_STEP(cudaEventSynchronize(e1));
+    PROBE_STEP(cudaEventElapsedTime(milliseconds, e0, e1));
+#undef PROBE_STEP
+    if (h_in) cudaFreeHost(h_in);
+    if (h_out) cudaFreeHost(h_out);
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    for (cudaEvent_t ev : {e0, e1, ea, eb}) if (ev) cudaEventDestroy(ev);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, e == cudaErrorMemoryAllocation ? PCMB200_ERR_NOMEM : PCMB200_ERR_CUDA, std::string("pcmb200_pcie_probe: ") + cudaGetErrorString(e));
+    }
+    return PCMB200_OK;
+}
+
 int pcmb200_timer_start(pcmb200_ctx *ctx)
 {
     NEED(ctx, "pcmb200_timer_start: ctx is NULL");
@@ -1079,8 +1226,23 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
         NEED(value >= 4 && value <= 160, "pcmb200_tune: meter_tile_kb must be in [4, 160]");
         ctx->tune.meter_tile_kb = (int)value;
     } else if (k == "meter_kernel") {
-        NEED(value == 0 || value == 1, "pcmb200_tune: meter_kernel must be 0 or 1");
+        NEED(value >= 0 && value <= 2, "pcmb200_tune: meter_kernel must be 0, 1 or 2");
         ctx->tune.meter_kernel = (int)value;
+    } else if (k == "overlap_ticks") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: overlap_ticks must be 0 or 1");
+        ctx->tune.overlap_ticks = (int)value;
+    } else if (k == "ws_consumers") {
+        NEED(value >= 1 && value <= 16, "pcmb200_tune: ws_consumers must be in [1, 16]");
+        ctx->tune.ws_consumers = (int)value;
+    } else if (k == "ws_depth") {
+        NEED(value >= 1 && value <= 8, "pcmb200_tune: ws_depth must be in [1, 8]");
+        ctx->tune.ws_depth = (int)value;
+    } else if (k == "ws_rows") {
+        NEED(value >= 0 && value <= 32, "pcmb200_tune: ws_rows must be in [0, 32]");
+        ctx->tune.ws_rows = (int)value;
+    } else if (k == "ws_smem_kb") {
+        NEED(value >= 16 && value <= 220, "pcmb200_tune: ws_smem_kb must be in [16, 220]");
+        ctx->tune.ws_smem_kb = (int)value;
     } else if (k == "meter_stages") {
         NEED(value == 1 || value == 2, "pcmb200_tune: meter_stages must be 1 or 2");
         ctx->tune.meter_stages = (int)value;
@@ -1123,7 +1285,8 @@ extern "C" int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in, si
             s = get_lut(ctx, n_in, in_rate, (uint32_t)n_out, &lut);
             if (s) return s;
         }
-        if (launch_frames_meter(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, m))
+        if (launch_frames_meter_ws(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, m) ||
+            launch_frames_meter(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, m))
             took = rows;
         else
             took = launch_tile(ctx, ctx->stream, in, pitch_in, out, pitch_out, rows, n_in, (uint32_t)n_out, lut, R, &m);
@@ -1155,6 +1318,80 @@ extern "C" int pcmb200_keepalive_frame(int16_t *out, size_t capacity, size_t *n)
     if (capacity < PCMB200_KEEPALIVE_SAMPLES) return fail(nullptr, PCMB200_ERR_CAPACITY, "pcmb200_keepalive_frame: capacity < 1600 samples");
     std::memset(out, 0, PCMB200_KEEPALIVE_SAMPLES * sizeof(int16_t));   // new Int16Array(1600), App.tsx:294
     *n = PCMB200_KEEPALIVE_SAMPLES;
+    return PCMB200_OK;
+}
+
+// Per-session wire payloads over a converted batch.  The reference sends one WebSocket binary message
+// per frame whose payload is the Int16Array's buffer (App.tsx:284: ws.send(pcm16.buffer)), the voice
+// server relays those bytes untouched (apps/voice/src/server.ts:260-265) into DeepgramClient.sendAudio
+// (apps/voice/src/deepgram.ts:55-58).  After a batched call all sessions' frames sit in ONE block; this
+// gives every row's payload as (byte offset, byte length) into that block so the host can hand out
+// views (Buffer.from(arrayBuffer, offset, length), memoryview slices) instead of copies.
+extern "C" int pcmb200_egress_table(uint32_t rows, size_t n_out, size_t pitch_out, unsigned long long *byte_offset,
+                                    uint32_t *byte_length)
+{
+    pcmb200_ctx *ctx = nullptr;
+    if (rows == 0) return PCMB200_OK;
+    NEED(byte_offset && byte_length, "pcmb200_egress_table: NULL argument");
+    NEED(pitch_out >= n_out || rows == 1, "pcmb200_egress_table: pitch_out < n_out");
+    NEED(n_out <= 0x7FFFFFFFull, "pcmb200_egress_table: frame longer than 2^31 samples");
+    for (uint32_t r = 0; r < rows; r++) {
+        byte_offset[r] = (unsigned long long)r * pitch_out * sizeof(int16_t);
+        byte_length[r] = (uint32_t)(n_out * sizeof(int16_t));        // byteLength = 2 * N_out, no header
+    }
+    return PCMB200_OK;
+}
+
+// The same for the frames of an aggregator push (variable lengths, offsets in samples).
+extern "C" int pcmb200_egress_table_frames(uint32_t n_frames, const unsigned long long *frame_offset, const uint32_t *frame_len,
+                                           unsigned long long *byte_offset, uint32_t *byte_length)
+{
+    pcmb200_ctx *ctx = nullptr;
+    if (n_frames == 0) return PCMB200_OK;
+    NEED(frame_offset && frame_len && byte_offset && byte_length, "pcmb200_egress_table_frames: NULL argument");
+    for (uint32_t f = 0; f < n_frames; f++) {
+        byte_offset[f] = frame_offset[f] * sizeof(int16_t);
+        byte_length[f] = frame_len[f] * (uint32_t)sizeof(int16_t);
+    }
+    return PCMB200_OK;
+}
+
+// Keep-alive schedule.  The reference arms `setInterval(..., 2000)` when capture starts and, on every
+// tick, sends 1600 zero samples if the socket is open -- whether or not audio is flowing
+// (App.tsx:291-296); stop() clears the timer (:309-312).  For a fleet the timers become arithmetic on an
+// injected clock: session s was started at start_ms[s]; its timer has ticked floor((now - start) / period)
+// times; ticks_done[s] says how many of those were already served.  A poll serves each session at most
+// once (a browser coalesces the ticks of a blocked timer the same way) and marks all its elapsed ticks
+// done.  A session whose socket is not open still consumes its ticks (the callback runs and returns at
+// its first line) but is not reported.  start_ms[s] = NaN means "no timer armed".
+extern "C" int pcmb200_keepalive_due(double now_ms, uint32_t n_sessions, const double *start_ms, unsigned long long *ticks_done,
+                                     const uint8_t *socket_open, double period_ms, uint32_t *due_sessions, uint32_t max_due,
+                                     uint32_t *n_due)
+{
+    pcmb200_ctx *ctx = nullptr;
+    NEED(n_due, "pcmb200_keepalive_due: n_due is NULL");
+    *n_due = 0;
+    if (n_sessions == 0) return PCMB200_OK;
+    NEED(start_ms && ticks_done && socket_open && (due_sessions || max_due == 0), "pcmb200_keepalive_due: NULL argument");
+    NEED(period_ms > 0, "pcmb200_keepalive_due: period must be positive");
+    // two passes so that a too-small output leaves every counter untouched
+    uint32_t count = 0;
+    for (uint32_t s = 0; s < n_sessions; s++) {
+        const double el = now_ms - start_ms[s];
+        if (!(el >= 0)) continue;                                       // NaN start (no timer) or a clock before the start
+        const double ticks = std::floor(el / period_ms);
+        if (ticks > (double)ticks_done[s] && socket_open[s]) count++;
+    }
+    if (count > max_due) return fail(nullptr, PCMB200_ERR_CAPACITY, "pcmb200_keepalive_due: more sessions are due than max_due");
+    for (uint32_t s = 0; s < n_sessions; s++) {
+        const double el = now_ms - start_ms[s];
+        if (!(el >= 0)) continue;
+        const double ticks = std::floor(el / period_ms);
+        if (ticks > (double)ticks_done[s]) {
+            ticks_done[s] = (unsigned long long)ticks;
+            if (socket_open[s]) due_sessions[(*n_due)++] = s;
+        }
+    }
     return PCMB200_OK;
 }
 

@@ -151,6 +151,12 @@ __global__ void __launch_bounds__(512)
 k_decim_coal(const float *__restrict__ in, int16_t *__restrict__ out, unsigned long long n_tiles, int hint)
 {
     extern __shared__ __align__(16) int16_t smem_tiles[];
+    // Programmatic dependent launch: when the NEXT launch in the stream carries the programmatic
+    // serialisation attribute (tuning knob "overlap_ticks"), its blocks may start as soon as every block
+    // of this grid has got this far, i.e. while this grid's last wave is still draining -- the tail of one
+    // tick is filled with the head of the next.  Ticks are independent frames, nothing is waited for.
+    // Without the attribute this is a no-op.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int warps_per_block = blockDim.x >> 5;
@@ -287,17 +293,24 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// Waits for the phase with the given parity.  try_wait suspends the thread in hardware for a while per
+// attempt, so the loop is not a busy spin.  A pipeline bug here would otherwise hang the GPU until a
+// watchdog somewhere else kills the process: after ~2^26 failed attempts (seconds, against waits that
+// are microseconds) the kernel traps, which surfaces as a CUDA error on the host instead of a hang.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+    const uint32_t addr = smem_u32(bar);
+    for (uint32_t tries = 0;; tries++) {
+        uint32_t done;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+        if (tries > (1u << 26)) asm volatile("trap;");
+    }
 }
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
 {
@@ -370,6 +383,60 @@ __device__ __forceinline__ double widen_abs_fast(float x, bool &odd)
 __device__ __forceinline__ double js_max(double a, double b)
 {
     return (a != a || b != b) ? __longlong_as_double(0x7FF8000000000000ll) : (a > b ? a : b);
+}
+
+
+// rms = sqrt(sum(x*x) / Q) of one quantum that sits in shared memory (16-byte aligned), accumulated in
+// sample order by ONE lane: LDS.128 + 4 x (2 IMAD, LEA.HI, VIADDMNMX, DFMA), fully unrolled for the
+// 128-sample quantum.  widen_abs_fast's two escape hatches are tested once per quantum: a nonzero
+// sample below 2^-60 (the running minimum of `2|x| bits - 2`, where zeros wrap to the top) or an
+// Inf / NaN (an impossible sum) send the quantum through the exact widening instead.
+__device__ __forceinline__ double quantum_rms(const float4 *src4, uint32_t Q)
+{
+    double sum = 0.0;
+    uint32_t lowest = 0xFFFFFFFFu;
+    auto four = [&](const float4 v) {
+        const float xs[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const uint32_t b = __float_as_uint(xs[j]);
+            const uint32_t t2 = b << 1;                                       // sign gone
+            lowest = min(lowest, t2 - 2u);
+            const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;      // (|x| bits >> 3) + re-bias
+            const double x = __hiloint2double((int)hi, (int)(b << 29));
+            sum = __fma_rn(x, x, sum);
+        }
+    };
+    if (Q == 128u) {
+#pragma unroll 8
+        for (uint32_t g = 0; g < 32u; g++) four(src4[g]);
+    } else {
+        for (uint32_t g = 0; g < (Q >> 2); g++) four(src4[g]);
+    }
+    bool odd = lowest < (2u * 0x21800000u - 2u);                              // 0 < |x| < 2^-60 somewhere
+    odd |= !(sum < __hiloint2double(0x4F900000, 0));                          // >= 2^250 or NaN: an Inf / NaN sample
+    if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;                     // < 2^-200: every sample was zero
+    if (odd) {
+        sum = 0.0;
+        const float *src = reinterpret_cast<const float *>(src4);
+        for (uint32_t k = 0; k < Q; k++) {
+            const double x = widen_abs(src[k]);
+            sum = __fma_rn(x, x, sum);
+        }
+    }
+    return rms_of(sum, Q);
+}
+
+// One step of App.tsx:271, level = Math.max(rms, level * 0.85): NaN if either side is NaN, and a NaN
+// level stays NaN.  NaN-ness is tracked with integer tests so a step costs one DMUL and one DSETP on
+// the long-latency FP64 pipe.
+__device__ __forceinline__ void level_step(double &lv, bool &poisoned, double rms)
+{
+    const uint32_t hi = (uint32_t)__double2hiint(rms) & 0x7FFFFFFFu;
+    poisoned |= hi > 0x7FF00000u || (hi == 0x7FF00000u && __double2loint(rms) != 0);
+    const double dec = __dmul_rn(lv, 0.85);
+    lv = rms > dec ? rms : dec;
+    if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
 }
 
 template <int STAGES, bool METER>
@@ -759,41 +826,7 @@ k_frames_meter(const float *__restrict__ in, int16_t *__restrict__ out, TileMete
         for (uint32_t w = (((warp + 8u - rot) & 7u) << 5) + lane; w < ((items + 31u) & ~31u); w += blockDim.x) {
             const uint32_t q = div_magic(w, geo.magic_K), r = w - q * K;
             if (w >= items || r >= nr) continue;            // partial tile / partly filled last warp
-            const float4 *src4 = reinterpret_cast<const float4 *>(tile + r * P + q * Q);
-            double sum = 0.0;
-            uint32_t lowest = 0xFFFFFFFFu;                    // min over samples of (2|x| bits - 2), zeros wrap to the top
-            auto four = [&](const float4 v) {
-                const float xs[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const uint32_t b = __float_as_uint(xs[j]);
-                    const uint32_t t2 = b << 1;                               // sign gone
-                    lowest = min(lowest, t2 - 2u);
-                    const uint32_t hi = __umulhi(t2, 0x10000000u) + 0x38000000u;   // (|x| bits >> 3) + re-bias
-                    const double x = __hiloint2double((int)hi, (int)(b << 29));
-                    sum = __fma_rn(x, x, sum);
-                }
-            };
-            if (Q == 128u) {
-#pragma unroll 8
-                for (uint32_t g = 0; g < 32u; g++) four(src4[g]);
-            } else {
-                for (uint32_t g = 0; g < (Q >> 2); g++) four(src4[g]);
-            }
-            // widen_abs_fast's escape hatches: a nonzero sample below 2^-60 (denormals included), or an
-            // Inf / NaN (shows up as an impossible sum) -> redo the quantum with the exact widening
-            bool odd = lowest < (2u * 0x21800000u - 2u);
-            odd |= !(sum < __hiloint2double(0x4F900000, 0));                  // 2^250; also true for NaN
-            if (sum < __hiloint2double(0x33700000, 0)) sum = 0.0;             // < 2^-200: every sample was zero
-            if (odd) {
-                sum = 0.0;
-                const float *src = reinterpret_cast<const float *>(src4);
-                for (uint32_t k = 0; k < Q; k++) {
-                    const double x = widen_abs(src[k]);
-                    sum = __fma_rn(x, x, sum);
-                }
-            }
-            rms_s[w] = rms_of(sum, Q);
+            rms_s[w] = quantum_rms(reinterpret_cast<const float4 *>(tile + r * P + q * Q), Q);
         }
         __syncthreads();
         for (uint32_t rr = threadIdx.x; rr < nr; rr += blockDim.x) {
@@ -817,6 +850,195 @@ k_frames_meter(const float *__restrict__ in, int16_t *__restrict__ out, TileMete
             const unsigned long long tn = t + (unsigned long long)STAGES * gridDim.x;
             if (tn < n_tiles) issue(tn, s);
         }
+    }
+}
+
+// ---- kernel 2d: frames + level meter, warp-specialised producer / consumer pipeline -------------------
+// Kernel 2c cut the instruction count in half and stopped being issue-bound -- and did not get faster:
+// ncu showed 37 % issue utilisation, 61 % DRAM, warps parked on the tile's mbarrier and on the block
+// barrier.  A block there does load -> pick -> meter -> level chain strictly in sequence, the meter
+// alone is a 128-long dependent DFMA chain per lane (>= 1 000 clocks whatever the tile size), and only
+// three 62 KB tiles fit per SM, so the time a tile occupies shared memory caps the bytes in flight.
+// This kernel decouples loading from computing and makes the unit of compute small:
+//   * one CTA per SM, persistent; shared memory is a ring of n_stages small stages (Ks rows, chosen so
+//     that a stage holds at most 32 quanta: 4 frames of 960 samples, or ONE 2944-sample frame);
+//   * every 128-sample quantum is its own slot (slot pitch = quantum + 4 floats = 33 sixteen-byte
+//     units, odd) and its own bulk copy, so the lanes of a warp -- one per quantum -- read conflict-free
+//     whatever the frame length, and rows need no particular count;
+//   * warp 0 is the PRODUCER: it only waits for a free stage (empty[s]) and issues the bulk copies of
+//     the next tile (completing on full[s]), so HBM reads never stop for compute;
+//   * warps 1..NC are CONSUMERS, each on its own stage: pick + encode + store the stage's rows, one
+//     lane per quantum for the meter, the level chain on the first Ks lanes, then one arrive on
+//     empty[s].  NC stages are in compute at any time, which hides the meter's latency, and there is
+//     no block-wide barrier after the prologue -- not even a named one.
+//   * picks go through a shared-memory table of ROW-RELATIVE shared-memory offsets (built once per CTA
+//     from the pick table or the stride), so the padded layout costs the gather nothing; a pick outside
+//     the input (JS `undefined` -> NaN -> 0) points at a NaN kept in the first slot's padding.
+// n_stages is a MULTIPLE of NC, so stage s is always consumed by warp s % NC: a parity wait only means
+// something one phase ahead of what the waiter has already seen (a warp that skipped a phase of a
+// barrier can neither wait for it afterwards nor tell "two ahead" from "done"), and with fixed ownership
+// every warp sees every phase of its stages' barriers in turn.
+// Arithmetic (quantum_rms, level_step, enc_s32) is shared with the other kernels: bit-identical results.
+// Requirements (launcher): n_in % 4 == 0, quantum % 4 == 0, dense rows, in / out 16-byte aligned.
+struct WsGeom {
+    uint32_t n_in, n_out;
+    uint32_t Ks;             // rows per stage
+    uint32_t rows;           // rows of the batch (the last tile may be partial)
+    uint32_t spr;            // slots per row = ceil(n_in / quantum)
+    uint32_t slot_pitch;     // floats: quantum + 4
+    uint32_t stride;         // integer ratio when there is no table
+    uint32_t magic_cpr, magic_nout, magic_q, magic_nq, magic_spr;
+    uint32_t stage_bytes;    // Ks * spr * slot_pitch * 4 rounded up to 128
+    uint32_t n_stages;       // a multiple of NC
+    uint32_t NC;             // consumer warps
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(544, 1)
+k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeom geo, unsigned long long n_tiles,
+                  const uint32_t *__restrict__ lut, int hint, MeterArgs meter)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // layout: [n_stages][stage_bytes] | offset table u32[n_out] | full[n_stages] | empty[n_stages] | rms [NC][32]
+    const uint32_t n_in = geo.n_in, n_out = geo.n_out, Ks = geo.Ks, NS = geo.n_stages, SP = geo.slot_pitch;
+    uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)NS * geo.stage_bytes);
+    const uint32_t tab_bytes = (n_out * 4u + 15u) & ~15u;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t)NS * geo.stage_bytes + tab_bytes);
+    uint64_t *empty = full + NS;
+    double *rms_all = reinterpret_cast<double *>(empty + NS);
+    const uint32_t nq = meter.nq, Q = meter.quantum;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t row_floats = geo.spr * SP;                 // shared-memory floats per row
+
+    if (threadIdx.x == 0) {
+        for (uint32_t s = 0; s < NS; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (uint32_t o = threadIdx.x; o < n_out; o += blockDim.x) {
+        const uint32_t i = lut ? __ldg(lut + o) : o * geo.stride;
+        uint32_t off = Q;                                      // the NaN in slot 0's padding
+        if (i < n_in) { const uint32_t j = div_magic(i, geo.magic_q); off = j * SP + (i - j * Q); }
+        tab[o] = off;
+    }
+    for (uint32_t i = threadIdx.x; i < Ks * NS; i += blockDim.x) {   // one NaN per row of every stage
+        float *row = reinterpret_cast<float *>(smem_raw + (size_t)(i / Ks) * geo.stage_bytes) + (size_t)(i % Ks) * row_floats;
+        row[Q] = __int_as_float(0x7FC00000);
+    }
+    __syncthreads();
+
+    // this CTA's steps: step `it` is tile blockIdx.x + it * gridDim.x, in stage it % NS
+    const unsigned long long n_it = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0ull;
+
+    if (warp == 0) {
+        // ---- producer ----
+        for (unsigned long long it = 0; it < n_it; it++) {
+            const uint32_t s = (uint32_t)(it % NS);
+            const unsigned long long use = it / NS;
+            if (use > 0) mbar_wait(&empty[s], (uint32_t)((use - 1) & 1ull));
+            const unsigned long long row0 = (blockIdx.x + it * gridDim.x) * Ks;
+            const uint32_t nr = (uint32_t)((geo.rows - row0 < Ks) ? geo.rows - row0 : Ks);
+            if (lane == 0) mbar_expect_tx(&full[s], nr * n_in * 4u);
+            __syncwarp();
+            float *dst = reinterpret_cast<float *>(smem_raw + (size_t)s * geo.stage_bytes);
+            for (uint32_t c = lane; c < nr * geo.spr; c += 32u) {
+                const uint32_t r = div_magic(c, geo.magic_spr), j = c - r * geo.spr;
+                const uint32_t len = min(Q, n_in - j * Q);
+                bulk_g2s(dst + (size_t)c * SP, in + (row0 + r) * n_in + (size_t)j * Q, len * 4u, &full[s]);
+            }
+        }
+        return;
+    }
+
+    // ---- consumers: warp cw takes steps cw, cw + NC, ... ----
+    const uint32_t cw = warp - 1u;
+    if (cw >= geo.NC) return;
+    const bool rows_aligned = (n_out & 7u) == 0u;
+    const uint32_t cpr = n_out >> 3;
+    double *rms_s = rms_all + (size_t)cw * 32u;
+    for (unsigned long long it = cw; it < n_it; it += geo.NC) {
+        const uint32_t s = (uint32_t)(it % NS);
+        const unsigned long long use = it / NS;
+        const unsigned long long row0 = (blockIdx.x + it * gridDim.x) * Ks;
+        const uint32_t nr = (uint32_t)((geo.rows - row0 < Ks) ? geo.rows - row0 : Ks);
+        const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * geo.stage_bytes);
+        double lv_in = 0.0;
+        if (lane < nr) lv_in = meter.state[row0 + lane];       // needed after the meter: the latency hides behind it
+        mbar_wait(&full[s], (uint32_t)(use & 1ull));
+
+        // ---- frames: pick + encode + store ------------------------------------------------------------
+        const unsigned long long first = row0 * n_out;
+        const uint32_t outs = nr * n_out;
+        if (rows_aligned) {
+            const uint32_t n_chunks = nr * cpr;
+            for (uint32_t c8 = lane; c8 < n_chunks; c8 += 32u) {
+                const uint32_t rr = div_magic(c8, geo.magic_cpr), c = c8 - rr * cpr;
+                const float *row = tile + rr * row_floats;
+                const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
+                const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
+                int e[8];
+                e[0] = enc_s32(row[a.x]); e[1] = enc_s32(row[a.y]); e[2] = enc_s32(row[a.z]); e[3] = enc_s32(row[a.w]);
+                e[4] = enc_s32(row[b.x]); e[5] = enc_s32(row[b.y]); e[6] = enc_s32(row[b.z]); e[7] = enc_s32(row[b.w]);
+                uint4 o4;
+                o4.x = pack_s16x2_sat(e[0], e[1]);
+                o4.y = pack_s16x2_sat(e[2], e[3]);
+                o4.z = pack_s16x2_sat(e[4], e[5]);
+                o4.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(out + first + (size_t)c8 * 8u, o4, hint);
+            }
+        } else {
+            // the tile's output is one flat run of `outs` samples starting anywhere: an aligned body of
+            // 8-sample chunks (which may straddle frames) plus < 8 samples before and after it
+            const unsigned long long body0 = (first + 7ull) & ~7ull;
+            const unsigned long long body1 = (first + outs) & ~7ull;
+            const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
+            const uint32_t head = n_body ? (uint32_t)(body0 - first) : outs;
+            for (uint32_t c8 = lane; c8 < n_body; c8 += 32u) {
+                const uint32_t f = head + 8u * c8;
+                uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                const float *row = tile + rr * row_floats;
+                int e[8];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    e[j] = enc_s32(row[tab[o]]);
+                    if (++o == n_out) { o = 0; row += row_floats; }
+                }
+                uint4 o4;
+                o4.x = pack_s16x2_sat(e[0], e[1]);
+                o4.y = pack_s16x2_sat(e[2], e[3]);
+                o4.z = pack_s16x2_sat(e[4], e[5]);
+                o4.w = pack_s16x2_sat(e[6], e[7]);
+                st_128(out + body0 + (size_t)c8 * 8u, o4, hint);
+            }
+            const uint32_t tail0 = head + 8u * n_body, n_edge = head + (outs - tail0);
+            for (uint32_t k = lane; k < n_edge; k += 32u) {
+                const uint32_t f = k < head ? k : tail0 + (k - head);
+                const uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                out[first + f] = enc_s16(tile[rr * row_floats + tab[o]]);
+            }
+        }
+
+        // ---- level meter: lane w <-> (row r, quantum q), w = r * nq + q (Ks * nq <= 32) --------------------
+        if (lane < Ks * nq) {
+            const uint32_t r = div_magic(lane, geo.magic_nq), q = lane - r * nq;
+            if (r < nr) rms_s[lane] = quantum_rms(reinterpret_cast<const float4 *>(tile + r * row_floats + q * SP), Q);
+        }
+        __syncwarp();
+        if (lane < nr) {
+            const unsigned long long row = row0 + lane;
+            double lv = lv_in;
+            bool poisoned = lv != lv;
+            for (uint32_t q = 0; q < nq; q++) {
+                level_step(lv, poisoned, rms_s[lane * nq + q]);
+                if (meter.levels) meter.levels[row * nq + q] = lv;
+            }
+            meter.state[row] = lv;
+        }
+        __syncwarp();                                         // every lane is done with the stage and with rms_s
+        if (lane == 0) mbar_arrive(&empty[s]);
     }
 }
 

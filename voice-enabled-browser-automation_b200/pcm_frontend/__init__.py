@@ -25,7 +25,6 @@ from .api import (  # noqa: F401
     Aggregator,
     Context,
     DeviceBuffer,
-    FrameBatcher,
     PinnedBuffer,
     TickGraph,
     default_context,
@@ -38,8 +37,17 @@ from .api import (  # noqa: F401
     shard_sessions,
 )
 
+from .ingest import (  # noqa: F401,E402
+    Connection,
+    GpuGroupConverter,
+    KeepAliveScheduler,
+    TickBatcher,
+    classify_message,
+)
+
 __all__ = [
-    "Aggregator", "Context", "DeviceBuffer", "FrameBatcher", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
+    "Connection", "GpuGroupConverter", "KeepAliveScheduler", "TickBatcher", "classify_message",
+    "Aggregator", "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
     "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table", "keepalive_frame",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",
 ]

@@ -52,6 +52,7 @@ SYMBOLS = {
     "pcmb200_resample_to_16k": (_int, [_vp, _vp, _sz, _dbl, _vp, _sz, _P(_sz), _int]),
     "pcmb200_frames_encode": (_int, [_vp, _vp, _sz, _vp, _sz, _u32, _u32, _dbl, _int, _P(_sz)]),
     "pcmb200_synth_fill": (_int, [_vp, _vp, _sz, _u32, _u32, _dbl, _u64, _u64]),
+    "pcmb200_pcie_probe": (_int, [_vp, _sz, _sz, _int, _P(C.c_float)]),
     "pcmb200_timer_start": (_int, [_vp]),
     "pcmb200_timer_stop": (_int, [_vp, _P(C.c_float)]),
     "pcmb200_tune": (_int, [_vp, C.c_char_p, C.c_longlong]),
@@ -67,6 +68,9 @@ SYMBOLS = {
     "pcmb200_aggregator_push": (_int, [_vp, _vp, _u32, _vp, _vp, _vp, _int, _vp, _sz, _int, _vp, _vp, _vp, _u32, _P(_u32)]),
     "pcmb200_keepalive_frame": (_int, [_vp, _sz, _P(_sz)]),
     "pcmb200_wire_is_little_endian": (_int, []),
+    "pcmb200_egress_table": (_int, [_u32, _sz, _sz, _vp, _vp]),
+    "pcmb200_egress_table_frames": (_int, [_u32, _vp, _vp, _vp, _vp]),
+    "pcmb200_keepalive_due": (_int, [_dbl, _u32, _vp, _vp, _vp, _dbl, _vp, _u32, _P(_u32)]),
     "pcmb200_tick_graph_create": (_int, [_vp, _vp, _sz, _vp, _sz, _u32, _u32, _dbl, _P(_vp)]),
     "pcmb200_tick_graph_launch": (_int, [_vp, _vp]),
     "pcmb200_tick_graph_destroy": (_int, [_vp, _vp]),

@@ -397,36 +397,6 @@ class Aggregator:
         self.handle = None
 
 
-class FrameBatcher:
-    """Cross-connection tick batching (the Python twin of node/voice-glue.ts):
-    frames that arrive during a tick are grouped by (rate, length); flush() converts every group with
-    ONE fused call and hands each session its PCM16 bytes, ready for the unchanged
-    DeepgramClient.sendAudio (apps/voice/src/deepgram.ts:55-58)."""
-
-    def __init__(self, ctx: Context):
-        self.ctx = ctx
-        self._groups = {}
-
-    def push(self, session_id, rate: float, frame: np.ndarray, sink=None):
-        """One Float32 frame of one session (the payload of a WS binary message)."""
-        f = _as_f32_1d(frame)
-        self._groups.setdefault((float(rate), f.size), []).append((session_id, f, sink))
-
-    def flush(self):
-        """Returns [(session_id, pcm16 bytes), ...] in arrival order per group; calls each sink(bytes)."""
-        out = []
-        for (rate, n_in), items in self._groups.items():
-            batch = np.stack([f for _, f, _ in items]) if n_in else np.zeros((len(items), 0), np.float32)
-            pcm = self.ctx.frames_encode(batch, rate)
-            for row, (sid, _, sink) in zip(pcm, items):
-                payload = row.astype("<i2", copy=False).tobytes()      # raw little-endian int16, no header
-                if sink is not None:
-                    sink(payload)
-                out.append((sid, payload))
-        self._groups = {}
-        return out
-
-
 def _as_f32_1d(a) -> np.ndarray:
     x = np.asarray(a)
     if x.dtype != np.float32:
