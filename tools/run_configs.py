@@ -288,11 +288,10 @@ def main():
         pts = [dict(meter_kernel=0, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0),
                dict(meter_kernel=1, meter_tile_kb=64, meter_stages=1, blocks_per_sm=0)]
         # kernel 2d: stage size, ring size, CTAs per SM (2 CTAs need the ring to be <= ~110 KB each)
-        for smem_kb in (160, 212, 224):
-            for cons in (4, 6, 8, 12):
-                for depth in (1, 2, 3):
-                    for rows in (0, 2):
-                        pts.append(dict(meter_kernel=2, ws_smem_kb=smem_kb, ws_consumers=cons, ws_depth=depth, ws_rows=rows, blocks_per_sm=0))
+        for pairs in (4, 6, 8, 12, 16):
+            for depth in (1, 2, 3):
+                for chunk in (4, 8):
+                    pts.append(dict(meter_kernel=2, ws_smem_kb=212, ws_pairs=pairs, ws_depth=depth, ws_chunk=chunk, blocks_per_sm=0))
         for pt in pts:
             try:
                 ctx.tune(**pt)

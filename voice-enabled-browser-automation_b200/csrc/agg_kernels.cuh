@@ -14,8 +14,8 @@
 //                    writes scratch (the session's new state, per-quantum flush marks and ring slots).
 //   5 scan B         over quanta: frame index and output offset of every flush, in flush order
 //                    (= ascending i); its apply pass also emits the caller's frame arrays.
-//   6 k_agg_convert  every flushed frame: its quanta are staged into shared memory with one bulk copy
-//                    each -- from the session's ring (quanta carried over from earlier pushes) or
+//   6 k_agg_convert  every flushed frame: its quanta are staged into shared memory with async
+//                    copies -- from the session's ring (quanta carried over from earlier pushes) or
 //                    straight from the push (never written to the ring at all) -- then picked, encoded,
 //                    stored; with the meter on, each quantum's rms is computed from the staged copy.
 //   7 k_agg_levels   level = max(rms, level * 0.85) along each session's flushed quanta, in order
@@ -325,11 +325,24 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     if (m > frame_start) atomicAdd(&ctl->n_leftover, m - frame_start);
 }
 
+// 16-byte asynchronous global -> shared copy (LDGSTS, L2 only).  The aggregator stages single 512-byte
+// quanta that are scattered through the push; one bulk copy per quantum turned out to be bound by the
+// copy engine's per-request cost (~80 clocks per request, measured), so the quanta are moved as plain
+// 16-byte async copies issued by all threads: a warp-wide instruction is one contiguous 512-byte quantum.
+__device__ __forceinline__ void cp_async_16(void *dst_smem, const void *src_gmem)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst_smem)), "l"(src_gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.commit_group;\n cp.async.wait_group 0;" ::: "memory");
+}
+
 // ---- 6: convert -------------------------------------------------------------------------------------------------
 // A CTA takes G consecutive frames at a time.  Their quanta are packed into `slots` of shared memory
 // (slot pitch = quantum + 4 floats: 33 sixteen-byte units for the 128-sample quantum, odd, so that the
-// eight lanes of an LDS.128 phase -- eight consecutive quanta -- hit eight different bank groups), one
-// bulk copy per quantum.  Then all threads pick + encode + store; with METER each of the first T lanes
+// eight lanes of an LDS.128 phase -- eight consecutive quanta -- hit eight different bank groups) with
+// 16-byte async copies, all in flight together.  Then all threads pick + encode + store; with METER each of the first T lanes
 // accumulates its quantum's sum of squares in sample order (same arithmetic as kernel 2c).
 struct AggConvertArgs {
     const float *samples;            // the push's quanta
@@ -357,17 +370,14 @@ k_agg_convert(AggGeom g, AggConvertArgs a)
     const uint32_t Q = g.quantum, pitch = Q + 4u;
     const uint32_t max_slots = a.G * g.half_quanta;
     float *arena = reinterpret_cast<float *>(smem_raw);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (((size_t)max_slots * pitch * 4u + 127u) & ~(size_t)127u));
-    uint32_t *qstart = reinterpret_cast<uint32_t *>(bar + 2);        // [G + 1] first slot of each frame
+    const float **slot_src = reinterpret_cast<const float **>(smem_raw + (((size_t)max_slots * pitch * 4u + 127u) & ~(size_t)127u));   // [max_slots]
+    uint32_t *qstart = reinterpret_cast<uint32_t *>(slot_src + max_slots);   // [G + 1] first slot of each frame
     uint32_t *cstart = qstart + (a.G + 1u);                           // [G + 1] first 8-output chunk of each frame
     AggFrameDesc *fd = reinterpret_cast<AggFrameDesc *>(cstart + (a.G + 1u) + ((2u * a.G + 2u) & 1u));   // [G], 8-byte aligned
     unsigned long long *foff = reinterpret_cast<unsigned long long *>(fd + a.G);                          // [G]
 
     const uint32_t n_frames = a.ctl->n_frames;
-    if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
+    const uint32_t gpq = Q >> 2;                               // 16-byte granules per quantum
     uint32_t it = 0;
     for (uint32_t f0 = blockIdx.x * a.G; f0 < n_frames; f0 += gridDim.x * a.G, it++) {
         const uint32_t nf = min(a.G, n_frames - f0);
@@ -385,20 +395,24 @@ k_agg_convert(AggGeom g, AggConvertArgs a)
                 cs += (__ldg(a.nout_of + fd[k].nq) + 7u) >> 3;
             }
             qstart[nf] = qs; cstart[nf] = cs;
-            mbar_expect_tx(bar, qs * Q * 4u);
         }
         __syncthreads();
         const uint32_t T = qstart[nf];
-        for (uint32_t sl = threadIdx.x; sl < T; sl += blockDim.x) {
+        for (uint32_t sl = threadIdx.x; sl < T; sl += blockDim.x) {          // where every slot's quantum comes from
             uint32_t k = 0;
             while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
             const uint32_t j = sl - qstart[k];
             const AggFrameDesc d = fd[k];
-            const float *src = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
-                                                : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
-            bulk_g2s(arena + (size_t)sl * pitch, src, Q * 4u, bar);
+            slot_src[sl] = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
+                                            : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
         }
-        mbar_wait(bar, it & 1u);
+        __syncthreads();
+        for (uint32_t idx = threadIdx.x; idx < T * gpq; idx += blockDim.x) {  // all quanta in flight at once
+            const uint32_t sl = idx / gpq, gi = idx - sl * gpq;
+            cp_async_16(arena + (size_t)sl * pitch + 4u * gi, slot_src[sl] + 4u * gi);
+        }
+        cp_async_wait_all();
+        __syncthreads();
 
         // ---- pick + encode + store: work item = 8 consecutive outputs of one frame ----------------------
         const uint32_t n_chunks = cstart[nf];
@@ -483,7 +497,7 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
 // Quanta that did not flush go to their ring slot.  Without the meter: one warp per quantum, 128-bit
 // copies, nothing else.  With the meter the quantum's rms must be accumulated in sample order by ONE
 // lane (handing a running sum from lane to lane costs ~15 warp-instructions per sample), so a CTA stages
-// 64 consecutive quanta of the push in shared memory (bulk copies, slot pitch quantum + 4 floats), lane t
+// 64 consecutive quanta of the push in shared memory (16-byte async copies, slot pitch quantum + 4 floats), lane t
 // meters slot t exactly like kernel 2c, and the warps then copy the slots out to the rings.
 template <bool METER>
 __global__ void __launch_bounds__(256)
@@ -508,13 +522,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t pitch = quantum + 4u;
     float *arena = reinterpret_cast<float *>(smem_raw);
-    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (((size_t)TILE * pitch * 4u + 127u) & ~(size_t)127u));
     __shared__ uint32_t slot_s[TILE];
-    if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    uint32_t it = 0;
     for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
         __syncthreads();
         uint32_t slot = 0xFFFFFFFFu;
@@ -522,12 +530,12 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         if (threadIdx.x < TILE) slot_s[threadIdx.x] = slot;
         const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
         if (live == 0) continue;
-        if (threadIdx.x == 0) mbar_expect_tx(bar, (uint32_t)live * quantum * 4u);
+        for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
+            const uint32_t t = idx / granules, gi = idx - t * granules;
+            if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+        }
+        cp_async_wait_all();
         __syncthreads();
-        if (slot != 0xFFFFFFFFu)
-            bulk_g2s(arena + (size_t)threadIdx.x * pitch, samples + (size_t)(i0 + threadIdx.x) * quantum, quantum * 4u, bar);
-        mbar_wait(bar, it & 1u);
-        it++;
         if (slot != 0xFFFFFFFFu) {                        // threads 0..63: the meter of slot t
             ring_rms[slot] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
         }

@@ -140,7 +140,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     NEED(probe <= 0x7FFFFFFFull, "pcmb200_aggregator_create: frame too long");
     // one frame (max_frame_quanta quanta at a pitch of quantum + 4 floats) must fit in shared memory
     const size_t slot_bytes = (size_t)(quantum + 4) * 4;
-    NEED((size_t)max_frame_quanta * slot_bytes <= 200 * 1024,
+    NEED((size_t)max_frame_quanta * (slot_bytes + 8) <= 200 * 1024,
          "pcmb200_aggregator_create: max_frame_quanta * quantum is too long to stage one frame on chip (limit ~200 KB, "
          "e.g. 387 quanta of 128 samples = 1 s at 48 kHz)");
     CU(cudaSetDevice(ctx->device));
@@ -172,8 +172,9 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
 
     // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
     a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (64 * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
-    a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 16 + 8 * (a->G + 1) + 24 * a->G;
-    a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127) + 16;
+    a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 8 * (size_t)a->G * max_frame_quanta +
+                      8 * (a->G + 1) + 24 * a->G;
+    a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127);
 
     cudaError_t e = cudaSuccess;
     const size_t S = max_sessions, P = max_push_quanta;

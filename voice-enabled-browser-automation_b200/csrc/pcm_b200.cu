@@ -62,9 +62,10 @@ struct Tuning {
     int meter_stages = 1;    // ... and stages (1 or 2)
     int meter_kernel = 2;    // 2: kernel 2d (producer/consumer pipeline), 1: kernel 2c (padded-row tiles), 0: kernel 2b only
     int overlap_ticks = 0;   // 1: consecutive dense integer-ratio ticks may overlap on the GPU (programmatic dependent launch)
-    int ws_smem_kb = 212;    // kernel 2d: shared memory for the ring of stages ...
-    int ws_consumers = 8;    // ... consumer warps (1..16; fewer if the ring does not fit) ...
-    int ws_depth = 2;        // ... stages per consumer warp ...
+    int ws_smem_kb = 212;    // kernel 2d: shared memory for all stages ...
+    int ws_pairs = 16;       // ... warp pairs per CTA (1..16; fewer if their stages do not fit) ...
+    int ws_depth = 1;        // ... stages per pair (measured: more pairs beat deeper pairs) ...
+    int ws_chunk = 4;        // ... quanta per bulk copy (0 = one copy per row) ...
     int ws_rows = 0;         // ... and a cap on the rows per stage (0 = as many as fill one warp with quanta)
     size_t slice_bytes = 32u << 20;
 };
@@ -482,35 +483,46 @@ bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, 
     if (pitch_in != n_in || pitch_out != n_out || n_out == 0 || n_out > 8192 || rows == 0) return false;
     if ((n_in & 3u) || (meter.quantum & 3u) || meter.nq == 0 || meter.nq > 32u) return false;
     if (!aligned(in, 16) || !aligned(out, 16)) return false;
-    const uint32_t Q = meter.quantum, spr = (n_in + Q - 1) / Q, slot_pitch = Q + 4;
-    const size_t row_bytes = (size_t)spr * slot_pitch * 4;
+    const uint32_t Q = meter.quantum;
+    // chunk copies: C quanta each (tuning ws_chunk; 0 = whole rows), 16 bytes of padding after every chunk
+    uint32_t chunk = ctx->tune.ws_chunk > 0 ? (uint32_t)ctx->tune.ws_chunk * Q : n_in;
+    if (chunk > n_in) chunk = n_in;
+    const uint32_t ncopies = (n_in + chunk - 1) / chunk;
+    const uint32_t row_floats = n_in + 4u * ncopies;
+    const size_t row_bytes = (size_t)row_floats * 4;
     // rows per stage: as many as keep the stage's quanta within one warp (one lane per quantum)
-    uint32_t Ks = 32u / meter.nq;
-    if (ctx->tune.ws_rows > 0 && (uint32_t)ctx->tune.ws_rows < Ks) Ks = (uint32_t)ctx->tune.ws_rows;
-    if (Ks > rows) Ks = rows;
-    while (Ks > 1 && (size_t)Ks * row_bytes > 48 * 1024) Ks--;
+    // (a power of two, so that the lanes of one row -- Ks apart -- can be max-reduced with xor shuffles)
+    uint32_t Ks = 1;
+    while (Ks * 2u * meter.nq <= 32u) Ks *= 2u;
+    while (Ks > 1 && ((ctx->tune.ws_rows > 0 && Ks > (uint32_t)ctx->tune.ws_rows) || Ks > rows || (size_t)Ks * row_bytes > 48 * 1024)) Ks >>= 1;
     if ((size_t)Ks * row_bytes > 64 * 1024) return false;
     const uint32_t stage_bytes = (uint32_t)(((size_t)Ks * row_bytes + 127) & ~(size_t)127);
     const size_t tab = (n_out * 4u + 15u) & ~15u;
-    const size_t per_stage = (size_t)stage_bytes + 16;
     const size_t budget = (size_t)ctx->tune.ws_smem_kb * 1024;
-    // Consumer warps and ring size go together: n_stages = depth * NC, so that warp w owns stages
-    // w, w + NC, ... (see the kernel's header).  Two stages per warp (one loading while the other is
-    // computed on) unless the tuning says otherwise; as many warps as then fit, at most ws_consumers.
+    // warp pairs (meter warp + frames/loader warp), `depth` stages each; as many pairs as fit, at most ws_pairs
     const uint32_t depth = (uint32_t)ctx->tune.ws_depth;
-    uint32_t NC = (uint32_t)ctx->tune.ws_consumers;
-    while (NC > 1 && tab + (size_t)NC * 32 * 8 + (size_t)depth * NC * per_stage > budget) NC--;
-    const size_t fixed = tab + (size_t)NC * 32 * 8;
-    if (fixed + (size_t)depth * NC * per_stage > budget) return false;
-    const uint32_t n_stages = depth * NC;
-    const size_t smem = (size_t)n_stages * per_stage + fixed;
-    if ((unsigned long long)Ks * n_out * n_out >= 0xF0000000ull || (unsigned long long)n_in * Q >= 0xF0000000ull) return false;
+    const size_t per_pair = (size_t)depth * ((size_t)stage_bytes + 16) + 32 * 8;
+    uint32_t pairs = (uint32_t)ctx->tune.ws_pairs;
+    while (pairs > 1 && tab + pairs * per_pair > budget) pairs--;
+    if (tab + pairs * per_pair > budget) return false;
+    if (pairs > 2) pairs &= ~1u;     // an even number of pairs loads the four warp schedulers evenly (measured: 12 beats 13)
+    const size_t smem = tab + pairs * per_pair;
+    if ((unsigned long long)Ks * n_out * n_out >= 0xF0000000ull || (unsigned long long)n_in * chunk >= 0xF0000000ull) return false;
     WsGeom geo;
-    geo.n_in = n_in; geo.n_out = n_out; geo.Ks = Ks; geo.rows = rows; geo.spr = spr; geo.slot_pitch = slot_pitch;
+    geo.n_in = n_in; geo.n_out = n_out; geo.Ks = Ks; geo.rows = rows; geo.chunk = chunk; geo.ncopies = ncopies;
+    geo.row_floats = row_floats;
     geo.stride = lut ? 0u : (R ? R : 1u);
-    geo.magic_cpr = magic_for(n_out / 8); geo.magic_nout = magic_for(n_out); geo.magic_q = magic_for(Q);
-    geo.magic_nq = magic_for(meter.nq); geo.magic_spr = magic_for(spr);
-    geo.stage_bytes = stage_bytes; geo.n_stages = n_stages; geo.NC = NC;
+    geo.magic_cpr = magic_for(n_out / 8); geo.magic_nout = magic_for(n_out); geo.magic_chunk = magic_for(chunk);
+    geo.magic_Ks = magic_for(Ks); geo.magic_ncopies = magic_for(ncopies);
+    geo.stage_bytes = stage_bytes; geo.pairs = pairs; geo.depth = depth;
+    {   // quantum order for the meter lanes: walk the chunks round-robin (position 0 of every chunk, then
+        // position 1, ...), so that neighbouring lanes -- one LDS.128 phase is 8 of them -- sit in different chunks
+        const uint32_t qpc = chunk / Q ? chunk / Q : 1u;   // whole quanta per chunk
+        uint32_t k = 0;
+        for (uint32_t pos = 0; pos < qpc && k < 32; pos++)
+            for (uint32_t c = 0; c * qpc + pos < meter.nq && k < 32; c++) geo.lane_q[k++] = (unsigned char)(c * qpc + pos);
+        for (; k < 32; k++) geo.lane_q[k] = 0;
+    }
     const unsigned long long n_tiles = ((unsigned long long)rows + Ks - 1) / Ks;
     static size_t granted[64] = {0};
     const int dev = ctx->device & 63;
@@ -522,7 +534,7 @@ bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, 
         granted[dev] = smem;
     }
     const int grid = (int)(n_tiles < (unsigned long long)ctx->sm_count ? n_tiles : (unsigned long long)ctx->sm_count);
-    k_frames_meter_ws<<<grid, 32 * (1 + NC), smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
+    k_frames_meter_ws<<<grid, 64 * pairs, smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
     if (cudaGetLastError() != cudaSuccess) return false;
     ctx->launches++;
     return true;
@@ -1231,9 +1243,12 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "overlap_ticks") {
         NEED(value == 0 || value == 1, "pcmb200_tune: overlap_ticks must be 0 or 1");
         ctx->tune.overlap_ticks = (int)value;
-    } else if (k == "ws_consumers") {
-        NEED(value >= 1 && value <= 16, "pcmb200_tune: ws_consumers must be in [1, 16]");
-        ctx->tune.ws_consumers = (int)value;
+    } else if (k == "ws_pairs") {
+        NEED(value >= 1 && value <= 16, "pcmb200_tune: ws_pairs must be in [1, 16]");
+        ctx->tune.ws_pairs = (int)value;
+    } else if (k == "ws_chunk") {
+        NEED(value >= 0 && value <= 64, "pcmb200_tune: ws_chunk must be in [0, 64]");
+        ctx->tune.ws_chunk = (int)value;
     } else if (k == "ws_depth") {
         NEED(value >= 1 && value <= 8, "pcmb200_tune: ws_depth must be in [1, 8]");
         ctx->tune.ws_depth = (int)value;

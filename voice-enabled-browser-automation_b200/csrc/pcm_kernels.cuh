@@ -295,7 +295,7 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 }
 // Waits for the phase with the given parity.  try_wait suspends the thread in hardware for a while per
 // attempt, so the loop is not a busy spin.  A pipeline bug here would otherwise hang the GPU until a
-// watchdog somewhere else kills the process: after ~2^26 failed attempts (seconds, against waits that
+// watchdog somewhere else kills the process: after ~4 million failed attempts (seconds at most, against waits that
 // are microseconds) the kernel traps, which surfaces as a CUDA error on the host instead of a hang.
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
@@ -305,11 +305,11 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x2000;\n"   // suspend up to ~8 us per attempt instead of spinning
             "selp.u32 %0, 1, 0, p;\n"
             "}\n" : "=r"(done) : "r"(addr), "r"(parity) : "memory");
         if (done) return;
-        if (tries > (1u << 26)) asm volatile("trap;");
+        if (tries > (1u << 22)) asm volatile("trap;");
     }
 }
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
@@ -853,44 +853,49 @@ k_frames_meter(const float *__restrict__ in, int16_t *__restrict__ out, TileMete
     }
 }
 
-// ---- kernel 2d: frames + level meter, warp-specialised producer / consumer pipeline -------------------
+// ---- kernel 2d: frames + level meter, warp-pair pipelines ---------------------------------------------
 // Kernel 2c cut the instruction count in half and stopped being issue-bound -- and did not get faster:
 // ncu showed 37 % issue utilisation, 61 % DRAM, warps parked on the tile's mbarrier and on the block
 // barrier.  A block there does load -> pick -> meter -> level chain strictly in sequence, the meter
 // alone is a 128-long dependent DFMA chain per lane (>= 1 000 clocks whatever the tile size), and only
 // three 62 KB tiles fit per SM, so the time a tile occupies shared memory caps the bytes in flight.
-// This kernel decouples loading from computing and makes the unit of compute small:
-//   * one CTA per SM, persistent; shared memory is a ring of n_stages small stages (Ks rows, chosen so
-//     that a stage holds at most 32 quanta: 4 frames of 960 samples, or ONE 2944-sample frame);
-//   * every 128-sample quantum is its own slot (slot pitch = quantum + 4 floats = 33 sixteen-byte
-//     units, odd) and its own bulk copy, so the lanes of a warp -- one per quantum -- read conflict-free
-//     whatever the frame length, and rows need no particular count;
-//   * warp 0 is the PRODUCER: it only waits for a free stage (empty[s]) and issues the bulk copies of
-//     the next tile (completing on full[s]), so HBM reads never stop for compute;
-//   * warps 1..NC are CONSUMERS, each on its own stage: pick + encode + store the stage's rows, one
-//     lane per quantum for the meter, the level chain on the first Ks lanes, then one arrive on
-//     empty[s].  NC stages are in compute at any time, which hides the meter's latency, and there is
-//     no block-wide barrier after the prologue -- not even a named one.
+// Shared memory is the buffer between HBM and the compute: throughput = bytes resident / time a byte
+// stays resident.  This kernel keeps that time short and the buffer full:
+//   * one CTA per SM, persistent; the CTA is NP independent warp PAIRS, each with its own `depth` small
+//     stages (a stage = Ks rows holding at most 32 quanta: 4 frames of 960 samples, ONE 2944-sample frame);
+//   * in a pair, warp A is the METER: one lane per quantum, then the level chain on its first Ks lanes;
+//     warp B does the FRAMES (pick + encode + store) at the same time and is also the pair's loader:
+//     when both warps are done with a stage (done[s], two arrivals) it issues the bulk copies of the
+//     pair's next tile into it (completing on full[s]).  With depth 2 the other stage is loading while
+//     this one is computed on.  Nothing is shared between pairs, so there is no block-wide barrier after
+//     the prologue, no producer warp to become the bottleneck (a single dedicated producer measured ~660
+//     clocks + ~130 per copy per stage: 3 samples/clk/SM against the 4.3 the HBM share needs), and no
+//     head-of-line blocking between stages;
+//   * a row is copied in chunks of C quanta (one bulk copy each, 16 bytes of padding after every chunk)
+//     so that the quanta of a row do not all start in the same bank group; the meter lanes are mapped
+//     so that the 8 lanes of an LDS.128 phase fall into as many different chunks / rows as there are.
+//     One bulk copy PER QUANTUM would be conflict-free but is far too fine for the copy engine
+//     (measured ~80 clocks per 512-byte request: 6 B/clk/SM against the 22 B/clk/SM HBM share);
 //   * picks go through a shared-memory table of ROW-RELATIVE shared-memory offsets (built once per CTA
 //     from the pick table or the stride), so the padded layout costs the gather nothing; a pick outside
-//     the input (JS `undefined` -> NaN -> 0) points at a NaN kept in the first slot's padding.
-// n_stages is a MULTIPLE of NC, so stage s is always consumed by warp s % NC: a parity wait only means
-// something one phase ahead of what the waiter has already seen (a warp that skipped a phase of a
-// barrier can neither wait for it afterwards nor tell "two ahead" from "done"), and with fixed ownership
-// every warp sees every phase of its stages' barriers in turn.
+//     the input (JS `undefined` -> NaN -> 0) points at a NaN kept in the first chunk's padding.
+// Every mbarrier is waited on by the same warp in every one of its phases (a parity wait only means
+// something one phase ahead of what the waiter has already seen).
 // Arithmetic (quantum_rms, level_step, enc_s32) is shared with the other kernels: bit-identical results.
 // Requirements (launcher): n_in % 4 == 0, quantum % 4 == 0, dense rows, in / out 16-byte aligned.
 struct WsGeom {
     uint32_t n_in, n_out;
     uint32_t Ks;             // rows per stage
     uint32_t rows;           // rows of the batch (the last tile may be partial)
-    uint32_t spr;            // slots per row = ceil(n_in / quantum)
-    uint32_t slot_pitch;     // floats: quantum + 4
+    uint32_t chunk;          // samples per chunk copy (C * quantum, or n_in for whole rows)
+    uint32_t ncopies;        // chunk copies per row = ceil(n_in / chunk)
+    uint32_t row_floats;     // shared-memory floats per row = n_in + 4 * ncopies
     uint32_t stride;         // integer ratio when there is no table
-    uint32_t magic_cpr, magic_nout, magic_q, magic_nq, magic_spr;
-    uint32_t stage_bytes;    // Ks * spr * slot_pitch * 4 rounded up to 128
-    uint32_t n_stages;       // a multiple of NC
-    uint32_t NC;             // consumer warps
+    uint32_t magic_cpr, magic_nout, magic_chunk, magic_Ks, magic_ncopies;
+    uint32_t stage_bytes;    // Ks * row_floats * 4 rounded up to 128
+    unsigned char lane_q[32];   // meter: item w -> row w % Ks, quantum lane_q[w / Ks] (spreads a phase over the chunks)
+    uint32_t pairs;          // warp pairs per CTA
+    uint32_t depth;          // stages per pair
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
@@ -898,147 +903,196 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-__global__ void __launch_bounds__(544, 1)
+__global__ void __launch_bounds__(1024, 1)
 k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeom geo, unsigned long long n_tiles,
                   const uint32_t *__restrict__ lut, int hint, MeterArgs meter)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    // layout: [n_stages][stage_bytes] | offset table u32[n_out] | full[n_stages] | empty[n_stages] | rms [NC][32]
-    const uint32_t n_in = geo.n_in, n_out = geo.n_out, Ks = geo.Ks, NS = geo.n_stages, SP = geo.slot_pitch;
+    // layout: [pairs * depth][stage_bytes] | offset table u32[n_out] | full[NS] | done[NS] | rms [pairs][32]
+    const uint32_t n_in = geo.n_in, n_out = geo.n_out, Ks = geo.Ks, NS = geo.pairs * geo.depth;
     uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)NS * geo.stage_bytes);
     const uint32_t tab_bytes = (n_out * 4u + 15u) & ~15u;
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t)NS * geo.stage_bytes + tab_bytes);
-    uint64_t *empty = full + NS;
-    double *rms_all = reinterpret_cast<double *>(empty + NS);
+    uint64_t *done = full + NS;
+    double *rms_all = reinterpret_cast<double *>(done + NS);
     const uint32_t nq = meter.nq, Q = meter.quantum;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t row_floats = geo.spr * SP;                 // shared-memory floats per row
+    const uint32_t row_floats = geo.row_floats;               // shared-memory floats per row (chunks + their padding)
+    const uint32_t nan_off = min(geo.chunk, n_in);            // the padding right after a row's first chunk holds a NaN
 
     if (threadIdx.x == 0) {
-        for (uint32_t s = 0; s < NS; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (uint32_t s = 0; s < NS; s++) { mbar_init(&full[s], 1); mbar_init(&done[s], 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (uint32_t o = threadIdx.x; o < n_out; o += blockDim.x) {
         const uint32_t i = lut ? __ldg(lut + o) : o * geo.stride;
-        uint32_t off = Q;                                      // the NaN in slot 0's padding
-        if (i < n_in) { const uint32_t j = div_magic(i, geo.magic_q); off = j * SP + (i - j * Q); }
-        tab[o] = off;
+        // sample i sits 4 floats further for every chunk boundary before it
+        tab[o] = i < n_in ? i + 4u * div_magic(i, geo.magic_chunk) : nan_off;
     }
     for (uint32_t i = threadIdx.x; i < Ks * NS; i += blockDim.x) {   // one NaN per row of every stage
         float *row = reinterpret_cast<float *>(smem_raw + (size_t)(i / Ks) * geo.stage_bytes) + (size_t)(i % Ks) * row_floats;
-        row[Q] = __int_as_float(0x7FC00000);
+        row[nan_off] = __int_as_float(0x7FC00000);
     }
     __syncthreads();
 
-    // this CTA's steps: step `it` is tile blockIdx.x + it * gridDim.x, in stage it % NS
-    const unsigned long long n_it = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0ull;
+    // this CTA's steps: step `it` is tile blockIdx.x + it * gridDim.x; pair p takes steps p, p + pairs, ...
+    const uint32_t n_it = blockIdx.x < n_tiles ? (uint32_t)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0u;
+    const uint32_t pair = warp >> 1, role = warp & 1u;
+    if (pair >= geo.pairs) return;
+    const uint32_t my_steps = pair < n_it ? (n_it - pair + geo.pairs - 1) / geo.pairs : 0u;   // k = 0 .. my_steps-1 -> it = pair + k * pairs
+    const uint32_t s0 = pair * geo.depth;
+    auto stage_of = [&](uint32_t k) { return s0 + k % geo.depth; };
+    auto rows_of = [&](uint32_t k, unsigned long long &row0) {
+        row0 = ((unsigned long long)blockIdx.x + (unsigned long long)(pair + k * geo.pairs) * gridDim.x) * Ks;
+        return (uint32_t)((geo.rows - row0 < Ks) ? geo.rows - row0 : Ks);
+    };
 
-    if (warp == 0) {
-        // ---- producer ----
-        for (unsigned long long it = 0; it < n_it; it++) {
-            const uint32_t s = (uint32_t)(it % NS);
-            const unsigned long long use = it / NS;
-            if (use > 0) mbar_wait(&empty[s], (uint32_t)((use - 1) & 1ull));
-            const unsigned long long row0 = (blockIdx.x + it * gridDim.x) * Ks;
-            const uint32_t nr = (uint32_t)((geo.rows - row0 < Ks) ? geo.rows - row0 : Ks);
+    if (role == 1u) {
+        // ---- warp B: loader + frames -----------------------------------------------------------------
+        auto load = [&](uint32_t k) {
+            unsigned long long row0;
+            const uint32_t nr = rows_of(k, row0), s = stage_of(k);
             if (lane == 0) mbar_expect_tx(&full[s], nr * n_in * 4u);
             __syncwarp();
             float *dst = reinterpret_cast<float *>(smem_raw + (size_t)s * geo.stage_bytes);
-            for (uint32_t c = lane; c < nr * geo.spr; c += 32u) {
-                const uint32_t r = div_magic(c, geo.magic_spr), j = c - r * geo.spr;
-                const uint32_t len = min(Q, n_in - j * Q);
-                bulk_g2s(dst + (size_t)c * SP, in + (row0 + r) * n_in + (size_t)j * Q, len * 4u, &full[s]);
+            for (uint32_t c = lane; c < nr * geo.ncopies; c += 32u) {
+                const uint32_t r = div_magic(c, geo.magic_ncopies), j = c - r * geo.ncopies;
+                const uint32_t len = min(geo.chunk, n_in - j * geo.chunk);
+                bulk_g2s(dst + (size_t)r * row_floats + (size_t)j * (geo.chunk + 4u), in + (row0 + r) * n_in + (size_t)j * geo.chunk,
+                         len * 4u, &full[s]);
+            }
+        };
+        for (uint32_t k = 0; k < geo.depth && k < my_steps; k++) load(k);
+        const bool rows_aligned = (n_out & 7u) == 0u;
+        const uint32_t cpr = n_out >> 3;
+        for (uint32_t k = 0; k < my_steps; k++) {
+            const uint32_t s = stage_of(k), par = (k / geo.depth) & 1u;
+            unsigned long long row0;
+            const uint32_t nr = rows_of(k, row0);
+            const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * geo.stage_bytes);
+            mbar_wait(&full[s], par);
+            const unsigned long long first = row0 * n_out;
+            const uint32_t outs = nr * n_out;
+            if (rows_aligned) {
+                const uint32_t n_chunks = nr * cpr;
+                for (uint32_t c8 = lane; c8 < n_chunks; c8 += 32u) {
+                    const uint32_t rr = div_magic(c8, geo.magic_cpr), c = c8 - rr * cpr;
+                    const float *row = tile + rr * row_floats;
+                    const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
+                    const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
+                    int e[8];
+                    e[0] = enc_s32(row[a.x]); e[1] = enc_s32(row[a.y]); e[2] = enc_s32(row[a.z]); e[3] = enc_s32(row[a.w]);
+                    e[4] = enc_s32(row[b.x]); e[5] = enc_s32(row[b.y]); e[6] = enc_s32(row[b.z]); e[7] = enc_s32(row[b.w]);
+                    uint4 o4;
+                    o4.x = pack_s16x2_sat(e[0], e[1]);
+                    o4.y = pack_s16x2_sat(e[2], e[3]);
+                    o4.z = pack_s16x2_sat(e[4], e[5]);
+                    o4.w = pack_s16x2_sat(e[6], e[7]);
+                    st_128(out + first + (size_t)c8 * 8u, o4, hint);
+                }
+            } else {
+                // the tile's output is one flat run of `outs` samples starting anywhere: an aligned body of
+                // 8-sample chunks (which may straddle frames) plus < 8 samples before and after it
+                const unsigned long long body0 = (first + 7ull) & ~7ull;
+                const unsigned long long body1 = (first + outs) & ~7ull;
+                const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
+                const uint32_t head = n_body ? (uint32_t)(body0 - first) : outs;
+                for (uint32_t c8 = lane; c8 < n_body; c8 += 32u) {
+                    const uint32_t f = head + 8u * c8;
+                    uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                    const float *row = tile + rr * row_floats;
+                    int e[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        e[j] = enc_s32(row[tab[o]]);
+                        if (++o == n_out) { o = 0; row += row_floats; }
+                    }
+                    uint4 o4;
+                    o4.x = pack_s16x2_sat(e[0], e[1]);
+                    o4.y = pack_s16x2_sat(e[2], e[3]);
+                    o4.z = pack_s16x2_sat(e[4], e[5]);
+                    o4.w = pack_s16x2_sat(e[6], e[7]);
+                    st_128(out + body0 + (size_t)c8 * 8u, o4, hint);
+                }
+                const uint32_t tail0 = head + 8u * n_body, n_edge = head + (outs - tail0);
+                for (uint32_t e = lane; e < n_edge; e += 32u) {
+                    const uint32_t f = e < head ? e : tail0 + (e - head);
+                    const uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
+                    out[first + f] = enc_s16(tile[rr * row_floats + tab[o]]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&done[s]);
+            if (k + geo.depth < my_steps) {                    // refill this stage once the meter warp has left it too
+                mbar_wait(&done[s], par);
+                load(k + geo.depth);
             }
         }
         return;
     }
 
-    // ---- consumers: warp cw takes steps cw, cw + NC, ... ----
-    const uint32_t cw = warp - 1u;
-    if (cw >= geo.NC) return;
-    const bool rows_aligned = (n_out & 7u) == 0u;
-    const uint32_t cpr = n_out >> 3;
-    double *rms_s = rms_all + (size_t)cw * 32u;
-    for (unsigned long long it = cw; it < n_it; it += geo.NC) {
-        const uint32_t s = (uint32_t)(it % NS);
-        const unsigned long long use = it / NS;
-        const unsigned long long row0 = (blockIdx.x + it * gridDim.x) * Ks;
-        const uint32_t nr = (uint32_t)((geo.rows - row0 < Ks) ? geo.rows - row0 : Ks);
+    // ---- warp A: level meter ---------------------------------------------------------------------------
+    double *rms_s = rms_all + (size_t)pair * 32u;
+    for (uint32_t k = 0; k < my_steps; k++) {
+        const uint32_t s = stage_of(k), par = (k / geo.depth) & 1u;
+        unsigned long long row0;
+        const uint32_t nr = rows_of(k, row0);
         const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * geo.stage_bytes);
         double lv_in = 0.0;
         if (lane < nr) lv_in = meter.state[row0 + lane];       // needed after the meter: the latency hides behind it
-        mbar_wait(&full[s], (uint32_t)(use & 1ull));
-
-        // ---- frames: pick + encode + store ------------------------------------------------------------
-        const unsigned long long first = row0 * n_out;
-        const uint32_t outs = nr * n_out;
-        if (rows_aligned) {
-            const uint32_t n_chunks = nr * cpr;
-            for (uint32_t c8 = lane; c8 < n_chunks; c8 += 32u) {
-                const uint32_t rr = div_magic(c8, geo.magic_cpr), c = c8 - rr * cpr;
-                const float *row = tile + rr * row_floats;
-                const uint4 a = *reinterpret_cast<const uint4 *>(tab + 8u * c);
-                const uint4 b = *reinterpret_cast<const uint4 *>(tab + 8u * c + 4u);
-                int e[8];
-                e[0] = enc_s32(row[a.x]); e[1] = enc_s32(row[a.y]); e[2] = enc_s32(row[a.z]); e[3] = enc_s32(row[a.w]);
-                e[4] = enc_s32(row[b.x]); e[5] = enc_s32(row[b.y]); e[6] = enc_s32(row[b.z]); e[7] = enc_s32(row[b.w]);
-                uint4 o4;
-                o4.x = pack_s16x2_sat(e[0], e[1]);
-                o4.y = pack_s16x2_sat(e[2], e[3]);
-                o4.z = pack_s16x2_sat(e[4], e[5]);
-                o4.w = pack_s16x2_sat(e[6], e[7]);
-                st_128(out + first + (size_t)c8 * 8u, o4, hint);
-            }
-        } else {
-            // the tile's output is one flat run of `outs` samples starting anywhere: an aligned body of
-            // 8-sample chunks (which may straddle frames) plus < 8 samples before and after it
-            const unsigned long long body0 = (first + 7ull) & ~7ull;
-            const unsigned long long body1 = (first + outs) & ~7ull;
-            const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
-            const uint32_t head = n_body ? (uint32_t)(body0 - first) : outs;
-            for (uint32_t c8 = lane; c8 < n_body; c8 += 32u) {
-                const uint32_t f = head + 8u * c8;
-                uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
-                const float *row = tile + rr * row_floats;
-                int e[8];
-#pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    e[j] = enc_s32(row[tab[o]]);
-                    if (++o == n_out) { o = 0; row += row_floats; }
-                }
-                uint4 o4;
-                o4.x = pack_s16x2_sat(e[0], e[1]);
-                o4.y = pack_s16x2_sat(e[2], e[3]);
-                o4.z = pack_s16x2_sat(e[4], e[5]);
-                o4.w = pack_s16x2_sat(e[6], e[7]);
-                st_128(out + body0 + (size_t)c8 * 8u, o4, hint);
-            }
-            const uint32_t tail0 = head + 8u * n_body, n_edge = head + (outs - tail0);
-            for (uint32_t k = lane; k < n_edge; k += 32u) {
-                const uint32_t f = k < head ? k : tail0 + (k - head);
-                const uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
-                out[first + f] = enc_s16(tile[rr * row_floats + tab[o]]);
-            }
-        }
-
-        // ---- level meter: lane w <-> (row r, quantum q), w = r * nq + q (Ks * nq <= 32) --------------------
+        mbar_wait(&full[s], par);
+        // lane w <-> (row w % Ks, quantum lane_q[w / Ks]) (Ks * nq <= 32)
         if (lane < Ks * nq) {
-            const uint32_t r = div_magic(lane, geo.magic_nq), q = lane - r * nq;
-            if (r < nr) rms_s[lane] = quantum_rms(reinterpret_cast<const float4 *>(tile + r * row_floats + q * SP), Q);
+            const uint32_t kq = div_magic(lane, geo.magic_Ks), r = lane - kq * Ks, q = geo.lane_q[kq];
+            const uint32_t i0 = q * Q;
+            if (r < nr)
+                rms_s[r * nq + q] = quantum_rms(reinterpret_cast<const float4 *>(tile + r * row_floats + i0 + 4u * div_magic(i0, geo.magic_chunk)), Q);
         }
         __syncwarp();
-        if (lane < nr) {
-            const unsigned long long row = row0 + lane;
-            double lv = lv_in;
-            bool poisoned = lv != lv;
-            for (uint32_t q = 0; q < nq; q++) {
-                level_step(lv, poisoned, rms_s[lane * nq + q]);
-                if (meter.levels) meter.levels[row * nq + q] = lv;
+        if (lane == 0) mbar_arrive(&done[s]);                  // the samples are no longer needed: the stage may be refilled
+        if (meter.levels) {
+            // per-quantum trace wanted: the plain sequential chain, one lane per row
+            if (lane < nr) {
+                const unsigned long long row = row0 + lane;
+                double lv = lv_in;
+                bool poisoned = lv != lv;
+                for (uint32_t q = 0; q < nq; q++) {
+                    level_step(lv, poisoned, rms_s[lane * nq + q]);
+                    meter.levels[row * nq + q] = lv;
+                }
+                meter.state[row] = lv;
             }
-            meter.state[row] = lv;
+        } else {
+            // Only the level after the frame's last quantum is wanted.  level_q = max(rms_q, f(level_{q-1}))
+            // with f(x) = fl(x * 0.85); f is monotone, so f(max(a, b)) = max(f(a), f(b)) EXACTLY and the
+            // chain unrolls to  level_last = max( f^nq(level_in), max_q f^(nq-1-q)(rms_q) ):  every lane
+            // decays its own quantum's rms the right number of times -- all lanes at once instead of one
+            // lane per row walking the quanta -- and a row's lanes are then max-reduced.  Math.max's NaN
+            // rule (any NaN in, NaN out, and it sticks) is a flag carried beside the values.
+            const uint32_t kq = div_magic(lane, geo.magic_Ks), r = lane - kq * Ks;      // this lane's row and position
+            const bool mine = lane < Ks * nq && r < nr;
+            const uint32_t q = mine ? geo.lane_q[kq] : 0u;
+            double v = mine ? rms_s[r * nq + q] : 0.0;
+            bool nan = v != v;
+            for (uint32_t t = q + 1u; t < nq; t++) v = __dmul_rn(v, 0.85);             // nq-1-q decays (0 for the idle lanes: q = 0, v = 0)
+            // the row's incoming level travels with the lane that holds the row's first slot (kq == 0)
+            double lvv = __shfl_sync(0xFFFFFFFFu, lv_in, r);                            // lv_in sits in lane r
+            if (mine && kq == 0u) {
+                nan |= lvv != lvv;
+                for (uint32_t t = 0; t < nq; t++) lvv = __dmul_rn(lvv, 0.85);
+                v = lvv > v ? lvv : v;
+            }
+            if (!mine) v = 0.0;
+            // lanes of one row are Ks apart (lane = kq * Ks + r, Ks a power of two): xor-reduce over kq
+            uint32_t any_nan = nan ? 1u : 0u;
+            for (uint32_t d = Ks; d < 32u; d <<= 1) {
+                const double o = __shfl_xor_sync(0xFFFFFFFFu, v, d);
+                any_nan |= __shfl_xor_sync(0xFFFFFFFFu, any_nan, d);
+                v = o > v ? o : v;
+            }
+            if (lane < nr) meter.state[row0 + lane] = any_nan ? __longlong_as_double(0x7FF8000000000000ll) : v;
         }
-        __syncwarp();                                         // every lane is done with the stage and with rms_s
-        if (lane == 0) mbar_arrive(&empty[s]);
+        __syncwarp();                                         // rms_s is reused by the next step
     }
 }
 
@@ -1059,123 +1113,8 @@ k_pick_f32(const uint32_t *__restrict__ in, size_t pitch_in, uint32_t *__restric
     }
 }
 
-// ---- kernels 5/6: device-side aggregator (App.tsx:273-288) ---------------------------------------------
-// The reference grows a Float32Array by one 128-sample quantum per worklet message (re-allocating
-// and re-copying it every time) and, once >= desiredMs have passed, converts the whole buffer.  On
-// the device each session owns two fixed half-buffers ("ring"); a quantum is appended in place and a
-// flush is a pick+encode over the rows of the sessions that flushed.
-//
-// k_append_quanta: quantum i of the push (512 contiguous bytes at src + i*quantum) goes to
-// ring + dst_slot[i]*quantum.  One warp per quantum, 128-bit loads/stores.  When a push holds
-// several flushes of one session it is appended in rounds (q_round[i] == round).
-__global__ void __launch_bounds__(256)
-k_append_quanta(const float *__restrict__ src, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
-                uint32_t n_quanta, uint32_t quantum, const uint8_t *__restrict__ q_round, uint8_t round)
-{
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n_quanta; i += warps) {
-        if (q_round && __ldg(q_round + i) != round) continue;   // this launch appends one round only
-        const float *s = src + (size_t)i * quantum;
-        float *d = ring + (size_t)__ldg(dst_slot + i) * quantum;
-        if ((quantum & 3u) == 0u) {
-            for (uint32_t k = lane; k < (quantum >> 2); k += 32u)
-                reinterpret_cast<float4 *>(d)[k] = __ldg(reinterpret_cast<const float4 *>(s) + k);
-        } else {
-            for (uint32_t k = lane; k < quantum; k += 32u) d[k] = __ldg(s + k);
-        }
-    }
-}
-
-// k_rows_pick_encode: kernel 2 with indirect rows -- frame r reads the ring row src_row[r]
-// (row pitch `pitch_in` floats) and writes n_out int16 at out + dst_off[r] (offsets are multiples
-// of 8 samples, so pairs are 4-byte aligned).
-template <int U>
-__global__ void __launch_bounds__(512)
-k_rows_pick_encode(const float *__restrict__ ring, size_t pitch_in, const uint32_t *__restrict__ src_row,
-                   int16_t *__restrict__ out, const unsigned long long *__restrict__ dst_off, uint32_t n_in,
-                   uint32_t n_out, const uint32_t *__restrict__ lut, uint32_t stride, unsigned long long n_pairs)
-{
-    const uint32_t ppr = (n_out + 1u) >> 1;
-    const unsigned long long tile_pairs = (unsigned long long)blockDim.x * U;
-    const unsigned long long n_tiles = (n_pairs + tile_pairs - 1) / tile_pairs;
-    for (unsigned long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const unsigned long long w0 = tile * tile_pairs + threadIdx.x;
-        float a[U], b[U];
-        int16_t *dst[U];
-        bool two[U];
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            const unsigned long long w = w0 + (unsigned long long)u * blockDim.x;
-            dst[u] = nullptr;
-            two[u] = false;
-            a[u] = b[u] = 0.0f;
-            if (w < n_pairs) {
-                const uint32_t r = (uint32_t)(w / ppr);
-                const uint32_t o = (uint32_t)(w - (unsigned long long)r * ppr) * 2u;
-                const float *row = ring + (size_t)__ldg(src_row + r) * pitch_in;
-                dst[u] = out + __ldg(dst_off + r) + o;
-                two[u] = (o + 1u < n_out);
-                uint32_t i0, i1 = 0xFFFFFFFFu;
-                if (lut) {
-                    i0 = __ldg(lut + o);
-                    if (two[u]) i1 = __ldg(lut + o + 1);
-                } else {
-                    i0 = o * stride;
-                    i1 = i0 + stride;
-                }
-                a[u] = (i0 < n_in) ? __ldg(row + i0) : __int_as_float(0x7FC00000);
-                b[u] = (two[u] && i1 < n_in) ? __ldg(row + i1) : __int_as_float(0x7FC00000);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; u++) {
-            if (dst[u] != nullptr) {
-                const uint32_t p = pack_s16x2_sat(enc_s32(a[u]), enc_s32(b[u]));
-                if (two[u]) *reinterpret_cast<uint32_t *>(dst[u]) = p;
-                else dst[u][0] = (int16_t)(p & 0xFFFFu);
-            }
-        }
-    }
-}
-
-// k_rows_meter: the level meter (App.tsx:267-271) over the frames an aggregator push flushed.  One
-// warp per frame; lane l accumulates quantum l of the frame in sample order (exact widening), then
-// the session's level runs through the frame's quanta in order.  session = src_row >> 1.
-__global__ void __launch_bounds__(256)
-k_rows_meter(const float *__restrict__ ring, size_t pitch_in, const uint32_t *__restrict__ src_row, uint32_t n_frames,
-             uint32_t nq, uint32_t quantum, double *__restrict__ level)
-{
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t f = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; f < n_frames; f += warps) {
-        const uint32_t row = __ldg(src_row + f);
-        const float *base = ring + (size_t)row * pitch_in;
-        double lv = level[row >> 1];
-        bool poisoned = lv != lv;
-        for (uint32_t q0 = 0; q0 < nq; q0 += 32u) {
-            const uint32_t q = q0 + lane;
-            double sum = 0.0;
-            if (q < nq) {
-                const float *src = base + (size_t)q * quantum;
-                for (uint32_t k = 0; k < quantum; k++) {
-                    const double x = widen_abs(__ldg(src + k));
-                    sum = __fma_rn(x, x, sum);
-                }
-            }
-            const double rms = rms_of(sum, quantum);
-            const uint32_t cnt = nq - q0 < 32u ? nq - q0 : 32u;
-            for (uint32_t j = 0; j < cnt; j++) {          // every lane runs the same chain; lane 0 stores it
-                const double r = __shfl_sync(0xFFFFFFFFu, rms, j);
-                poisoned |= r != r;
-                const double dec = __dmul_rn(lv, 0.85);
-                lv = r > dec ? r : dec;
-                if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
-            }
-        }
-        if (lane == 0) level[row >> 1] = lv;
-    }
-}
+// (The device-side aggregator's kernels -- count / scan / scatter / walk / convert / levels / append /
+// commit -- are in agg_kernels.cuh.)
 
 // ---- kernel 4: level meter alone (any layout; one thread per session, sequential) ----------------------
 // Fallback for batches kernel 2b cannot take (pitched rows, long frames).  Correct, not fast.
