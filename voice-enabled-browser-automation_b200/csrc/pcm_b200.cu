@@ -501,7 +501,8 @@ bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, 
     const size_t budget = (size_t)ctx->tune.ws_smem_kb * 1024;
     // warp pairs (meter warp + frames/loader warp), `depth` stages each; as many pairs as fit, at most ws_pairs
     const uint32_t depth = (uint32_t)ctx->tune.ws_depth;
-    const size_t per_pair = (size_t)depth * ((size_t)stage_bytes + 16) + 32 * 8;
+    const uint32_t stg_samples = (Ks * n_out + 8u + 7u) & ~7u;              // output staging of one pair (int16)
+    const size_t per_pair = (size_t)depth * ((size_t)stage_bytes + 16) + 32 * 8 + (size_t)stg_samples * 2;
     uint32_t pairs = (uint32_t)ctx->tune.ws_pairs;
     while (pairs > 1 && tab + pairs * per_pair > budget) pairs--;
     if (tab + pairs * per_pair > budget) return false;
@@ -514,7 +515,7 @@ bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, 
     geo.stride = lut ? 0u : (R ? R : 1u);
     geo.magic_cpr = magic_for(n_out / 8); geo.magic_nout = magic_for(n_out); geo.magic_chunk = magic_for(chunk);
     geo.magic_Ks = magic_for(Ks); geo.magic_ncopies = magic_for(ncopies);
-    geo.stage_bytes = stage_bytes; geo.pairs = pairs; geo.depth = depth;
+    geo.stage_bytes = stage_bytes; geo.pairs = pairs; geo.depth = depth; geo.stg_samples = stg_samples;
     {   // quantum order for the meter lanes: walk the chunks round-robin (position 0 of every chunk, then
         // position 1, ...), so that neighbouring lanes -- one LDS.128 phase is 8 of them -- sit in different chunks
         const uint32_t qpc = chunk / Q ? chunk / Q : 1u;   // whole quanta per chunk

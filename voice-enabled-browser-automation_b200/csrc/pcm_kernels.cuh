@@ -896,6 +896,7 @@ struct WsGeom {
     unsigned char lane_q[32];   // meter: item w -> row w % Ks, quantum lane_q[w / Ks] (spreads a phase over the chunks)
     uint32_t pairs;          // warp pairs per CTA
     uint32_t depth;          // stages per pair
+    uint32_t stg_samples;    // int16 per pair in the output staging buffer: Ks * n_out + 8, rounded up to 8
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
@@ -908,7 +909,7 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
                   const uint32_t *__restrict__ lut, int hint, MeterArgs meter)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    // layout: [pairs * depth][stage_bytes] | offset table u32[n_out] | full[NS] | done[NS] | rms [pairs][32]
+    // layout: [pairs * depth][stage_bytes] | offset table u32[n_out] | full[NS] | done[NS] | rms [pairs][32] | out staging [pairs][stg_samples]
     const uint32_t n_in = geo.n_in, n_out = geo.n_out, Ks = geo.Ks, NS = geo.pairs * geo.depth;
     uint32_t *tab = reinterpret_cast<uint32_t *>(smem_raw + (size_t)NS * geo.stage_bytes);
     const uint32_t tab_bytes = (n_out * 4u + 15u) & ~15u;
@@ -937,7 +938,10 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
 
     // this CTA's steps: step `it` is tile blockIdx.x + it * gridDim.x; pair p takes steps p, p + pairs, ...
     const uint32_t n_it = blockIdx.x < n_tiles ? (uint32_t)((n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0u;
-    const uint32_t pair = warp >> 1, role = warp & 1u;
+    // A warp's scheduler is fixed by its index (warp % 4).  The meter warp issues about twice as many
+    // instructions as the frames warp, so the roles alternate from pair to pair in a pattern that puts the
+    // meter warps of consecutive pairs on schedulers 0, 2, 1, 3, ... instead of always on 0 and 2.
+    const uint32_t pair = warp >> 1, role = ((warp ^ (pair >> 1)) & 1u);
     if (pair >= geo.pairs) return;
     const uint32_t my_steps = pair < n_it ? (n_it - pair + geo.pairs - 1) / geo.pairs : 0u;   // k = 0 .. my_steps-1 -> it = pair + k * pairs
     const uint32_t s0 = pair * geo.depth;
@@ -963,8 +967,14 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
             }
         };
         for (uint32_t k = 0; k < geo.depth && k < my_steps; k++) load(k);
-        const bool rows_aligned = (n_out & 7u) == 0u;
-        const uint32_t cpr = n_out >> 3;
+        // Picks with consecutive lanes on consecutive OUTPUTS: the table reads are then consecutive words and
+        // the picks are ratio-strided floats (conflict-free for odd ratios) -- the earlier layout, a lane per
+        // 8-output chunk, made every table read and every pick an 8-way bank conflict and put shared memory at
+        // 79 % of its bandwidth on 2944-sample frames.  The encoded samples go through a small per-pair
+        // staging buffer and leave as 128-bit stores; staging index i holds global output (first - shift) + i,
+        // shift = first mod 8, so 16-byte chunks line up in both.
+        int16_t *stg = reinterpret_cast<int16_t *>(reinterpret_cast<unsigned char *>(rms_all + (size_t)geo.pairs * 32u)) +
+                       (size_t)pair * geo.stg_samples;
         for (uint32_t k = 0; k < my_steps; k++) {
             const uint32_t s = stage_of(k), par = (k / geo.depth) & 1u;
             unsigned long long row0;
@@ -972,9 +982,13 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
             const float *tile = reinterpret_cast<const float *>(smem_raw + (size_t)s * geo.stage_bytes);
             mbar_wait(&full[s], par);
             const unsigned long long first = row0 * n_out;
-            const uint32_t outs = nr * n_out;
-            if (rows_aligned) {
-                const uint32_t n_chunks = nr * cpr;
+            const uint32_t outs = nr * n_out, shift = (uint32_t)(first & 7ull);
+            if ((n_out & 7u) == 0u) {
+                // frames that are whole 8-sample chunks (960 -> 320): a lane per chunk, table read as two
+                // 128-bit loads, straight to a 128-bit store.  The picks conflict here too, but these short
+                // frames leave shared memory far from saturated and the 8 independent picks per lane are
+                // worth more (measured: 1.02 of peak this way, 0.87 through the staging buffer).
+                const uint32_t cpr = n_out >> 3, n_chunks = nr * cpr;
                 for (uint32_t c8 = lane; c8 < n_chunks; c8 += 32u) {
                     const uint32_t rr = div_magic(c8, geo.magic_cpr), c = c8 - rr * cpr;
                     const float *row = tile + rr * row_floats;
@@ -990,36 +1004,41 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
                     o4.w = pack_s16x2_sat(e[6], e[7]);
                     st_128(out + first + (size_t)c8 * 8u, o4, hint);
                 }
-            } else {
-                // the tile's output is one flat run of `outs` samples starting anywhere: an aligned body of
-                // 8-sample chunks (which may straddle frames) plus < 8 samples before and after it
-                const unsigned long long body0 = (first + 7ull) & ~7ull;
-                const unsigned long long body1 = (first + outs) & ~7ull;
-                const uint32_t n_body = body1 > body0 ? (uint32_t)((body1 - body0) >> 3) : 0u;
-                const uint32_t head = n_body ? (uint32_t)(body0 - first) : outs;
-                for (uint32_t c8 = lane; c8 < n_body; c8 += 32u) {
-                    const uint32_t f = head + 8u * c8;
-                    uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
-                    const float *row = tile + rr * row_floats;
-                    int e[8];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&done[s]);
+                if (k + geo.depth < my_steps) {
+                    mbar_wait(&done[s], par);
+                    load(k + geo.depth);
+                }
+                continue;
+            }
+            for (uint32_t rr = 0; rr < nr; rr++) {
+                const float *row = tile + rr * row_floats;
+                int16_t *dst = stg + shift + rr * n_out;
+                uint32_t o = lane;
+                for (; o + 224u < n_out; o += 256u) {              // 8 independent picks per lane in flight
+                    uint32_t off[8];
+                    float x[8];
 #pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        e[j] = enc_s32(row[tab[o]]);
-                        if (++o == n_out) { o = 0; row += row_floats; }
-                    }
-                    uint4 o4;
-                    o4.x = pack_s16x2_sat(e[0], e[1]);
-                    o4.y = pack_s16x2_sat(e[2], e[3]);
-                    o4.z = pack_s16x2_sat(e[4], e[5]);
-                    o4.w = pack_s16x2_sat(e[6], e[7]);
-                    st_128(out + body0 + (size_t)c8 * 8u, o4, hint);
+                    for (int j = 0; j < 8; j++) off[j] = tab[o + 32u * j];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) x[j] = row[off[j]];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) dst[o + 32u * j] = enc_s16(x[j]);
                 }
-                const uint32_t tail0 = head + 8u * n_body, n_edge = head + (outs - tail0);
-                for (uint32_t e = lane; e < n_edge; e += 32u) {
-                    const uint32_t f = e < head ? e : tail0 + (e - head);
-                    const uint32_t rr = div_magic(f, geo.magic_nout), o = f - rr * n_out;
-                    out[first + f] = enc_s16(tile[rr * row_floats + tab[o]]);
-                }
+                for (; o < n_out; o += 32u) dst[o] = enc_s16(row[tab[o]]);
+            }
+            __syncwarp();
+            // [shift, shift + outs) of the staging buffer is global [first, first + outs): whole 8-sample chunks
+            // of it as 128-bit stores, the < 8 samples before and after one by one
+            const uint32_t lo = shift ? 8u : 0u, hi = (shift + outs) & ~7u;       // staging indices of the aligned body
+            int16_t *gbase = out + (first - shift);
+            if (hi > lo) {
+                for (uint32_t i = lo + 8u * lane; i < hi; i += 256u) st_128(gbase + i, *reinterpret_cast<const uint4 *>(stg + i), hint);
+                if (lane < lo - shift && shift) gbase[shift + lane] = stg[shift + lane];
+                if (lane < shift + outs - hi) gbase[hi + lane] = stg[hi + lane];
+            } else {
+                for (uint32_t i = shift + lane; i < shift + outs; i += 32u) gbase[i] = stg[i];
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&done[s]);
