@@ -275,10 +275,15 @@ def main():
     ap.add_argument("--only-meter", action="store_true")
     ap.add_argument("--meter-once", type=int, default=0, help="n_in: a short frames+meter run of that frame length (for ncu)")
     ap.add_argument("--tune", default="", help="comma list key=value for pcmb200_tune")
+    ap.add_argument("--agg-once", action="store_true", help="the aggregator benchmark alone (for ncu)")
     ap.add_argument("--sweep-meter", action="store_true")
     args = ap.parse_args()
     if args.tune:
         ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
+    if args.agg_once:
+        print(json.dumps(aggregator(ctx)), flush=True)
+        print(json.dumps(aggregator(ctx, meter=True)), flush=True)
+        return
     if args.meter_once:
         print(json.dumps(meter(ctx, args.meter_once, (1 << 19) if args.meter_once < 2000 else (1 << 17), reps=3)), flush=True)
         return
