@@ -228,7 +228,7 @@ def kernel_name(args):
     r = int(RATE // 16000)
     if "path=1" in args.tune or "tile=0" in args.tune and RATE % 16000 != 0:
         return "k_pick_encode"
-    if RATE % 16000 != 0 or r not in (1, 2, 3, 4, 6) or "path=2" in args.tune:
+    if RATE % 16000 != 0 or r not in (1, 2, 3, 4, 5, 6, 8, 12) or "path=2" in args.tune:
         return "k_tile_pick (cp.async.bulk tile staging)"
     if r == 1 or "coalesced=0" in args.tune:
         return f"k_decim_int<R={r}>"
