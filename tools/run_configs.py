@@ -267,6 +267,45 @@ def aggregator(ctx, S=65536, rate=48000, meter=False):
                     "the call to the end of pcmb200_aggregator_wait"}
 
 
+def aggregator_streaming(ctx, S=65536, rate=48000, meter=False, pushes=92):
+    """8f next-2 in the regime a live server runs in: every push carries ONE quantum per session (2.67 ms
+    of 48 kHz audio, sessions in random order), so 22 pushes out of 23 only append to the sessions'
+    buffers and the 23rd flushes every session.  Device-resident; per-push wall time from the call to the
+    end of pcmb200_aggregator_wait, averaged over `pushes` pushes (4 flush cycles)."""
+    rng = np.random.RandomState(1)
+    q_ms = 128e3 / rate
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=S, max_out_samples=16)
+    if meter:
+        agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
+    d_samples = ctx.device_buffer(S * 128 * 4)
+    ctx.synth_fill(d_samples.ptr, 128, S, 128, rate)
+    d_out = ctx.device_buffer(S * 984 * 2)
+    d_sess, d_arr = ctx.device_buffer(S * 4), ctx.device_buffer(S * 8)
+    d_fs, d_fl, d_fo = ctx.device_buffer(S * 4), ctx.device_buffer(S * 4), ctx.device_buffer(S * 8)
+    d_sess.upload(rng.permutation(S).astype(np.uint32))
+    times, frames = [], 0
+    for p in range(pushes):
+        d_arr.upload(np.full(S, (p + 1) * q_ms))
+        ctx.sync()
+        t0 = time.perf_counter()
+        agg.push_device(S, d_sess.ptr, d_arr.ptr, d_samples.ptr, d_out.ptr, S * 984, d_fs.ptr, d_fl.ptr, d_fo.ptr, S)
+        nf, _ = agg.wait()
+        times.append(time.perf_counter() - t0)
+        frames += nf
+    assert frames == S * (pushes // 23), frames
+    agg.close()
+    for d in (d_samples, d_out, d_sess, d_arr, d_fs, d_fl, d_fo):
+        d.free()
+    t = np.array(times[23:])                      # skip the first cycle (warm-up)
+    flush = t[22::23]
+    return {"config": "next-2 aggregator, streaming regime (one quantum per session per push)", "meter": meter, "sessions": S,
+            "ms_per_push_mean": float(t.mean() * 1e3), "ms_per_append_only_push": float(np.median(np.delete(t, np.s_[22::23])) * 1e3),
+            "ms_per_flushing_push": float(np.median(flush) * 1e3), "audio_ms_per_push": q_ms,
+            "realtime_sessions_at_48k": S * (q_ms * 1e-3) / float(t.mean()),
+            "note": "real-time capacity = sessions x (audio time per push / wall time per push)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
@@ -276,13 +315,24 @@ def main():
     ap.add_argument("--meter-once", type=int, default=0, help="n_in: a short frames+meter run of that frame length (for ncu)")
     ap.add_argument("--tune", default="", help="comma list key=value for pcmb200_tune")
     ap.add_argument("--agg-once", action="store_true", help="the aggregator benchmark alone (for ncu)")
+    ap.add_argument("--sweep-agg", action="store_true", help="sweep the aggregator convert kernel's CTA size and step size")
     ap.add_argument("--sweep-meter", action="store_true")
     args = ap.parse_args()
     if args.tune:
         ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
+    if args.sweep_agg:
+        for blk in (64, 128, 256):
+            for kb in (17, 34, 51, 68, 102):
+                ctx.tune(agg_block=blk, agg_stage_kb=kb)
+                for m in (False, True):
+                    r = aggregator(ctx, meter=m)
+                    print(json.dumps(dict(agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        return
     if args.agg_once:
         print(json.dumps(aggregator(ctx)), flush=True)
         print(json.dumps(aggregator(ctx, meter=True)), flush=True)
+        print(json.dumps(aggregator_streaming(ctx)), flush=True)
+        print(json.dumps(aggregator_streaming(ctx, meter=True)), flush=True)
         return
     if args.meter_once:
         print(json.dumps(meter(ctx, args.meter_once, (1 << 19) if args.meter_once < 2000 else (1 << 17), reps=3)), flush=True)
@@ -310,7 +360,7 @@ def main():
         for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)

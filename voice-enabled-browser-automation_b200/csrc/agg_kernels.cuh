@@ -7,7 +7,7 @@
 //
 // One push of n quanta (quantum i belongs to sessions[i], arrived at arrival[i]):
 //   1 k_agg_count    count[s]++ per quantum; the first toucher of a session appends it to `touched`
-//   2 scan A         exclusive scan of count[touched[k]] -> where each touched session's index list starts
+//   2 k_agg_reserve  where each touched session's index list starts (one atomic per session: any order will do)
 //   3 k_agg_scatter  sorted[cursor[s]++] = i   (atomic, so the order inside a session is arbitrary ...)
 //   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
 //                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
@@ -42,6 +42,8 @@ struct AggCtl {                  // lives in device memory; copied to the host a
     uint32_t n_frames;
     uint32_t n_leftover;         // quanta of this push that went to a ring
     unsigned long long out_total;   // output samples incl. the padding of every frame to 8 samples
+    uint32_t n_listed;           // running total of the per-session index lists (k_agg_reserve)
+    uint32_t pad_;
 };
 
 struct AggFrameDesc {
@@ -67,6 +69,19 @@ k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sess
     const uint32_t s = __ldg(sessions + i);
     if (s >= max_sessions) { atomicOr(&ctl->status, AGG_ST_BAD_SESSION); return; }
     if (atomicAdd(count + s, 1u) == 0u) touched[atomicAdd(&ctl->n_touched, 1u)] = s;
+}
+
+// ---- 2: reserve --------------------------------------------------------------------------------------------
+// Where each touched session's index list starts in `sorted`.  The lists may sit in any order, so no scan
+// is needed: every touched session takes count[s] slots from a running total with one atomic.
+__global__ void __launch_bounds__(256)
+k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
+              AggCtl *__restrict__ ctl)
+{
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= ctl->n_touched) return;
+    const uint32_t s = touched[k];
+    cursor[s] = atomicAdd(&ctl->n_listed, count[s]);
 }
 
 // ---- scans (two u32 channels, 2048 items per block) --------------------------------------------------------
@@ -200,6 +215,18 @@ struct ScanApplyB {
     uint32_t max_frames;
 };
 
+// Emits frame number `f` / output offset `off` for flushing quantum idx (shared by both scan B variants).
+__device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &ap, uint32_t idx, uint32_t f, unsigned long long off)
+{
+    if (f >= ap.max_frames) return;
+    const uint32_t nq = a.fl_nq[idx], s = ap.sessions[idx];
+    if (ap.frame_session) ap.frame_session[f] = s;
+    if (ap.frame_len) ap.frame_len[f] = __ldg(a.nout_of + nq);
+    if (ap.frame_offset) ap.frame_offset[f] = off;
+    ap.fdesc[f] = AggFrameDesc{s, nq, ap.fl_ring[idx], ap.fl_pos[idx]};
+    ap.fdesc_off[f] = off;
+}
+
 template <int MODE, typename Apply>
 __global__ void __launch_bounds__(kScanThreads)
 k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, Apply ap)
@@ -225,14 +252,7 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned lon
             if constexpr (MODE == 0) {
                 ap.cursor[a.touched[idx]] = ea;          // where this session's index list starts
             } else {
-                if (va[k] && ea < ap.max_frames) {        // quantum idx flushes frame number ea
-                    const uint32_t nq = a.fl_nq[idx], s = ap.sessions[idx];
-                    if (ap.frame_session) ap.frame_session[ea] = s;
-                    if (ap.frame_len) ap.frame_len[ea] = __ldg(a.nout_of + nq);
-                    if (ap.frame_offset) ap.frame_offset[ea] = eb;
-                    ap.fdesc[ea] = AggFrameDesc{s, nq, ap.fl_ring[idx], ap.fl_pos[idx]};
-                    ap.fdesc_off[ea] = eb;
-                }
+                if (va[k]) emit_frame(a, ap, idx, ea, eb);   // quantum idx flushes frame number ea
             }
         }
         ea += va[k]; eb += vb[k];
@@ -453,9 +473,10 @@ k_agg_convert(AggGeom g, AggConvertArgs a)
         if (METER) {
             // lane <-> slot; ring-carried quanta were metered when they were appended
             const uint32_t m_warps = (T + 31u) >> 5;
-            const uint32_t rot = m_warps < 8u ? (it * m_warps) & 7u : 0u;
+            const uint32_t nw = blockDim.x >> 5;
+            const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
             const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-            for (uint32_t sl = (((warp + 8u - rot) & 7u) << 5) + lane; sl < T; sl += blockDim.x) {
+            for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < T; sl += blockDim.x) {
                 uint32_t k = 0;
                 while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
                 const uint32_t j = sl - qstart[k];

@@ -76,18 +76,16 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const int scan_blocks = (int)((n + kScanBlock - 1) / kScanBlock);
     k_agg_count<<<blocks_n, 256, 0, st>>>(sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
     ScanArgs sa{n, a->touched, a->count, a->fl_nq, a->nout_of, a->ctl};
-    k_scan_reduce<0><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
-    k_scan_sums<0><<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, 0u, 0ull);
-    k_scan_apply<0, ScanApplyA><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ScanApplyA{a->cursor});
+    k_agg_reserve<<<blocks_n, 256, 0, st>>>(a->touched, a->count, a->cursor, a->ctl);
     k_agg_scatter<<<blocks_n, 256, 0, st>>>(sessions, n, a->cursor, a->sorted, a->ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
     k_agg_walk<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill,
                                                          a->last_send, wo, a->ctl);
+    ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     k_scan_reduce<1><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
     k_scan_sums<1><<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
-    ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     k_scan_apply<1, ScanApplyB><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ab);
-    ctx->launches += 9;
+    ctx->launches += 7;
 
     AggConvertArgs ca{};
     ca.samples = samples; ca.ring = a->ring; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
@@ -98,8 +96,9 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     unsigned long long conv_blocks = ((unsigned long long)n + a->G - 1) / a->G;
     const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
     if (conv_blocks > cap) conv_blocks = cap;
-    if (a->meter) k_agg_convert<true><<<(int)conv_blocks, 256, a->convert_smem, st>>>(a->geo, ca);
-    else k_agg_convert<false><<<(int)conv_blocks, 256, a->convert_smem, st>>>(a->geo, ca);
+    const int conv_threads = ctx->tune.agg_block;
+    if (a->meter) k_agg_convert<true><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
+    else k_agg_convert<false><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
     if (a->meter) {
         k_agg_levels<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms,
                                                              a->rms_at, a->level, a->ctl);
@@ -171,7 +170,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
 
     // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
-    a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (64 * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
+    a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, ((size_t)ctx->tune.agg_stage_kb * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
     a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 8 * (size_t)a->G * max_frame_quanta +
                       8 * (a->G + 1) + 24 * a->G;
     a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127);

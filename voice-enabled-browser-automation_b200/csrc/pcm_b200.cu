@@ -61,6 +61,9 @@ struct Tuning {
     int meter_tile_kb = 64;  // kernels 2b/2c with the fused level meter: tile size ...
     int meter_stages = 1;    // ... and stages (1 or 2)
     int meter_kernel = 2;    // 2: kernel 2d (producer/consumer pipeline), 1: kernel 2c (padded-row tiles), 0: kernel 2b only
+    int agg_block = 128;     // aggregator convert kernel: threads per CTA ...
+    int agg_stage_kb = 20;   // ... and shared memory for the frames of one step (read when an aggregator is created);
+                             //     measured best: one ~23-quanta frame per step, 128 threads (profiles/r02_sweep_aggregator.jsonl)
     int overlap_ticks = 0;   // 1: consecutive dense integer-ratio ticks may overlap on the GPU (programmatic dependent launch)
     int ws_smem_kb = 212;    // kernel 2d: shared memory for all stages ...
     int ws_pairs = 16;       // ... warp pairs per CTA (1..16; fewer if their stages do not fit) ...
@@ -1241,6 +1244,12 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "meter_kernel") {
         NEED(value >= 0 && value <= 2, "pcmb200_tune: meter_kernel must be 0, 1 or 2");
         ctx->tune.meter_kernel = (int)value;
+    } else if (k == "agg_block") {
+        NEED(value >= 64 && value <= 256 && value % 32 == 0, "pcmb200_tune: agg_block must be a multiple of 32 in [64, 256]");
+        ctx->tune.agg_block = (int)value;
+    } else if (k == "agg_stage_kb") {
+        NEED(value >= 8 && value <= 200, "pcmb200_tune: agg_stage_kb must be in [8, 200]");
+        ctx->tune.agg_stage_kb = (int)value;
     } else if (k == "overlap_ticks") {
         NEED(value == 0 || value == 1, "pcmb200_tune: overlap_ticks must be 0 or 1");
         ctx->tune.overlap_ticks = (int)value;
