@@ -98,3 +98,51 @@ def test_host_array_convenience(ctx):
     want = _oracle_levels(x, 2944, state)
     assert np.array_equal(levels.view(np.uint64), want.view(np.uint64))
     assert np.array_equal(new_state.view(np.uint64), want[:, -1].view(np.uint64))
+
+
+@pytest.mark.parametrize("rate,n_in,rows,quantum", [
+    (44100, 2816, 333, 128),     # pick table + kernel 2d (n_in % 4 == 0), 22 quanta: one frame per stage
+    (48000, 4096, 97, 128),      # 32 quanta: a stage's lanes exactly full
+    (48000, 4224, 41, 128),      # 33 quanta: more than a warp of quanta per frame -> kernel 2c / 2b take it
+    (16000, 2048, 130, 128),     # ratio 1
+    (96000, 3840, 77, 128),      # ratio 6, whole 8-sample chunks
+    (8000, 1024, 50, 128),       # upsampling (table), n_out = 2 * n_in
+    (48000, 960, 1, 128), (48000, 960, 3, 128), (48000, 2944, 1, 128), (48000, 2944, 2, 128),   # fewer rows than a stage
+    (48000, 1920, 211, 64),      # other quanta: 64 ...
+    (48000, 3072, 59, 256),      # ... and 256 samples
+    (44100, 3528, 35, 84),       # a quantum that is not a power of two (sum / quantum is a real division)
+])
+def test_meter_shapes_of_kernel_2d(ctx, rate, n_in, rows, quantum):
+    """Shapes that steer kernel 2d (warp pairs) through its corners -- tables, full and partial stages, a
+    single row, other quantum sizes -- and past its limits into the fallbacks; PCM, per-quantum trace
+    and final state bit-identical to the oracle, with and without the trace (the no-trace path runs the
+    level chain in its parallel form)."""
+    rng = np.random.RandomState(n_in * 7 + rows + quantum)
+    n_out = oracle.resample_len(n_in, rate)
+    nq = n_in // quantum
+    x = (rng.uniform(-1, 1, size=(rows, n_in)) * rng.uniform(0.001, 1.0, size=(rows, 1))).astype(np.float32)
+    x[0, :quantum] = 0.0                                   # a silent first quantum
+    if rows > 2:
+        x[2, quantum + 1] = np.float32(np.nan)             # poisons row 2 from its second quantum on
+        x[1, 5] = np.float32(1e-41)                        # a denormal among ordinary samples
+    state = rng.uniform(0, 2, rows)
+    state[rows // 2] = np.nan if rows > 4 else state[rows // 2]
+    want = np.empty((rows, nq))
+    for r in range(rows):
+        want[r] = oracle.level_meter(x[r, : nq * quantum], quantum, state[r])
+    d_in, d_out = ctx.device_buffer(x.nbytes), ctx.device_buffer(max(rows * n_out * 2, 16))
+    d_state, d_lv = ctx.device_buffer(rows * 8), ctx.device_buffer(rows * nq * 8)
+    d_in.upload(x)
+    for with_trace in (True, False):
+        d_state.upload(state)
+        d_out.memset(0x22)
+        ctx.frames_encode_meter_ptr(d_in.ptr, n_in, d_out.ptr, n_out, rows, n_in, rate, d_state.ptr,
+                                    d_lv.ptr if with_trace else None, quantum)
+        ctx.sync()
+        assert np.array_equal(d_out.download(np.int16, rows * n_out).reshape(rows, n_out), oracle.frames(x, n_in, rate))
+        if with_trace:
+            got = d_lv.download(np.float64, rows * nq).reshape(rows, nq)
+            assert np.array_equal(got.view(np.uint64), want.view(np.uint64))
+        assert np.array_equal(d_state.download(np.float64, rows).view(np.uint64), want[:, -1].view(np.uint64)), with_trace
+    for d in (d_in, d_out, d_state, d_lv):
+        d.free()
