@@ -112,6 +112,7 @@ def config3(ctx, ms_frame):
     """65,536 x 48 kHz frames, 16 distinct tick buffers (4.7 GB at 20 ms) rotated to defeat L2."""
     S, n_in = 65536, 48 * ms_frame
     n_out = n_in // 3
+    ctx.tune(overlap_ticks=1)        # 16 / 8 distinct tick buffers: consecutive ticks are independent
     ticks = 16 if ms_frame == 20 else 8
     bufs = [(ctx.device_buffer(S * n_in * 4), ctx.device_buffer(S * n_out * 2)) for _ in range(ticks)]
     for t, (di, _) in enumerate(bufs):
@@ -129,6 +130,7 @@ def config3(ctx, ms_frame):
     assert np.array_equal(bufs[0][1].download(np.int16, 4096 * n_out).reshape(4096, n_out), oracle.frames(x, n_in, 48000, threads=8))
     for di, do in bufs:
         di.free(); do.free()
+    ctx.tune(overlap_ticks=0)
     return {"config": 3, "sessions": S, "frame_ms": ms_frame, "n_in": n_in, "n_out": n_out, "distinct_ticks": ticks,
             "bytes_per_tick": algo, "us_per_tick": ms * 1e3, "in_samples_per_s": S * n_in / (ms * 1e-3),
             "gbs": algo / (ms * 1e-3) / 1e9, "frac_of_measured_peak": algo / (ms * 1e-3) / 1e9 / PEAK}
@@ -360,7 +362,7 @@ def main():
         for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: aggregator_streaming(ctx, S=1 << 20, pushes=69), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)

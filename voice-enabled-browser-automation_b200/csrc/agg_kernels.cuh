@@ -12,7 +12,7 @@
 //   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
 //                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
 //                    writes scratch (the session's new state, per-quantum flush marks and ring slots).
-//   5 scan B         over quanta: frame index and output offset of every flush, in flush order
+//   5 scan           over quanta: frame index and output offset of every flush, in flush order
 //                    (= ascending i); its apply pass also emits the caller's frame arrays.
 //   6 k_agg_convert  every flushed frame: its quanta are staged into shared memory with async
 //                    copies -- from the session's ring (quanta carried over from earlier pushes) or
@@ -84,36 +84,27 @@ k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__
     cursor[s] = atomicAdd(&ctl->n_listed, count[s]);
 }
 
-// ---- scans (two u32 channels, 2048 items per block) --------------------------------------------------------
-// A three-pass scan: per-block totals, one block scans the totals, per-block rescan + apply.  The
-// length is read on the device (n_touched is not known to the host); blocks past it do nothing.
+// ---- 5: scan over the push's quanta (two channels, 2048 items per block) ---------------------------------------
+// Frame number and output offset of every flush, in flush order (= ascending quantum index): a three-pass
+// scan -- per-block totals, one block scans the totals, per-block rescan + emit.  Channel a counts the
+// flushes, channel b adds up the frames' output lengths rounded up to 8 samples.
 constexpr int kScanThreads = 256, kScanItems = 8, kScanBlock = kScanThreads * kScanItems;
 
 struct ScanArgs {
-    // mode 0 (scan A): item k < ctl->n_touched, a = count[touched[k]]
-    // mode 1 (scan B): item i < n, a = fl_nq[i] != 0, b = padded output length of that frame
-    uint32_t n;
-    const uint32_t *touched, *count;
+    uint32_t n;                      // item i < n: a = fl_nq[i] != 0, b = padded output length of that frame
     const uint32_t *fl_nq, *nout_of;
     const AggCtl *ctl;
 };
 
-template <int MODE>
 __device__ __forceinline__ void scan_load(const ScanArgs &a, uint32_t idx, uint32_t len, uint32_t &va, uint32_t &vb)
 {
     va = 0; vb = 0;
     if (idx >= len) return;
-    if (MODE == 0) {
-        va = a.count[a.touched[idx]];
-    } else {
-        // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
-        if (a.ctl->status != 0u) return;
-        const uint32_t nq = a.fl_nq[idx];
-        if (nq) { va = 1u; vb = (__ldg(a.nout_of + nq) + 7u) & ~7u; }
-    }
+    // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
+    if (a.ctl->status != 0u) return;
+    const uint32_t nq = a.fl_nq[idx];
+    if (nq) { va = 1u; vb = (__ldg(a.nout_of + nq) + 7u) & ~7u; }
 }
-template <int MODE>
-__device__ __forceinline__ uint32_t scan_len(const ScanArgs &a) { return MODE == 0 ? a.ctl->n_touched : a.n; }
 
 // exclusive block scan of one value per thread (256 threads); returns the block total in `total`
 __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_sums, uint32_t &total)
@@ -139,19 +130,18 @@ __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_sums
     return base + inc - v;
 }
 
-template <int MODE>
 __global__ void __launch_bounds__(kScanThreads)
 k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b)
 {
     __shared__ uint32_t ws[kScanThreads / 32];
-    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
     uint32_t sa = 0, sb = 0;
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) {
         uint32_t va, vb;
-        scan_load<MODE>(a, base + threadIdx.x * kScanItems + k, len, va, vb);
+        scan_load(a, base + threadIdx.x * kScanItems + k, len, va, vb);
         sa += va; sb += vb;
     }
     uint32_t ta, tb;
@@ -161,15 +151,14 @@ k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ 
 }
 
 // One block turns the per-block totals into exclusive offsets (64-bit for channel b: sample counts).
-// MODE 1 also checks the two capacities and publishes n_frames / out_total.
-template <int MODE>
+// It also checks the two capacities and publishes n_frames / out_total.
 __global__ void __launch_bounds__(1024)
 k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b, unsigned long long *__restrict__ offs_b,
             AggCtl *__restrict__ ctl, uint32_t max_frames, unsigned long long out_capacity)
 {
     __shared__ unsigned long long carry_a, carry_b;
     __shared__ unsigned long long wsum_a[32], wsum_b[32];
-    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t len = a.n;
     const uint32_t nb = (len + kScanBlock - 1) / kScanBlock;
     if (threadIdx.x == 0) { carry_a = 0; carry_b = 0; }
     __syncthreads();
@@ -195,7 +184,7 @@ k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ su
         if (threadIdx.x == 0) { carry_a += ta; carry_b += tb; }
         __syncthreads();
     }
-    if (MODE == 1 && threadIdx.x == 0) {
+    if (threadIdx.x == 0) {
         ctl->n_frames = (uint32_t)carry_a;
         ctl->out_total = carry_b;
         uint32_t st = 0;
@@ -205,7 +194,6 @@ k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ su
     }
 }
 
-struct ScanApplyA { uint32_t *cursor; };
 struct ScanApplyB {
     const uint32_t *sessions, *fl_ring, *fl_pos;
     uint32_t *frame_session, *frame_len;
@@ -215,7 +203,7 @@ struct ScanApplyB {
     uint32_t max_frames;
 };
 
-// Emits frame number `f` / output offset `off` for flushing quantum idx (shared by both scan B variants).
+// Emits frame number `f` / output offset `off` for flushing quantum idx.
 __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &ap, uint32_t idx, uint32_t f, unsigned long long off)
 {
     if (f >= ap.max_frames) return;
@@ -227,19 +215,18 @@ __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &
     ap.fdesc_off[f] = off;
 }
 
-template <int MODE, typename Apply>
 __global__ void __launch_bounds__(kScanThreads)
-k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, Apply ap)
+k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, ScanApplyB ap)
 {
     __shared__ uint32_t ws[kScanThreads / 32];
-    const uint32_t len = scan_len<MODE>(a);
+    const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
-    if (MODE == 1 && a.ctl->status != 0u) return;      // rejected push: nothing to emit
+    if (a.ctl->status != 0u) return;                   // rejected push: nothing to emit
     uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) {
-        scan_load<MODE>(a, base + threadIdx.x * kScanItems + k, len, va[k], vb[k]);
+        scan_load(a, base + threadIdx.x * kScanItems + k, len, va[k], vb[k]);
         sa += va[k]; sb += vb[k];
     }
     uint32_t ta, tb;
@@ -249,11 +236,7 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned lon
     for (int k = 0; k < kScanItems; k++) {
         const uint32_t idx = base + threadIdx.x * kScanItems + k;
         if (idx < len) {
-            if constexpr (MODE == 0) {
-                ap.cursor[a.touched[idx]] = ea;          // where this session's index list starts
-            } else {
-                if (va[k]) emit_frame(a, ap, idx, ea, eb);   // quantum idx flushes frame number ea
-            }
+            if (va[k]) emit_frame(a, ap, idx, ea, eb);       // quantum idx flushes frame number ea
         }
         ea += va[k]; eb += vb[k];
     }

@@ -75,16 +75,16 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const int blocks_n = (int)((n + 255u) / 256u);
     const int scan_blocks = (int)((n + kScanBlock - 1) / kScanBlock);
     k_agg_count<<<blocks_n, 256, 0, st>>>(sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
-    ScanArgs sa{n, a->touched, a->count, a->fl_nq, a->nout_of, a->ctl};
+    ScanArgs sa{n, a->fl_nq, a->nout_of, a->ctl};
     k_agg_reserve<<<blocks_n, 256, 0, st>>>(a->touched, a->count, a->cursor, a->ctl);
     k_agg_scatter<<<blocks_n, 256, 0, st>>>(sessions, n, a->cursor, a->sorted, a->ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
     k_agg_walk<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill,
                                                          a->last_send, wo, a->ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
-    k_scan_reduce<1><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
-    k_scan_sums<1><<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
-    k_scan_apply<1, ScanApplyB><<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ab);
+    k_scan_reduce<<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
+    k_scan_sums<<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
+    k_scan_apply<<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ab);
     ctx->launches += 7;
 
     AggConvertArgs ca{};
