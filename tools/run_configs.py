@@ -335,6 +335,7 @@ def main():
         print(json.dumps(aggregator(ctx, meter=True)), flush=True)
         print(json.dumps(aggregator_streaming(ctx)), flush=True)
         print(json.dumps(aggregator_streaming(ctx, meter=True)), flush=True)
+        print(json.dumps(aggregator_streaming(ctx, S=1 << 20, pushes=69)), flush=True)
         return
     if args.meter_once:
         print(json.dumps(meter(ctx, args.meter_once, (1 << 19) if args.meter_once < 2000 else (1 << 17), reps=3)), flush=True)

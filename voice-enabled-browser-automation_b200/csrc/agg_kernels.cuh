@@ -78,10 +78,21 @@ __global__ void __launch_bounds__(256)
 k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
               AggCtl *__restrict__ ctl)
 {
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ctl->n_touched) return;
-    const uint32_t s = touched[k];
-    cursor[s] = atomicAdd(&ctl->n_listed, count[s]);
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+    const bool live = k < ctl->n_touched;
+    const uint32_t s = live ? touched[k] : 0u, c = live ? count[s] : 0u;
+    // one atomic per WARP (a million sessions hitting one counter cost 33 us): prefix-sum the warp's counts,
+    // lane 31 reserves the warp's total, everyone adds its own offset
+    uint32_t inc = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
+        if (lane >= (uint32_t)d) inc += o;
+    }
+    uint32_t base = 0;
+    if (lane == 31u && inc) base = atomicAdd(&ctl->n_listed, inc);
+    base = __shfl_sync(0xFFFFFFFFu, base, 31);
+    if (live) cursor[s] = base + inc - c;
 }
 
 // ---- 5: scan over the push's quanta (two channels, 2048 items per block) ---------------------------------------
@@ -512,13 +523,30 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t granules = quantum >> 2;
     if (!METER) {
+        // A warp takes 4 consecutive quanta per step and has all their loads in flight before the first store
+        // (one quantum at a time left every warp waiting out a full slot-lookup + load round trip per 512 bytes).
         const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-        for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < n; i += warps) {
-            const uint32_t slot = __ldg(dst_slot + i);
-            if (slot == 0xFFFFFFFFu) continue;
-            const float4 *s4 = reinterpret_cast<const float4 *>(samples + (size_t)i * quantum);
-            float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)slot * quantum);
-            for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = __ldg(s4 + gi);
+        for (uint32_t i0 = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 4u; i0 < n; i0 += warps * 4u) {
+            uint32_t slot[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) slot[u] = i0 + u < n ? __ldg(dst_slot + i0 + u) : 0xFFFFFFFFu;
+            if (granules == 32u) {                                  // the 128-sample quantum: one float4 per lane
+                float4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (slot[u] != 0xFFFFFFFFu) v[u] = __ldg(reinterpret_cast<const float4 *>(samples + (size_t)(i0 + u) * quantum) + lane);
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (slot[u] != 0xFFFFFFFFu) reinterpret_cast<float4 *>(ring + (size_t)slot[u] * quantum)[lane] = v[u];
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (slot[u] == 0xFFFFFFFFu) continue;
+                    const float4 *s4 = reinterpret_cast<const float4 *>(samples + (size_t)(i0 + u) * quantum);
+                    float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)slot[u] * quantum);
+                    for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = __ldg(s4 + gi);
+                }
+            }
         }
         return;
     }

@@ -107,7 +107,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
         k_agg_append<true><<<grid, 256, a->append_smem, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
         ctx->launches += 1;
     } else {
-        const unsigned long long warps_blocks = ((unsigned long long)n + 7ull) / 8ull;
+        const unsigned long long warps_blocks = ((unsigned long long)n + 31ull) / 32ull;   // 8 warps x 4 quanta per block step
         const int grid = (int)(warps_blocks < cap ? warps_blocks : cap);
         k_agg_append<false><<<grid, 256, 0, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
     }
