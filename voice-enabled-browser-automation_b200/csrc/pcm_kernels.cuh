@@ -863,11 +863,14 @@ k_frames_meter(const float *__restrict__ in, int16_t *__restrict__ out, TileMete
 // stays resident.  This kernel keeps that time short and the buffer full:
 //   * one CTA per SM, persistent; the CTA is NP independent warp PAIRS, each with its own `depth` small
 //     stages (a stage = Ks rows holding at most 32 quanta: 4 frames of 960 samples, ONE 2944-sample frame);
-//   * in a pair, warp A is the METER: one lane per quantum, then the level chain on its first Ks lanes;
+//   * in a pair, warp A is the METER: one lane per quantum, then the level chain (all lanes at once in its
+//     unrolled form when only the final level is wanted, else one lane per row);
 //     warp B does the FRAMES (pick + encode + store) at the same time and is also the pair's loader:
 //     when both warps are done with a stage (done[s], two arrivals) it issues the bulk copies of the
 //     pair's next tile into it (completing on full[s]).  With depth 2 the other stage is loading while
-//     this one is computed on.  Nothing is shared between pairs, so there is no block-wide barrier after
+//     this one is computed on; measured, more pairs with ONE stage each beat fewer, deeper pairs (the
+//     other pairs cover a pair's load latency), so the default is depth 1 and 12-16 pairs.  Nothing is
+//     shared between pairs, so there is no block-wide barrier after
 //     the prologue, no producer warp to become the bottleneck (a single dedicated producer measured ~660
 //     clocks + ~130 per copy per stage: 3 samples/clk/SM against the 4.3 the HBM share needs), and no
 //     head-of-line blocking between stages;
