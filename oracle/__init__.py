@@ -1,8 +1,9 @@
 """ctypes binding of the CPU oracle (oracle/pcm_oracle.c).  TEST INFRASTRUCTURE ONLY.
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / ``--impl reference``
-legs may import this package; the product path never does.  PARITY UNPINNED: see the
-header of pcm_oracle.c (no JS engine here, no golden vectors in the reference).
+legs may import this package; the product path never does.  Parity: pinned to the reference's
+source text run by tests/golden/mini_js.py (tests/test_ref_exec.py), not yet by a production
+JavaScript engine -- see the header of pcm_oracle.c.
 """
 from __future__ import annotations
 

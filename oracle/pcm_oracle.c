@@ -11,16 +11,25 @@
  *   level meter       /root/reference/apps/web/src/App.tsx:267-271
  *   keep-alive frame  /root/reference/apps/web/src/App.tsx:291-296
  *
- * PARITY UNPINNED: the reference is TypeScript for a browser.  No JavaScript
- * engine (node, deno, bun, QuickJS, V8 ...) exists in the build container or
- * can be installed, and the reference's own test-suite holds no golden vector,
- * known-answer test or fixture for any of these functions.
- * The oracle is therefore pinned only by (1) the source text cited above, (2)
- * the ECMA-262 definitions of Number arithmetic (IEEE-754 binary64), Math.floor,
- * Float32Array element reads (exact widening) and Int16Array element writes
- * (ToInt16: non-finite -> 0, truncate toward zero, modulo 2^16), and (3) an
- * independent second restatement in pure Python floats (tests/golden/make_golden.py)
- * whose committed outputs this file must reproduce.
+ * PARITY: pinned to outputs of the reference's own source text, executed in the
+ * build container by tests/golden/mini_js.py -- a small interpreter for the
+ * JavaScript / TypeScript subset these functions are written in, made for this
+ * purpose because no JavaScript engine (node, deno, bun, QuickJS, V8 ...) exists in
+ * the image or can be installed, and the reference's own test-suite holds no golden
+ * vector for these functions.  tests/golden/make_ref_exec.py
+ * slices the functions out of App.tsx at run time, runs that text on the committed
+ * input vectors and writes tests/golden/ref_exec.npz; tests/test_ref_exec.py requires
+ * this file to reproduce every output (encoder, frames, the onmessage handler's flush
+ * decisions / frames / levels, the keep-alive timer).  NOT YET CONFIRMED BY A
+ * PRODUCTION ENGINE: the language semantics under that run are mini_js.py's reading
+ * of ECMA-262 (unit-tested rule by rule in the same test file);
+ * `node tools/pin_with_node.mjs` is the one-command check that remains.
+ * Beside that pin: (1) the ECMA-262 definitions of Number arithmetic (IEEE-754
+ * binary64), Math.floor, Float32Array reads (exact widening) and Int16Array writes
+ * (ToInt16: non-finite -> 0, truncate toward zero, modulo 2^16); (2) a second
+ * restatement in pure Python floats and (3) a third in integers only
+ * (tests/golden/make_golden.py) whose committed outputs this file must reproduce --
+ * and which the reference text, run as above, reproduces too.
  *
  * Who may use this file: tests/, __graft_entry__.smoke() and bench.py's
  * cpu_baseline / --impl reference legs, as the CHECKER or the timed CPU

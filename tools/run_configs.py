@@ -203,7 +203,7 @@ def meter(ctx, n_in, S, reps=20):
             "in_samples_per_s": S * n_in / (ms_fused * 1e-3)}
 
 
-def aggregator(ctx, S=65536, rate=48000, meter=False):
+def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
     """8f next-2: S sessions, every push carries 23 quanta per session (61.3 ms of 48 kHz audio), so
     every session flushes one 2944-sample frame per push.  Everything device-resident
     (pcmb200_aggregator_push_device): `enqueue_ms` is the host time of the call, `total_ms` runs from
@@ -214,8 +214,12 @@ def aggregator(ctx, S=65536, rate=48000, meter=False):
     if meter:
         agg.set_meter(True)
     agg.reset_range(0, S, 0.0)
-    sessions = np.tile(np.arange(S, dtype=np.uint32), nq)                  # quantum-major arrival order
-    base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
+    if order == "quantum":                                                 # quantum-major arrival order (what time order gives)
+        sessions = np.tile(np.arange(S, dtype=np.uint32), nq)
+        base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
+    else:                                                                  # diagnostic: every session's quanta adjacent in the push
+        sessions = np.repeat(np.arange(S, dtype=np.uint32), nq)
+        base = np.tile(np.arange(1, nq + 1) * (128e3 / rate), S)
     d_samples = ctx.device_buffer(n * 128 * 4)
     ctx.synth_fill(d_samples.ptr, 128, n, 128, rate)
     d_out = ctx.device_buffer(S * 984 * 2)
@@ -236,7 +240,8 @@ def aggregator(ctx, S=65536, rate=48000, meter=False):
     fl, fo, fs = d_fl.download(np.uint32, S), d_fo.download(np.uint64, S), d_fs.download(np.uint32, S)
     assert (fl == 981).all() and (fs == np.arange(S)).all()
     # every frame against the oracle: session s holds quanta s, s+S, ... of the push
-    x = d_samples.download(np.float32, n * 128).reshape(nq, S, 128).transpose(1, 0, 2).reshape(S, nq * 128)
+    x = d_samples.download(np.float32, n * 128)
+    x = x.reshape(nq, S, 128).transpose(1, 0, 2).reshape(S, nq * 128) if order == "quantum" else x.reshape(S, nq * 128)
     want = oracle.frames(np.ascontiguousarray(x), nq * 128, rate, threads=os.cpu_count() or 1)
     got = d_out.download(np.int16, S * 984).reshape(S, 984)[:, :981]
     assert np.array_equal(got, want)
@@ -261,7 +266,7 @@ def aggregator(ctx, S=65536, rate=48000, meter=False):
     t = min(total[1:])
     # bytes the push has to move: every quantum read once (512 B), every frame written once
     algo = n * 512 + S * 981 * 2
-    return {"config": "next-2 device aggregator (device-resident quanta, ids, times and frames)", "meter": meter, "sessions": S,
+    return {"config": "next-2 device aggregator (device-resident quanta, ids, times and frames)", "meter": meter, "sessions": S, "push_order": order,
             "quanta_per_push": n, "enqueue_ms": min(enq[1:]) * 1e3, "total_ms": t * 1e3, "in_samples_per_s": n * 128 / t,
             "realtime_sessions_at_48k": n * 128 / t / rate, "algorithmic_gbs": algo / t / 1e9, "frac_of_measured_peak": algo / t / 1e9 / PEAK,
             "host_metadata_push_ms": min(host_meta) * 1e3, "frames_checked_against_oracle": S,
@@ -319,16 +324,21 @@ def main():
     ap.add_argument("--agg-once", action="store_true", help="the aggregator benchmark alone (for ncu)")
     ap.add_argument("--sweep-agg", action="store_true", help="sweep the aggregator convert kernel's CTA size and step size")
     ap.add_argument("--sweep-meter", action="store_true")
+    ap.add_argument("--agg-order", default="", help="diagnostic: run the big-push aggregator benchmark alone with this push order (quantum | session)")
     args = ap.parse_args()
     if args.tune:
         ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
     if args.sweep_agg:
-        for blk in (64, 128, 256):
-            for kb in (17, 34, 51, 68, 102):
-                ctx.tune(agg_block=blk, agg_stage_kb=kb)
-                for m in (False, True):
-                    r = aggregator(ctx, meter=m)
-                    print(json.dumps(dict(agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        for pipe in (1, 0):
+            for blk in (64, 128, 256):
+                for kb in (17, 34, 51, 68):
+                    ctx.tune(agg_block=blk, agg_stage_kb=kb, agg_pipe=pipe)
+                    for m in (False, True):
+                        r = aggregator(ctx, meter=m)
+                        print(json.dumps(dict(agg_pipe=pipe, agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        return
+    if args.agg_order:
+        print(json.dumps(aggregator(ctx, order=args.agg_order)), flush=True)
         return
     if args.agg_once:
         print(json.dumps(aggregator(ctx)), flush=True)

@@ -316,18 +316,33 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     const uint32_t c0 = fill[s];
     uint32_t f = c0, ring_cnt = c0, frame_start = 0;
     double last = last_send[s];
-    for (uint32_t j = 0; j < m; j++) {
-        const uint32_t i = list[j];
-        if (f >= g.half_quanta) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
-        f++;
-        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
-        const double now = arrival[i];
-        if (now - last >= g.desired_ms) {
-            o.fl_nq[i] = f; o.fl_ring[i] = ring_cnt; o.fl_pos[i] = base + frame_start;
-            f = 0; ring_cnt = 0; frame_start = j + 1u;
-            last = now;                                                    // App.tsx:287
-        } else {
-            o.fl_nq[i] = 0u;
+    // The rule is sequential in `last`, but the addresses are not: the arrival times of a batch of quanta are
+    // fetched together (one memory round trip per 8 quanta instead of one per quantum -- the kernel was a chain of
+    // dependent misses, 23 deep for a 60 ms frame).
+    constexpr uint32_t B = 8;
+    for (uint32_t j0 = 0; j0 < m; j0 += B) {
+        uint32_t idx[B];
+        double at[B];
+#pragma unroll
+        for (uint32_t u = 0; u < B; u++) idx[u] = j0 + u < m ? list[j0 + u] : 0u;
+#pragma unroll
+        for (uint32_t u = 0; u < B; u++) at[u] = j0 + u < m ? arrival[idx[u]] : 0.0;
+#pragma unroll
+        for (uint32_t u = 0; u < B; u++) {
+            const uint32_t j = j0 + u;
+            if (j >= m) break;
+            const uint32_t i = idx[u];
+            if (f >= g.half_quanta) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
+            f++;
+            // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+            const double now = at[u];
+            if (now - last >= g.desired_ms) {
+                o.fl_nq[i] = f; o.fl_ring[i] = ring_cnt; o.fl_pos[i] = base + frame_start;
+                f = 0; ring_cnt = 0; frame_start = j + 1u;
+                last = now;                                                    // App.tsx:287
+            } else {
+                o.fl_nq[i] = 0u;
+            }
         }
     }
     // quanta after the last flush stay in the session's buffer: behind what was there if nothing flushed
@@ -478,6 +493,184 @@ k_agg_convert(AggGeom g, AggConvertArgs a)
                 a.rms_at[fd[k].pos + (j - fd[k].ring_count)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
             }
         }
+    }
+}
+
+// ---- 6': convert, software-pipelined -------------------------------------------------------------------------------
+// Same work as k_agg_convert; what ncu said about that kernel shaped this one.  There a CTA step was a chain of
+// dependent round trips -- frame descriptor (L2) -> index list entry (L2) -> the quanta themselves (HBM) -> picks ->
+// stores -- with a block barrier between each, and the arena sat empty during the first two: the bytes a CTA keeps
+// in flight are what its shared memory buys, and for half of every step it bought nothing.  Here
+//   * the descriptors and source addresses of step i+1 are fetched while the async copies of step i are in flight
+//     (two meta buffers; warp 0 turns the step's descriptors into slot / pair offsets with one warp scan), so the
+//     arena goes from "consumed" straight back to "filling";
+//   * a step has 3 block barriers instead of 5;
+//   * the picks are lane <-> PAIR of adjacent outputs (lane stride 2*ratio words in shared memory: at most 2-way bank
+//     conflicts; lane <-> 8 outputs was 8-way for ratio 3), written as one 32-bit streaming store per lane, 128
+//     contiguous bytes per warp.
+struct AggMetaLayout { uint32_t slot_src, foff, fd, qstart, pstart, nout, bytes; };
+__host__ __device__ inline AggMetaLayout agg_meta_layout(uint32_t G, uint32_t max_slots)
+{
+    AggMetaLayout L;
+    uint32_t o = 0;
+    L.slot_src = o; o += max_slots * 8u;       // const float * per slot
+    L.foff = o; o += G * 8u;                   // output offset of each frame
+    L.fd = o; o += G * 16u;                    // AggFrameDesc
+    L.qstart = o; o += (G + 1u) * 4u;          // first slot of each frame
+    L.pstart = o; o += (G + 1u) * 4u;          // first output pair of each frame
+    L.nout = o; o += G * 4u;                   // output length of each frame
+    L.bytes = (o + 15u) & ~15u;
+    return L;
+}
+__host__ __device__ inline size_t agg_arena_bytes(uint32_t G, uint32_t half_quanta, uint32_t quantum)
+{
+    return (((size_t)G * half_quanta * (quantum + 4u) * 4u) + 127u) & ~(size_t)127u;
+}
+
+__device__ __forceinline__ void st_32(int16_t *p, uint32_t v, int hint)
+{
+    if (hint == 1) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    else *reinterpret_cast<uint32_t *>(p) = v;
+}
+
+struct AggMeta {
+    const float **slot_src;
+    unsigned long long *foff;
+    AggFrameDesc *fd;
+    uint32_t *qstart, *pstart, *nout;
+    __device__ __forceinline__ AggMeta(unsigned char *base, const AggMetaLayout &L)
+        : slot_src(reinterpret_cast<const float **>(base + L.slot_src)), foff(reinterpret_cast<unsigned long long *>(base + L.foff)),
+          fd(reinterpret_cast<AggFrameDesc *>(base + L.fd)), qstart(reinterpret_cast<uint32_t *>(base + L.qstart)),
+          pstart(reinterpret_cast<uint32_t *>(base + L.pstart)), nout(reinterpret_cast<uint32_t *>(base + L.nout)) {}
+};
+
+// Descriptors of frames f0 .. f0+nf-1 -> m (one block barrier inside; every thread of the CTA must call it).
+__device__ __forceinline__ void agg_build_meta(const AggGeom &g, const AggConvertArgs &a, uint32_t f0, uint32_t nf, const AggMeta &m)
+{
+    const uint32_t lane = threadIdx.x & 31u;
+    if (threadIdx.x < 32u) {                              // G <= 32: one lane per frame, offsets by a warp scan
+        AggFrameDesc d{0u, 0u, 0u, 0u};
+        unsigned long long off = 0;
+        uint32_t no = 0;
+        if (lane < nf) { d = a.fdesc[f0 + lane]; off = a.fdesc_off[f0 + lane]; no = __ldg(a.nout_of + d.nq); }
+        uint32_t iq = d.nq, ip = (no + 1u) >> 1;
+        const uint32_t vq = iq, vp = ip;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const uint32_t oq = __shfl_up_sync(0xFFFFFFFFu, iq, s), op = __shfl_up_sync(0xFFFFFFFFu, ip, s);
+            if (lane >= (uint32_t)s) { iq += oq; ip += op; }
+        }
+        if (lane < nf) { m.fd[lane] = d; m.foff[lane] = off; m.nout[lane] = no; m.qstart[lane] = iq - vq; m.pstart[lane] = ip - vp; }
+        if (lane == 31u) { m.qstart[nf] = iq; m.pstart[nf] = ip; }
+    }
+    __syncthreads();
+    const uint32_t T = m.qstart[nf], Q = g.quantum;
+    for (uint32_t sl = threadIdx.x; sl < T; sl += blockDim.x) {          // where every slot's quantum comes from
+        uint32_t k = 0;
+        while (k + 1u < nf && sl >= m.qstart[k + 1u]) k++;
+        const uint32_t j = sl - m.qstart[k];
+        const AggFrameDesc d = m.fd[k];
+        m.slot_src[sl] = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
+                                          : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
+    }
+}
+
+template <bool METER, bool LUT>
+__global__ void __launch_bounds__(256)
+k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
+{
+    if (a.ctl->status != 0u) return;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2;
+    const AggMetaLayout L = agg_meta_layout(a.G, a.G * g.half_quanta);
+    float *arena = reinterpret_cast<float *>(smem_raw);
+    unsigned char *meta_base = smem_raw + agg_arena_bytes(a.G, g.half_quanta, Q);
+
+    const uint32_t n_frames = a.ctl->n_frames, step = gridDim.x * a.G;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = blockDim.x >> 5;
+    uint32_t f0 = blockIdx.x * a.G;
+    if (f0 >= n_frames) return;
+    agg_build_meta(g, a, f0, min(a.G, n_frames - f0), AggMeta(meta_base, L));
+    __syncthreads();
+    for (uint32_t it = 0;; it++) {
+        const AggMeta m(meta_base + (it & 1u) * L.bytes, L);
+        const uint32_t nf = min(a.G, n_frames - f0);
+        const uint32_t T = m.qstart[nf];
+        // all quanta of the step in flight at once: a warp-wide copy instruction moves one 512-byte quantum (the
+        // slot index is warp-uniform, so no per-thread division and one broadcast read of the source address)
+        if (gpq == 32u) {                                   // the AudioWorklet quantum (128 samples): the whole loop body is
+            const uint32_t dst0 = smem_u32(arena) + 16u * lane;     // one LDS.64, one IMAD and the copy -- ncu showed the generic
+            for (uint32_t sl = warp; sl < T; sl += nw)      // form below at ~70 instructions per quantum, half of the kernel
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + sl * (pitch * 4u)), "l"(m.slot_src[sl] + 4u * lane) : "memory");
+        } else {
+            for (uint32_t sl = warp; sl < T; sl += nw) {
+                const float *src = m.slot_src[sl];
+                float *dst = arena + (size_t)sl * pitch;
+#pragma unroll 1
+                for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(dst + 4u * gi, src + 4u * gi);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const uint32_t f_next = f0 + step;
+        const bool more = f_next < n_frames;                                   // block-uniform
+        if (more) agg_build_meta(g, a, f_next, min(a.G, n_frames - f_next), AggMeta(meta_base + ((it + 1u) & 1u) * L.bytes, L));
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+
+        // ---- pick + encode + store: frame by frame, work item = 2 adjacent outputs ---------------------------
+        // The kernel is issue-bound (ncu: 70-80 % of the issue slots), so the inner loop carries nothing it does not
+        // need: everything per frame is read once outside it, the table / stride choice is a template parameter, full
+        // pairs need no tail logic, and an integer-ratio pick can never fall outside its frame (n_out = floor(n_in / R)),
+        // so only table picks are range-checked.  Sample i of a frame sits at word i + 4 * (i / quantum) of its slots.
+        for (uint32_t k = 0; k < nf; k++) {
+            const uint32_t n_in = m.fd[k].nq * Q, n_out = m.nout[k];
+            const float *fr = arena + (size_t)m.qstart[k] * pitch;
+            int16_t *dstf = a.out + m.foff[k];
+            const float qnan = __int_as_float(0x7FC00000);                     // outside the frame: undefined -> NaN -> 0
+            if (a.out_aligned16) {
+                const uint32_t nfull = n_out >> 1, R = g.stride, mq = a.magic_q;
+                const uint2 *lut2 = reinterpret_cast<const uint2 *>(a.lut);
+#pragma unroll 2
+                for (uint32_t p = threadIdx.x; p < nfull; p += blockDim.x) {
+                    float x0, x1;
+                    if (LUT) {
+                        const uint2 ii = __ldg(lut2 + p);
+                        x0 = ii.x < n_in ? fr[ii.x + 4u * div_magic(ii.x, mq)] : qnan;
+                        x1 = ii.y < n_in ? fr[ii.y + 4u * div_magic(ii.y, mq)] : qnan;
+                    } else {
+                        const uint32_t i0 = 2u * p * R, i1 = i0 + R;
+                        x0 = fr[i0 + 4u * div_magic(i0, mq)];
+                        x1 = fr[i1 + 4u * div_magic(i1, mq)];
+                    }
+                    st_32(dstf + 2u * p, pack_s16x2_sat(enc_s32(x0), enc_s32(x1)), a.hint);
+                }
+                if ((n_out & 1u) && threadIdx.x == 0u) {                       // the odd last output
+                    const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
+                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * div_magic(i, mq)] : qnan);
+                }
+            } else {                                                           // unaligned caller buffer: 16-bit stores
+                for (uint32_t o = threadIdx.x; o < n_out; o += blockDim.x) {
+                    const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
+                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * div_magic(i, a.magic_q)] : qnan);
+                }
+            }
+        }
+
+        if (METER) {
+            // lane <-> slot; ring-carried quanta were metered when they were appended
+            const uint32_t m_warps = (T + 31u) >> 5;
+            const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
+            for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < T; sl += blockDim.x) {
+                uint32_t k = 0;
+                while (k + 1u < nf && sl >= m.qstart[k + 1u]) k++;
+                const uint32_t j = sl - m.qstart[k];
+                if (j < m.fd[k].ring_count) continue;
+                a.rms_at[m.fd[k].pos + (j - m.fd[k].ring_count)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+            }
+        }
+        if (!more) break;
+        __syncthreads();                                   // the arena and this step's meta buffer are free again
+        f0 = f_next;
     }
 }
 

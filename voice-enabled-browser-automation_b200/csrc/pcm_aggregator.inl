@@ -43,7 +43,7 @@ struct pcmb200_aggregator {
     AggCtl *h_ctl = nullptr;               // pinned copy
     // convert kernel geometry
     uint32_t G = 1;
-    size_t convert_smem = 0, append_smem = 0;
+    size_t convert_smem = 0, convert_pipe_smem = 0, append_smem = 0;
     bool pending = false;                  // a push was enqueued and its result not yet collected
 };
 
@@ -97,8 +97,14 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
     if (conv_blocks > cap) conv_blocks = cap;
     const int conv_threads = ctx->tune.agg_block;
-    if (a->meter) k_agg_convert<true><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
-    else k_agg_convert<false><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
+    if (ctx->tune.agg_pipe) {
+        auto kern = a->meter ? (a->lut ? k_agg_convert_pipe<true, true> : k_agg_convert_pipe<true, false>)
+                             : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
+        kern<<<(int)conv_blocks, conv_threads, a->convert_pipe_smem, st>>>(a->geo, ca);
+    } else {
+        if (a->meter) k_agg_convert<true><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
+        else k_agg_convert<false><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
+    }
     if (a->meter) {
         k_agg_levels<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms,
                                                              a->rms_at, a->level, a->ctl);
@@ -164,7 +170,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
             h_nout[nq] = (uint32_t)no;
         }
         if (a->geo.stride == 0) {
-            h_lut.resize(a->nout_max ? a->nout_max : 1);
+            h_lut.assign((size_t)a->nout_max + 1, 0xFFFFFFFFu);        // one entry of padding: the convert kernel reads the table in pairs
             build_index_table((size_t)max_frame_quanta * quantum, in_rate, a->nout_max, h_lut.data());
         }
     } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
@@ -173,6 +179,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, ((size_t)ctx->tune.agg_stage_kb * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
     a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 8 * (size_t)a->G * max_frame_quanta +
                       8 * (a->G + 1) + 24 * a->G;
+    a->convert_pipe_smem = agg_arena_bytes(a->G, max_frame_quanta, quantum) + 2 * (size_t)agg_meta_layout(a->G, a->G * max_frame_quanta).bytes;
     a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127);
 
     cudaError_t e = cudaSuccess;
@@ -223,6 +230,10 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     if (a->geo.stride == 0) AGG_STEP(cudaMemcpyAsync(a->lut, h_lut.data(), h_lut.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
 #undef AGG_STEP
