@@ -59,11 +59,26 @@ struct AggGeom {
     double desired_ms;
 };
 
+// Programmatic dependent launch (opt-out: tune agg_pdl = 0).  A push is a chain of a dozen short kernels, each
+// needing everything its predecessor wrote; launched the plain way, every link pays a full launch latency after
+// the previous grid has drained.  With the programmatic-serialisation launch attribute a grid may be scheduled
+// as soon as every block of its predecessor has passed pdl_enter()'s trigger (or exited), and its blocks then
+// sit in `griddepcontrol.wait` until the predecessor has completed and its writes are visible.  EVERY block of
+// EVERY kernel in the chain calls pdl_enter() first thing, unconditionally: a grid therefore cannot complete
+// before its predecessor has, which is what makes results of kernels further up the chain safe to read too.
+// Launched without the attribute both instructions do nothing.
+__device__ __forceinline__ void pdl_enter()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- 1: count ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sessions, uint32_t *__restrict__ count,
             uint32_t *__restrict__ touched, AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t s = __ldg(sessions + i);
@@ -78,6 +93,7 @@ __global__ void __launch_bounds__(256)
 k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
               AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
     const bool live = k < ctl->n_touched;
     const uint32_t s = live ? touched[k] : 0u, c = live ? count[s] : 0u;
@@ -107,14 +123,30 @@ struct ScanArgs {
     const AggCtl *ctl;
 };
 
-__device__ __forceinline__ void scan_load(const ScanArgs &a, uint32_t idx, uint32_t len, uint32_t &va, uint32_t &vb)
+// The kScanItems consecutive items of one thread: va[k] = 1 if quantum idx0 + k flushes a frame, vb[k] = that
+// frame's output length rounded up to 8 samples.  The flags are read as two 128-bit loads (the per-item form was a
+// chain of three dependent loads per item and made these three passes latency-bound).
+__device__ __forceinline__ void scan_load8(const ScanArgs &a, uint32_t idx0, uint32_t len, uint32_t (&va)[kScanItems], uint32_t (&vb)[kScanItems])
 {
-    va = 0; vb = 0;
-    if (idx >= len) return;
+    static_assert(kScanItems == 8, "two uint4 loads per thread");
+    uint32_t nq[kScanItems];
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) nq[k] = 0u;
     // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
-    if (a.ctl->status != 0u) return;
-    const uint32_t nq = a.fl_nq[idx];
-    if (nq) { va = 1u; vb = (__ldg(a.nout_of + nq) + 7u) & ~7u; }
+    if (a.ctl->status == 0u && idx0 < len) {
+        if (idx0 + kScanItems <= len) {
+            const uint4 lo = *reinterpret_cast<const uint4 *>(a.fl_nq + idx0), hi = *reinterpret_cast<const uint4 *>(a.fl_nq + idx0 + 4);
+            nq[0] = lo.x; nq[1] = lo.y; nq[2] = lo.z; nq[3] = lo.w; nq[4] = hi.x; nq[5] = hi.y; nq[6] = hi.z; nq[7] = hi.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < kScanItems; k++) if (idx0 + k < len) nq[k] = a.fl_nq[idx0 + k];
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        va[k] = nq[k] ? 1u : 0u;
+        vb[k] = nq[k] ? (__ldg(a.nout_of + nq[k]) + 7u) & ~7u : 0u;
+    }
 }
 
 // exclusive block scan of one value per thread (256 threads); returns the block total in `total`
@@ -144,17 +176,15 @@ __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *warp_sums
 __global__ void __launch_bounds__(kScanThreads)
 k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b)
 {
+    pdl_enter();
     __shared__ uint32_t ws[kScanThreads / 32];
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
-    uint32_t sa = 0, sb = 0;
+    uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
+    scan_load8(a, base + threadIdx.x * kScanItems, len, va, vb);
 #pragma unroll
-    for (int k = 0; k < kScanItems; k++) {
-        uint32_t va, vb;
-        scan_load(a, base + threadIdx.x * kScanItems + k, len, va, vb);
-        sa += va; sb += vb;
-    }
+    for (int k = 0; k < kScanItems; k++) { sa += va[k]; sb += vb[k]; }
     uint32_t ta, tb;
     block_exscan(sa, ws, ta);
     block_exscan(sb, ws, tb);
@@ -167,6 +197,7 @@ __global__ void __launch_bounds__(1024)
 k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b, unsigned long long *__restrict__ offs_b,
             AggCtl *__restrict__ ctl, uint32_t max_frames, unsigned long long out_capacity)
 {
+    pdl_enter();
     __shared__ unsigned long long carry_a, carry_b;
     __shared__ unsigned long long wsum_a[32], wsum_b[32];
     const uint32_t len = a.n;
@@ -229,17 +260,16 @@ __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &
 __global__ void __launch_bounds__(kScanThreads)
 k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, ScanApplyB ap)
 {
+    pdl_enter();
     __shared__ uint32_t ws[kScanThreads / 32];
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
     if (a.ctl->status != 0u) return;                   // rejected push: nothing to emit
     uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
+    scan_load8(a, base + threadIdx.x * kScanItems, len, va, vb);
 #pragma unroll
-    for (int k = 0; k < kScanItems; k++) {
-        scan_load(a, base + threadIdx.x * kScanItems + k, len, va[k], vb[k]);
-        sa += va[k]; sb += vb[k];
-    }
+    for (int k = 0; k < kScanItems; k++) { sa += va[k]; sb += vb[k]; }
     uint32_t ta, tb;
     uint32_t ea = block_exscan(sa, ws, ta) + sums_a[blockIdx.x];
     unsigned long long eb = (unsigned long long)block_exscan(sb, ws, tb) + offs_b[blockIdx.x];
@@ -258,6 +288,7 @@ __global__ void __launch_bounds__(256)
 k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted,
               const AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     if (ctl->status != 0u) return;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -307,6 +338,7 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
            const uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted, const uint32_t *__restrict__ fill,
            const double *__restrict__ last_send, AggWalkOut o, AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     if (ctl->status != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= ctl->n_touched) return;
@@ -394,6 +426,7 @@ template <bool METER>
 __global__ void __launch_bounds__(256)
 k_agg_convert(AggGeom g, AggConvertArgs a)
 {
+    pdl_enter();
     if (a.ctl->status != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t Q = g.quantum, pitch = Q + 4u;
@@ -579,6 +612,7 @@ template <bool METER, bool LUT>
 __global__ void __launch_bounds__(256)
 k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
 {
+    pdl_enter();
     if (a.ctl->status != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2;
@@ -628,30 +662,37 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
             int16_t *dstf = a.out + m.foff[k];
             const float qnan = __int_as_float(0x7FC00000);                     // outside the frame: undefined -> NaN -> 0
             if (a.out_aligned16) {
-                const uint32_t nfull = n_out >> 1, R = g.stride, mq = a.magic_q;
+                // mq = ceil(2^32 / quantum) is never 0 here (quantum >= 4), so i / quantum is one multiply-high
+                const uint32_t nfull = n_out >> 1, R = g.stride, mq = a.magic_q, bd = blockDim.x;
                 const uint2 *lut2 = reinterpret_cast<const uint2 *>(a.lut);
-#pragma unroll 2
-                for (uint32_t p = threadIdx.x; p < nfull; p += blockDim.x) {
+                auto pair = [&](uint32_t p) -> uint32_t {
                     float x0, x1;
                     if (LUT) {
                         const uint2 ii = __ldg(lut2 + p);
-                        x0 = ii.x < n_in ? fr[ii.x + 4u * div_magic(ii.x, mq)] : qnan;
-                        x1 = ii.y < n_in ? fr[ii.y + 4u * div_magic(ii.y, mq)] : qnan;
+                        x0 = ii.x < n_in ? fr[ii.x + 4u * __umulhi(ii.x, mq)] : qnan;
+                        x1 = ii.y < n_in ? fr[ii.y + 4u * __umulhi(ii.y, mq)] : qnan;
                     } else {
                         const uint32_t i0 = 2u * p * R, i1 = i0 + R;
-                        x0 = fr[i0 + 4u * div_magic(i0, mq)];
-                        x1 = fr[i1 + 4u * div_magic(i1, mq)];
+                        x0 = fr[i0 + 4u * __umulhi(i0, mq)];
+                        x1 = fr[i1 + 4u * __umulhi(i1, mq)];
                     }
-                    st_32(dstf + 2u * p, pack_s16x2_sat(enc_s32(x0), enc_s32(x1)), a.hint);
+                    return pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
+                };
+                // two pairs per trip, by hand: `#pragma unroll 2` made the compiler divide by blockDim.x for the trip count
+                for (uint32_t p = threadIdx.x; p < nfull; p += 2u * bd) {
+                    const uint32_t pb = p + bd;
+                    const uint32_t va = pair(p), vb = pb < nfull ? pair(pb) : 0u;
+                    st_32(dstf + 2u * p, va, 1);                               // streaming stores: frames are written once
+                    if (pb < nfull) st_32(dstf + 2u * pb, vb, 1);
                 }
                 if ((n_out & 1u) && threadIdx.x == 0u) {                       // the odd last output
                     const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
-                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * div_magic(i, mq)] : qnan);
+                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             } else {                                                           // unaligned caller buffer: 16-bit stores
                 for (uint32_t o = threadIdx.x; o < n_out; o += blockDim.x) {
                     const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
-                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * div_magic(i, a.magic_q)] : qnan);
+                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, a.magic_q)] : qnan);
                 }
             }
         }
@@ -682,6 +723,7 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
              const uint32_t *__restrict__ fill, const uint32_t *__restrict__ flushed, const double *__restrict__ ring_rms,
              const double *__restrict__ rms_at, double *__restrict__ level, const AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     if (ctl->status != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= ctl->n_touched) return;
@@ -712,6 +754,7 @@ __global__ void __launch_bounds__(256)
 k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
              double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     if (ctl->status != 0u || ctl->n_leftover == 0u) return;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t granules = quantum >> 2;
@@ -781,6 +824,7 @@ k_agg_commit(const uint32_t *__restrict__ touched, uint32_t *__restrict__ count,
              double *__restrict__ last_send, const uint32_t *__restrict__ new_fill, const double *__restrict__ new_last,
              const AggCtl *__restrict__ ctl)
 {
+    pdl_enter();
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= ctl->n_touched) return;
     const uint32_t s = touched[k];

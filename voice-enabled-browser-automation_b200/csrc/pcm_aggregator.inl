@@ -65,6 +65,25 @@ cudaError_t agg_alloc(T **p, size_t count)
     return cudaMalloc((void **)p, (count ? count : 1) * sizeof(T));
 }
 
+// One link of the push chain.  With tune.agg_pdl the launch carries the programmatic-serialisation attribute
+// (see pdl_enter in agg_kernels.cuh); without it this is a plain <<<>>> launch.
+template <typename... Params, typename... Args>
+void agg_launch(pcmb200_ctx *ctx, void (*kern)(Params...), unsigned grid, unsigned block, size_t smem, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = ctx->tune.agg_pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+    ctx->launches += 1;
+}
+
 // Enqueue the whole push on the context's stream.  Every pointer is device memory.
 int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint32_t *sessions, const double *arrival,
                 const float *samples, int16_t *out, size_t out_capacity, uint32_t *frame_session, uint32_t *frame_len,
@@ -72,20 +91,18 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
 {
     cudaStream_t st = ctx->stream;
     CU(cudaMemsetAsync(a->ctl, 0, sizeof(AggCtl), st));
-    const int blocks_n = (int)((n + 255u) / 256u);
-    const int scan_blocks = (int)((n + kScanBlock - 1) / kScanBlock);
-    k_agg_count<<<blocks_n, 256, 0, st>>>(sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
+    const unsigned blocks_n = (n + 255u) / 256u, blocks_128 = (n + 127u) / 128u;
+    const unsigned scan_blocks = (n + kScanBlock - 1) / kScanBlock;
+    agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
     ScanArgs sa{n, a->fl_nq, a->nout_of, a->ctl};
-    k_agg_reserve<<<blocks_n, 256, 0, st>>>(a->touched, a->count, a->cursor, a->ctl);
-    k_agg_scatter<<<blocks_n, 256, 0, st>>>(sessions, n, a->cursor, a->sorted, a->ctl);
+    agg_launch(ctx, k_agg_reserve, blocks_n, 256, 0, a->touched, a->count, a->cursor, a->ctl);
+    agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, a->ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
-    k_agg_walk<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill,
-                                                         a->last_send, wo, a->ctl);
+    agg_launch(ctx, k_agg_walk, blocks_128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, a->ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
-    k_scan_reduce<<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->sums_b);
-    k_scan_sums<<<1, 1024, 0, st>>>(sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
-    k_scan_apply<<<scan_blocks, kScanThreads, 0, st>>>(sa, a->sums_a, a->offs_b, ab);
-    ctx->launches += 7;
+    agg_launch(ctx, k_scan_reduce, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b);
+    agg_launch(ctx, k_scan_sums, 1u, 1024, 0, sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
+    agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->offs_b, ab);
 
     AggConvertArgs ca{};
     ca.samples = samples; ca.ring = a->ring; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
@@ -96,29 +113,26 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     unsigned long long conv_blocks = ((unsigned long long)n + a->G - 1) / a->G;
     const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
     if (conv_blocks > cap) conv_blocks = cap;
-    const int conv_threads = ctx->tune.agg_block;
+    const unsigned conv_threads = (unsigned)ctx->tune.agg_block;
     if (ctx->tune.agg_pipe) {
         auto kern = a->meter ? (a->lut ? k_agg_convert_pipe<true, true> : k_agg_convert_pipe<true, false>)
                              : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
-        kern<<<(int)conv_blocks, conv_threads, a->convert_pipe_smem, st>>>(a->geo, ca);
+        agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
     } else {
-        if (a->meter) k_agg_convert<true><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
-        else k_agg_convert<false><<<(int)conv_blocks, conv_threads, a->convert_smem, st>>>(a->geo, ca);
+        agg_launch(ctx, a->meter ? k_agg_convert<true> : k_agg_convert<false>, (unsigned)conv_blocks, conv_threads, a->convert_smem, a->geo, ca);
     }
     if (a->meter) {
-        k_agg_levels<<<(int)((n + 127u) / 128u), 128, 0, st>>>(a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms,
-                                                             a->rms_at, a->level, a->ctl);
+        agg_launch(ctx, k_agg_levels, blocks_128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
+                   a->level, a->ctl);
         const unsigned long long tiles = ((unsigned long long)n + 63ull) / 64ull;
-        const int grid = (int)(tiles < cap ? tiles : cap);
-        k_agg_append<true><<<grid, 256, a->append_smem, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
-        ctx->launches += 1;
+        agg_launch(ctx, k_agg_append<true>, (unsigned)(tiles < cap ? tiles : cap), 256, a->append_smem, samples, a->dst_slot, a->ring, a->ring_rms, n,
+                   a->geo.quantum, a->ctl);
     } else {
         const unsigned long long warps_blocks = ((unsigned long long)n + 31ull) / 32ull;   // 8 warps x 4 quanta per block step
-        const int grid = (int)(warps_blocks < cap ? warps_blocks : cap);
-        k_agg_append<false><<<grid, 256, 0, st>>>(samples, a->dst_slot, a->ring, a->ring_rms, n, a->geo.quantum, a->ctl);
+        agg_launch(ctx, k_agg_append<false>, (unsigned)(warps_blocks < cap ? warps_blocks : cap), 256, 0, samples, a->dst_slot, a->ring, a->ring_rms, n,
+                   a->geo.quantum, a->ctl);
     }
-    k_agg_commit<<<blocks_n, 256, 0, st>>>(a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
-    ctx->launches += 3;
+    agg_launch(ctx, k_agg_commit, blocks_n, 256, 0, a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(a->h_ctl, a->ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
     a->pending = true;
