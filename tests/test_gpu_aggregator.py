@@ -238,3 +238,74 @@ def test_aggregator_device_resident_push_and_wait(ctx):
     agg.close()
     for b in d.values():
         b.free()
+
+
+@pytest.mark.parametrize("rate, max_q", [(96000, 64), (96000, 96), (88200, 64)])
+def test_aggregator_long_frames(ctx, rate, max_q):
+    """60 ms at 96 kHz is 45-46 quanta per frame: more than one warp's worth of push quanta per frame, and
+    -- with pushes cut at uneven places -- more than 32 quanta carried over in a session's buffer.  max_q = 64
+    takes the one-frame-per-step convert kernel (descriptors in registers, two index registers per lane),
+    max_q = 96 the general one; 88.2 kHz adds the pick table.  Frames and levels against the oracle."""
+    rng = np.random.RandomState(rate // 100 + max_q)
+    S, q_ms = 23, 128e3 / rate
+    nq = int(400 / q_ms)
+    audio = (rng.uniform(-1.05, 1.05, size=(S, nq, 128)) * rng.uniform(0.1, 1, size=(S, 1, 1))).astype(np.float32)
+    times = 3.0 * rng.rand(S, 1) + np.cumsum(q_ms + rng.uniform(-0.2, 0.2, size=(S, nq)), axis=1)
+    events = sorted((times[s, q], s, q) for s in range(S) for q in range(nq))
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=max_q, max_push_quanta=2048, max_out_samples=1 << 18)
+    agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
+    got = {s: [] for s in range(S)}
+    i, k, sizes = 0, 0, [S * 40, 7, S * 3, S * 37, 100, S * 50, 1]      # cuts that leave 0 ... 44 quanta waiting
+    while i < len(events):
+        chunk = events[i:i + sizes[k % len(sizes)]]
+        i += len(chunk); k += 1
+        for s, pcm in agg.push(np.array([e[1] for e in chunk]), np.array([e[0] for e in chunk]),
+                               np.stack([audio[e[1], e[2]] for e in chunk])):
+            got[s].append(pcm)
+    levels = agg.levels(0, S)
+    agg.close()
+    for s in range(S):
+        want, start, _ = _session_frames(audio[s], times[s], rate)
+        assert len(got[s]) == len(want) >= 5, (s, len(got[s]), len(want))
+        assert max(f.size for f in want) > 32 * 128 * 16000 // rate          # frames longer than 32 quanta
+        for a, b in zip(got[s], want):
+            assert a.size == b.size and np.array_equal(a, b), s
+        want_lv = oracle.level_meter(audio[s, :start].reshape(-1))[-1]
+        assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
+
+
+@pytest.mark.parametrize("max_q", [32, 96])
+@pytest.mark.parametrize("rate", [48000, 44100])
+def test_aggregator_unaligned_device_output(ctx, rate, max_q):
+    """An output pointer that is only 2-byte aligned (frames still start every 8 samples from it): both convert
+    kernels fall back to 16-bit stores; nothing outside the frames is written."""
+    rng = np.random.RandomState(5)
+    S, nq = 300, 24
+    n = S * nq
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=max_q, max_push_quanta=n, max_out_samples=16)
+    agg.reset_range(0, S, 0.0)
+    sess = np.tile(np.arange(S, dtype=np.uint32), nq)
+    t = np.repeat((np.arange(nq) + 1) * (128e3 / rate), S)
+    x = rng.uniform(-1, 1, size=(n, 128)).astype(np.float32)
+    flush, _ = oracle.aggregator_plan(t[::S], 60.0, 0.0)
+    fq = int(np.nonzero(flush)[0][0]) + 1                           # quanta in the one frame every session flushes
+    n_out = oracle.resample_len(fq * 128, rate)
+    pad = (n_out + 7) // 8 * 8
+    d = {k: ctx.device_buffer(v) for k, v in dict(s=n * 4, t=n * 8, x=n * 512, o=(S * pad + 16) * 2, fl=n * 4, fo=n * 8).items()}
+    d["s"].upload(sess); d["t"].upload(t); d["x"].upload(x)
+    d["o"].upload(np.full(S * pad + 16, 0x2222, np.int16))
+    agg.push_device(n, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr + 2, S * pad, None, d["fl"].ptr, d["fo"].ptr, n)
+    nf, ns = agg.wait()
+    assert nf == S and ns == S * pad
+    fl, fo = d["fl"].download(np.uint32, S), d["fo"].download(np.uint64, S)
+    assert (fl == n_out).all() and (fo == np.arange(S) * pad).all()
+    raw = d["o"].download(np.int16, S * pad + 16)
+    assert raw[0] == 0x2222 and (raw[1 + S * pad:] == 0x2222).all()
+    got = raw[1:1 + S * pad].reshape(S, pad)
+    xs = x.reshape(nq, S, 128).transpose(1, 0, 2)[:, :fq].reshape(S, fq * 128)
+    assert np.array_equal(got[:, :n_out], oracle.frames(np.ascontiguousarray(xs), fq * 128, rate, threads=4))
+    assert (got[:, n_out:] == 0x2222).all()                          # the padding between frames is left alone
+    agg.close()
+    for b in d.values():
+        b.free()

@@ -329,13 +329,12 @@ def main():
     if args.tune:
         ctx.tune(**{k: int(v) for k, v in (kv.split("=") for kv in args.tune.split(","))})
     if args.sweep_agg:
-        for pipe in (1, 0):
-            for blk in (64, 128, 256):
-                for kb in (17, 34, 51, 68):
-                    ctx.tune(agg_block=blk, agg_stage_kb=kb, agg_pipe=pipe)
-                    for m in (False, True):
-                        r = aggregator(ctx, meter=m)
-                        print(json.dumps(dict(agg_pipe=pipe, agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        for blk in (64, 96, 128, 192, 256):
+            for kb in (17, 34, 51):
+                ctx.tune(agg_block=blk, agg_stage_kb=kb)
+                for m in (False, True):
+                    r = aggregator(ctx, meter=m)
+                    print(json.dumps(dict(agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
         return
     if args.agg_order:
         print(json.dumps(aggregator(ctx, order=args.agg_order)), flush=True)

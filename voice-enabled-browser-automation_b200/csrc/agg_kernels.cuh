@@ -14,7 +14,7 @@
 //                    writes scratch (the session's new state, per-quantum flush marks and ring slots).
 //   5 scan           over quanta: frame index and output offset of every flush, in flush order
 //                    (= ascending i); its apply pass also emits the caller's frame arrays.
-//   6 k_agg_convert  every flushed frame: its quanta are staged into shared memory with async
+//   6 k_agg_convert_one / _pipe   every flushed frame: its quanta are staged into shared memory with async
 //                    copies -- from the session's ring (quanta carried over from earlier pushes) or
 //                    straight from the push (never written to the ring at all) -- then picked, encoded,
 //                    stored; with the meter on, each quantum's rms is computed from the staged copy.
@@ -400,11 +400,19 @@ __device__ __forceinline__ void cp_async_wait_all()
 }
 
 // ---- 6: convert -------------------------------------------------------------------------------------------------
-// A CTA takes G consecutive frames at a time.  Their quanta are packed into `slots` of shared memory
-// (slot pitch = quantum + 4 floats: 33 sixteen-byte units for the 128-sample quantum, odd, so that the
-// eight lanes of an LDS.128 phase -- eight consecutive quanta -- hit eight different bank groups) with
-// 16-byte async copies, all in flight together.  Then all threads pick + encode + store; with METER each of the first T lanes
-// accumulates its quantum's sum of squares in sample order (same arithmetic as kernel 2c).
+// A CTA takes G consecutive frames per step.  Their quanta are packed into `slots` of shared memory (slot pitch =
+// quantum + 4 floats) with 16-byte async copies, all in flight together: a warp-wide copy instruction moves one
+// 512-byte quantum.  Then all threads pick + encode + store, one PAIR of adjacent outputs per lane (lane stride
+// 2 * ratio words in shared memory: at most 2-way bank conflicts; lane <-> 8 outputs was 8-way for ratio 3), one
+// 32-bit streaming store per lane, 128 contiguous bytes per warp.  With METER the first T lanes each accumulate
+// their quantum's sum of squares in sample order (same arithmetic as kernel 2c).
+// Two forms: k_agg_convert_one (G = 1, at most 64 quanta per frame, at most 128 threads: the usual ~60 ms frame)
+// and k_agg_convert_pipe (everything else).  How they got here, by ncu (65 536 frames of 23 quanta, 0.9 GB):
+//   step by step, one barrier per dependent round trip, lane <-> 8 outputs           200 us, issue slots 78 % busy
+//   + next step's descriptors fetched while this step's copies fly (pipe)            200 us: it was issue-bound --
+//       170 M warp-instructions, half of them a generic copy loop that spent ~70 instructions per quantum
+//   + copy loop specialised for the 128-sample quantum, lean pair loop               160 us, 103 M instructions
+//   + descriptors in registers, prefetched two frames ahead, persistent grid (one)   ~150 us, 0.92 of the HBM peak
 struct AggConvertArgs {
     const float *samples;            // the push's quanta
     const float *ring;               // [max_sessions][half_quanta][quantum]
@@ -417,120 +425,13 @@ struct AggConvertArgs {
     double *rms_at;                  // [n] rms of push quantum sorted[p] at rms_at[p] (METER)
     const AggCtl *ctl;
     uint32_t G;                      // frames per CTA step
-    uint32_t magic_q;                // ceil(2^32 / quantum), 0 for quantum == 1
-    int out_aligned16;               // `out` is 16-byte aligned: 128-bit stores
-    int hint;
+    uint32_t magic_q;                // ceil(2^32 / quantum); never 0 here (quantum >= 4)
+    int out_aligned16;               // `out` is 16-byte aligned: 32-bit stores (else 16-bit ones)
+    int hint;                        // unused by the convert kernels (their stores are always streaming)
 };
 
-template <bool METER>
-__global__ void __launch_bounds__(256)
-k_agg_convert(AggGeom g, AggConvertArgs a)
-{
-    pdl_enter();
-    if (a.ctl->status != 0u) return;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const uint32_t Q = g.quantum, pitch = Q + 4u;
-    const uint32_t max_slots = a.G * g.half_quanta;
-    float *arena = reinterpret_cast<float *>(smem_raw);
-    const float **slot_src = reinterpret_cast<const float **>(smem_raw + (((size_t)max_slots * pitch * 4u + 127u) & ~(size_t)127u));   // [max_slots]
-    uint32_t *qstart = reinterpret_cast<uint32_t *>(slot_src + max_slots);   // [G + 1] first slot of each frame
-    uint32_t *cstart = qstart + (a.G + 1u);                           // [G + 1] first 8-output chunk of each frame
-    AggFrameDesc *fd = reinterpret_cast<AggFrameDesc *>(cstart + (a.G + 1u) + ((2u * a.G + 2u) & 1u));   // [G], 8-byte aligned
-    unsigned long long *foff = reinterpret_cast<unsigned long long *>(fd + a.G);                          // [G]
-
-    const uint32_t n_frames = a.ctl->n_frames;
-    const uint32_t gpq = Q >> 2;                               // 16-byte granules per quantum
-    uint32_t it = 0;
-    for (uint32_t f0 = blockIdx.x * a.G; f0 < n_frames; f0 += gridDim.x * a.G, it++) {
-        const uint32_t nf = min(a.G, n_frames - f0);
-        __syncthreads();                                   // previous step's readers are done with the arena
-        if (threadIdx.x < nf) {
-            fd[threadIdx.x] = a.fdesc[f0 + threadIdx.x];
-            foff[threadIdx.x] = a.fdesc_off[f0 + threadIdx.x];
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t qs = 0, cs = 0;
-            for (uint32_t k = 0; k < nf; k++) {
-                qstart[k] = qs; cstart[k] = cs;
-                qs += fd[k].nq;
-                cs += (__ldg(a.nout_of + fd[k].nq) + 7u) >> 3;
-            }
-            qstart[nf] = qs; cstart[nf] = cs;
-        }
-        __syncthreads();
-        const uint32_t T = qstart[nf];
-        for (uint32_t sl = threadIdx.x; sl < T; sl += blockDim.x) {          // where every slot's quantum comes from
-            uint32_t k = 0;
-            while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
-            const uint32_t j = sl - qstart[k];
-            const AggFrameDesc d = fd[k];
-            slot_src[sl] = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
-                                            : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
-        }
-        __syncthreads();
-        for (uint32_t idx = threadIdx.x; idx < T * gpq; idx += blockDim.x) {  // all quanta in flight at once
-            const uint32_t sl = idx / gpq, gi = idx - sl * gpq;
-            cp_async_16(arena + (size_t)sl * pitch + 4u * gi, slot_src[sl] + 4u * gi);
-        }
-        cp_async_wait_all();
-        __syncthreads();
-
-        // ---- pick + encode + store: work item = 8 consecutive outputs of one frame ----------------------
-        const uint32_t n_chunks = cstart[nf];
-        for (uint32_t c = threadIdx.x; c < n_chunks; c += blockDim.x) {
-            uint32_t k = 0;
-            while (k + 1u < nf && c >= cstart[k + 1u]) k++;
-            const uint32_t nq = fd[k].nq, n_in = nq * Q, n_out = __ldg(a.nout_of + nq);
-            const uint32_t o0 = (c - cstart[k]) * 8u;
-            const float *fr = arena + (size_t)qstart[k] * pitch;
-            int e[8];
-#pragma unroll
-            for (int jj = 0; jj < 8; jj++) {
-                const uint32_t o = o0 + jj;
-                uint32_t i = 0xFFFFFFFFu;
-                if (o < n_out) i = a.lut ? __ldg(a.lut + o) : o * g.stride;
-                float x = __int_as_float(0x7FC00000);                    // outside the frame: undefined -> NaN -> 0
-                if (i < n_in) {
-                    const uint32_t qi = div_magic(i, a.magic_q);
-                    x = fr[qi * pitch + (i - qi * Q)];
-                }
-                e[jj] = enc_s32(x);
-            }
-            int16_t *dst = a.out + foff[k] + o0;
-            if (o0 + 8u <= n_out && a.out_aligned16) {
-                uint4 o4;
-                o4.x = pack_s16x2_sat(e[0], e[1]);
-                o4.y = pack_s16x2_sat(e[2], e[3]);
-                o4.z = pack_s16x2_sat(e[4], e[5]);
-                o4.w = pack_s16x2_sat(e[6], e[7]);
-                st_128(dst, o4, a.hint);
-            } else {
-#pragma unroll
-                for (int jj = 0; jj < 8; jj++)
-                    if (o0 + jj < n_out) dst[jj] = (int16_t)(pack_s16x2_sat(e[jj], 0) & 0xFFFFu);
-            }
-        }
-
-        if (METER) {
-            // lane <-> slot; ring-carried quanta were metered when they were appended
-            const uint32_t m_warps = (T + 31u) >> 5;
-            const uint32_t nw = blockDim.x >> 5;
-            const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
-            const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
-            for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < T; sl += blockDim.x) {
-                uint32_t k = 0;
-                while (k + 1u < nf && sl >= qstart[k + 1u]) k++;
-                const uint32_t j = sl - qstart[k];
-                if (j < fd[k].ring_count) continue;
-                a.rms_at[fd[k].pos + (j - fd[k].ring_count)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
-            }
-        }
-    }
-}
-
-// ---- 6': convert, software-pipelined -------------------------------------------------------------------------------
-// Same work as k_agg_convert; what ncu said about that kernel shaped this one.  There a CTA step was a chain of
+// ---- 6 (general form): convert, software-pipelined ----------------------------------------------------------------
+// What ncu said about the first, step-by-step version shaped this one.  There a CTA step was a chain of
 // dependent round trips -- frame descriptor (L2) -> index list entry (L2) -> the quanta themselves (HBM) -> picks ->
 // stores -- with a block barrier between each, and the arena sat empty during the first two: the bytes a CTA keeps
 // in flight are what its shared memory buys, and for half of every step it bought nothing.  Here
@@ -715,6 +616,166 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
     }
 }
 
+// ---- 6 (usual form): convert, one frame per step, descriptors in registers -----------------------------------------
+// The common geometry -- one ~60 ms frame per 128-thread step, at most 64 quanta per frame -- needs none of the
+// shared-memory bookkeeping of k_agg_convert_pipe: ncu counted ~600 of its 1 570 warp-instructions per frame in
+// per-step address arithmetic for the meta buffers and ~100 in building them.  Here every thread holds the frame's
+// descriptor in registers, lane l of every warp holds the push index of the frame's l-th (and l+32-nd) push quantum
+// (turned into source addresses at the top of a trip and broadcast with a shuffle when the warp copies that slot);
+// descriptors are fetched two frames ahead and index lists one frame ahead, while copies are in flight.  No meta
+// buffers, two block barriers per frame, a persistent grid (the CTAs resident at once).
+template <bool METER, bool LUT>
+__global__ void __launch_bounds__(128, 10)
+k_agg_convert_one(AggGeom g, AggConvertArgs a)
+{
+    pdl_enter();
+    if (a.ctl->status != 0u) return;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float *arena = reinterpret_cast<float *>(smem_raw);
+    const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2, mq = a.magic_q, bd = blockDim.x;
+    const uint32_t n_frames = a.ctl->n_frames;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = bd >> 5;
+    uint32_t f = blockIdx.x;
+    if (f >= n_frames) return;
+
+    // What a thread keeps of a frame: its descriptor, and in lane l the push index of the frame's l-th and (l+32)-nd
+    // push quantum (slots ring_count + l, ring_count + l + 32).  The descriptor is fetched TWO frames ahead and the
+    // index list one frame ahead, so that the list's address (it depends on the descriptor) is known when the list is
+    // asked for, and nothing is computed from a prefetched value before the next trip: a thread never waits for a
+    // prefetch in the middle of a trip (ncu: a third of all stall samples sat on that dependency before).
+    struct Desc {
+        unsigned long long off;
+        uint32_t session, nq, rc, pos;
+    };
+    struct Frame {
+        Desc d;
+        uint32_t idx0, idx1, n_out;
+    };
+    auto fetch_desc = [&](uint32_t fi) -> Desc {
+        const uint4 raw = *reinterpret_cast<const uint4 *>(a.fdesc + fi);        // {session, nq, ring_count, pos}
+        return Desc{a.fdesc_off[fi], raw.x, raw.y, raw.z, raw.w};
+    };
+    auto fetch_list = [&](const Desc &d) -> Frame {
+        const uint32_t npush = d.nq - d.rc;
+        Frame fr;
+        fr.d = d;
+        fr.idx0 = lane < npush ? a.sorted[d.pos + lane] : 0u;
+        fr.idx1 = lane + 32u < npush ? a.sorted[d.pos + lane + 32u] : 0u;
+        fr.n_out = __ldg(a.nout_of + d.nq);
+        return fr;
+    };
+    const uint32_t stride_f = gridDim.x;
+    Frame cur = fetch_list(fetch_desc(f));
+    Desc nxt_d = cur.d;                                                        // descriptor of the frame after `cur`
+    if (f + stride_f < n_frames) nxt_d = fetch_desc(f + stride_f);
+    const uint32_t dst_lane = smem_u32(arena) + 16u * lane, pitch_b = pitch * 4u;
+    for (uint32_t it = 0;; it++) {
+        const uint32_t nq = cur.d.nq, rc = cur.d.rc;
+        // lane l: where slots l and l + 32 come from (the first ring_count slots are the session's ring, carried
+        // over from earlier pushes; the rest are this push's quanta), already offset to this lane's 16 bytes
+        const float *ring_base = a.ring + (size_t)cur.d.session * g.half_quanta * Q;
+        const uint32_t j0 = lane - rc, j1 = lane + 32u - rc;                 // push quantum behind slot lane / lane + 32
+        const uint32_t a0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j0 & 31u);
+        const uint32_t b0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j1 & 31u), b1 = __shfl_sync(0xFFFFFFFFu, cur.idx1, j1 & 31u);
+        const float *src0 = lane < rc ? ring_base + (size_t)lane * Q : a.samples + (size_t)a0 * Q;
+        const float *src1 = lane + 32u < rc ? ring_base + (size_t)(lane + 32u) * Q : a.samples + (size_t)(j1 < 32u ? b0 : b1) * Q;
+        // ---- all quanta of the frame in flight at once: one warp-wide 16-byte-per-lane copy per 512-byte quantum.
+        // Four slots per trip, addresses first and the four copies back to back (the compiler pads every isolated
+        // LDGSTS with three dummy instructions; 32 instructions per quantum in the one-at-a-time form, per ncu).
+        if (gpq == 32u) {
+            for (uint32_t s0 = warp; s0 < nq; s0 += 4u * nw) {
+                const float *src[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t sl = s0 + (uint32_t)u * nw;                    // warp-uniform
+                    const unsigned long long p = (unsigned long long)(sl < 32u ? src0 : src1);
+                    src[u] = reinterpret_cast<const float *>(__shfl_sync(0xFFFFFFFFu, p, sl & 31u)) + 4u * lane;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t sl = s0 + (uint32_t)u * nw;
+                    if (sl < nq) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_lane + sl * pitch_b), "l"(src[u]) : "memory");
+                }
+            }
+        } else {
+            for (uint32_t sl = warp; sl < nq; sl += nw) {
+                const unsigned long long p = (unsigned long long)(sl < 32u ? src0 : src1);
+                const float *src = reinterpret_cast<const float *>(__shfl_sync(0xFFFFFFFFu, p, sl & 31u));
+#pragma unroll 1
+                for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(arena + (size_t)sl * pitch + 4u * gi, src + 4u * gi);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        // the frame after this one: its descriptor is here already (fetched a trip ago), so its index list can be asked
+        // for now; and the descriptor of the frame after that.  Both land while this frame's copies are in flight.
+        const uint32_t f_next = f + stride_f;
+        const bool more = f_next < n_frames;                                   // block-uniform
+        Frame nxt = cur;
+        Desc ahead = nxt_d;
+        if (more) {
+            nxt = fetch_list(nxt_d);
+            if (f_next + stride_f < n_frames) ahead = fetch_desc(f_next + stride_f);
+        }
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+
+        // ---- pick + encode + store (see k_agg_convert_pipe); pointers and indices advance by addition ---------------------
+        {
+            const uint32_t n_in = nq * Q, n_out = cur.n_out;
+            int16_t *dstf = a.out + cur.d.off;
+            const float qnan = __int_as_float(0x7FC00000);
+            if (a.out_aligned16) {
+                const uint32_t nfull = n_out >> 1, R = g.stride;
+                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + threadIdx.x;
+                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + threadIdx.x;
+                uint32_t i0 = 2u * threadIdx.x * R;
+                const uint32_t di = 2u * bd * R;                                // index step from pair p to pair p + bd
+                auto pair = [&](uint32_t ia, const uint2 *l) -> uint32_t {
+                    float x0, x1;
+                    if (LUT) {
+                        const uint2 ii = __ldg(l);
+                        x0 = ii.x < n_in ? arena[ii.x + 4u * __umulhi(ii.x, mq)] : qnan;
+                        x1 = ii.y < n_in ? arena[ii.y + 4u * __umulhi(ii.y, mq)] : qnan;
+                    } else {
+                        const uint32_t ib = ia + R;
+                        x0 = arena[ia + 4u * __umulhi(ia, mq)];
+                        x1 = arena[ib + 4u * __umulhi(ib, mq)];
+                    }
+                    return pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
+                };
+                for (uint32_t p = threadIdx.x; p < nfull; p += 2u * bd, dp += 2u * bd, lp += 2u * bd, i0 += 2u * di) {
+                    const bool second = p + bd < nfull;
+                    const uint32_t va = pair(i0, lp), vb = second ? pair(i0 + di, lp + bd) : 0u;
+                    asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp), "r"(va) : "memory");   // streaming: frames are written once
+                    if (second) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp + bd), "r"(vb) : "memory");
+                }
+                if ((n_out & 1u) && threadIdx.x == 0u) {
+                    const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
+                    dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                }
+            } else {
+                for (uint32_t o = threadIdx.x; o < n_out; o += bd) {
+                    const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
+                    dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                }
+            }
+        }
+        if (METER) {
+            // lane <-> slot; ring-carried quanta were metered when they were appended.  The metering warps rotate from
+            // frame to frame so that the long sum-of-squares chains do not always land on the same scheduler.
+            const uint32_t m_warps = (nq + 31u) >> 5;
+            const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
+            for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < nq; sl += bd)
+                if (sl >= rc) a.rms_at[cur.d.pos + (sl - rc)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+        }
+        if (!more) break;
+        __syncthreads();                                   // the arena is free again
+        f = f_next;
+        cur = nxt;
+        nxt_d = ahead;
+    }
+}
+
 // ---- 7: levels ---------------------------------------------------------------------------------------------------
 // App.tsx:271 along every touched session's FLUSHED quanta, in arrival order: first the quanta that were
 // waiting in its ring (their rms was stored when they were appended), then this push's.
@@ -798,9 +859,14 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         if (threadIdx.x < TILE) slot_s[threadIdx.x] = slot;
         const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
         if (live == 0) continue;
-        for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
-            const uint32_t t = idx / granules, gi = idx - t * granules;
-            if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+        if (granules == 32u) {                           // the 128-sample quantum: one warp-wide copy per quantum, no division
+            for (uint32_t t = warp; t < TILE; t += 8u)
+                if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
+        } else {
+            for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
+                const uint32_t t = idx / granules, gi = idx - t * granules;
+                if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+            }
         }
         cp_async_wait_all();
         __syncthreads();

@@ -43,7 +43,9 @@ struct pcmb200_aggregator {
     AggCtl *h_ctl = nullptr;               // pinned copy
     // convert kernel geometry
     uint32_t G = 1;
-    size_t convert_smem = 0, convert_pipe_smem = 0, append_smem = 0;
+    size_t convert_pipe_smem = 0, convert_one_smem = 0, append_smem = 0;
+    unsigned one_grid = 0;                 // k_agg_convert_one: resident CTAs on the whole device for ...
+    int one_grid_key = -1;                 // ... this (threads per CTA, meter) combination
     bool pending = false;                  // a push was enqueued and its result not yet collected
 };
 
@@ -114,12 +116,25 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
     if (conv_blocks > cap) conv_blocks = cap;
     const unsigned conv_threads = (unsigned)ctx->tune.agg_block;
-    if (ctx->tune.agg_pipe) {
+    if (a->G == 1 && a->geo.half_quanta <= 64 && conv_threads <= 128) {
+        // one frame per step and at most 64 quanta per frame: descriptors in registers, no meta buffers
+        auto kern = a->meter ? (a->lut ? k_agg_convert_one<true, true> : k_agg_convert_one<true, false>)
+                             : (a->lut ? k_agg_convert_one<false, true> : k_agg_convert_one<false, false>);
+        // a persistent grid: exactly the CTAs that are resident at once, each walking over frames with the grid's
+        // stride (a larger grid left the last wave two thirds full: 55 % of the warp slots active, ncu)
+        const int key = (int)conv_threads * 2 + (a->meter ? 1 : 0);
+        if (a->one_grid_key != key) {
+            int per_sm = 0;
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, (int)conv_threads, a->convert_one_smem));
+            a->one_grid = (unsigned)(std::max(per_sm, 1) * ctx->sm_count);
+            a->one_grid_key = key;
+        }
+        if (ctx->tune.agg_persistent && conv_blocks > a->one_grid) conv_blocks = a->one_grid;
+        agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_one_smem, a->geo, ca);
+    } else {
         auto kern = a->meter ? (a->lut ? k_agg_convert_pipe<true, true> : k_agg_convert_pipe<true, false>)
                              : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
         agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
-    } else {
-        agg_launch(ctx, a->meter ? k_agg_convert<true> : k_agg_convert<false>, (unsigned)conv_blocks, conv_threads, a->convert_smem, a->geo, ca);
     }
     if (a->meter) {
         agg_launch(ctx, k_agg_levels, blocks_128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
@@ -191,9 +206,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
 
     // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
     a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, ((size_t)ctx->tune.agg_stage_kb * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
-    a->convert_smem = (((size_t)a->G * max_frame_quanta * slot_bytes + 127) & ~(size_t)127) + 8 * (size_t)a->G * max_frame_quanta +
-                      8 * (a->G + 1) + 24 * a->G;
     a->convert_pipe_smem = agg_arena_bytes(a->G, max_frame_quanta, quantum) + 2 * (size_t)agg_meta_layout(a->G, a->G * max_frame_quanta).bytes;
+    a->convert_one_smem = agg_arena_bytes(1, max_frame_quanta, quantum);
     a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127);
 
     cudaError_t e = cudaSuccess;
@@ -242,12 +256,16 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(cudaMemsetAsync(a->ring_rms, 0, S * max_frame_quanta * 8, ctx->stream));
     AGG_STEP(cudaMemcpyAsync(a->nout_of, h_nout.data(), h_nout.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (a->geo.stride == 0) AGG_STEP(cudaMemcpyAsync(a->lut, h_lut.data(), h_lut.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-    AGG_STEP(cudaFuncSetAttribute(k_agg_convert<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
-    AGG_STEP(cudaFuncSetAttribute(k_agg_convert<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
+    if (a->G == 1 && max_frame_quanta <= 64) {
+        AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
+        AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
+        AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
+        AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
+    }
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
 #undef AGG_STEP
