@@ -344,42 +344,86 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     if (k >= ctl->n_touched) return;
     const uint32_t s = touched[k], m = count[s], base = cursor[s] - m;
     uint32_t *list = sorted + base;
-    sort_indices(list, m);
     const uint32_t c0 = fill[s];
     uint32_t f = c0, ring_cnt = c0, frame_start = 0;
     double last = last_send[s];
-    // The rule is sequential in `last`, but the addresses are not: the arrival times of a batch of quanta are
-    // fetched together (one memory round trip per 8 quanta instead of one per quantum -- the kernel was a chain of
-    // dependent misses, 23 deep for a 60 ms frame).
+    bool too_long = false;
+    // the reference's rule for the j-th quantum of the session in this push (push index i, arrival time `now`)
+    auto rule = [&](uint32_t i, double now, uint32_t j) {
+        if (f >= g.half_quanta) { too_long = true; return; }
+        f++;
+        // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
+        if (now - last >= g.desired_ms) {
+            o.fl_nq[i] = f; o.fl_ring[i] = ring_cnt; o.fl_pos[i] = base + frame_start;
+            f = 0; ring_cnt = 0; frame_start = j + 1u;
+            last = now;                                                        // App.tsx:287
+        } else {
+            o.fl_nq[i] = 0u;
+        }
+    };
+    // The rule is sequential in `last`, but the addresses are not: arrival times are fetched in batches of 8 (one
+    // memory round trip per batch instead of one per quantum -- the kernel was a chain of dependent misses).
     constexpr uint32_t B = 8;
-    for (uint32_t j0 = 0; j0 < m; j0 += B) {
-        uint32_t idx[B];
-        double at[B];
+    if (m <= 32u) {
+        // The usual case (~23 quanta per 60 ms, 1 per push when streaming): the index list lives in registers.
+        // Arrival order by a bitonic network -- 240 compare-exchanges, no memory traffic, no divergence; the
+        // in-place insertion sort this replaces stored to the list on every step and then waited for its own
+        // stores to come back from L2 (a third of the kernel, ncu).
+        uint32_t v[32];
 #pragma unroll
-        for (uint32_t u = 0; u < B; u++) idx[u] = j0 + u < m ? list[j0 + u] : 0u;
+        for (int u = 0; u < 32; u++) v[u] = (uint32_t)u < m ? list[u] : 0xFFFFFFFFu;
+        if (m > 1u) {
 #pragma unroll
-        for (uint32_t u = 0; u < B; u++) at[u] = j0 + u < m ? arrival[idx[u]] : 0.0;
+            for (int kk = 2; kk <= 32; kk <<= 1) {
 #pragma unroll
-        for (uint32_t u = 0; u < B; u++) {
-            const uint32_t j = j0 + u;
-            if (j >= m) break;
-            const uint32_t i = idx[u];
-            if (f >= g.half_quanta) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
-            f++;
-            // App.tsx:279-280: elapsed = performance.now() - lastSend; if (elapsed >= desiredMs) flush
-            const double now = at[u];
-            if (now - last >= g.desired_ms) {
-                o.fl_nq[i] = f; o.fl_ring[i] = ring_cnt; o.fl_pos[i] = base + frame_start;
-                f = 0; ring_cnt = 0; frame_start = j + 1u;
-                last = now;                                                    // App.tsx:287
-            } else {
-                o.fl_nq[i] = 0u;
+                for (int jj = kk >> 1; jj > 0; jj >>= 1) {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) {
+                        const int l = i ^ jj;
+                        if (l > i) {
+                            const uint32_t lo = min(v[i], v[l]), hi = max(v[i], v[l]);
+                            const bool up = (i & kk) == 0;
+                            v[i] = up ? lo : hi;
+                            v[l] = up ? hi : lo;
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 32; u++) if ((uint32_t)u < m) list[u] = v[u];  // the convert and level kernels read it
+        }
+#pragma unroll
+        for (int b0 = 0; b0 < 32; b0 += (int)B) {
+            if ((uint32_t)b0 < m) {
+                double at[B];
+#pragma unroll
+                for (int u = 0; u < (int)B; u++) at[u] = (uint32_t)(b0 + u) < m ? arrival[v[b0 + u]] : 0.0;
+#pragma unroll
+                for (int u = 0; u < (int)B; u++) if ((uint32_t)(b0 + u) < m) rule(v[b0 + u], at[u], (uint32_t)(b0 + u));
             }
         }
+        if (too_long) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
+        // quanta after the last flush stay in the session's buffer: behind what was there if nothing flushed
+        const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
+#pragma unroll
+        for (int u = 0; u < 32; u++)
+            if ((uint32_t)u < m) o.dst_slot[v[u]] = (uint32_t)u >= frame_start ? first_slot + ((uint32_t)u - frame_start) : 0xFFFFFFFFu;
+    } else {
+        sort_indices(list, m);
+        for (uint32_t j0 = 0; j0 < m; j0 += B) {
+            uint32_t idx[B];
+            double at[B];
+#pragma unroll
+            for (uint32_t u = 0; u < B; u++) idx[u] = j0 + u < m ? list[j0 + u] : 0u;
+#pragma unroll
+            for (uint32_t u = 0; u < B; u++) at[u] = j0 + u < m ? arrival[idx[u]] : 0.0;
+#pragma unroll
+            for (uint32_t u = 0; u < B; u++) if (j0 + u < m) rule(idx[u], at[u], j0 + u);
+        }
+        if (too_long) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
+        const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
+        for (uint32_t j = 0; j < m; j++) o.dst_slot[list[j]] = j >= frame_start ? first_slot + (j - frame_start) : 0xFFFFFFFFu;
     }
-    // quanta after the last flush stay in the session's buffer: behind what was there if nothing flushed
-    const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
-    for (uint32_t j = 0; j < m; j++) o.dst_slot[list[j]] = j >= frame_start ? first_slot + (j - frame_start) : 0xFFFFFFFFu;
     o.new_fill[k] = f;
     o.new_last[k] = last;
     o.flushed[k] = frame_start;

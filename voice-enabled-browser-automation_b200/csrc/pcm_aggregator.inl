@@ -93,14 +93,16 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
 {
     cudaStream_t st = ctx->stream;
     CU(cudaMemsetAsync(a->ctl, 0, sizeof(AggCtl), st));
-    const unsigned blocks_n = (n + 255u) / 256u, blocks_128 = (n + 127u) / 128u;
+    // kernels with one thread per QUANTUM, and kernels with one thread per TOUCHED SESSION (at most min(n, max_sessions))
+    const uint32_t max_touched = std::min(n, a->geo.max_sessions);
+    const unsigned blocks_n = (n + 255u) / 256u, blocks_t = (max_touched + 255u) / 256u, blocks_t128 = (max_touched + 127u) / 128u;
     const unsigned scan_blocks = (n + kScanBlock - 1) / kScanBlock;
     agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
     ScanArgs sa{n, a->fl_nq, a->nout_of, a->ctl};
-    agg_launch(ctx, k_agg_reserve, blocks_n, 256, 0, a->touched, a->count, a->cursor, a->ctl);
+    agg_launch(ctx, k_agg_reserve, blocks_t, 256, 0, a->touched, a->count, a->cursor, a->ctl);
     agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, a->ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
-    agg_launch(ctx, k_agg_walk, blocks_128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, a->ctl);
+    agg_launch(ctx, k_agg_walk, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, a->ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     agg_launch(ctx, k_scan_reduce, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b);
     agg_launch(ctx, k_scan_sums, 1u, 1024, 0, sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
@@ -137,7 +139,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
         agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
     }
     if (a->meter) {
-        agg_launch(ctx, k_agg_levels, blocks_128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
+        agg_launch(ctx, k_agg_levels, blocks_t128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
                    a->level, a->ctl);
         const unsigned long long tiles = ((unsigned long long)n + 63ull) / 64ull;
         agg_launch(ctx, k_agg_append<true>, (unsigned)(tiles < cap ? tiles : cap), 256, a->append_smem, samples, a->dst_slot, a->ring, a->ring_rms, n,
@@ -147,7 +149,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
         agg_launch(ctx, k_agg_append<false>, (unsigned)(warps_blocks < cap ? warps_blocks : cap), 256, 0, samples, a->dst_slot, a->ring, a->ring_rms, n,
                    a->geo.quantum, a->ctl);
     }
-    agg_launch(ctx, k_agg_commit, blocks_n, 256, 0, a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
+    agg_launch(ctx, k_agg_commit, blocks_t, 256, 0, a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(a->h_ctl, a->ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
     a->pending = true;
