@@ -324,6 +324,7 @@ def main():
     ap.add_argument("--agg-once", action="store_true", help="the aggregator benchmark alone (for ncu)")
     ap.add_argument("--sweep-agg", action="store_true", help="sweep the aggregator convert kernel's CTA size and step size")
     ap.add_argument("--sweep-meter", action="store_true")
+    ap.add_argument("--agg-stream", type=int, default=0, help="the streaming-regime aggregator benchmark alone with this many sessions (for ncu)")
     ap.add_argument("--agg-order", default="", help="diagnostic: run the big-push aggregator benchmark alone with this push order (quantum | session)")
     args = ap.parse_args()
     if args.tune:
@@ -335,6 +336,9 @@ def main():
                 for m in (False, True):
                     r = aggregator(ctx, meter=m)
                     print(json.dumps(dict(agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        return
+    if args.agg_stream:
+        print(json.dumps(aggregator_streaming(ctx, S=args.agg_stream, pushes=46)), flush=True)
         return
     if args.agg_order:
         print(json.dumps(aggregator(ctx, order=args.agg_order)), flush=True)

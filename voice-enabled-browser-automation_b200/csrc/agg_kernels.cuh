@@ -7,7 +7,7 @@
 //
 // One push of n quanta (quantum i belongs to sessions[i], arrived at arrival[i]):
 //   1 k_agg_count    count[s]++ per quantum; the first toucher of a session appends it to `touched`
-//   2 k_agg_reserve  where each touched session's index list starts (one atomic per session: any order will do)
+//   2 k_agg_reserve  where each touched session's index list starts (one atomic per block: the lists may sit in any order)
 //   3 k_agg_scatter  sorted[cursor[s]++] = i   (atomic, so the order inside a session is arbitrary ...)
 //   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
 //                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
@@ -40,7 +40,8 @@ struct AggCtl {                  // lives in device memory; copied to the host a
     uint32_t status;
     uint32_t n_touched;
     uint32_t n_frames;
-    uint32_t n_leftover;         // quanta of this push that went to a ring
+    uint32_t reserved_;          // (was a count of the quanta that went to a ring: a million threads updating one word cost
+                                 //  more than the early exit it bought the append kernel)
     unsigned long long out_total;   // output samples incl. the padding of every frame to 8 samples
     uint32_t n_listed;           // running total of the per-session index lists (k_agg_reserve)
     uint32_t pad_;
@@ -74,41 +75,73 @@ __device__ __forceinline__ void pdl_enter()
 }
 
 // ---- 1: count ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sessions, uint32_t *__restrict__ count,
-            uint32_t *__restrict__ touched, AggCtl *__restrict__ ctl)
+// Exclusive scan of one value per thread over a 256-thread block (all threads must call); `total` = the block's sum.
+__device__ __forceinline__ uint32_t block_exscan256(uint32_t v, uint32_t *warp_sums, uint32_t &total)
 {
-    pdl_enter();
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t s = __ldg(sessions + i);
-    if (s >= max_sessions) { atomicOr(&ctl->status, AGG_ST_BAD_SESSION); return; }
-    if (atomicAdd(count + s, 1u) == 0u) touched[atomicAdd(&ctl->n_touched, 1u)] = s;
-}
-
-// ---- 2: reserve --------------------------------------------------------------------------------------------
-// Where each touched session's index list starts in `sorted`.  The lists may sit in any order, so no scan
-// is needed: every touched session takes count[s] slots from a running total with one atomic.
-__global__ void __launch_bounds__(256)
-k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
-              AggCtl *__restrict__ ctl)
-{
-    pdl_enter();
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
-    const bool live = k < ctl->n_touched;
-    const uint32_t s = live ? touched[k] : 0u, c = live ? count[s] : 0u;
-    // one atomic per WARP (a million sessions hitting one counter cost 33 us): prefix-sum the warp's counts,
-    // lane 31 reserves the warp's total, everyone adds its own offset
-    uint32_t inc = c;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
         const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, d);
         if (lane >= (uint32_t)d) inc += o;
     }
-    uint32_t base = 0;
-    if (lane == 31u && inc) base = atomicAdd(&ctl->n_listed, inc);
-    base = __shfl_sync(0xFFFFFFFFu, base, 31);
-    if (live) cursor[s] = base + inc - c;
+    if (lane == 31u) warp_sums[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        const uint32_t ws = warp_sums[w];
+        if ((uint32_t)w < warp) base += ws;
+        tot += ws;
+    }
+    __syncthreads();
+    total = tot;
+    return base + inc - v;
+}
+
+// Space for `v` items per thread out of one running total: ONE atomic per block (a million threads -- or even their
+// 32 768 warps -- adding to the same address serialise in L2 at about a nanosecond each: 33 us per kernel, measured).
+__device__ __forceinline__ uint32_t block_reserve256(uint32_t v, uint32_t *counter, uint32_t *smem9)
+{
+    uint32_t total;
+    const uint32_t off = block_exscan256(v, smem9, total);
+    if (threadIdx.x == 0) smem9[8] = total ? atomicAdd(counter, total) : 0u;
+    __syncthreads();
+    return smem9[8] + off;
+}
+
+__global__ void __launch_bounds__(256)
+k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sessions, uint32_t *__restrict__ count,
+            uint32_t *__restrict__ touched, AggCtl *__restrict__ ctl)
+{
+    pdl_enter();
+    __shared__ uint32_t sm[9];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t s = 0;
+    bool first = false;
+    if (i < n) {
+        s = __ldg(sessions + i);
+        if (s >= max_sessions) atomicOr(&ctl->status, AGG_ST_BAD_SESSION);
+        else first = atomicAdd(count + s, 1u) == 0u;                  // the first toucher lists the session
+    }
+    const uint32_t at = block_reserve256(first ? 1u : 0u, &ctl->n_touched, sm);
+    if (first) touched[at] = s;
+}
+
+// ---- 2: reserve --------------------------------------------------------------------------------------------
+// Where each touched session's index list starts in `sorted`.  The lists may sit in any order, so no grid-wide
+// scan is needed: every block takes the slots of its sessions from a running total.
+__global__ void __launch_bounds__(256)
+k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor,
+              AggCtl *__restrict__ ctl)
+{
+    pdl_enter();
+    __shared__ uint32_t sm[9];
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = k < ctl->n_touched;
+    const uint32_t s = live ? touched[k] : 0u, c = live ? count[s] : 0u;
+    const uint32_t at = block_reserve256(c, &ctl->n_listed, sm);       // one atomic per block
+    if (live) cursor[s] = at;
 }
 
 // ---- 5: scan over the push's quanta (two channels, 2048 items per block) ---------------------------------------
@@ -427,7 +460,6 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     o.new_fill[k] = f;
     o.new_last[k] = last;
     o.flushed[k] = frame_start;
-    if (m > frame_start) atomicAdd(&ctl->n_leftover, m - frame_start);
 }
 
 // 16-byte asynchronous global -> shared copy (LDGSTS, L2 only).  The aggregator stages single 512-byte
@@ -763,17 +795,18 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
 
-        // ---- pick + encode + store (see k_agg_convert_pipe); pointers and indices advance by addition ---------------------
-        {
+        // ---- pick + encode + store (see k_agg_convert_pipe); pointers and indices advance by addition.  `tid` of `nthr`
+        // threads share the frame's pairs: all of the CTA, or -- with the meter -- the warps that are not metering.
+        auto picks = [&](uint32_t tid, uint32_t nthr) {
             const uint32_t n_in = nq * Q, n_out = cur.n_out;
             int16_t *dstf = a.out + cur.d.off;
             const float qnan = __int_as_float(0x7FC00000);
             if (a.out_aligned16) {
                 const uint32_t nfull = n_out >> 1, R = g.stride;
-                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + threadIdx.x;
-                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + threadIdx.x;
-                uint32_t i0 = 2u * threadIdx.x * R;
-                const uint32_t di = 2u * bd * R;                                // index step from pair p to pair p + bd
+                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + tid;
+                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + tid;
+                uint32_t i0 = 2u * tid * R;
+                const uint32_t di = 2u * nthr * R;                              // index step from pair p to pair p + nthr
                 auto pair = [&](uint32_t ia, const uint2 *l) -> uint32_t {
                     float x0, x1;
                     if (LUT) {
@@ -787,30 +820,42 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                     }
                     return pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
                 };
-                for (uint32_t p = threadIdx.x; p < nfull; p += 2u * bd, dp += 2u * bd, lp += 2u * bd, i0 += 2u * di) {
-                    const bool second = p + bd < nfull;
-                    const uint32_t va = pair(i0, lp), vb = second ? pair(i0 + di, lp + bd) : 0u;
+                for (uint32_t p = tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
+                    const bool second = p + nthr < nfull;
+                    const uint32_t va = pair(i0, lp), vb = second ? pair(i0 + di, lp + nthr) : 0u;
                     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp), "r"(va) : "memory");   // streaming: frames are written once
-                    if (second) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp + bd), "r"(vb) : "memory");
+                    if (second) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp + nthr), "r"(vb) : "memory");
                 }
-                if ((n_out & 1u) && threadIdx.x == 0u) {
+                if ((n_out & 1u) && tid == 0u) {
                     const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
                     dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             } else {
-                for (uint32_t o = threadIdx.x; o < n_out; o += bd) {
+                for (uint32_t o = tid; o < n_out; o += nthr) {
                     const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
                     dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             }
-        }
-        if (METER) {
-            // lane <-> slot; ring-carried quanta were metered when they were appended.  The metering warps rotate from
-            // frame to frame so that the long sum-of-squares chains do not always land on the same scheduler.
+        };
+        if (!METER) {
+            picks(threadIdx.x, bd);
+        } else {
+            // lane <-> slot; ring-carried quanta were metered when they were appended.  A quantum's sum of squares is a
+            // 128-long dependent chain (~1 300 clocks) during which the arena cannot be refilled, so the metering warps
+            // start on it at once and the OTHER warps share the picks; which warps meter rotates from frame to frame so
+            // that the chains do not always land on the same scheduler.
             const uint32_t m_warps = (nq + 31u) >> 5;
-            const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
-            for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < nq; sl += bd)
-                if (sl >= rc) a.rms_at[cur.d.pos + (sl - rc)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+            auto meter = [&](uint32_t sl) {
+                if (sl < nq && sl >= rc) a.rms_at[cur.d.pos + (sl - rc)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+            };
+            if (m_warps < nw) {
+                const uint32_t wrel = (warp + nw - (it * m_warps) % nw) % nw;
+                if (wrel < m_warps) meter((wrel << 5) + lane);
+                else picks(((wrel - m_warps) << 5) + lane, (nw - m_warps) << 5);
+            } else {
+                picks(threadIdx.x, bd);
+                for (uint32_t sl = threadIdx.x; sl < nq; sl += bd) meter(sl);
+            }
         }
         if (!more) break;
         __syncthreads();                                   // the arena is free again
@@ -843,8 +888,18 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
         lv = rms > dec ? rms : dec;
         if (poisoned) lv = __longlong_as_double(0x7FF8000000000000ll);
     };
-    for (uint32_t j = 0; j < c0; j++) step(ring_rms[(size_t)s * g.half_quanta + j]);
-    for (uint32_t j = 0; j < nfl; j++) step(rms_at[base + j]);
+    // the chain is sequential, the loads are not: fetch 8 rms values per round trip
+    auto run = [&](const double *src, uint32_t cnt) {
+        for (uint32_t j0 = 0; j0 < cnt; j0 += 8u) {
+            double r[8];
+#pragma unroll
+            for (uint32_t u = 0; u < 8u; u++) r[u] = j0 + u < cnt ? src[j0 + u] : 0.0;
+#pragma unroll
+            for (uint32_t u = 0; u < 8u; u++) if (j0 + u < cnt) step(r[u]);
+        }
+    };
+    run(ring_rms + (size_t)s * g.half_quanta, c0);
+    run(rms_at + base, nfl);
     level[s] = lv;
 }
 
@@ -860,7 +915,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
              double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ctl->status != 0u || ctl->n_leftover == 0u) return;
+    if (ctl->status != 0u) return;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t granules = quantum >> 2;
     if (!METER) {
