@@ -18,5 +18,10 @@ ncu --set full --clock-control none --import-source on -k regex:k_frames_meter_w
 timeout 300 python tools/run_configs.py --agg-once > $O/r02_plain_agg.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file $O/r02_launches_agg.csv python tools/run_configs.py --agg-once > $O/r02_ncu_agg_launches.log 2>&1
 timeout 300 python tools/run_configs.py --agg-once > $O/r02_plain_agg2.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_agg_convert -s 2 -c 1 -o $O/r02_prof_agg_convert python tools/run_configs.py --agg-once > $O/r02_ncu_agg_convert.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_agg_convert_one -s 2 -c 1 -o $O/r02_prof_agg_convert python tools/run_configs.py --agg-order quantum > $O/r02_ncu_agg_convert.log 2>&1
+timeout 300 python tools/run_configs.py --agg-order quantum > $O/r02_plain_agg3.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_agg_walk -s 2 -c 1 -o $O/r02_prof_agg_walk python tools/run_configs.py --agg-order quantum > $O/r02_ncu_agg_walk.log 2>&1
+timeout 300 python tools/run_configs.py --agg-stream 1048576 > $O/r02_plain_stream.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/r02_launches_agg_stream.csv python tools/run_configs.py --agg-stream 1048576 > $O/r02_ncu_agg_stream.log 2>&1
+timeout 300 python tools/run_configs.py --sweep-agg > $O/r02_sweep_aggregator.jsonl 2> $O/r02_sweep_aggregator.err
 ls -la $O | tail -30

@@ -10,6 +10,8 @@ Number, `math.floor`/`math.trunc` match Math.floor/ToInt16 truncation -- written
     /root/reference/apps/web/src/App.tsx:18-32  (resampleTo16k)
 It shares no code with oracle/pcm_oracle.c (C) or the CUDA kernels; the tests require all
 three to agree.  Run:  python tests/golden/make_golden.py   (rewrites the fixtures).
+Since then tests/golden/make_ref_exec.py has executed the reference's own source text (with
+tests/golden/mini_js.py) on every input held here and found every expectation below reproduced.
 """
 import hashlib
 import json

@@ -145,7 +145,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
         agg_launch(ctx, k_agg_append<true>, (unsigned)(tiles < cap ? tiles : cap), 256, a->append_smem, samples, a->dst_slot, a->ring, a->ring_rms, n,
                    a->geo.quantum, a->ctl);
     } else {
-        const unsigned long long warps_blocks = ((unsigned long long)n + 31ull) / 32ull;   // 8 warps x 4 quanta per block step
+        const unsigned long long warps_blocks = ((unsigned long long)n + 255ull) / 256ull;   // 8 warps x 32 quanta per block step
         agg_launch(ctx, k_agg_append<false>, (unsigned)(warps_blocks < cap ? warps_blocks : cap), 256, 0, samples, a->dst_slot, a->ring, a->ring_rms, n,
                    a->geo.quantum, a->ctl);
     }
