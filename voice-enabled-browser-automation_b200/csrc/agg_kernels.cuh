@@ -20,7 +20,7 @@
 //                    stored; with the meter on, each quantum's rms is computed from the staged copy.
 //   7 k_agg_levels   level = max(rms, level * 0.85) along each session's flushed quanta, in order
 //   8 k_agg_append   quanta that did not flush go to their session's ring (with their rms)
-//   9 k_agg_commit   fill / lastSend take their new values; per-push counters are cleared
+//   9 (commit, inside the append kernel)   fill / lastSend take their new values; per-push counters are cleared
 // Steps 6-9 look at the push's status word first: if any check failed (unknown session, a buffer
 // longer than max_frame_quanta, too many frames, output too small) they change nothing, which IS the
 // rollback -- the plan so far lives only in scratch.
@@ -145,8 +145,8 @@ k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__
 }
 
 // ---- 5: scan over the push's quanta (two channels, 2048 items per block) ---------------------------------------
-// Frame number and output offset of every flush, in flush order (= ascending quantum index): a three-pass
-// scan -- per-block totals, one block scans the totals, per-block rescan + emit.  Channel a counts the
+// Frame number and output offset of every flush, in flush order (= ascending quantum index): a two-pass
+// scan -- per-block totals, then per-block rescan + emit (each block adds up the totals before it).  Channel a counts the
 // flushes, channel b adds up the frames' output lengths rounded up to 8 samples.
 constexpr int kScanThreads = 256, kScanItems = 8, kScanBlock = kScanThreads * kScanItems;
 
@@ -224,51 +224,6 @@ k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ 
     if (threadIdx.x == 0) { sums_a[blockIdx.x] = ta; sums_b[blockIdx.x] = tb; }
 }
 
-// One block turns the per-block totals into exclusive offsets (64-bit for channel b: sample counts).
-// It also checks the two capacities and publishes n_frames / out_total.
-__global__ void __launch_bounds__(1024)
-k_scan_sums(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ sums_b, unsigned long long *__restrict__ offs_b,
-            AggCtl *__restrict__ ctl, uint32_t max_frames, unsigned long long out_capacity)
-{
-    pdl_enter();
-    __shared__ unsigned long long carry_a, carry_b;
-    __shared__ unsigned long long wsum_a[32], wsum_b[32];
-    const uint32_t len = a.n;
-    const uint32_t nb = (len + kScanBlock - 1) / kScanBlock;
-    if (threadIdx.x == 0) { carry_a = 0; carry_b = 0; }
-    __syncthreads();
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    for (uint32_t b0 = 0; b0 < nb; b0 += 1024u) {
-        const uint32_t b = b0 + threadIdx.x;
-        unsigned long long va = b < nb ? sums_a[b] : 0ull, vb = b < nb ? sums_b[b] : 0ull;
-        unsigned long long ia = va, ib = vb;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned long long oa = __shfl_up_sync(0xFFFFFFFFu, ia, d), ob = __shfl_up_sync(0xFFFFFFFFu, ib, d);
-            if (lane >= (uint32_t)d) { ia += oa; ib += ob; }
-        }
-        if (lane == 31u) { wsum_a[warp] = ia; wsum_b[warp] = ib; }
-        __syncthreads();
-        unsigned long long ba = carry_a, bb = carry_b, ta = 0, tb = 0;
-        for (uint32_t w = 0; w < 32u; w++) {
-            if (w < warp) { ba += wsum_a[w]; bb += wsum_b[w]; }
-            ta += wsum_a[w]; tb += wsum_b[w];
-        }
-        if (b < nb) { sums_a[b] = (uint32_t)(ba + ia - va); offs_b[b] = bb + ib - vb; }
-        __syncthreads();
-        if (threadIdx.x == 0) { carry_a += ta; carry_b += tb; }
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) {
-        ctl->n_frames = (uint32_t)carry_a;
-        ctl->out_total = carry_b;
-        uint32_t st = 0;
-        if (carry_a > max_frames) st |= AGG_ST_TOO_MANY_FRAMES;
-        if (carry_b > out_capacity) st |= AGG_ST_OUT_TOO_SMALL;
-        if (st) atomicOr(&ctl->status, st);
-    }
-}
-
 struct ScanApplyB {
     const uint32_t *sessions, *fl_ring, *fl_pos;
     uint32_t *frame_session, *frame_len;
@@ -290,22 +245,39 @@ __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &
     ap.fdesc_off[f] = off;
 }
 
+// Second pass: every block adds up the totals of the blocks before it (a few hundred numbers: cheaper than a third
+// kernel whose only job was to scan them), rescans its own items and emits the frames.  The last block knows the
+// grand totals: it publishes n_frames / out_total and checks the two capacities.  Frames emitted by earlier blocks
+// of a push that then turns out too large are harmless: emit_frame never writes past max_frames, and nothing
+// downstream runs once the status word is set.
 __global__ void __launch_bounds__(kScanThreads)
-k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned long long *__restrict__ offs_b, ScanApplyB ap)
+k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__restrict__ sums_b, ScanApplyB ap,
+             AggCtl *__restrict__ ctl, unsigned long long out_capacity)
 {
     pdl_enter();
     __shared__ uint32_t ws[kScanThreads / 32];
+    __shared__ unsigned long long red_a[kScanThreads / 32], red_b[kScanThreads / 32];
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
     if (a.ctl->status != 0u) return;                   // rejected push: nothing to emit
+    unsigned long long pa = 0, pb = 0;                 // totals of the blocks before this one
+    for (uint32_t b = threadIdx.x; b < blockIdx.x; b += kScanThreads) { pa += sums_a[b]; pb += sums_b[b]; }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { pa += __shfl_xor_sync(0xFFFFFFFFu, pa, d); pb += __shfl_xor_sync(0xFFFFFFFFu, pb, d); }
+    if ((threadIdx.x & 31u) == 0u) { red_a[threadIdx.x >> 5] = pa; red_b[threadIdx.x >> 5] = pb; }
     uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
     scan_load8(a, base + threadIdx.x * kScanItems, len, va, vb);
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) { sa += va[k]; sb += vb[k]; }
     uint32_t ta, tb;
-    uint32_t ea = block_exscan(sa, ws, ta) + sums_a[blockIdx.x];
-    unsigned long long eb = (unsigned long long)block_exscan(sb, ws, tb) + offs_b[blockIdx.x];
+    const uint32_t xa = block_exscan(sa, ws, ta);      // (its barriers also publish red_a / red_b)
+    const uint32_t xb = block_exscan(sb, ws, tb);
+    pa = 0; pb = 0;
+#pragma unroll
+    for (int w = 0; w < kScanThreads / 32; w++) { pa += red_a[w]; pb += red_b[w]; }
+    uint32_t ea = xa + (uint32_t)pa;
+    unsigned long long eb = (unsigned long long)xb + pb;
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) {
         const uint32_t idx = base + threadIdx.x * kScanItems + k;
@@ -313,6 +285,15 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const unsigned lon
             if (va[k]) emit_frame(a, ap, idx, ea, eb);       // quantum idx flushes frame number ea
         }
         ea += va[k]; eb += vb[k];
+    }
+    if (blockIdx.x == gridDim.x - 1u && threadIdx.x == 0u) {
+        const unsigned long long total_a = pa + ta, total_b = pb + tb;
+        ctl->n_frames = (uint32_t)total_a;
+        ctl->out_total = total_b;
+        uint32_t st = 0;
+        if (total_a > ap.max_frames) st |= AGG_ST_TOO_MANY_FRAMES;
+        if (total_b > out_capacity) st |= AGG_ST_OUT_TOO_SMALL;
+        if (st) atomicOr(&ctl->status, st);
     }
 }
 
@@ -909,13 +890,38 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
 // lane (handing a running sum from lane to lane costs ~15 warp-instructions per sample), so a CTA stages
 // 64 consecutive quanta of the push in shared memory (16-byte async copies, slot pitch quantum + 4 floats), lane t
 // meters slot t exactly like kernel 2c, and the warps then copy the slots out to the rings.
+// What the commit step needs (it rides in the append kernel: one launch fewer per push).
+struct AggCommitArgs {
+    const uint32_t *touched;
+    uint32_t *count, *fill;
+    double *last_send;
+    const uint32_t *new_fill;
+    const double *new_last;
+    AggCtl *ctl_next;                // the NEXT push's control block: cleared here
+};
+
 template <bool METER>
 __global__ void __launch_bounds__(256)
 k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
-             double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl)
+             double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl, AggCommitArgs cm)
 {
     pdl_enter();
-    if (ctl->status != 0u) return;
+    // ---- 9: commit.  fill / lastSend of every touched session take their new values (only if the push stands) and
+    // the per-push counters are cleared (always: the next push starts from clean counters).  The append work neither
+    // reads nor writes any of this, so where the commit sits in the kernel is only a matter of overlap: the plain
+    // copy path runs it after its loads and stores have been issued.
+    const bool ok = ctl->status == 0u;
+    auto commit = [&]() {
+        const uint32_t nt = ctl->n_touched;
+        if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
+        for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nt; k += gridDim.x * blockDim.x) {
+            const uint32_t s = cm.touched[k];
+            cm.count[s] = 0u;
+            if (ok) { cm.fill[s] = cm.new_fill[k]; cm.last_send[s] = cm.new_last[k]; }
+        }
+    };
+    if (!ok || METER) commit();
+    if (!ok) return;
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t granules = quantum >> 2;
     if (!METER) {
@@ -954,6 +960,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
                 }
             }
         }
+        commit();
         return;
     }
     constexpr uint32_t TILE = 64;
@@ -991,20 +998,6 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
             for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = s4[gi];
         }
     }
-}
-
-// ---- 9: commit ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
-k_agg_commit(const uint32_t *__restrict__ touched, uint32_t *__restrict__ count, uint32_t *__restrict__ fill,
-             double *__restrict__ last_send, const uint32_t *__restrict__ new_fill, const double *__restrict__ new_last,
-             const AggCtl *__restrict__ ctl)
-{
-    pdl_enter();
-    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ctl->n_touched) return;
-    const uint32_t s = touched[k];
-    count[s] = 0u;                                        // always: the next push starts from clean counters
-    if (ctl->status == 0u) { fill[s] = new_fill[k]; last_send[s] = new_last[k]; }
 }
 
 __global__ void k_agg_reset(uint32_t *__restrict__ fill, double *__restrict__ last_send, uint32_t first, uint32_t n, double now_ms)

@@ -33,13 +33,13 @@ struct pcmb200_aggregator {
              *dst_slot = nullptr, *new_fill = nullptr, *flushed = nullptr;
     double *new_last = nullptr, *rms_at = nullptr;
     uint32_t *sums_a = nullptr, *sums_b = nullptr;
-    unsigned long long *offs_b = nullptr;
     AggFrameDesc *fdesc = nullptr;
     unsigned long long *fdesc_off = nullptr;
     uint32_t *f_session = nullptr, *f_len = nullptr;     // frame arrays when the caller's are host memory
     unsigned long long *f_off = nullptr;
     int16_t *d_out = nullptr;              // [out_cap] when the caller's output is host memory
-    AggCtl *ctl = nullptr;                 // device
+    AggCtl *ctl = nullptr;                 // device: two blocks, used by alternate pushes (see agg_enqueue)
+    int ctl_idx = 0;
     AggCtl *h_ctl = nullptr;               // pinned copy
     // convert kernel geometry
     uint32_t G = 1;
@@ -92,25 +92,28 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
                 unsigned long long *frame_offset, uint32_t max_frames)
 {
     cudaStream_t st = ctx->stream;
-    CU(cudaMemsetAsync(a->ctl, 0, sizeof(AggCtl), st));
+    // Two control blocks, used in turn: the kernels of this push work on `ctl`, and the last one clears the other
+    // block for the next push (that one was read back at the end of the previous push, which this stream has
+    // finished).  Saves a memset call per push on a path that is bound by the host's enqueue time.
+    AggCtl *ctl = a->ctl + a->ctl_idx, *ctl_next = a->ctl + (a->ctl_idx ^ 1);
+    a->ctl_idx ^= 1;
     // kernels with one thread per QUANTUM, and kernels with one thread per TOUCHED SESSION (at most min(n, max_sessions))
     const uint32_t max_touched = std::min(n, a->geo.max_sessions);
     const unsigned blocks_n = (n + 255u) / 256u, blocks_t = (max_touched + 255u) / 256u, blocks_t128 = (max_touched + 127u) / 128u;
     const unsigned scan_blocks = (n + kScanBlock - 1) / kScanBlock;
-    agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, a->ctl);
-    ScanArgs sa{n, a->fl_nq, a->nout_of, a->ctl};
-    agg_launch(ctx, k_agg_reserve, blocks_t, 256, 0, a->touched, a->count, a->cursor, a->ctl);
-    agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, a->ctl);
+    agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, ctl);
+    ScanArgs sa{n, a->fl_nq, a->nout_of, ctl};
+    agg_launch(ctx, k_agg_reserve, blocks_t, 256, 0, a->touched, a->count, a->cursor, ctl);
+    agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
-    agg_launch(ctx, k_agg_walk, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, a->ctl);
+    agg_launch(ctx, k_agg_walk, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     agg_launch(ctx, k_scan_reduce, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b);
-    agg_launch(ctx, k_scan_sums, 1u, 1024, 0, sa, a->sums_a, a->sums_b, a->offs_b, a->ctl, max_frames, (unsigned long long)out_capacity);
-    agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->offs_b, ab);
+    agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b, ab, ctl, (unsigned long long)out_capacity);
 
     AggConvertArgs ca{};
     ca.samples = samples; ca.ring = a->ring; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
-    ca.nout_of = a->nout_of; ca.lut = a->lut; ca.out = out; ca.rms_at = a->rms_at; ca.ctl = a->ctl; ca.G = a->G;
+    ca.nout_of = a->nout_of; ca.lut = a->lut; ca.out = out; ca.rms_at = a->rms_at; ca.ctl = ctl; ca.G = a->G;
     ca.magic_q = magic_for(a->geo.quantum); ca.out_aligned16 = aligned(out, 16) ? 1 : 0; ca.hint = ctx->tune.store_hint;
     // frames <= quanta; a frame has about desired_ms worth of quanta, so n / G blocks is an upper bound
     // that is far too generous: cap the grid and let the blocks loop
@@ -138,20 +141,20 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
                              : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
         agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
     }
+    const AggCommitArgs cm{a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, ctl_next};
     if (a->meter) {
         agg_launch(ctx, k_agg_levels, blocks_t128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
-                   a->level, a->ctl);
+                   a->level, ctl);
         const unsigned long long tiles = ((unsigned long long)n + 63ull) / 64ull;
         agg_launch(ctx, k_agg_append<true>, (unsigned)(tiles < cap ? tiles : cap), 256, a->append_smem, samples, a->dst_slot, a->ring, a->ring_rms, n,
-                   a->geo.quantum, a->ctl);
+                   a->geo.quantum, ctl, cm);
     } else {
         const unsigned long long warps_blocks = ((unsigned long long)n + 255ull) / 256ull;   // 8 warps x 32 quanta per block step
         agg_launch(ctx, k_agg_append<false>, (unsigned)(warps_blocks < cap ? warps_blocks : cap), 256, 0, samples, a->dst_slot, a->ring, a->ring_rms, n,
-                   a->geo.quantum, a->ctl);
+                   a->geo.quantum, ctl, cm);
     }
-    agg_launch(ctx, k_agg_commit, blocks_t, 256, 0, a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, a->ctl);
     CU(cudaGetLastError());
-    CU(cudaMemcpyAsync(a->h_ctl, a->ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(a->h_ctl, ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
     a->pending = true;
     return PCMB200_OK;
 }
@@ -241,14 +244,14 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     const size_t nb = (P + kScanBlock - 1) / kScanBlock;
     AGG_STEP(agg_alloc(&a->sums_a, nb));
     AGG_STEP(agg_alloc(&a->sums_b, nb));
-    AGG_STEP(agg_alloc(&a->offs_b, nb));
     AGG_STEP(agg_alloc(&a->fdesc, P));
     AGG_STEP(agg_alloc(&a->fdesc_off, P));
     AGG_STEP(agg_alloc(&a->f_session, P));
     AGG_STEP(agg_alloc(&a->f_len, P));
     AGG_STEP(agg_alloc(&a->f_off, P));
     AGG_STEP(agg_alloc(&a->d_out, max_out_samples_per_push));
-    AGG_STEP(agg_alloc(&a->ctl, 1));
+    AGG_STEP(agg_alloc(&a->ctl, 2));
+    AGG_STEP(cudaMemsetAsync(a->ctl, 0, 2 * sizeof(AggCtl), ctx->stream));
     AGG_STEP(cudaHostAlloc((void **)&a->h_ctl, sizeof(AggCtl), cudaHostAllocDefault));
     AGG_STEP(cudaMemsetAsync(a->fill, 0, S * 4, ctx->stream));
     AGG_STEP(cudaMemsetAsync(a->count, 0, S * 4, ctx->stream));
@@ -290,7 +293,7 @@ extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *
     cudaStreamSynchronize(ctx->stream);
     void *dev[] = {a->ring, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
                    a->d_arrival, a->d_stage, a->touched, a->sorted, a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill,
-                   a->flushed, a->new_last, a->rms_at, a->sums_a, a->sums_b, a->offs_b, a->fdesc, a->fdesc_off, a->f_session,
+                   a->flushed, a->new_last, a->rms_at, a->sums_a, a->sums_b, a->fdesc, a->fdesc_off, a->f_session,
                    a->f_len, a->f_off, a->d_out, a->ctl};
     for (void *p : dev) if (p) cudaFree(p);
     if (a->h_ctl) cudaFreeHost(a->h_ctl);
