@@ -309,3 +309,46 @@ def test_aggregator_unaligned_device_output(ctx, rate, max_q):
     agg.close()
     for b in d.values():
         b.free()
+
+
+@pytest.mark.parametrize("knobs", [dict(agg_pdl=0), dict(agg_persistent=0), dict(agg_block=64), dict(agg_block=256),
+                                   dict(agg_block=128, agg_stage_kb=68), dict(agg_block=256, agg_stage_kb=51, agg_pdl=0)])
+@pytest.mark.parametrize("rate", [48000, 44100])
+def test_aggregator_every_kernel_form(ctx, knobs, rate):
+    """The tuning knobs choose between kernel forms (one frame per step with descriptors in registers / several
+    frames per step with shared-memory descriptors; persistent or oversized grid; plain or programmatic dependent
+    launches).  Every form must give the oracle's frames and levels: 700 sessions, buffers carried across three
+    pushes, sessions interleaved at random, the meter on."""
+    defaults = dict(agg_pdl=1, agg_persistent=1, agg_block=128, agg_stage_kb=20)
+    rng = np.random.RandomState(sum(knobs.values()) + rate // 100)
+    S, q_ms, per_push = 700, 128e3 / rate, (10, 9, 12)
+    try:
+        ctx.tune(**knobs)                                          # read when the aggregator is created / on every push
+        agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=S * 12, max_out_samples=S * 1000)
+        agg.set_meter(True)
+        agg.reset_range(0, S, 0.0)
+        nq = sum(per_push)
+        audio = rng.uniform(-1.02, 1.02, size=(S, nq, 128)).astype(np.float32)
+        times = 2.0 * rng.rand(S, 1) + np.cumsum(q_ms + rng.uniform(-0.3, 0.3, size=(S, nq)), axis=1)
+        got = {s: [] for s in range(S)}
+        q0 = 0
+        for pp in per_push:
+            ev = sorted((times[s, q], s, q) for s in range(S) for q in range(q0, q0 + pp))
+            q0 += pp
+            for s, pcm in agg.push(np.array([e[1] for e in ev]), np.array([e[0] for e in ev]), np.stack([audio[e[1], e[2]] for e in ev])):
+                got[s].append(pcm)
+        levels = agg.levels(0, S)
+        agg.close()
+    finally:
+        ctx.tune(**defaults)
+    n_frames = 0
+    for s in range(S):
+        want, start, _ = _session_frames(audio[s], times[s], rate)
+        assert len(got[s]) == len(want), (s, len(got[s]), len(want))
+        for a, b in zip(got[s], want):
+            assert a.size == b.size and np.array_equal(a, b), s
+        n_frames += len(want)
+        if start:
+            want_lv = oracle.level_meter(audio[s, :start].reshape(-1))[-1]
+            assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
+    assert n_frames >= S
