@@ -304,6 +304,52 @@ int main(int argc, char **argv)
     p = call(env, exports, "framesEncodeAsync", {pin_in, num(2), num(960), num(-5), pin_out});
     CHECK(p == nullptr && env->pending && env->pending->err_class == "RangeError", "framesEncodeAsync(rate < 0) throws RangeError");
 
+    // the capture aggregator (App.tsx:273-288) for two connections: 23 quanta each, 128e3/48000 ms apart; the 23rd
+    // arrives 61.3 ms after lastSend = 0 and flushes 2944 samples -> 981 outputs per connection
+    {
+        napi_value h = call(env, exports, "aggregatorCreate", {num(4), num(48000), num(32), num(64), num(4096)});
+        CHECK(h && h->kind == napi_value__::Number && !env->pending, "aggregatorCreate returns a handle");
+        call(env, exports, "aggregatorReset", {h, num(0), num(0)});
+        call(env, exports, "aggregatorReset", {h, num(1), num(0)});
+        CHECK(!env->pending, "aggregatorReset");
+        const int nq = 23, n = 2 * nq;
+        std::vector<uint32_t> sess(n);
+        std::vector<double> times(n);
+        std::vector<float> x((size_t)n * 128);
+        for (int q = 0; q < nq; q++)
+            for (int c = 0; c < 2; c++) {
+                const int i = q * 2 + c;
+                sess[i] = (uint32_t)c;
+                times[i] = (q + 1) * (128e3 / 48000);
+                for (int k = 0; k < 128; k++) x[(size_t)i * 128 + k] = (c ? -0.5f : 0.25f) + 0.001f * (float)((q * 128 + k) % 97);
+            }
+        napi_value a_sess = typed<uint32_t>(env, napi_uint32_array, sess), a_t = typed<double>(env, napi_float64_array, times);
+        napi_value a_x = typed<float>(env, napi_float32_array, x);
+        napi_value a_out = typed<int16_t>(env, napi_int16_array, std::vector<int16_t>(4096, 0x1111));
+        napi_value a_fs = typed<uint32_t>(env, napi_uint32_array, std::vector<uint32_t>(8, 9)), a_fl = typed<uint32_t>(env, napi_uint32_array, std::vector<uint32_t>(8, 9));
+        napi_value a_fo = typed<double>(env, napi_float64_array, std::vector<double>(8, -1.0));
+        r = call(env, exports, "aggregatorPush", {h, num(n), a_sess, a_t, a_x, a_out, a_fs, a_fl, a_fo});
+        CHECK(r && !env->pending && r->num == 2.0, "aggregatorPush: both connections flush one frame");
+        bool ok = r && ptr<uint32_t>(a_fl)[0] == 981 && ptr<uint32_t>(a_fl)[1] == 981 && ptr<uint32_t>(a_fs)[0] == 0 && ptr<uint32_t>(a_fs)[1] == 1 &&
+                  ptr<double>(a_fo)[0] == 0.0 && ptr<double>(a_fo)[1] == 984.0;
+        CHECK(ok, "frames: session order, 981 samples each, second frame starts at the next multiple of 8");
+        // output o of connection c is sample 3 * o of its 2944-sample buffer: quantum q = 3o / 128, k = 3o % 128
+        for (int c = 0; c < 2 && ok; c++)
+            for (int o = 0; o < 981; o += 140) {
+                const int q = (3 * o) / 128, k = (3 * o) % 128;
+                const float v = x[(size_t)(q * 2 + c) * 128 + k];
+                const int16_t want = (int16_t)std::trunc((double)v * (v < 0 ? 32768.0 : 32767.0));
+                ok = ok && ptr<int16_t>(a_out)[c * 984 + o] == want;
+            }
+        CHECK(ok && ptr<int16_t>(a_out)[2 * 984] == 0x1111, "frame samples are the reference's (pick every 3rd, encode); nothing written past the frames");
+        r = call(env, exports, "aggregatorPush", {h, num(n), a_sess, a_t, a_x, a_fs, a_fs, a_fl, a_fo});
+        CHECK(r == nullptr && env->pending && env->pending->err_class == "TypeError", "aggregatorPush with a wrong array type throws TypeError");
+        call(env, exports, "aggregatorDestroy", {h});
+        CHECK(!env->pending, "aggregatorDestroy");
+        r = call(env, exports, "aggregatorReset", {h, num(0), num(0)});
+        CHECK(env->pending && env->pending->err_class == "TypeError", "a destroyed handle is refused");
+    }
+
     // garbage collection of the pinned buffers, then environment teardown
     pin_in->buffer->finalize(env, pin_in->buffer->data, nullptr);
     pin_out->buffer->finalize(env, pin_out->buffer->data, nullptr);

@@ -190,3 +190,54 @@ def test_keepalive_due_capacity_leaves_state_untouched():
     assert done.tolist() == [0, 0, 0, 0]
     assert L.pcmb200_keepalive_due(2000.0, 4, start.ctypes.data, done.ctypes.data, op.ctypes.data, 2000.0,
                                    due.ctypes.data, 4, C.byref(n)) == 0 and n.value == 4 and done.tolist() == [1] * 4
+
+
+def test_quanta_framing_is_announced_in_the_audio_format_frame():
+    """"framing": "quanta" (raw AudioWorklet quanta, aggregated by the server) needs Float32; anything else is refused."""
+    c = ingest.Connection("q", lambda b: None)
+    assert c.framing == "frames" and c.slot == -1
+    assert c.on_control({"type": "audio_format", "encoding": "f32le", "sample_rate": 48000}) == "audio_format" and c.framing == "frames"
+    assert c.on_control({"type": "audio_format", "encoding": "f32le", "sample_rate": 44100, "framing": "quanta"}) == "audio_format"
+    assert c.framing == "quanta" and c.sample_rate == 44100.0
+    for bad in ({"encoding": "pcm16", "framing": "quanta"}, {"encoding": "f32le", "framing": "pages"}):
+        assert c.on_control({"type": "audio_format", "sample_rate": 48000, **bad}) == "bad_audio_format"
+    assert c.framing == "quanta" and c.protocol_errors == 2
+
+
+def test_quantum_batcher_protocol_slots_and_back_pressure():
+    """QuantumBatcher with a stand-in aggregator: malformed payloads are counted, slots are handed out on the first
+    message and reused after disconnect, a full tick refuses the message (back-pressure), frames go to their connection."""
+    class FakeAgg:
+        def __init__(self):
+            self.free, self.staged, self.cap = [1, 0], [], 4
+        def open(self, now):
+            return self.free.pop() if self.free else -1
+        def release(self, slot):
+            self.free.append(slot)
+        def add(self, slot, samples, now):
+            if len(self.staged) + samples.size // 128 > self.cap:
+                return False
+            self.staged += [(slot, now)] * (samples.size // 128)
+            return True
+        def push(self):
+            out, self.staged = [(s, bytes([s])) for s, _ in self.staged], []
+            return out
+        def close(self):
+            pass
+    got = {k: [] for k in "abc"}
+    conns = {k: ingest.Connection(k, got[k].append) for k in "abc"}
+    for c in conns.values():
+        c.on_control({"type": "audio_format", "encoding": "f32le", "sample_rate": 48000, "framing": "quanta"})
+    qb = ingest.QuantumBatcher(lambda rate: FakeAgg(), tick_ms=20.0)
+    q = np.zeros(128, np.float32).tobytes()
+    assert qb.offer(conns["a"], q[:100], 0.0) and conns["a"].protocol_errors == 1 and not qb.due(100.0)
+    assert qb.offer(conns["a"], q * 2, 1.0) and qb.offer(conns["b"], q, 2.0) and conns["a"].slot == 0 and conns["b"].slot == 1
+    assert qb.offer(conns["c"], q, 3.0) and conns["c"].slot == -1 and qb.stats["no_slot"] == 1      # both slots taken
+    assert not qb.offer(conns["b"], q * 2, 4.0) and qb.stats["blocked"] == 1                          # 3 staged + 2 > 4
+    assert not qb.due(20.9) and qb.due(21.0)
+    assert qb.flush() == 3 and got["a"] == [b"\x00", b"\x00"] and got["b"] == [b"\x01"] and not qb.due(1e9)
+    qb.disconnect(conns["a"])
+    assert qb.offer(conns["c"], q, 30.0) and conns["c"].slot == 0                                     # a's slot, reused
+    conns["b"].closed = True
+    assert qb.offer(conns["b"], q, 31.0) and qb.flush() == 1 and got["c"] == [b"\x00"]
+    qb.close()

@@ -293,11 +293,151 @@ napi_value alloc_pinned(napi_env env, napi_callback_info info, napi_typedarray_t
 napi_value AllocPinnedFloat32(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_float32_array, 4); }
 napi_value AllocPinnedInt16(napi_env env, napi_callback_info info) { return alloc_pinned(env, info, napi_int16_array, 2); }
 
+// ---- the capture aggregator (App.tsx:148-157, :273-288) for many connections, on the GPU ---------------------------
+// aggregatorCreate(maxSessions, rate, maxFrameQuanta, maxPushQuanta, maxOutSamples): number      -> a small handle
+// aggregatorReset(h, slot, nowMs)                              buffer empty, lastSend = nowMs (a new connection)
+// aggregatorPush(h, n, sessions: Uint32Array, timesMs: Float64Array, samples: Float32Array, out: Int16Array,
+//                frameSession: Uint32Array, frameLen: Uint32Array, frameOffset: Float64Array): number of frames
+//                (frame f = out.subarray(frameOffset[f], frameOffset[f] + frameLen[f]) of session frameSession[f])
+// aggregatorDestroy(h)
+constexpr int kMaxAggregators = 16;
+struct AggSlot { pcmb200_aggregator *agg = nullptr; unsigned long long *offsets = nullptr; uint32_t max_push = 0; };
+AggSlot g_aggs[kMaxAggregators];
+
+bool get_ta(napi_env env, napi_value v, napi_typedarray_type want, void **data, size_t *len, const char *what)
+{
+    bool is_ta = false;
+    napi_typedarray_type t;
+    if (napi_is_typedarray(env, v, &is_ta) != napi_ok || !is_ta ||
+        napi_get_typedarray_info(env, v, &t, len, data, nullptr, nullptr) != napi_ok || t != want) {
+        napi_throw_type_error(env, "PCMB200_TYPE", what);
+        return false;
+    }
+    return true;
+}
+
+AggSlot *agg_of(napi_env env, napi_value v)
+{
+    uint32_t h = 0;
+    if (napi_get_value_uint32(env, v, &h) != napi_ok || h >= (uint32_t)kMaxAggregators || !g_aggs[h].agg) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "not an aggregator handle");
+        return nullptr;
+    }
+    return &g_aggs[h];
+}
+
+napi_value AggregatorCreate(napi_env env, napi_callback_info info)
+{
+    size_t argc = 5;
+    napi_value argv[5];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    uint32_t max_sessions = 0, max_frame_quanta = 0, max_push = 0;
+    double rate = 0, max_out = 0;
+    if (argc < 5 || napi_get_value_uint32(env, argv[0], &max_sessions) != napi_ok || napi_get_value_double(env, argv[1], &rate) != napi_ok ||
+        napi_get_value_uint32(env, argv[2], &max_frame_quanta) != napi_ok || napi_get_value_uint32(env, argv[3], &max_push) != napi_ok ||
+        napi_get_value_double(env, argv[4], &max_out) != napi_ok || !(max_out >= 1)) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "aggregatorCreate(maxSessions, rate, maxFrameQuanta, maxPushQuanta, maxOutSamples)");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    int h = 0;
+    while (h < kMaxAggregators && g_aggs[h].agg) h++;
+    if (h == kMaxAggregators) { napi_throw_error(env, "PCMB200_6", "too many aggregators (16)"); return nullptr; }
+    unsigned long long *offs = static_cast<unsigned long long *>(std::malloc(sizeof(unsigned long long) * (max_push ? max_push : 1)));
+    if (!offs) { napi_throw_error(env, "PCMB200_5", "out of host memory"); return nullptr; }
+    pcmb200_aggregator *a = nullptr;
+    // 128-sample quanta and the reference's 60 ms (App.tsx:156)
+    if (throw_status(env, pcmb200_aggregator_create(g_ctx, max_sessions, rate, 128, 60.0, max_frame_quanta, max_push, (size_t)max_out, &a))) {
+        std::free(offs);
+        return nullptr;
+    }
+    g_aggs[h] = AggSlot{a, offs, max_push};
+    napi_value res = nullptr;
+    napi_create_double(env, (double)h, &res);
+    return res;
+}
+
+napi_value AggregatorReset(napi_env env, napi_callback_info info)
+{
+    size_t argc = 3;
+    napi_value argv[3];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    uint32_t slot = 0;
+    double now = 0;
+    AggSlot *s = argc >= 3 ? agg_of(env, argv[0]) : nullptr;
+    if (!s) return nullptr;
+    if (napi_get_value_uint32(env, argv[1], &slot) != napi_ok || napi_get_value_double(env, argv[2], &now) != napi_ok) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "aggregatorReset(handle, slot, nowMs)");
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    throw_status(env, pcmb200_aggregator_reset_session(g_ctx, s->agg, slot, now));
+    return nullptr;
+}
+
+napi_value AggregatorPush(napi_env env, napi_callback_info info)
+{
+    size_t argc = 9;
+    napi_value argv[9];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    AggSlot *s = argc >= 9 ? agg_of(env, argv[0]) : nullptr;
+    if (!s) return nullptr;
+    uint32_t n = 0;
+    void *sess, *times, *samples, *out, *fs, *fl, *fo;
+    size_t n_sess, n_times, n_samples, n_out, n_fs, n_fl, n_fo;
+    if (napi_get_value_uint32(env, argv[1], &n) != napi_ok ||
+        !get_ta(env, argv[2], napi_uint32_array, &sess, &n_sess, "sessions must be a Uint32Array") ||
+        !get_ta(env, argv[3], napi_float64_array, &times, &n_times, "timesMs must be a Float64Array") ||
+        !get_ta(env, argv[4], napi_float32_array, &samples, &n_samples, "samples must be a Float32Array") ||
+        !get_ta(env, argv[5], napi_int16_array, &out, &n_out, "out must be an Int16Array") ||
+        !get_ta(env, argv[6], napi_uint32_array, &fs, &n_fs, "frameSession must be a Uint32Array") ||
+        !get_ta(env, argv[7], napi_uint32_array, &fl, &n_fl, "frameLen must be a Uint32Array") ||
+        !get_ta(env, argv[8], napi_float64_array, &fo, &n_fo, "frameOffset must be a Float64Array"))
+        return nullptr;
+    size_t max_frames = n_fs < n_fl ? n_fs : n_fl;
+    if (n_fo < max_frames) max_frames = n_fo;
+    if (max_frames > s->max_push) max_frames = s->max_push;
+    if (n > n_sess || n > n_times || (size_t)n * 128 > n_samples) {
+        napi_throw_type_error(env, "PCMB200_TYPE", "aggregatorPush: n exceeds sessions / timesMs / samples (128 samples per quantum)");
+        return nullptr;
+    }
+    uint32_t nf = 0;
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    if (throw_status(env, pcmb200_aggregator_push(g_ctx, s->agg, n, static_cast<const uint32_t *>(sess), static_cast<const double *>(times),
+                                                  static_cast<const float *>(samples), PCMB200_MEM_HOST, static_cast<int16_t *>(out), n_out,
+                                                  PCMB200_MEM_HOST, static_cast<uint32_t *>(fs), static_cast<uint32_t *>(fl), s->offsets,
+                                                  (uint32_t)max_frames, &nf)))
+        return nullptr;
+    for (uint32_t f = 0; f < nf; f++) static_cast<double *>(fo)[f] = (double)s->offsets[f];   // sample offsets: far below 2^53
+    napi_value res = nullptr;
+    napi_create_double(env, (double)nf, &res);
+    return res;
+}
+
+napi_value AggregatorDestroy(napi_env env, napi_callback_info info)
+{
+    size_t argc = 1;
+    napi_value argv[1];
+    napi_get_cb_info(env, info, &argc, argv, nullptr, nullptr);
+    AggSlot *s = argc >= 1 ? agg_of(env, argv[0]) : nullptr;
+    if (!s) return nullptr;
+    std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    pcmb200_aggregator_destroy(g_ctx, s->agg);
+    std::free(s->offsets);
+    *s = AggSlot{};
+    return nullptr;
+}
+
 // Environment teardown.  Waits (on the lock) for a conversion that is still running on a worker
 // thread, then destroys the context; jobs that start later see g_ctx == NULL and reject.
 void cleanup(void *)
 {
     std::lock_guard<std::mutex> lock(g_ctx_mutex);
+    for (AggSlot &s : g_aggs) {
+        if (s.agg) pcmb200_aggregator_destroy(g_ctx, s.agg);
+        std::free(s.offsets);
+        s = AggSlot{};
+    }
     pcmb200_ctx_destroy(g_ctx);
     g_ctx = nullptr;
 }
@@ -316,6 +456,10 @@ napi_value Init(napi_env env, napi_value exports)
         {"resampleLen", nullptr, ResampleLen, nullptr, nullptr, nullptr, 0, nullptr},
         {"allocPinnedFloat32", nullptr, AllocPinnedFloat32, nullptr, nullptr, nullptr, 0, nullptr},
         {"allocPinnedInt16", nullptr, AllocPinnedInt16, nullptr, nullptr, nullptr, 0, nullptr},
+        {"aggregatorCreate", nullptr, AggregatorCreate, nullptr, nullptr, nullptr, 0, nullptr},
+        {"aggregatorReset", nullptr, AggregatorReset, nullptr, nullptr, nullptr, 0, nullptr},
+        {"aggregatorPush", nullptr, AggregatorPush, nullptr, nullptr, nullptr, 0, nullptr},
+        {"aggregatorDestroy", nullptr, AggregatorDestroy, nullptr, nullptr, nullptr, 0, nullptr},
     };
     napi_define_properties(env, exports, sizeof props / sizeof props[0], props);
     return exports;

@@ -11,3 +11,11 @@ export function resampleLen(n: number, rate: number): number;
 /** Typed arrays over page-locked host memory (no staging copy on H2D / D2H). */
 export function allocPinnedFloat32(length: number): Float32Array;
 export function allocPinnedInt16(length: number): Int16Array;
+/** The capture aggregator of App.tsx:148-157, :273-288 for many connections on the GPU (128-sample quanta, 60 ms). Returns a handle. */
+export function aggregatorCreate(maxSessions: number, rate: number, maxFrameQuanta: number, maxPushQuanta: number, maxOutSamples: number): number;
+/** Empty buffer, lastSend = nowMs for one session slot (a new connection). */
+export function aggregatorReset(handle: number, slot: number, nowMs: number): void;
+/** One push of n quanta (arrival order). Frame f of the result is out.subarray(frameOffset[f], frameOffset[f] + frameLen[f]) for session frameSession[f]; returns the number of frames. A rejected push (Error code "PCMB200_6": capacity) changes nothing. */
+export function aggregatorPush(handle: number, n: number, sessions: Uint32Array, timesMs: Float64Array, samples: Float32Array, out: Int16Array,
+  frameSession: Uint32Array, frameLen: Uint32Array, frameOffset: Float64Array): number;
+export function aggregatorDestroy(handle: number): void;

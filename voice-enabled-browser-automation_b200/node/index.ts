@@ -14,3 +14,9 @@ export const framesEncodeAsync: (batch: Float32Array, rows: number, nIn: number,
 export const resampleLen: (n: number, rate: number) => number = native.resampleLen;
 export const allocPinnedFloat32: (length: number) => Float32Array = native.allocPinnedFloat32;
 export const allocPinnedInt16: (length: number) => Int16Array = native.allocPinnedInt16;
+export const aggregatorCreate: (maxSessions: number, rate: number, maxFrameQuanta: number, maxPushQuanta: number, maxOutSamples: number) => number =
+  native.aggregatorCreate;
+export const aggregatorReset: (handle: number, slot: number, nowMs: number) => void = native.aggregatorReset;
+export const aggregatorPush: (handle: number, n: number, sessions: Uint32Array, timesMs: Float64Array, samples: Float32Array, out: Int16Array,
+  frameSession: Uint32Array, frameLen: Uint32Array, frameOffset: Float64Array) => number = native.aggregatorPush;
+export const aggregatorDestroy: (handle: number) => void = native.aggregatorDestroy;

@@ -9,10 +9,16 @@
 // sub-protocol is added:
 //     text frame   {"type": "audio_format", "encoding": "f32le", "sample_rate": 48000}
 //     binary frame raw little-endian Float32 samples of ONE flushed capture buffer (App.tsx:281)
+// and, with "framing": "quanta" in the announcement, raw 128-sample AudioWorklet quanta (one or more per message):
+// the SERVER then runs the capture aggregator of App.tsx:148-157, :273-288 for every connection on the GPU
+// (QuantumBatcher below; the arrival time of a message plays performance.now()).
 // With `ws` ^8 a TEXT frame is also delivered as a Buffer, so `Buffer.isBuffer(data)` (server.ts:261) is
 // true for both kinds and the reference's control branch is unreachable: use the `isBinary` flag that
 // `ws` passes as the second argument of the "message" event.
-import { allocPinnedFloat32, allocPinnedInt16, framesEncodeAsync, resampleLen } from "./index";
+import {
+  aggregatorCreate, aggregatorDestroy, aggregatorPush, aggregatorReset, allocPinnedFloat32, allocPinnedInt16, framesEncodeAsync,
+  resampleLen,
+} from "./index";
 
 export type Kind = "audio" | "control" | "ignored";
 export const OVERFLOW_POLICIES = ["drop_oldest", "drop_newest", "block"] as const;
@@ -36,6 +42,8 @@ export class Connection {
   context: Record<string, any> = {};
   closed = false;
   protocolErrors = 0;
+  framing: "frames" | "quanta" = "frames"; // "quanta": raw AudioWorklet quanta, aggregated on the GPU
+  slot = -1; // QuantumBatcher slot
   constructor(
     readonly sessionId: string,
     public sendAudio: (chunk: Buffer | ArrayBuffer | Uint8Array) => void, // DeepgramClient.sendAudio, unchanged
@@ -60,8 +68,14 @@ export class Connection {
         this.protocolErrors += 1;
         return "bad_audio_format";
       }
+      const framing = msg.framing ?? "frames";
+      if ((framing !== "frames" && framing !== "quanta") || (framing === "quanta" && enc !== "f32le")) {
+        this.protocolErrors += 1;
+        return "bad_audio_format";
+      }
       this.encoding = enc;
       this.sampleRate = rate;
+      this.framing = framing;
       return "audio_format";
     }
     return null;
@@ -198,6 +212,163 @@ export class TickBatcher {
       this.stats.flushes += 1;
     }
     return delivered;
+  }
+}
+
+/** One device-side capture aggregator for the connections of ONE capture rate (see pcm_frontend/ingest.py GpuQuantumAggregator). */
+export class GpuQuantumAggregator {
+  private handle: number;
+  private sess: Uint32Array;
+  private time: Float64Array;
+  private x: Float32Array;
+  private out: Int16Array;
+  private fs: Uint32Array;
+  private fl: Uint32Array;
+  private fo: Float64Array;
+  private free: number[] = [];
+  private n = 0;
+  private maxOut: number;
+
+  constructor(readonly rate: number, maxSessions: number, readonly maxPush: number, readonly quantum = 128, maxFrameQuanta = 64) {
+    const nOutMax = resampleLen(maxFrameQuanta * quantum, rate);
+    this.maxOut = Math.min(maxPush * (Math.ceil(nOutMax / 8) * 8), Math.max(1 << 16, 2 * maxPush * quantum));
+    this.handle = aggregatorCreate(maxSessions, rate, maxFrameQuanta, maxPush, this.maxOut);
+    this.sess = new Uint32Array(maxPush);
+    this.time = new Float64Array(maxPush);
+    this.x = allocPinnedFloat32(maxPush * quantum);
+    this.out = allocPinnedInt16(this.maxOut);
+    this.fs = new Uint32Array(maxPush);
+    this.fl = new Uint32Array(maxPush);
+    this.fo = new Float64Array(maxPush);
+    for (let s = maxSessions - 1; s >= 0; s--) this.free.push(s);
+  }
+
+  /** A slot for a new connection: empty buffer, lastSend = now (App.tsx:148-157).  -1 if all are taken. */
+  open(nowMs: number): number {
+    const slot = this.free.pop();
+    if (slot === undefined) return -1;
+    aggregatorReset(this.handle, slot, nowMs);
+    return slot;
+  }
+
+  release(slot: number): void {
+    if (slot >= 0) this.free.push(slot);
+  }
+
+  /** Stage the quanta of one message.  False if the tick is full. */
+  add(slot: number, samples: Float32Array, nowMs: number): boolean {
+    const k = samples.length / this.quantum;
+    if (this.n + k > this.maxPush) return false;
+    this.sess.fill(slot, this.n, this.n + k);
+    this.time.fill(nowMs, this.n, this.n + k);
+    this.x.set(samples, this.n * this.quantum);
+    this.n += k;
+    return true;
+  }
+
+  /** Run the staged quanta through the aggregator: [slot, frame bytes] in flush order (views, valid until the next push). */
+  push(): [number, Buffer][] {
+    const n = this.n;
+    this.n = 0;
+    return n ? this.pushRange(0, n, false) : [];
+  }
+
+  private pushRange(lo: number, hi: number, copy: boolean): [number, Buffer][] {
+    const n = hi - lo;
+    let nf: number;
+    try {
+      nf = aggregatorPush(this.handle, n, this.sess.subarray(lo, hi), this.time.subarray(lo, hi),
+        this.x.subarray(lo * this.quantum, hi * this.quantum), this.out, this.fs, this.fl, this.fo);
+    } catch (e: any) {
+      if (e?.code !== "PCMB200_6" || n < 2) throw e; // 6 = capacity: a tick larger than the output block goes in halves
+      const mid = lo + (n >> 1);
+      return [...this.pushRange(lo, mid, true), ...this.pushRange(mid, hi, true)];
+    }
+    const frames: [number, Buffer][] = [];
+    for (let f = 0; f < nf; f++) {
+      const view = Buffer.from(this.out.buffer, this.out.byteOffset + this.fo[f] * 2, this.fl[f] * 2);
+      frames.push([this.fs[f], copy ? Buffer.from(view) : view]);
+    }
+    return frames;
+  }
+
+  close(): void {
+    aggregatorDestroy(this.handle);
+  }
+}
+
+/** The "framing": "quanta" path (see pcm_frontend/ingest.py QuantumBatcher). */
+export class QuantumBatcher {
+  private aggs = new Map<number, GpuQuantumAggregator>();
+  private conns = new Map<string, Connection>();
+  private oldest: number | null = null;
+  readonly stats = { quanta: 0, blocked: 0, protocol_errors: 0, no_slot: 0, frames: 0, flushes: 0 };
+
+  constructor(private make: (rate: number) => GpuQuantumAggregator, readonly tickMs = 20, readonly quantum = 128) {}
+
+  /** Returns false when the message did not fit the tick (back-pressure: ws.pause() until the next flush). */
+  offer(conn: Connection, payload: Buffer, nowMs: number): boolean {
+    if (conn.closed) return true;
+    const nBytes = payload.length;
+    if (nBytes === 0 || nBytes % (4 * this.quantum) !== 0) {
+      conn.protocolErrors += 1;
+      this.stats.protocol_errors += 1;
+      return true;
+    }
+    let agg = this.aggs.get(conn.sampleRate);
+    if (!agg) this.aggs.set(conn.sampleRate, (agg = this.make(conn.sampleRate)));
+    if (conn.slot < 0) {
+      conn.slot = agg.open(nowMs);
+      if (conn.slot < 0) {
+        this.stats.no_slot += 1;
+        return true;
+      }
+      this.conns.set(`${conn.sampleRate}:${conn.slot}`, conn);
+    }
+    // a Float32Array needs 4-byte alignment; a Buffer from `ws` may sit at any offset of its pool: copy if it does
+    const aligned = payload.byteOffset % 4 === 0 ? payload : Buffer.from(payload);
+    if (!agg.add(conn.slot, new Float32Array(aligned.buffer, aligned.byteOffset, nBytes / 4), nowMs)) {
+      this.stats.blocked += 1;
+      return false;
+    }
+    this.stats.quanta += nBytes / (4 * this.quantum);
+    if (this.oldest === null) this.oldest = nowMs;
+    return true;
+  }
+
+  due(nowMs: number): boolean {
+    return this.oldest !== null && nowMs - this.oldest >= this.tickMs;
+  }
+
+  flush(): number {
+    let delivered = 0;
+    for (const [rate, agg] of this.aggs) {
+      for (const [slot, view] of agg.push()) {
+        const conn = this.conns.get(`${rate}:${slot}`);
+        if (conn && !conn.closed) {
+          conn.sendAudio(view);
+          delivered += 1;
+        }
+      }
+    }
+    this.oldest = null;
+    this.stats.frames += delivered;
+    this.stats.flushes += 1;
+    return delivered;
+  }
+
+  /** The socket closed: its slot can serve another connection. */
+  disconnect(conn: Connection): void {
+    if (conn.slot >= 0) {
+      this.conns.delete(`${conn.sampleRate}:${conn.slot}`);
+      this.aggs.get(conn.sampleRate)?.release(conn.slot);
+      conn.slot = -1;
+    }
+  }
+
+  close(): void {
+    for (const agg of this.aggs.values()) agg.close();
+    this.aggs.clear();
   }
 }
 

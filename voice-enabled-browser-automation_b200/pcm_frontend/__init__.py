@@ -40,13 +40,15 @@ from .api import (  # noqa: F401
 from .ingest import (  # noqa: F401,E402
     Connection,
     GpuGroupConverter,
+    GpuQuantumAggregator,
+    QuantumBatcher,
     KeepAliveScheduler,
     TickBatcher,
     classify_message,
 )
 
 __all__ = [
-    "Connection", "GpuGroupConverter", "KeepAliveScheduler", "TickBatcher", "classify_message",
+    "Connection", "GpuGroupConverter", "GpuQuantumAggregator", "QuantumBatcher", "KeepAliveScheduler", "TickBatcher", "classify_message",
     "Aggregator", "Context", "DeviceBuffer", "PinnedBuffer", "TickGraph", "PcmError", "PcmRangeError", "MEM_HOST", "MEM_DEVICE",
     "floatTo16BitPCM", "resampleTo16k", "frames_encode", "resample_len", "index_table", "keepalive_frame",
     "shard_sessions", "default_context", "load", "lib_path", "SYMBOLS",

@@ -10,6 +10,11 @@ module keeps that behaviour for clients that still send PCM16 and adds a Float32
     binary frame raw little-endian Float32 samples of ONE flushed capture buffer
                  (what the browser would have passed to resampleTo16k, App.tsx:281)
 
+and, with "framing": "quanta" in the announcement, a thinner client still: it forwards the AudioWorklet's
+128-sample quanta as they come (one or more per message) and the SERVER runs the capture aggregator of
+App.tsx:148-157, :273-288 for every connection on the GPU (QuantumBatcher below: the arrival time of a message
+plays performance.now(), frames come out when `elapsed >= desiredMs`, exactly as in the browser).
+
 Telling the two kinds of frame apart: with `ws` ^8 (apps/voice/package.json:19) a TEXT frame is also
 delivered as a Buffer, so the reference's `Buffer.isBuffer(data)` test (server.ts:261) is true for both
 and its control branch is unreachable; the glue must use the `isBinary` flag that `ws` passes as the
@@ -59,6 +64,8 @@ class Connection:
     context: Dict[str, Any] = field(default_factory=dict)
     closed: bool = False
     protocol_errors: int = 0
+    framing: str = "frames"                           # "frames": one flushed capture buffer per message; "quanta": raw
+    slot: int = -1                                    #   AudioWorklet quanta, aggregated on the GPU (QuantumBatcher slot)
 
     def on_control(self, msg: dict) -> Optional[str]:
         """server.ts:267-280 ("close", "context_update") + the audio_format announcement.
@@ -77,7 +84,11 @@ class Connection:
             if enc not in ("f32le", "pcm16") or not isinstance(rate, (int, float)) or isinstance(rate, bool) or not rate > 0:
                 self.protocol_errors += 1
                 return "bad_audio_format"
-            self.encoding, self.sample_rate = enc, float(rate)
+            framing = msg.get("framing", "frames")
+            if framing not in ("frames", "quanta") or (framing == "quanta" and enc != "f32le"):
+                self.protocol_errors += 1
+                return "bad_audio_format"
+            self.encoding, self.sample_rate, self.framing = enc, float(rate), framing
             return "audio_format"
         return None
 
@@ -240,6 +251,160 @@ class GpuGroupConverter:
             if b is not None:
                 b.free()
         self._in = self._out = None
+
+
+class GpuQuantumAggregator:
+    """One device-side capture aggregator (pcmb200_aggregator_*) for the connections of ONE capture rate, with
+    pinned staging for a tick's quanta and a pinned output block: push() is one H2D of the tick's quanta, the
+    planned push on the GPU, one D2H of the flushed frames; every frame is handed out as a view (no copy)."""
+
+    def __init__(self, ctx, rate: float, max_sessions: int, max_push_quanta: int, quantum: int = 128, desired_ms: float = 60.0,
+                 max_frame_quanta: int = 64):
+        from .api import Aggregator, resample_len
+        self.ctx, self.rate, self.quantum, self.max_push = ctx, float(rate), int(quantum), int(max_push_quanta)
+        n_out_max = resample_len(max_frame_quanta * quantum, rate)
+        self.max_out = int(max_push_quanta) * ((n_out_max + 7) // 8 * 8)         # worst case: every quantum flushes a frame
+        self.max_out = min(self.max_out, max(1 << 16, 2 * max_push_quanta * quantum))
+        self.agg = Aggregator(ctx, max_sessions, rate, quantum=quantum, desired_ms=desired_ms, max_frame_quanta=max_frame_quanta,
+                              max_push_quanta=max_push_quanta, max_out_samples=self.max_out)
+        self._sess, self._time = ctx.pinned(max_push_quanta, np.uint32), ctx.pinned(max_push_quanta, np.float64)
+        self._x = ctx.pinned((max_push_quanta, quantum), np.float32)
+        self._out = ctx.pinned(self.max_out, np.int16)
+        self._fs, self._fl = np.empty(max_push_quanta, np.uint32), np.empty(max_push_quanta, np.uint32)
+        self._fo = np.empty(max_push_quanta, np.uint64)
+        self._free = list(range(max_sessions - 1, -1, -1))
+        self.n = 0
+
+    def open(self, now_ms: float) -> int:
+        """A slot for a new connection: empty buffer, lastSend = now (App.tsx:148-157).  -1 if all are taken."""
+        if not self._free:
+            return -1
+        slot = self._free.pop()
+        self.agg.reset_session(slot, now_ms)
+        return slot
+
+    def release(self, slot: int):
+        if slot >= 0:
+            self._free.append(slot)
+
+    def add(self, slot: int, samples: np.ndarray, now_ms: float) -> bool:
+        """Stage the quanta of one message (samples.size is a multiple of the quantum).  False if the tick is full."""
+        k = samples.size // self.quantum
+        if self.n + k > self.max_push:
+            return False
+        self._sess.array[self.n:self.n + k] = slot
+        self._time.array[self.n:self.n + k] = now_ms
+        self._x.array[self.n:self.n + k] = samples.reshape(k, self.quantum)
+        self.n += k
+        return True
+
+    def push(self):
+        """Run the staged quanta through the aggregator.  Returns [(slot, frame bytes)] in flush order; normally the
+        frames are views into the pinned output block, valid until the next push.  The block is sized for real-time
+        traffic, not for the worst case (every quantum of the tick completing a full-length frame); a tick that
+        overflows it is rejected by the library with nothing changed, and is then pushed in halves, in order."""
+        n, self.n = self.n, 0
+        return self._push_range(0, n, copy=False) if n else []
+
+    def _push_range(self, lo: int, hi: int, copy: bool):
+        from ._capi import ERR_CAPACITY, MEM_HOST, PcmError
+        n = hi - lo
+        nf = C.c_uint32(0)
+        try:
+            check(load().pcmb200_aggregator_push(self.ctx.handle, self.agg.handle, n, self._sess.ptr + 4 * lo, self._time.ptr + 8 * lo,
+                                                 self._x.ptr + 4 * self.quantum * lo, MEM_HOST, self._out.ptr, self.max_out, MEM_HOST,
+                                                 self._fs.ctypes.data, self._fl.ctypes.data, self._fo.ctypes.data, self._fs.size,
+                                                 C.byref(nf)), self.ctx.handle)
+        except PcmError as e:
+            if e.status != ERR_CAPACITY or n < 2:
+                raise
+            mid = lo + n // 2
+            return self._push_range(lo, mid, copy=True) + self._push_range(mid, hi, copy=True)
+        if nf.value == 0:
+            return []
+        off, ln = np.empty(nf.value, np.uint64), np.empty(nf.value, np.uint32)
+        check(load().pcmb200_egress_table_frames(nf.value, self._fo.ctypes.data, self._fl.ctypes.data, off.ctypes.data, ln.ctypes.data),
+              self.ctx.handle)
+        block = memoryview((C.c_char * (self.max_out * 2)).from_address(self._out.ptr)).cast("B")
+        views = [(int(self._fs[f]), block[int(off[f]): int(off[f]) + int(ln[f])]) for f in range(nf.value)]
+        return [(s, bytes(v)) for s, v in views] if copy else views
+
+    def close(self):
+        self.agg.close()
+        for b in (self._sess, self._time, self._x, self._out):
+            b.free()
+
+
+class QuantumBatcher:
+    """The "framing": "quanta" path: connections forward raw AudioWorklet quanta, the server aggregates.
+
+    offer()  one binary message (k * quantum Float32 samples) of a quanta-framed connection; the connection gets an
+             aggregator slot on its first message (lastSend = that moment, as the browser sets it at start);
+    flush()  one aggregator push per capture rate; every frame that flushed goes to its connection's send_audio as a
+             view of its raw little-endian int16 bytes (frames of one connection in flush order).
+    Bounded by max_push_quanta per rate and tick; a message that does not fit is refused (offer() returns False:
+    back-pressure, as TickBatcher's "block" policy).  make_aggregator(rate) builds a GpuQuantumAggregator."""
+
+    def __init__(self, make_aggregator: Callable[[float], "GpuQuantumAggregator"], tick_ms: float = 20.0, quantum: int = 128):
+        self.make, self.tick_ms, self.quantum = make_aggregator, float(tick_ms), int(quantum)
+        self._aggs: Dict[float, GpuQuantumAggregator] = {}
+        self._conns: Dict[Tuple[float, int], Connection] = {}
+        self._oldest: Optional[float] = None
+        self.stats = {"quanta": 0, "blocked": 0, "protocol_errors": 0, "no_slot": 0, "frames": 0, "flushes": 0}
+
+    def offer(self, conn: Connection, payload: Any, now_ms: float) -> bool:
+        if conn.closed:
+            return True
+        n_bytes = len(payload)
+        if n_bytes == 0 or n_bytes % (4 * self.quantum) != 0:
+            conn.protocol_errors += 1
+            self.stats["protocol_errors"] += 1
+            return True
+        agg = self._aggs.get(conn.sample_rate)
+        if agg is None:
+            agg = self._aggs[conn.sample_rate] = self.make(conn.sample_rate)
+        if conn.slot < 0:
+            conn.slot = agg.open(now_ms)
+            if conn.slot < 0:
+                self.stats["no_slot"] += 1
+                return True
+            self._conns[(conn.sample_rate, conn.slot)] = conn
+        if not agg.add(conn.slot, np.frombuffer(payload, dtype="<f4"), float(now_ms)):
+            self.stats["blocked"] += 1
+            return False
+        self.stats["quanta"] += n_bytes // (4 * self.quantum)
+        if self._oldest is None:
+            self._oldest = float(now_ms)
+        return True
+
+    def due(self, now_ms: float) -> bool:
+        return self._oldest is not None and now_ms - self._oldest >= self.tick_ms
+
+    def flush(self) -> int:
+        delivered = 0
+        for rate, agg in self._aggs.items():
+            for slot, view in agg.push():
+                conn = self._conns.get((rate, slot))
+                if conn is not None and not conn.closed:
+                    conn.send_audio(view)
+                    delivered += 1
+        self._oldest = None
+        self.stats["frames"] += delivered
+        self.stats["flushes"] += 1
+        return delivered
+
+    def disconnect(self, conn: Connection):
+        """The socket closed: its slot can serve another connection (whatever it had buffered is dropped, as the
+        browser drops agg.buf when the page goes away)."""
+        if conn.slot >= 0:
+            self._conns.pop((conn.sample_rate, conn.slot), None)
+            self._aggs[conn.sample_rate].release(conn.slot)
+            conn.slot = -1
+
+    def close(self):
+        for agg in self._aggs.values():
+            agg.close()
+        self._aggs.clear()
 
 
 class KeepAliveScheduler:
