@@ -313,6 +313,66 @@ def aggregator_streaming(ctx, S=65536, rate=48000, meter=False, pushes=92):
             "note": "real-time capacity = sessions x (audio time per push / wall time per push)"}
 
 
+def quanta_ingest(ctx, S=65536, rate=48000, tick_ms=20.0, ticks=12):
+    """next-2 + next-4 end to end from host memory: S connections with "framing": "quanta"; every tick the quanta that
+    arrived in tick_ms (pinned staging, as GpuQuantumAggregator fills it) go through ONE aggregator push -- H2D of ids,
+    times and samples, the planned push on the GPU, D2H of the frames that flushed -- and come back as views.  Timed:
+    push() alone (staging is the socket layer's copy).  Frames of the last tick are checked against the oracle."""
+    from pcm_frontend.ingest import GpuQuantumAggregator
+    q_ms = 128e3 / rate
+    per_tick = int(round(tick_ms / q_ms))                                   # quanta per connection per tick
+    n = S * per_tick
+    g = GpuQuantumAggregator(ctx, float(rate), max_sessions=S, max_push_quanta=n, max_frame_quanta=32)
+    for _ in range(S):
+        g.open(0.0)
+    rng = np.random.RandomState(7)
+    x = rng.uniform(-1, 1, size=(ticks * per_tick, 1024, 128)).astype(np.float32)    # audio: 1024 patterns, tiled over S
+    sess = np.tile(np.arange(S, dtype=np.uint32), per_tick)
+    times, calls, frames_last, hist = [], [], None, {}
+    for t in range(ticks):
+        q0 = t * per_tick
+        g._sess.array[:n] = sess
+        g._time.array[:n] = np.repeat((np.arange(q0, q0 + per_tick) + 1) * q_ms, S)
+        for k in range(per_tick):
+            g._x.array[k * S:(k + 1) * S] = np.tile(x[q0 + k], (S // 1024, 1))
+        g.n = n
+        ctx.sync()
+        t0 = time.perf_counter()
+        frames_last = g.push()
+        times.append(time.perf_counter() - t0)
+        calls.append(g.last_call_s)
+        hist[t] = len(frames_last)
+    # the last flushing tick against the oracle: every connection s holds pattern s % 1024
+    flush, _ = oracle.aggregator_plan((np.arange(ticks * per_tick) + 1) * q_ms, 60.0, 0.0)
+    ends = np.nonzero(flush)[0]
+    checked = 0
+    if frames_last:
+        last_end = ends[ends < ticks * per_tick][-1]
+        start = ends[ends < last_end][-1] + 1 if (ends < last_end).any() else 0
+        for slot, b in frames_last[:4096]:
+            buf = x[start:last_end + 1, slot % 1024].reshape(1, -1)
+            assert np.array_equal(np.frombuffer(bytes(b), dtype="<i2"), oracle.frames(buf, buf.shape[1], rate)[0]), slot
+            checked += 1
+    flushing = [c for c, k in zip(calls, hist.values()) if k][1:] or [0.0]
+    quiet = [c for c, k in zip(calls, hist.values()) if not k][1:] or [0.0]
+    med = (sum(sorted(quiet)[len(quiet) // 2:len(quiet) // 2 + 1]) * 2 + sorted(flushing)[len(flushing) // 2]) / 3   # 2 quiet ticks per flushing one
+    h2d_bytes = n * (128 * 4 + 4 + 8)
+    dev = ctx.device_buffer(n * 512)
+    bare = timed(ctx, lambda: ctx.memcpy_h2d(dev.ptr, g._x.ptr, n * 512), 5, warm=1)     # the same pinned block, copy alone
+    dev.free()
+    g.close()
+    return {"config": "next-2 + next-4: quanta-framed ingest from pinned host memory, one aggregator push per tick",
+            "sessions": S, "tick_ms": tick_ms, "quanta_per_tick": n, "h2d_mb_per_tick": h2d_bytes / 2**20,
+            "ms_per_quiet_tick": sorted(quiet)[len(quiet) // 2] * 1e3, "ms_per_flushing_tick": sorted(flushing)[len(flushing) // 2] * 1e3,
+            "ms_per_tick_mean": med * 1e3, "bare_h2d_of_the_samples_ms": bare, "h2d_gbs": h2d_bytes / med / 1e9,
+            "in_samples_per_s": n * 128 / med, "realtime_sessions_at_48k": n * 128 / med / rate,
+            "fraction_of_a_tick": med * 1e3 / tick_ms, "python_push_ms_median_incl_views": sorted(times[2:])[len(times[2:]) // 2] * 1e3,
+            "frames_per_tick": hist, "frames_checked_against_oracle": checked,
+            "note": "times are the library call alone (pcmb200_aggregator_push with pinned host arrays: three H2D copies, the "
+                    "planned push, D2H of the frame arrays and frames); building 65 536 Python memoryviews on a flushing tick "
+                    "costs more than the call and is reported separately"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
@@ -324,6 +384,7 @@ def main():
     ap.add_argument("--agg-once", action="store_true", help="the aggregator benchmark alone (for ncu)")
     ap.add_argument("--sweep-agg", action="store_true", help="sweep the aggregator convert kernel's CTA size and step size")
     ap.add_argument("--sweep-meter", action="store_true")
+    ap.add_argument("--quanta-ingest", action="store_true", help="the quanta-framed host-ingest benchmark alone")
     ap.add_argument("--agg-stream", type=int, default=0, help="the streaming-regime aggregator benchmark alone with this many sessions (for ncu)")
     ap.add_argument("--agg-order", default="", help="diagnostic: run the big-push aggregator benchmark alone with this push order (quantum | session)")
     args = ap.parse_args()
@@ -336,6 +397,9 @@ def main():
                 for m in (False, True):
                     r = aggregator(ctx, meter=m)
                     print(json.dumps(dict(agg_block=blk, agg_stage_kb=kb, meter=m, total_ms=round(r["total_ms"], 4))), flush=True)
+        return
+    if args.quanta_ingest:
+        print(json.dumps(quanta_ingest(ctx)), flush=True)
         return
     if args.agg_stream:
         print(json.dumps(aggregator_streaming(ctx, S=args.agg_stream, pushes=46)), flush=True)
@@ -376,7 +440,7 @@ def main():
         for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: aggregator_streaming(ctx, S=1 << 20, pushes=69), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: aggregator_streaming(ctx, S=1 << 20, pushes=69), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx), lambda: quanta_ingest(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)

@@ -274,6 +274,7 @@ class GpuQuantumAggregator:
         self._fo = np.empty(max_push_quanta, np.uint64)
         self._free = list(range(max_sessions - 1, -1, -1))
         self.n = 0
+        self.last_call_s = 0.0
 
     def open(self, now_ms: float) -> int:
         """A slot for a new connection: empty buffer, lastSend = now (App.tsx:148-157).  -1 if all are taken."""
@@ -308,8 +309,10 @@ class GpuQuantumAggregator:
 
     def _push_range(self, lo: int, hi: int, copy: bool):
         from ._capi import ERR_CAPACITY, MEM_HOST, PcmError
+        import time
         n = hi - lo
         nf = C.c_uint32(0)
+        t0 = time.perf_counter()
         try:
             check(load().pcmb200_aggregator_push(self.ctx.handle, self.agg.handle, n, self._sess.ptr + 4 * lo, self._time.ptr + 8 * lo,
                                                  self._x.ptr + 4 * self.quantum * lo, MEM_HOST, self._out.ptr, self.max_out, MEM_HOST,
@@ -320,13 +323,14 @@ class GpuQuantumAggregator:
                 raise
             mid = lo + n // 2
             return self._push_range(lo, mid, copy=True) + self._push_range(mid, hi, copy=True)
+        self.last_call_s = time.perf_counter() - t0                   # the library call alone (copies + kernels), for benchmarks
         if nf.value == 0:
             return []
         off, ln = np.empty(nf.value, np.uint64), np.empty(nf.value, np.uint32)
         check(load().pcmb200_egress_table_frames(nf.value, self._fo.ctypes.data, self._fl.ctypes.data, off.ctypes.data, ln.ctypes.data),
               self.ctx.handle)
         block = memoryview((C.c_char * (self.max_out * 2)).from_address(self._out.ptr)).cast("B")
-        views = [(int(self._fs[f]), block[int(off[f]): int(off[f]) + int(ln[f])]) for f in range(nf.value)]
+        views = [(s, block[o: o + k]) for s, o, k in zip(self._fs[:nf.value].tolist(), off.tolist(), ln.tolist())]
         return [(s, bytes(v)) for s, v in views] if copy else views
 
     def close(self):
