@@ -352,3 +352,42 @@ def test_aggregator_every_kernel_form(ctx, knobs, rate):
             want_lv = oracle.level_meter(audio[s, :start].reshape(-1))[-1]
             assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
     assert n_frames >= S
+
+
+@pytest.mark.parametrize("quantum, max_q", [(64, 64), (64, 96), (256, 16), (32, 128), (512, 8)])
+def test_aggregator_other_quantum_sizes(ctx, quantum, max_q):
+    """The AudioWorklet render quantum is 128 today, but nothing in App.tsx:264-289 depends on it: the handler appends
+    whatever e.data holds.  Quanta of 32 ... 512 samples take the generic copy loops of every aggregator kernel
+    (the 128-sample case has its own); frames and levels against the oracle, the meter on."""
+    rate = 48000
+    rng = np.random.RandomState(quantum + max_q)
+    S, q_ms = 61, quantum * 1e3 / rate
+    nq = int(260 / q_ms)
+    audio = (rng.uniform(-1.05, 1.05, size=(S, nq, quantum)) * rng.uniform(0.1, 1, size=(S, 1, 1))).astype(np.float32)
+    times = 3.0 * rng.rand(S, 1) + np.cumsum(q_ms + rng.uniform(-0.1, 0.1, size=(S, nq)) * min(q_ms, 1.0), axis=1)
+    events = sorted((times[s, q], s, q) for s in range(S) for q in range(nq))
+    agg = pcm_frontend.Aggregator(ctx, S, rate, quantum=quantum, max_frame_quanta=max_q, max_push_quanta=4096, max_out_samples=1 << 18)
+    agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
+    got = {s: [] for s in range(S)}
+    i, k, sizes = 0, 0, [S * 11, 5, S * 30, 97, 4096]
+    while i < len(events):
+        chunk = events[i:i + sizes[k % len(sizes)]]
+        i += len(chunk); k += 1
+        for s, pcm in agg.push(np.array([e[1] for e in chunk]), np.array([e[0] for e in chunk]),
+                               np.stack([audio[e[1], e[2]] for e in chunk])):
+            got[s].append(pcm)
+    levels = agg.levels(0, S)
+    agg.close()
+    for s in range(S):
+        flush, _ = oracle.aggregator_plan(times[s], 60.0, 0.0)
+        want, start = [], 0
+        for q in np.nonzero(flush)[0]:
+            buf = audio[s, start:q + 1].reshape(1, -1)
+            want.append(oracle.frames(buf, buf.shape[1], rate)[0])
+            start = q + 1
+        assert len(got[s]) == len(want) >= 3, (s, len(got[s]), len(want))
+        for a, b in zip(got[s], want):
+            assert a.size == b.size and np.array_equal(a, b), s
+        want_lv = oracle.level_meter(audio[s, :start].reshape(-1), quantum)[-1]
+        assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
