@@ -386,6 +386,7 @@ def main():
     ap.add_argument("--sweep-meter", action="store_true")
     ap.add_argument("--quanta-ingest", action="store_true", help="the quanta-framed host-ingest benchmark alone")
     ap.add_argument("--agg-stream", type=int, default=0, help="the streaming-regime aggregator benchmark alone with this many sessions (for ncu)")
+    ap.add_argument("--agg-meter", action="store_true", help="with --agg-order: the meter on")
     ap.add_argument("--agg-order", default="", help="diagnostic: run the big-push aggregator benchmark alone with this push order (quantum | session)")
     args = ap.parse_args()
     if args.tune:
@@ -405,7 +406,7 @@ def main():
         print(json.dumps(aggregator_streaming(ctx, S=args.agg_stream, pushes=46)), flush=True)
         return
     if args.agg_order:
-        print(json.dumps(aggregator(ctx, order=args.agg_order)), flush=True)
+        print(json.dumps(aggregator(ctx, order=args.agg_order, meter=args.agg_meter)), flush=True)
         return
     if args.agg_once:
         print(json.dumps(aggregator(ctx)), flush=True)

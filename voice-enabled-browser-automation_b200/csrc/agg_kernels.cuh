@@ -664,7 +664,7 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
                 while (k + 1u < nf && sl >= m.qstart[k + 1u]) k++;
                 const uint32_t j = sl - m.qstart[k];
                 if (j < m.fd[k].ring_count) continue;
-                a.rms_at[m.fd[k].pos + (j - m.fd[k].ring_count)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+                a.rms_at[m.fd[k].pos + (j - m.fd[k].ring_count)] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
             }
         }
         if (!more) break;
@@ -827,7 +827,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
             // that the chains do not always land on the same scheduler.
             const uint32_t m_warps = (nq + 31u) >> 5;
             auto meter = [&](uint32_t sl) {
-                if (sl < nq && sl >= rc) a.rms_at[cur.d.pos + (sl - rc)] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
+                if (sl < nq && sl >= rc) a.rms_at[cur.d.pos + (sl - rc)] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)sl * pitch), Q);
             };
             if (m_warps < nw) {
                 const uint32_t wrel = (warp + nw - (it * m_warps) % nw) % nw;
@@ -987,7 +987,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         cp_async_wait_all();
         __syncthreads();
         if (slot != 0xFFFFFFFFu) {                        // threads 0..63: the meter of slot t
-            ring_rms[slot] = quantum_rms(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
+            ring_rms[slot] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
         }
         // copy out: warps 2..7 start at once, warps 0 and 1 join when their meter lanes are done
         for (uint32_t t = (warp + 6u) & 7u; t < TILE; t += 8u) {

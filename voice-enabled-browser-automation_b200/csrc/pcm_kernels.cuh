@@ -427,6 +427,33 @@ __device__ __forceinline__ double quantum_rms(const float4 *src4, uint32_t Q)
     return rms_of(sum, Q);
 }
 
+// The same quantity with the hardware conversion (F2F.F64.F32, exact for every float32: no escape hatches, 2 instead
+// of 6 instructions per sample).  The conversion runs on the XU pipe (16 lanes/clk/SM), which kernels 2b-2d cannot
+// afford -- there every sample of a batch that streams at HBM speed passes through it -- but the aggregator's kernels
+// meter with ONE warp per frame while the copies are what bounds them: ncu showed their issue slots, not the XU pipe,
+// as the cost of the integer widening (6 of every 6 instructions in that warp, the other warps waiting for it).
+// Measured in kernel 2d as well: all samples this way 0.97 / 1.02 of peak (2944- / 960-sample frames) against 0.95 /
+// 1.03 with the integer form, and a mix of the two gains nothing once the converted samples are watched for the
+// tiny-value hazard too (which the zero pollution of the integer form makes necessary) -- so 2d keeps the integer form.
+__device__ __forceinline__ double quantum_rms_cvt(const float4 *src4, uint32_t Q)
+{
+    double sum = 0.0;
+    auto four = [&](const float4 v) {
+        const double a = (double)v.x, b = (double)v.y, c = (double)v.z, d = (double)v.w;
+        sum = __fma_rn(a, a, sum);
+        sum = __fma_rn(b, b, sum);
+        sum = __fma_rn(c, c, sum);
+        sum = __fma_rn(d, d, sum);
+    };
+    if (Q == 128u) {
+#pragma unroll 8
+        for (uint32_t g = 0; g < 32u; g++) four(src4[g]);
+    } else {
+        for (uint32_t g = 0; g < (Q >> 2); g++) four(src4[g]);
+    }
+    return rms_of(sum, Q);
+}
+
 // One step of App.tsx:271, level = Math.max(rms, level * 0.85): NaN if either side is NaN, and a NaN
 // level stays NaN.  NaN-ness is tracked with integer tests so a step costs one DMUL and one DSETP on
 // the long-latency FP64 pipe.
