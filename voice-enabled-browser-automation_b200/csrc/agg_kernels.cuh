@@ -722,6 +722,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         return fr;
     };
     const uint32_t stride_f = gridDim.x;
+    __shared__ const float *ptab[4][64];                                       // per warp: where each slot's quantum comes from
     Frame cur = fetch_list(fetch_desc(f));
     Desc nxt_d = cur.d;                                                        // descriptor of the frame after `cur`
     if (f + stride_f < n_frames) nxt_d = fetch_desc(f + stride_f);
@@ -739,15 +740,17 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         // ---- all quanta of the frame in flight at once: one warp-wide 16-byte-per-lane copy per 512-byte quantum.
         // Four slots per trip, addresses first and the four copies back to back (the compiler pads every isolated
         // LDGSTS with three dummy instructions; 32 instructions per quantum in the one-at-a-time form, per ncu).
+        // Every warp parks its copy of the 64 source addresses in its own corner of shared memory (no block barrier:
+        // the table is private to the warp) and reads them back with warp-uniform, i.e. broadcast, loads: shuffling
+        // 64-bit addresses cost 20 instructions per quantum (two shuffles, two selects, a divergence guard ...), ncu.
+        ptab[warp][lane] = src0;
+        ptab[warp][lane + 32u] = src1;
+        __syncwarp();
         if (gpq == 32u) {
             for (uint32_t s0 = warp; s0 < nq; s0 += 4u * nw) {
                 const float *src[4];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const uint32_t sl = s0 + (uint32_t)u * nw;                    // warp-uniform
-                    const unsigned long long p = (unsigned long long)(sl < 32u ? src0 : src1);
-                    src[u] = reinterpret_cast<const float *>(__shfl_sync(0xFFFFFFFFu, p, sl & 31u)) + 4u * lane;
-                }
+                for (int u = 0; u < 4; u++) src[u] = ptab[warp][min(s0 + (uint32_t)u * nw, 63u)] + 4u * lane;
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
                     const uint32_t sl = s0 + (uint32_t)u * nw;
@@ -756,12 +759,12 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
             }
         } else {
             for (uint32_t sl = warp; sl < nq; sl += nw) {
-                const unsigned long long p = (unsigned long long)(sl < 32u ? src0 : src1);
-                const float *src = reinterpret_cast<const float *>(__shfl_sync(0xFFFFFFFFu, p, sl & 31u));
+                const float *src = ptab[warp][sl];
 #pragma unroll 1
                 for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(arena + (size_t)sl * pitch + 4u * gi, src + 4u * gi);
             }
         }
+        __syncwarp();                                      // the next trip rewrites the table
         asm volatile("cp.async.commit_group;" ::: "memory");
         // the frame after this one: its descriptor is here already (fetched a trip ago), so its index list can be asked
         // for now; and the descriptor of the frame after that.  Both land while this frame's copies are in flight.
