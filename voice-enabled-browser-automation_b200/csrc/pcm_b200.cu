@@ -72,6 +72,7 @@ struct Tuning {
     int ws_depth = 1;        // ... stages per pair (measured: more pairs beat deeper pairs) ...
     int ws_chunk = 4;        // ... quanta per bulk copy (0 = one copy per row) ...
     int ws_rows = 0;         // ... and a cap on the rows per stage (0 = as many as fill one warp with quanta)
+    int ws_cvt_quanta = 16;  // kernel 2d: frames of at least this many quanta meter with the hardware float->double conversion (0 = never)
     size_t slice_bytes = 32u << 20;
 };
 
@@ -530,17 +531,22 @@ bool launch_frames_meter_ws(pcmb200_ctx *ctx, cudaStream_t st, const float *in, 
         for (; k < 32; k++) geo.lane_q[k] = 0;
     }
     const unsigned long long n_tiles = ((unsigned long long)rows + Ks - 1) / Ks;
-    static size_t granted[64] = {0};
+    // long frames (>= ws_cvt_quanta quanta each) leave meter lanes idle: those meter with the hardware conversion
+    const bool cvt = ctx->tune.ws_cvt_quanta > 0 && meter.nq >= (uint32_t)ctx->tune.ws_cvt_quanta;
+    static size_t granted[64][2] = {{0}};
     const int dev = ctx->device & 63;
-    if (smem > granted[dev]) {
-        if (cudaFuncSetAttribute(k_frames_meter_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+    if (smem > granted[dev][cvt]) {
+        const cudaError_t e = cvt ? cudaFuncSetAttribute(k_frames_meter_ws<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                                  : cudaFuncSetAttribute(k_frames_meter_ws<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) {
             cudaGetLastError();
             return false;
         }
-        granted[dev] = smem;
+        granted[dev][cvt] = smem;
     }
     const int grid = (int)(n_tiles < (unsigned long long)ctx->sm_count ? n_tiles : (unsigned long long)ctx->sm_count);
-    k_frames_meter_ws<<<grid, 64 * pairs, smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
+    if (cvt) k_frames_meter_ws<true><<<grid, 64 * pairs, smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
+    else k_frames_meter_ws<false><<<grid, 64 * pairs, smem, st>>>(in, out, geo, n_tiles, lut, ctx->tune.store_hint, meter);
     if (cudaGetLastError() != cudaSuccess) return false;
     ctx->launches++;
     return true;
@@ -1273,6 +1279,9 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "ws_rows") {
         NEED(value >= 0 && value <= 32, "pcmb200_tune: ws_rows must be in [0, 32]");
         ctx->tune.ws_rows = (int)value;
+    } else if (k == "ws_cvt_quanta") {
+        NEED(value >= 0 && value <= 1024, "pcmb200_tune: ws_cvt_quanta must be in [0, 1024]");
+        ctx->tune.ws_cvt_quanta = (int)value;
     } else if (k == "ws_smem_kb") {
         NEED(value >= 16 && value <= 220, "pcmb200_tune: ws_smem_kb must be in [16, 220]");
         ctx->tune.ws_smem_kb = (int)value;

@@ -934,6 +934,11 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+// CVT: the meter lanes widen with the hardware conversion (quantum_rms_cvt) instead of the integer re-packing.  It
+// pays when frames leave meter lanes idle (23 quanta in a 32-lane warp: the kernel is then bound by that warp's issue
+// slots, 0.95 -> 0.97 of peak at 2944-sample frames) and costs when all lanes are busy (960-sample frames: the XU pipe
+// becomes the limit, 1.03 -> 1.02); the launcher picks by frame length.
+template <bool CVT>
 __global__ void __launch_bounds__(1024, 1)
 k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeom geo, unsigned long long n_tiles,
                   const uint32_t *__restrict__ lut, int hint, MeterArgs meter)
@@ -1094,8 +1099,10 @@ k_frames_meter_ws(const float *__restrict__ in, int16_t *__restrict__ out, WsGeo
         if (lane < Ks * nq) {
             const uint32_t kq = div_magic(lane, geo.magic_Ks), r = lane - kq * Ks, q = geo.lane_q[kq];
             const uint32_t i0 = q * Q;
-            if (r < nr)
-                rms_s[r * nq + q] = quantum_rms(reinterpret_cast<const float4 *>(tile + r * row_floats + i0 + 4u * div_magic(i0, geo.magic_chunk)), Q);
+            if (r < nr) {
+                const float4 *qsrc = reinterpret_cast<const float4 *>(tile + r * row_floats + i0 + 4u * div_magic(i0, geo.magic_chunk));
+                rms_s[r * nq + q] = CVT ? quantum_rms_cvt(qsrc, Q) : quantum_rms(qsrc, Q);
+            }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&done[s]);                  // the samples are no longer needed: the stage may be refilled
