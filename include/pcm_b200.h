@@ -275,7 +275,8 @@ PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
  * block), "blocks_per_sm" (0 = one tile per block; > 0 = capped, looping grid), "unroll", "path"
  * (0 auto, 1 general kernel only, 2 general path with the tile-staged kernel), "coalesced", "tile",
  * "tile_kb", "stages", "meter_tile_kb", "meter_stages", "occupancy", "store_hint",
- * "slice_bytes" (host pipeline slice), "meter_kernel", "ws_smem_kb", "ws_pairs", "ws_depth", "ws_rows", "ws_chunk";
+ * "slice_bytes" (host pipeline slice), "meter_kernel", "ws_smem_kb", "ws_pairs", "ws_depth", "ws_rows", "ws_chunk",
+ * "ws_cvt_quanta" (kernel 2d: frames of at least this many quanta widen float -> double in hardware; 0 = never);
  * for the aggregator "agg_block" / "agg_stage_kb" (convert kernel: threads per CTA, staging memory per step; read
  * when an aggregator is created), "agg_persistent" (convert grid = the CTAs resident at once) and "agg_pdl" (the
  * kernels of a push are chained by programmatic dependent launch; 0 = plain launches).
