@@ -309,6 +309,19 @@ def node_pin():
         return {"available": True, "error": repr(e)}
 
 
+def oracle_pin():
+    """How the oracle that this arm times is tied to the reference: the committed record of the run in which the
+    reference's own source text was executed on the golden vectors (tests/golden/make_ref_exec.py)."""
+    try:
+        rec = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_exec.json")))
+        return {"by": "the reference's source text (App.tsx slices) executed by tests/golden/mini_js.py; oracle and CUDA "
+                      "path held to its outputs in tests/test_ref_exec.py and tests/test_gpu_ref_exec.py",
+                "app_tsx_sha256": rec.get("app_tsx_sha256"), "checked_against_committed": rec.get("checked_against_committed"),
+                "production_js_engine": False}
+    except Exception as e:  # noqa: BLE001
+        return {"by": None, "error": repr(e)}
+
+
 def run_reference(args):
     """The reference's own CPU path for the same workload: every step converts the full tick (all
     --sessions sessions) with the C port of App.tsx:7-32,281-282 on all host threads.  Rank 0 only."""
@@ -340,7 +353,7 @@ def run_reference(args):
             "config": config_dict(args, world, n_in, n_out, per_gpu, args.sessions),
             "arm": {"runtime": "C port of the reference's JS (kind=port), all host threads; the reference itself is "
                                "single-threaded TypeScript for a browser",
-                    "sessions_per_step": rows, "host_threads": cores, "node": node},
+                    "sessions_per_step": rows, "host_threads": cores, "node": node, "oracle_pin": oracle_pin()},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
