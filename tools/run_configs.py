@@ -209,8 +209,12 @@ def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
     (pcmb200_aggregator_push_device): `enqueue_ms` is the host time of the call, `total_ms` runs from
     the call to the end of pcmb200_aggregator_wait (plan + convert on the GPU, 24 bytes read back).
     Also timed: the same push through pcmb200_aggregator_push with HOST session/arrival arrays."""
-    nq, n = 23, S * 23
-    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=n, max_out_samples=S * 984)
+    import math
+    nq = math.ceil(60.0 / (128e3 / rate) - 1e-9)                           # quanta until elapsed >= 60 ms: 23 at 48 kHz, 21 at 44.1 kHz
+    n = S * nq
+    n_out = pcm_frontend.resample_len(nq * 128, rate)
+    pad = (n_out + 7) // 8 * 8
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=max(32, nq + 9), max_push_quanta=n, max_out_samples=S * pad)
     if meter:
         agg.set_meter(True)
     agg.reset_range(0, S, 0.0)
@@ -222,7 +226,7 @@ def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
         base = np.tile(np.arange(1, nq + 1) * (128e3 / rate), S)
     d_samples = ctx.device_buffer(n * 128 * 4)
     ctx.synth_fill(d_samples.ptr, 128, n, 128, rate)
-    d_out = ctx.device_buffer(S * 984 * 2)
+    d_out = ctx.device_buffer(S * pad * 2)
     d_sess, d_arr = ctx.device_buffer(n * 4), ctx.device_buffer(n * 8)
     d_fs, d_fl, d_fo = ctx.device_buffer(n * 4), ctx.device_buffer(n * 4), ctx.device_buffer(n * 8)
     d_sess.upload(sessions)
@@ -231,19 +235,19 @@ def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
         d_arr.upload(base + p * nq * (128e3 / rate))
         ctx.sync()
         t0 = time.perf_counter()
-        agg.push_device(n, d_sess.ptr, d_arr.ptr, d_samples.ptr, d_out.ptr, S * 984, d_fs.ptr, d_fl.ptr, d_fo.ptr, n)
+        agg.push_device(n, d_sess.ptr, d_arr.ptr, d_samples.ptr, d_out.ptr, S * pad, d_fs.ptr, d_fl.ptr, d_fo.ptr, n)
         t1 = time.perf_counter()
         nf, ns = agg.wait()
         t2 = time.perf_counter()
         enq.append(t1 - t0); total.append(t2 - t0)
-        assert nf == S and ns == S * 984, (nf, ns)
+        assert nf == S and ns == S * pad, (nf, ns)
     fl, fo, fs = d_fl.download(np.uint32, S), d_fo.download(np.uint64, S), d_fs.download(np.uint32, S)
-    assert (fl == 981).all() and (fs == np.arange(S)).all()
+    assert (fl == n_out).all() and (fs == np.arange(S)).all()
     # every frame against the oracle: session s holds quanta s, s+S, ... of the push
     x = d_samples.download(np.float32, n * 128)
     x = x.reshape(nq, S, 128).transpose(1, 0, 2).reshape(S, nq * 128) if order == "quantum" else x.reshape(S, nq * 128)
     want = oracle.frames(np.ascontiguousarray(x), nq * 128, rate, threads=os.cpu_count() or 1)
-    got = d_out.download(np.int16, S * 984).reshape(S, 984)[:, :981]
+    got = d_out.download(np.int16, S * pad).reshape(S, pad)[:, :n_out]
     assert np.array_equal(got, want)
     # the same push with host metadata arrays (pageable numpy): pcmb200_aggregator_push
     L = pcm_frontend.load()
@@ -256,7 +260,7 @@ def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
         ctx.sync()
         t0 = time.perf_counter()
         check(L.pcmb200_aggregator_push(ctx.handle, agg.handle, n, sessions.ctypes.data, arr.ctypes.data, d_samples.ptr, MEM_DEVICE,
-                                        d_out.ptr, S * 984, MEM_DEVICE, fs_h.ctypes.data, fl_h.ctypes.data, fo_h.ctypes.data, n,
+                                        d_out.ptr, S * pad, MEM_DEVICE, fs_h.ctypes.data, fl_h.ctypes.data, fo_h.ctypes.data, n,
                                         C.byref(nf_c)), ctx.handle)
         host_meta.append(time.perf_counter() - t0)
         assert nf_c.value == S
@@ -265,8 +269,8 @@ def aggregator(ctx, S=65536, rate=48000, meter=False, order="quantum"):
         d.free()
     t = min(total[1:])
     # bytes the push has to move: every quantum read once (512 B), every frame written once
-    algo = n * 512 + S * 981 * 2
-    return {"config": "next-2 device aggregator (device-resident quanta, ids, times and frames)", "meter": meter, "sessions": S, "push_order": order,
+    algo = n * 512 + S * n_out * 2
+    return {"config": "next-2 device aggregator (device-resident quanta, ids, times and frames)", "meter": meter, "sessions": S, "rate": rate, "quanta_per_frame": nq, "push_order": order,
             "quanta_per_push": n, "enqueue_ms": min(enq[1:]) * 1e3, "total_ms": t * 1e3, "in_samples_per_s": n * 128 / t,
             "realtime_sessions_at_48k": n * 128 / t / rate, "algorithmic_gbs": algo / t / 1e9, "frac_of_measured_peak": algo / t / 1e9 / PEAK,
             "host_metadata_push_ms": min(host_meta) * 1e3, "frames_checked_against_oracle": S,
@@ -386,6 +390,7 @@ def main():
     ap.add_argument("--sweep-meter", action="store_true")
     ap.add_argument("--quanta-ingest", action="store_true", help="the quanta-framed host-ingest benchmark alone")
     ap.add_argument("--agg-stream", type=int, default=0, help="the streaming-regime aggregator benchmark alone with this many sessions (for ncu)")
+    ap.add_argument("--agg-rate", type=int, default=48000, help="with --agg-order: capture rate")
     ap.add_argument("--agg-meter", action="store_true", help="with --agg-order: the meter on")
     ap.add_argument("--agg-order", default="", help="diagnostic: run the big-push aggregator benchmark alone with this push order (quantum | session)")
     args = ap.parse_args()
@@ -406,7 +411,7 @@ def main():
         print(json.dumps(aggregator_streaming(ctx, S=args.agg_stream, pushes=46)), flush=True)
         return
     if args.agg_order:
-        print(json.dumps(aggregator(ctx, order=args.agg_order, meter=args.agg_meter)), flush=True)
+        print(json.dumps(aggregator(ctx, order=args.agg_order, meter=args.agg_meter, rate=args.agg_rate)), flush=True)
         return
     if args.agg_once:
         print(json.dumps(aggregator(ctx)), flush=True)
@@ -441,7 +446,7 @@ def main():
         for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True)):
             print(json.dumps(fn()), flush=True)
         return
-    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: aggregator_streaming(ctx, S=1 << 20, pushes=69), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx), lambda: quanta_ingest(ctx)):
+    for fn in (lambda: meter(ctx, 960, 1 << 20), lambda: meter(ctx, 2944, 1 << 18), lambda: aggregator(ctx), lambda: aggregator(ctx, meter=True), lambda: aggregator(ctx, rate=44100), lambda: aggregator_streaming(ctx), lambda: aggregator_streaming(ctx, meter=True), lambda: aggregator_streaming(ctx, S=1 << 20, pushes=69), lambda: config1(ctx), lambda: config2(ctx), lambda: config3(ctx, 20), lambda: config3(ctx, 60), lambda: config5(ctx), lambda: quanta_ingest(ctx)):
         r = fn()
         results["configs"].append(r)
         print(json.dumps(r), flush=True)
