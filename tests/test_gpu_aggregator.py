@@ -394,3 +394,55 @@ def test_aggregator_other_quantum_sizes(ctx, quantum, max_q):
             assert a.size == b.size and np.array_equal(a, b), s
         want_lv = oracle.level_meter(audio[s, :start].reshape(-1), quantum)[-1]
         assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_aggregator_fuzz_with_rejected_pushes(ctx, seed):
+    """Random pushes, some of which the library must refuse -- an unknown session id in the middle of a push, more
+    flushed frames than the output holds -- and then accept once the cause is removed (the bad id dropped, the push
+    cut in two).  A refused push must leave no trace: in the end every session has exactly the oracle's frames and level."""
+    rng = np.random.RandomState(1000 + seed)
+    S, rate, q_ms = 97, 48000, 128e3 / 48000
+    nq = 150
+    audio = (rng.uniform(-1.05, 1.05, size=(S, nq, 128)) * rng.uniform(0.05, 1, size=(S, 1, 1))).astype(np.float32)
+    times = 4.0 * rng.rand(S, 1) + np.cumsum(q_ms + rng.uniform(-0.3, 0.3, size=(S, nq)), axis=1)
+    events = sorted((times[s, q], s, q) for s in range(S) for q in range(nq))
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=4096, max_out_samples=30 * 984)
+    agg.set_meter(True)
+    agg.reset_range(0, S, 0.0)
+    got = {s: [] for s in range(S)}
+    refused = {"bad_id": 0, "too_big": 0}
+
+    def push(chunk):
+        try:
+            frames = agg.push(np.array([e[1] for e in chunk], dtype=np.uint32), np.array([e[0] for e in chunk]),
+                              np.stack([audio[e[1] % S, e[2]] for e in chunk]))
+        except pcm_frontend.PcmError as err:
+            if err.status == pcm_frontend._capi.ERR_INVALID:             # the injected unknown session: drop it, push again
+                refused["bad_id"] += 1
+                return push([e for e in chunk if e[1] < S])
+            assert err.status == pcm_frontend._capi.ERR_CAPACITY and len(chunk) > 1, err
+            refused["too_big"] += 1                                       # more frames than the output holds: halves, in order
+            return push(chunk[:len(chunk) // 2]), push(chunk[len(chunk) // 2:])
+        for s, pcm in frames:
+            got[s].append(pcm)
+
+    i = 0
+    while i < len(events):
+        n = int(rng.choice([1, 17, 97, 400, 1500, 4000]))
+        chunk = list(events[i:i + n])
+        i += len(chunk)
+        if rng.rand() < 0.3:                                              # an unknown session somewhere in the push
+            k = int(rng.randint(0, len(chunk)))
+            chunk.insert(k, (chunk[k][0], S + int(rng.randint(0, 5)), 0))
+        push(chunk)
+    levels = agg.levels(0, S)
+    agg.close()
+    assert refused["bad_id"] >= 3 and refused["too_big"] >= 3, refused
+    for s in range(S):
+        want, start, _ = _session_frames(audio[s], times[s], rate)
+        assert len(got[s]) == len(want) >= 5, (s, len(got[s]), len(want))
+        for a, b in zip(got[s], want):
+            assert a.size == b.size and np.array_equal(a, b), s
+        want_lv = oracle.level_meter(audio[s, :start].reshape(-1))[-1]
+        assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s

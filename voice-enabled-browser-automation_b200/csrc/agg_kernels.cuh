@@ -68,6 +68,19 @@ struct AggGeom {
 // EVERY kernel in the chain calls pdl_enter() first thing, unconditionally: a grid therefore cannot complete
 // before its predecessor has, which is what makes results of kernels further up the chain safe to read too.
 // Launched without the attribute both instructions do nothing.
+// With the grids of a push overlapping like that, an SM's L1 is no longer wiped between two kernels of the chain: a
+// line that a block of kernel K brought in (say the control block, read at K's start) can still sit there when a
+// block of kernel K+1 reads it on the same SM, after K's last block has changed it in L2.  Seen on the B200: a push
+// refused for lack of output space was nevertheless committed by some blocks, which read a stale status word.  So
+// everything that another kernel of the push (or the push before) has written is loaded with ld.global.cg -- L2 is
+// the point of coherence -- and only true inputs (the caller's arrays, the pick table) go through L1.
+template <typename T> __device__ __forceinline__ T ld_l2(const T *p) { return __ldcg(p); }
+__device__ __forceinline__ AggFrameDesc ld_l2(const AggFrameDesc *p)
+{
+    const uint4 r = __ldcg(reinterpret_cast<const uint4 *>(p));
+    return AggFrameDesc{r.x, r.y, r.z, r.w};
+}
+
 __device__ __forceinline__ void pdl_enter()
 {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -138,8 +151,8 @@ k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__
     pdl_enter();
     __shared__ uint32_t sm[9];
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = k < ctl->n_touched;
-    const uint32_t s = live ? touched[k] : 0u, c = live ? count[s] : 0u;
+    const bool live = k < ld_l2(&ctl->n_touched);
+    const uint32_t s = live ? ld_l2(touched + k) : 0u, c = live ? ld_l2(count + s) : 0u;
     const uint32_t at = block_reserve256(c, &ctl->n_listed, sm);       // one atomic per block
     if (live) cursor[s] = at;
 }
@@ -166,13 +179,13 @@ __device__ __forceinline__ void scan_load8(const ScanArgs &a, uint32_t idx0, uin
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) nq[k] = 0u;
     // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
-    if (a.ctl->status == 0u && idx0 < len) {
+    if (ld_l2(&a.ctl->status) == 0u && idx0 < len) {
         if (idx0 + kScanItems <= len) {
-            const uint4 lo = *reinterpret_cast<const uint4 *>(a.fl_nq + idx0), hi = *reinterpret_cast<const uint4 *>(a.fl_nq + idx0 + 4);
+            const uint4 lo = __ldcg(reinterpret_cast<const uint4 *>(a.fl_nq + idx0)), hi = __ldcg(reinterpret_cast<const uint4 *>(a.fl_nq + idx0 + 4));
             nq[0] = lo.x; nq[1] = lo.y; nq[2] = lo.z; nq[3] = lo.w; nq[4] = hi.x; nq[5] = hi.y; nq[6] = hi.z; nq[7] = hi.w;
         } else {
 #pragma unroll
-            for (int k = 0; k < kScanItems; k++) if (idx0 + k < len) nq[k] = a.fl_nq[idx0 + k];
+            for (int k = 0; k < kScanItems; k++) if (idx0 + k < len) nq[k] = ld_l2(a.fl_nq + idx0 + k);
         }
     }
 #pragma unroll
@@ -237,11 +250,11 @@ struct ScanApplyB {
 __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &ap, uint32_t idx, uint32_t f, unsigned long long off)
 {
     if (f >= ap.max_frames) return;
-    const uint32_t nq = a.fl_nq[idx], s = ap.sessions[idx];
+    const uint32_t nq = ld_l2(a.fl_nq + idx), s = ap.sessions[idx];
     if (ap.frame_session) ap.frame_session[f] = s;
     if (ap.frame_len) ap.frame_len[f] = __ldg(a.nout_of + nq);
     if (ap.frame_offset) ap.frame_offset[f] = off;
-    ap.fdesc[f] = AggFrameDesc{s, nq, ap.fl_ring[idx], ap.fl_pos[idx]};
+    ap.fdesc[f] = AggFrameDesc{s, nq, ld_l2(ap.fl_ring + idx), ld_l2(ap.fl_pos + idx)};
     ap.fdesc_off[f] = off;
 }
 
@@ -260,9 +273,9 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
-    if (a.ctl->status != 0u) return;                   // rejected push: nothing to emit
+    if (ld_l2(&a.ctl->status) != 0u) return;           // rejected push: nothing to emit
     unsigned long long pa = 0, pb = 0;                 // totals of the blocks before this one
-    for (uint32_t b = threadIdx.x; b < blockIdx.x; b += kScanThreads) { pa += sums_a[b]; pb += sums_b[b]; }
+    for (uint32_t b = threadIdx.x; b < blockIdx.x; b += kScanThreads) { pa += ld_l2(sums_a + b); pb += ld_l2(sums_b + b); }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) { pa += __shfl_xor_sync(0xFFFFFFFFu, pa, d); pb += __shfl_xor_sync(0xFFFFFFFFu, pb, d); }
     if ((threadIdx.x & 31u) == 0u) { red_a[threadIdx.x >> 5] = pa; red_b[threadIdx.x >> 5] = pb; }
@@ -303,7 +316,7 @@ k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__res
               const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ctl->status != 0u) return;
+    if (ld_l2(&ctl->status) != 0u) return;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     sorted[atomicAdd(cursor + __ldg(sessions + i), 1u)] = i;
@@ -311,14 +324,17 @@ k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__res
 
 // ---- 4: walk -------------------------------------------------------------------------------------------------
 // In-place heap sort for the rare session with a long list in one push (short lists use insertion sort).
+// (the list was written by the scatter kernel: its elements are read through L2, see ld_l2; the thread's own stores
+//  are seen by its own later loads in program order)
 __device__ inline void sift_down(uint32_t *a, uint32_t start, uint32_t end)
 {
     uint32_t root = start;
     while (2u * root + 1u < end) {
         uint32_t child = 2u * root + 1u;
-        if (child + 1u < end && a[child] < a[child + 1u]) child++;
-        if (a[root] >= a[child]) return;
-        const uint32_t t = a[root]; a[root] = a[child]; a[child] = t;
+        if (child + 1u < end && ld_l2(a + child) < ld_l2(a + child + 1u)) child++;
+        const uint32_t r = ld_l2(a + root), c = ld_l2(a + child);
+        if (r >= c) return;
+        a[root] = c; a[child] = r;
         root = child;
     }
 }
@@ -326,16 +342,21 @@ __device__ inline void sort_indices(uint32_t *a, uint32_t m)
 {
     if (m <= 48u) {
         for (uint32_t i = 1; i < m; i++) {
-            const uint32_t v = a[i];
+            const uint32_t v = ld_l2(a + i);
             uint32_t j = i;
-            while (j > 0 && a[j - 1] > v) { a[j] = a[j - 1]; j--; }
-            a[j] = v;
+            while (j > 0) {
+                const uint32_t p = ld_l2(a + j - 1);
+                if (p <= v) break;
+                a[j] = p; j--;
+            }
+            if (j != i) a[j] = v;
         }
         return;
     }
     for (uint32_t s = m / 2; s-- > 0;) sift_down(a, s, m);
     for (uint32_t e = m; e-- > 1;) {
-        const uint32_t t = a[0]; a[0] = a[e]; a[e] = t;
+        const uint32_t t = ld_l2(a), u = ld_l2(a + e);
+        a[0] = u; a[e] = t;
         sift_down(a, 0, e);
     }
 }
@@ -353,14 +374,14 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
            const double *__restrict__ last_send, AggWalkOut o, AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ctl->status != 0u) return;
+    if (ld_l2(&ctl->status) != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ctl->n_touched) return;
-    const uint32_t s = touched[k], m = count[s], base = cursor[s] - m;
+    if (k >= ld_l2(&ctl->n_touched)) return;
+    const uint32_t s = ld_l2(touched + k), m = ld_l2(count + s), base = ld_l2(cursor + s) - m;
     uint32_t *list = sorted + base;
-    const uint32_t c0 = fill[s];
+    const uint32_t c0 = ld_l2(fill + s);
     uint32_t f = c0, ring_cnt = c0, frame_start = 0;
-    double last = last_send[s];
+    double last = ld_l2(last_send + s);
     bool too_long = false;
     // the reference's rule for the j-th quantum of the session in this push (push index i, arrival time `now`)
     auto rule = [&](uint32_t i, double now, uint32_t j) {
@@ -385,7 +406,7 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
         // stores to come back from L2 (a third of the kernel, ncu).
         uint32_t v[32];
 #pragma unroll
-        for (int u = 0; u < 32; u++) v[u] = (uint32_t)u < m ? list[u] : 0xFFFFFFFFu;
+        for (int u = 0; u < 32; u++) v[u] = (uint32_t)u < m ? ld_l2(list + u) : 0xFFFFFFFFu;
         if (m > 1u) {
 #pragma unroll
             for (int kk = 2; kk <= 32; kk <<= 1) {
@@ -428,7 +449,7 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
             uint32_t idx[B];
             double at[B];
 #pragma unroll
-            for (uint32_t u = 0; u < B; u++) idx[u] = j0 + u < m ? list[j0 + u] : 0u;
+            for (uint32_t u = 0; u < B; u++) idx[u] = j0 + u < m ? ld_l2(list + j0 + u) : 0u;
 #pragma unroll
             for (uint32_t u = 0; u < B; u++) at[u] = j0 + u < m ? arrival[idx[u]] : 0.0;
 #pragma unroll
@@ -436,7 +457,7 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
         }
         if (too_long) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
         const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
-        for (uint32_t j = 0; j < m; j++) o.dst_slot[list[j]] = j >= frame_start ? first_slot + (j - frame_start) : 0xFFFFFFFFu;
+        for (uint32_t j = 0; j < m; j++) o.dst_slot[ld_l2(list + j)] = j >= frame_start ? first_slot + (j - frame_start) : 0xFFFFFFFFu;
     }
     o.new_fill[k] = f;
     o.new_last[k] = last;
@@ -543,7 +564,7 @@ __device__ __forceinline__ void agg_build_meta(const AggGeom &g, const AggConver
         AggFrameDesc d{0u, 0u, 0u, 0u};
         unsigned long long off = 0;
         uint32_t no = 0;
-        if (lane < nf) { d = a.fdesc[f0 + lane]; off = a.fdesc_off[f0 + lane]; no = __ldg(a.nout_of + d.nq); }
+        if (lane < nf) { d = ld_l2(a.fdesc + f0 + lane); off = ld_l2(a.fdesc_off + f0 + lane); no = __ldg(a.nout_of + d.nq); }
         uint32_t iq = d.nq, ip = (no + 1u) >> 1;
         const uint32_t vq = iq, vp = ip;
 #pragma unroll
@@ -562,7 +583,7 @@ __device__ __forceinline__ void agg_build_meta(const AggGeom &g, const AggConver
         const uint32_t j = sl - m.qstart[k];
         const AggFrameDesc d = m.fd[k];
         m.slot_src[sl] = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
-                                          : a.samples + (size_t)a.sorted[d.pos + (j - d.ring_count)] * Q;
+                                          : a.samples + (size_t)ld_l2(a.sorted + d.pos + (j - d.ring_count)) * Q;
     }
 }
 
@@ -571,14 +592,14 @@ __global__ void __launch_bounds__(256)
 k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
 {
     pdl_enter();
-    if (a.ctl->status != 0u) return;
+    if (ld_l2(&a.ctl->status) != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2;
     const AggMetaLayout L = agg_meta_layout(a.G, a.G * g.half_quanta);
     float *arena = reinterpret_cast<float *>(smem_raw);
     unsigned char *meta_base = smem_raw + agg_arena_bytes(a.G, g.half_quanta, Q);
 
-    const uint32_t n_frames = a.ctl->n_frames, step = gridDim.x * a.G;
+    const uint32_t n_frames = ld_l2(&a.ctl->n_frames), step = gridDim.x * a.G;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = blockDim.x >> 5;
     uint32_t f0 = blockIdx.x * a.G;
     if (f0 >= n_frames) return;
@@ -686,11 +707,11 @@ __global__ void __launch_bounds__(128, 10)
 k_agg_convert_one(AggGeom g, AggConvertArgs a)
 {
     pdl_enter();
-    if (a.ctl->status != 0u) return;
+    if (ld_l2(&a.ctl->status) != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *arena = reinterpret_cast<float *>(smem_raw);
     const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2, mq = a.magic_q, bd = blockDim.x;
-    const uint32_t n_frames = a.ctl->n_frames;
+    const uint32_t n_frames = ld_l2(&a.ctl->n_frames);
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = bd >> 5;
     uint32_t f = blockIdx.x;
     if (f >= n_frames) return;
@@ -709,15 +730,15 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         uint32_t idx0, idx1, n_out;
     };
     auto fetch_desc = [&](uint32_t fi) -> Desc {
-        const uint4 raw = *reinterpret_cast<const uint4 *>(a.fdesc + fi);        // {session, nq, ring_count, pos}
-        return Desc{a.fdesc_off[fi], raw.x, raw.y, raw.z, raw.w};
+        const uint4 raw = __ldcg(reinterpret_cast<const uint4 *>(a.fdesc + fi));   // {session, nq, ring_count, pos}
+        return Desc{ld_l2(a.fdesc_off + fi), raw.x, raw.y, raw.z, raw.w};
     };
     auto fetch_list = [&](const Desc &d) -> Frame {
         const uint32_t npush = d.nq - d.rc;
         Frame fr;
         fr.d = d;
-        fr.idx0 = lane < npush ? a.sorted[d.pos + lane] : 0u;
-        fr.idx1 = lane + 32u < npush ? a.sorted[d.pos + lane + 32u] : 0u;
+        fr.idx0 = lane < npush ? ld_l2(a.sorted + d.pos + lane) : 0u;
+        fr.idx1 = lane + 32u < npush ? ld_l2(a.sorted + d.pos + lane + 32u) : 0u;
         fr.n_out = __ldg(a.nout_of + d.nq);
         return fr;
     };
@@ -858,13 +879,13 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
              const double *__restrict__ rms_at, double *__restrict__ level, const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ctl->status != 0u) return;
+    if (ld_l2(&ctl->status) != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ctl->n_touched) return;
-    const uint32_t nfl = flushed[k];
+    if (k >= ld_l2(&ctl->n_touched)) return;
+    const uint32_t nfl = ld_l2(flushed + k);
     if (nfl == 0u) return;
-    const uint32_t s = touched[k], base = cursor[s] - count[s], c0 = fill[s];
-    double lv = level[s];
+    const uint32_t s = ld_l2(touched + k), base = ld_l2(cursor + s) - ld_l2(count + s), c0 = ld_l2(fill + s);
+    double lv = ld_l2(level + s);
     bool poisoned = lv != lv;
     auto step = [&](double rms) {
         poisoned |= rms != rms;
@@ -877,7 +898,7 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
         for (uint32_t j0 = 0; j0 < cnt; j0 += 8u) {
             double r[8];
 #pragma unroll
-            for (uint32_t u = 0; u < 8u; u++) r[u] = j0 + u < cnt ? src[j0 + u] : 0.0;
+            for (uint32_t u = 0; u < 8u; u++) r[u] = j0 + u < cnt ? ld_l2(src + j0 + u) : 0.0;
 #pragma unroll
             for (uint32_t u = 0; u < 8u; u++) if (j0 + u < cnt) step(r[u]);
         }
@@ -913,14 +934,14 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     // the per-push counters are cleared (always: the next push starts from clean counters).  The append work neither
     // reads nor writes any of this, so where the commit sits in the kernel is only a matter of overlap: the plain
     // copy path runs it after its loads and stores have been issued.
-    const bool ok = ctl->status == 0u;
+    const bool ok = ld_l2(&ctl->status) == 0u;
     auto commit = [&]() {
-        const uint32_t nt = ctl->n_touched;
+        const uint32_t nt = ld_l2(&ctl->n_touched);
         if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
         for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nt; k += gridDim.x * blockDim.x) {
-            const uint32_t s = cm.touched[k];
+            const uint32_t s = ld_l2(cm.touched + k);
             cm.count[s] = 0u;
-            if (ok) { cm.fill[s] = cm.new_fill[k]; cm.last_send[s] = cm.new_last[k]; }
+            if (ok) { cm.fill[s] = ld_l2(cm.new_fill + k); cm.last_send[s] = ld_l2(cm.new_last + k); }
         }
     };
     if (!ok || METER) commit();
@@ -933,7 +954,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         // which every quantum flushed costs one pass over dst_slot (6 MB for 1.5 M quanta) and nothing else.
         const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
         for (uint32_t base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u; base < n; base += warps * 32u) {
-            const uint32_t mine = base + lane < n ? __ldg(dst_slot + base + lane) : 0xFFFFFFFFu;
+            const uint32_t mine = base + lane < n ? ld_l2(dst_slot + base + lane) : 0xFFFFFFFFu;
             unsigned live = __ballot_sync(0xFFFFFFFFu, mine != 0xFFFFFFFFu);
             while (live) {
                 uint32_t q[4], slot[4];
@@ -974,7 +995,7 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
         __syncthreads();
         uint32_t slot = 0xFFFFFFFFu;
-        if (threadIdx.x < TILE && i0 + threadIdx.x < n) slot = __ldg(dst_slot + i0 + threadIdx.x);
+        if (threadIdx.x < TILE && i0 + threadIdx.x < n) slot = ld_l2(dst_slot + i0 + threadIdx.x);
         if (threadIdx.x < TILE) slot_s[threadIdx.x] = slot;
         const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
         if (live == 0) continue;
