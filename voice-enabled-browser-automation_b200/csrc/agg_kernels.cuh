@@ -81,6 +81,18 @@ __device__ __forceinline__ AggFrameDesc ld_l2(const AggFrameDesc *p)
     return AggFrameDesc{r.x, r.y, r.z, r.w};
 }
 
+// The head of the push's control block, fetched ONCE per block (thread 0, through L2) and handed to every thread:
+// a million threads asking L2 for the same word cost several microseconds per kernel.  Every thread of the block
+// must call it (it holds a barrier), right after pdl_enter().
+struct CtlHead { uint32_t status, n_touched, n_frames; };
+__device__ __forceinline__ CtlHead ctl_head(const AggCtl *ctl)
+{
+    __shared__ uint4 head;
+    if (threadIdx.x == 0) head = __ldcg(reinterpret_cast<const uint4 *>(ctl));   // {status, n_touched, n_frames, -}
+    __syncthreads();
+    return CtlHead{head.x, head.y, head.z};
+}
+
 __device__ __forceinline__ void pdl_enter()
 {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -151,7 +163,7 @@ k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__
     pdl_enter();
     __shared__ uint32_t sm[9];
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = k < ld_l2(&ctl->n_touched);
+    const bool live = k < ctl_head(ctl).n_touched;
     const uint32_t s = live ? ld_l2(touched + k) : 0u, c = live ? ld_l2(count + s) : 0u;
     const uint32_t at = block_reserve256(c, &ctl->n_listed, sm);       // one atomic per block
     if (live) cursor[s] = at;
@@ -172,14 +184,14 @@ struct ScanArgs {
 // The kScanItems consecutive items of one thread: va[k] = 1 if quantum idx0 + k flushes a frame, vb[k] = that
 // frame's output length rounded up to 8 samples.  The flags are read as two 128-bit loads (the per-item form was a
 // chain of three dependent loads per item and made these three passes latency-bound).
-__device__ __forceinline__ void scan_load8(const ScanArgs &a, uint32_t idx0, uint32_t len, uint32_t (&va)[kScanItems], uint32_t (&vb)[kScanItems])
+__device__ __forceinline__ void scan_load8(const ScanArgs &a, uint32_t status, uint32_t idx0, uint32_t len, uint32_t (&va)[kScanItems], uint32_t (&vb)[kScanItems])
 {
     static_assert(kScanItems == 8, "two uint4 loads per thread");
     uint32_t nq[kScanItems];
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) nq[k] = 0u;
     // a rejected push leaves fl_nq partly unwritten (the walk stops at the first problem): read nothing
-    if (ld_l2(&a.ctl->status) == 0u && idx0 < len) {
+    if (status == 0u && idx0 < len) {
         if (idx0 + kScanItems <= len) {
             const uint4 lo = __ldcg(reinterpret_cast<const uint4 *>(a.fl_nq + idx0)), hi = __ldcg(reinterpret_cast<const uint4 *>(a.fl_nq + idx0 + 4));
             nq[0] = lo.x; nq[1] = lo.y; nq[2] = lo.z; nq[3] = lo.w; nq[4] = hi.x; nq[5] = hi.y; nq[6] = hi.z; nq[7] = hi.w;
@@ -224,11 +236,12 @@ k_scan_reduce(ScanArgs a, uint32_t *__restrict__ sums_a, uint32_t *__restrict__ 
 {
     pdl_enter();
     __shared__ uint32_t ws[kScanThreads / 32];
+    const uint32_t status = ctl_head(a.ctl).status;
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
     uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
-    scan_load8(a, base + threadIdx.x * kScanItems, len, va, vb);
+    scan_load8(a, status, base + threadIdx.x * kScanItems, len, va, vb);
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) { sa += va[k]; sb += vb[k]; }
     uint32_t ta, tb;
@@ -270,17 +283,18 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__
     pdl_enter();
     __shared__ uint32_t ws[kScanThreads / 32];
     __shared__ unsigned long long red_a[kScanThreads / 32], red_b[kScanThreads / 32];
+    const uint32_t status = ctl_head(a.ctl).status;
     const uint32_t len = a.n;
     const uint32_t base = blockIdx.x * kScanBlock;
     if (base >= len) return;
-    if (ld_l2(&a.ctl->status) != 0u) return;           // rejected push: nothing to emit
+    if (status != 0u) return;                          // rejected push: nothing to emit
     unsigned long long pa = 0, pb = 0;                 // totals of the blocks before this one
     for (uint32_t b = threadIdx.x; b < blockIdx.x; b += kScanThreads) { pa += ld_l2(sums_a + b); pb += ld_l2(sums_b + b); }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) { pa += __shfl_xor_sync(0xFFFFFFFFu, pa, d); pb += __shfl_xor_sync(0xFFFFFFFFu, pb, d); }
     if ((threadIdx.x & 31u) == 0u) { red_a[threadIdx.x >> 5] = pa; red_b[threadIdx.x >> 5] = pb; }
     uint32_t va[kScanItems], vb[kScanItems], sa = 0, sb = 0;
-    scan_load8(a, base + threadIdx.x * kScanItems, len, va, vb);
+    scan_load8(a, status, base + threadIdx.x * kScanItems, len, va, vb);
 #pragma unroll
     for (int k = 0; k < kScanItems; k++) { sa += va[k]; sb += vb[k]; }
     uint32_t ta, tb;
@@ -316,7 +330,7 @@ k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__res
               const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ld_l2(&ctl->status) != 0u) return;
+    if (ctl_head(ctl).status != 0u) return;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     sorted[atomicAdd(cursor + __ldg(sessions + i), 1u)] = i;
@@ -374,9 +388,10 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
            const double *__restrict__ last_send, AggWalkOut o, AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ld_l2(&ctl->status) != 0u) return;
+    const CtlHead head = ctl_head(ctl);
+    if (head.status != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ld_l2(&ctl->n_touched)) return;
+    if (k >= head.n_touched) return;
     const uint32_t s = ld_l2(touched + k), m = ld_l2(count + s), base = ld_l2(cursor + s) - m;
     uint32_t *list = sorted + base;
     const uint32_t c0 = ld_l2(fill + s);
@@ -592,14 +607,15 @@ __global__ void __launch_bounds__(256)
 k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
 {
     pdl_enter();
-    if (ld_l2(&a.ctl->status) != 0u) return;
+    const CtlHead head = ctl_head(a.ctl);
+    if (head.status != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2;
     const AggMetaLayout L = agg_meta_layout(a.G, a.G * g.half_quanta);
     float *arena = reinterpret_cast<float *>(smem_raw);
     unsigned char *meta_base = smem_raw + agg_arena_bytes(a.G, g.half_quanta, Q);
 
-    const uint32_t n_frames = ld_l2(&a.ctl->n_frames), step = gridDim.x * a.G;
+    const uint32_t n_frames = head.n_frames, step = gridDim.x * a.G;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = blockDim.x >> 5;
     uint32_t f0 = blockIdx.x * a.G;
     if (f0 >= n_frames) return;
@@ -707,11 +723,12 @@ __global__ void __launch_bounds__(128, 10)
 k_agg_convert_one(AggGeom g, AggConvertArgs a)
 {
     pdl_enter();
-    if (ld_l2(&a.ctl->status) != 0u) return;
+    const CtlHead head = ctl_head(a.ctl);
+    if (head.status != 0u) return;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *arena = reinterpret_cast<float *>(smem_raw);
     const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2, mq = a.magic_q, bd = blockDim.x;
-    const uint32_t n_frames = ld_l2(&a.ctl->n_frames);
+    const uint32_t n_frames = head.n_frames;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = bd >> 5;
     uint32_t f = blockIdx.x;
     if (f >= n_frames) return;
@@ -879,9 +896,10 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
              const double *__restrict__ rms_at, double *__restrict__ level, const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ld_l2(&ctl->status) != 0u) return;
+    const CtlHead head = ctl_head(ctl);
+    if (head.status != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= ld_l2(&ctl->n_touched)) return;
+    if (k >= head.n_touched) return;
     const uint32_t nfl = ld_l2(flushed + k);
     if (nfl == 0u) return;
     const uint32_t s = ld_l2(touched + k), base = ld_l2(cursor + s) - ld_l2(count + s), c0 = ld_l2(fill + s);
@@ -934,9 +952,10 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     // the per-push counters are cleared (always: the next push starts from clean counters).  The append work neither
     // reads nor writes any of this, so where the commit sits in the kernel is only a matter of overlap: the plain
     // copy path runs it after its loads and stores have been issued.
-    const bool ok = ld_l2(&ctl->status) == 0u;
+    const CtlHead head = ctl_head(ctl);
+    const bool ok = head.status == 0u;
     auto commit = [&]() {
-        const uint32_t nt = ld_l2(&ctl->n_touched);
+        const uint32_t nt = head.n_touched;
         if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
         for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nt; k += gridDim.x * blockDim.x) {
             const uint32_t s = ld_l2(cm.touched + k);
