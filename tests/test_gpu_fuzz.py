@@ -67,3 +67,38 @@ def test_fuzz_host_resident(ctx, seed):
         x = rng.uniform(-1.25, 1.25, size=(rows, n_in + int(rng.choice([0, 0, 5])))).astype(np.float32)[:, :n_in]
         got = ctx.frames_encode(x, rate)
         assert np.array_equal(got, oracle.frames(np.ascontiguousarray(x), n_in, rate)), (rate, n_in, rows)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fuzz_fused_meter(ctx, seed):
+    """Random shapes through the fused frames + meter call: any rate, 1-40 quanta of 32-256 samples per frame, a few
+    to a few thousand rows, three ticks with the level state carried over; rows sprinkled with NaN, Inf, zeros,
+    denormals and values around the 2^-60 threshold of the integer widening.  PCM, the level after every quantum and
+    the state must be the oracle's, bit for bit (whichever meter kernel the shape lands on)."""
+    rng = np.random.RandomState(3000 + seed)
+    for _ in range(10):
+        rate = RATES[rng.randint(len(RATES))]
+        quantum = int(rng.choice([32, 64, 128, 128, 128, 256]))
+        nq = int(rng.choice([1, 2, 3, 7, 8, 15, 16, 23, 24, 31, 32, 33, 40]))
+        n_in = nq * quantum
+        rows = int(rng.choice([1, 2, 5, 31, 64, 100, 257, 1000, 3000]))
+        if rows * n_in > 4_000_000:
+            rows = max(1, 4_000_000 // n_in)
+        state = np.zeros(rows, dtype=np.float64)
+        for tick in range(3):
+            x = (rng.uniform(-1.2, 1.2, size=(rows, n_in)) * rng.uniform(1e-3, 1.0, size=(rows, 1))).astype(np.float32)
+            for _k in range(min(rows, 6)):                                   # special values somewhere
+                r, c = rng.randint(rows), rng.randint(n_in)
+                x[r, c] = np.float32(rng.choice([np.nan, np.inf, -np.inf, 0.0, -0.0, 1e-40, -3e-39, 2.0 ** -60, 2.0 ** -61, 1e-30]))
+            if rows > 2:
+                q0 = rng.randint(nq) * quantum
+                x[1, q0:q0 + quantum] = 0.0                                  # a silent quantum
+                x[2, q0:q0 + quantum] = (rng.randint(0, 2, quantum) * 2.0 ** rng.uniform(-64, -56, quantum)).astype(np.float32)
+            pcm, levels, new_state = ctx.frames_encode_meter(x, rate, state, quantum)
+            tag = (rate, quantum, nq, rows, tick)
+            assert np.array_equal(pcm, oracle.frames(x, n_in, rate)), tag
+            for r in range(rows):
+                want = oracle.level_meter(x[r], quantum, state[r])
+                assert np.array_equal(levels[r].view(np.uint64), want.view(np.uint64)), tag + (r,)
+                assert new_state[r:r + 1].view(np.uint64)[0] == want[-1:].view(np.uint64)[0], tag + (r,)
+            state = new_state
