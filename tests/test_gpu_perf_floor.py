@@ -78,3 +78,36 @@ def test_fused_meter_stays_above_its_floor(ctx, n_in, rows):
     st.free()
     print(f"PERF_FLOOR meter n_in={n_in} gbs={best:.0f} frac={best / _peak():.3f}")
     assert best / _peak() >= 0.75, f"meter, {n_in}-sample frames: {best:.0f} GB/s is {best / _peak():.2f} of the HBM peak"
+
+
+def test_aggregator_push_stays_below_its_ceiling(ctx):
+    """Device-side aggregator, 65 536 sessions x 23 quanta per push, everything device-resident: 0.25-0.31 ms measured
+    (round 1: 3.2 ms).  The ceiling is far above the measured value: only a real regression -- a
+    kernel of the chain falling off its fast path -- trips it."""
+    import time
+
+    import numpy as np
+    S, nq, rate = 65536, 23, 48000
+    n = S * nq
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=n, max_out_samples=S * 984)
+    agg.reset_range(0, S, 0.0)
+    d = {k: ctx.device_buffer(v) for k, v in dict(s=n * 4, t=n * 8, x=n * 512, o=S * 984 * 2, fs=n * 4, fl=n * 4, fo=n * 8).items()}
+    d["s"].upload(np.tile(np.arange(S, dtype=np.uint32), nq))
+    ctx.synth_fill(d["x"].ptr, 128, n, 128, rate)
+    base = np.repeat(np.arange(1, nq + 1) * (128e3 / rate), S)
+    best = 1e9
+    for p in range(5):
+        d["t"].upload(base + p * nq * (128e3 / rate))
+        ctx.sync()
+        t0 = time.perf_counter()
+        agg.push_device(n, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr, S * 984, d["fs"].ptr, d["fl"].ptr, d["fo"].ptr, n)
+        nf, _ = agg.wait()
+        dt = time.perf_counter() - t0
+        assert nf == S
+        if p:
+            best = min(best, dt)
+    agg.close()
+    for b in d.values():
+        b.free()
+    print(f"PERF_FLOOR aggregator push_ms={best * 1e3:.3f}")
+    assert best * 1e3 <= 0.6, f"aggregator push took {best * 1e3:.3f} ms (measured 0.25-0.31 ms)"
