@@ -204,3 +204,105 @@ def test_committed_vectors_are_what_the_reference_text_produces(vec):
     assert np.array_equal(flush, z[s["key"] + "_flush"][:40])
     assert np.array_equal(levels.view(np.uint64), z[s["key"] + "_levels"][:40].view(np.uint64))
     assert np.array_equal(np.concatenate(frames), z[s["key"] + "_frames"][:sum(f.size for f in frames)])
+
+
+# ---- 1b. differential test of the expression grammar: random trees, printed with MINIMAL parentheses (so that the
+# interpreter's precedence and associativity decide the meaning) against a direct evaluation of the tree with numpy
+# binary64 scalars (whose division, remainder and comparisons follow IEEE-754 without Python's exceptions) -----------
+_PREC = {"?:": 1, "||": 2, "&&": 3, "===": 4, "!==": 4, "<": 5, ">": 5, "<=": 5, ">=": 5, "+": 6, "-": 6, "*": 7, "/": 7, "%": 7, "neg": 8, "!": 8}
+
+
+def _gen_num(rng, depth):
+    if depth <= 0 or rng.rand() < 0.25:
+        kind = rng.randint(6)
+        if kind == 0:
+            return ("lit", str(int(rng.randint(0, 1000))))
+        if kind == 1:
+            return ("lit", f"{rng.uniform(0, 50):.6f}")
+        if kind == 2:
+            return ("lit", hex(int(rng.randint(0, 65536))))
+        if kind == 3:
+            return ("lit", rng.choice(["NaN", "Infinity", "0", "1e308", "5e-324", "0.5"]))
+        return ("lit", str(int(rng.randint(0, 10))))
+    kind = rng.randint(10)
+    if kind < 6:
+        return ("bin", rng.choice(["+", "-", "*", "/", "%"]), _gen_num(rng, depth - 1), _gen_num(rng, depth - 1))
+    if kind == 6:
+        return ("neg", _gen_num(rng, depth - 1))
+    if kind == 7:
+        return ("cond", _gen_bool(rng, depth - 1), _gen_num(rng, depth - 1), _gen_num(rng, depth - 1))
+    return ("call", rng.choice(["Math.floor", "Math.sqrt", "Math.max", "Math.min"]), _gen_num(rng, depth - 1), _gen_num(rng, depth - 1))
+
+
+def _gen_bool(rng, depth):
+    kind = rng.randint(6)
+    if depth <= 0 or kind < 3:
+        return ("cmp", rng.choice(["<", ">", "<=", ">=", "===", "!=="]), _gen_num(rng, depth - 1), _gen_num(rng, depth - 1))
+    if kind == 3:
+        return ("not", _gen_bool(rng, depth - 1))
+    return ("logic", rng.choice(["&&", "||"]), _gen_bool(rng, depth - 1), _gen_bool(rng, depth - 1))
+
+
+def _to_js(t, parent=0, right=False):
+    k = t[0]
+    if k == "lit":
+        return t[1]
+    if k == "call":
+        args = [_to_js(t[2])] if t[1] in ("Math.floor", "Math.sqrt") else [_to_js(t[2]), _to_js(t[3])]
+        return f"{t[1]}({', '.join(args)})"
+    if k == "neg":
+        inner = _to_js(t[1], _PREC["neg"])
+        s, p = ("- " + inner), _PREC["neg"]
+    elif k == "not":
+        s, p = "!" + _to_js(t[1], _PREC["!"]), _PREC["!"]
+    elif k == "cond":
+        p = _PREC["?:"]
+        s = f"{_to_js(t[1], p + 1)} ? {_to_js(t[2], p)} : {_to_js(t[3], p)}"
+    else:
+        op = t[1]
+        p = _PREC[op]
+        s = f"{_to_js(t[2], p)} {op} {_to_js(t[3], p, right=True)}"          # left-associative: the right child needs > p
+    need = p < parent or (p == parent and right) or (k == "cond" and parent >= p and parent != 0)
+    return f"({s})" if need else s
+
+
+def _eval_tree(t):
+    k = t[0]
+    with np.errstate(all="ignore"):
+        if k == "lit":
+            return np.float64(int(t[1], 16)) if t[1].startswith("0x") else np.float64({"NaN": "nan", "Infinity": "inf"}.get(t[1], t[1]))
+        if k == "neg":
+            return -_eval_tree(t[1])
+        if k == "not":
+            return not _eval_tree(t[1])
+        if k == "cond":
+            return _eval_tree(t[2]) if _eval_tree(t[1]) else _eval_tree(t[3])
+        if k == "logic":
+            a = _eval_tree(t[2])
+            return (a and _eval_tree(t[3])) if t[1] == "&&" else (a or _eval_tree(t[3]))
+        if k == "call":
+            a = _eval_tree(t[2])
+            if t[1] == "Math.floor":
+                return np.floor(a)
+            if t[1] == "Math.sqrt":
+                return np.sqrt(a)
+            b = _eval_tree(t[3])
+            if np.isnan(a) or np.isnan(b):
+                return np.float64("nan")
+            return np.maximum(a, b) if t[1] == "Math.max" else np.minimum(a, b)
+        a, b = _eval_tree(t[2]), _eval_tree(t[3])
+        if k == "cmp":
+            return bool({"<": a < b, ">": a > b, "<=": a <= b, ">=": a >= b, "===": a == b, "!==": a != b}[t[1]])
+        return {"+": a + b, "-": a - b, "*": a * b, "/": np.divide(a, b), "%": np.fmod(a, b)}[t[1]]
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_expression_grammar_against_direct_evaluation(seed):
+    rng = np.random.RandomState(500 + seed)
+    for _ in range(150):
+        tree = _gen_num(rng, 5)
+        src = _to_js(tree)
+        got = run(f"const r = {src};").get("r")
+        want = float(_eval_tree(tree))
+        ok = (got != got and want != want) or got == want           # (Math.max / fmod sign-of-zero corners are covered above)
+        assert ok, (src, got, want)
