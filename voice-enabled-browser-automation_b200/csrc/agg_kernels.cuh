@@ -60,7 +60,7 @@ struct AggGeom {
     double desired_ms;
 };
 
-// Programmatic dependent launch (opt-out: tune agg_pdl = 0).  A push is a chain of a dozen short kernels, each
+// Programmatic dependent launch (opt-out: tune agg_pdl = 0).  A push is a chain of eight or nine short kernels, each
 // needing everything its predecessor wrote; launched the plain way, every link pays a full launch latency after
 // the previous grid has drained.  With the programmatic-serialisation launch attribute a grid may be scheduled
 // as soon as every block of its predecessor has passed pdl_enter()'s trigger (or exited), and its blocks then
