@@ -105,11 +105,26 @@ def test_header_is_plain_c_and_links(tmp_path):
     """include/pcm_b200.h compiles as C11 and the example program links against the library and
     runs (without a GPU it stops at context creation, loudly, with exit code 0 by design)."""
     import subprocess
-    src = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "examples", "frames_c_abi.c")
     lib = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "lib")
-    exe = str(tmp_path / "frames_c_abi")
-    subprocess.run(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), src,
-                    "-L", lib, "-lpcm_b200", f"-Wl,-rpath,{lib}", "-lm", "-o", exe], check=True)
-    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
-    assert out.returncode == 0, out.stdout + out.stderr
-    assert "libpcm_b200 ABI" in out.stdout and ("frames of 320 samples" in out.stdout or "no device" in out.stdout)
+    for name, ok_line in (("frames_c_abi", "frames of 320 samples"), ("aggregator_c_abi", "3 frames from 3 connections")):
+        src = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "examples", name + ".c")
+        exe = str(tmp_path / name)
+        subprocess.run(["gcc", "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), src,
+                        "-L", lib, "-lpcm_b200", f"-Wl,-rpath,{lib}", "-lm", "-o", exe], check=True)
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0, name + ": " + out.stdout + out.stderr
+        assert ok_line in out.stdout or "no device" in out.stdout, out.stdout
+
+
+@pytest.mark.gpu
+def test_c_examples_run_on_the_gpu(tmp_path):
+    """The same two plain-C programs on a box with a device: they must get all the way through."""
+    import subprocess
+    lib = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "lib")
+    for name, ok_line in (("frames_c_abi", "frames of 320 samples"), ("aggregator_c_abi", "3 frames from 3 connections")):
+        src = os.path.join(ROOT, "voice-enabled-browser-automation_b200", "examples", name + ".c")
+        exe = str(tmp_path / name)
+        subprocess.run(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), src, "-L", lib, "-lpcm_b200", f"-Wl,-rpath,{lib}", "-lm",
+                        "-o", exe], check=True)
+        out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0 and ok_line in out.stdout, name + ": " + out.stdout + out.stderr
