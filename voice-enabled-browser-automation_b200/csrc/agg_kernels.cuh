@@ -508,7 +508,9 @@ __device__ __forceinline__ void cp_async_wait_all()
 //   + descriptors in registers, prefetched two frames ahead, persistent grid (one)   ~150 us, 0.92 of the HBM peak
 struct AggConvertArgs {
     const float *samples;            // the push's quanta
-    const float *ring;               // [max_sessions][half_quanta][quantum]
+    const int16_t *staged;           // [max_sessions][nout_pad] outputs of the quanta that were waiting (see AggAppendArgs)
+    const uint32_t *out_lo;          // [half_quanta + 1] first output of quantum j
+    uint32_t nout_pad;
     const uint32_t *sorted;
     const AggFrameDesc *fdesc;
     const unsigned long long *fdesc_off;
@@ -597,8 +599,8 @@ __device__ __forceinline__ void agg_build_meta(const AggGeom &g, const AggConver
         while (k + 1u < nf && sl >= m.qstart[k + 1u]) k++;
         const uint32_t j = sl - m.qstart[k];
         const AggFrameDesc d = m.fd[k];
-        m.slot_src[sl] = j < d.ring_count ? a.ring + ((size_t)d.session * g.half_quanta + j) * Q
-                                          : a.samples + (size_t)ld_l2(a.sorted + d.pos + (j - d.ring_count)) * Q;
+        // the first ring_count quanta of a frame were converted when they arrived (a.staged): nothing to fetch for them
+        m.slot_src[sl] = j < d.ring_count ? nullptr : a.samples + (size_t)ld_l2(a.sorted + d.pos + (j - d.ring_count)) * Q;
     }
 }
 
@@ -629,12 +631,15 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
         // slot index is warp-uniform, so no per-thread division and one broadcast read of the source address)
         if (gpq == 32u) {                                   // the AudioWorklet quantum (128 samples): the whole loop body is
             const uint32_t dst0 = smem_u32(arena) + 16u * lane;     // one LDS.64, one IMAD and the copy -- ncu showed the generic
-            for (uint32_t sl = warp; sl < T; sl += nw)      // form below at ~70 instructions per quantum, half of the kernel
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + sl * (pitch * 4u)), "l"(m.slot_src[sl] + 4u * lane) : "memory");
+            for (uint32_t sl = warp; sl < T; sl += nw) {    // form below at ~70 instructions per quantum, half of the kernel
+                const float *src = m.slot_src[sl];          // null: that quantum was converted when it arrived
+                if (src) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + sl * (pitch * 4u)), "l"(src + 4u * lane) : "memory");
+            }
         } else {
             for (uint32_t sl = warp; sl < T; sl += nw) {
                 const float *src = m.slot_src[sl];
                 float *dst = arena + (size_t)sl * pitch;
+                if (!src) continue;
 #pragma unroll 1
                 for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(dst + 4u * gi, src + 4u * gi);
             }
@@ -656,11 +661,19 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
             const float *fr = arena + (size_t)m.qstart[k] * pitch;
             int16_t *dstf = a.out + m.foff[k];
             const float qnan = __int_as_float(0x7FC00000);                     // outside the frame: undefined -> NaN -> 0
+            // outputs below `osplit` belong to quanta that were converted when they arrived: copied from a.staged
+            const uint32_t rc = m.fd[k].ring_count, osplit = rc ? __ldg(a.out_lo + rc) : 0u;
+            const int16_t *st = a.staged + (size_t)m.fd[k].session * a.nout_pad;
             if (a.out_aligned16) {
                 // mq = ceil(2^32 / quantum) is never 0 here (quantum >= 4), so i / quantum is one multiply-high
                 const uint32_t nfull = n_out >> 1, R = g.stride, mq = a.magic_q, bd = blockDim.x;
                 const uint2 *lut2 = reinterpret_cast<const uint2 *>(a.lut);
                 auto pair = [&](uint32_t p) -> uint32_t {
+                    if (2u * p + 1u < osplit) return ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
+                    if (2u * p < osplit) {                                     // the pair straddles the split
+                        const uint32_t i1 = LUT ? __ldg(a.lut + 2u * p + 1u) : (2u * p + 1u) * R;
+                        return pack_s16x2_sat((int)ld_l2(st + 2u * p), enc_s32(i1 < n_in ? fr[i1 + 4u * __umulhi(i1, mq)] : qnan));
+                    }
                     float x0, x1;
                     if (LUT) {
                         const uint2 ii = __ldg(lut2 + p);
@@ -682,12 +695,12 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
                 }
                 if ((n_out & 1u) && threadIdx.x == 0u) {                       // the odd last output
                     const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
-                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, mq)] : qnan);
+                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             } else {                                                           // unaligned caller buffer: 16-bit stores
                 for (uint32_t o = threadIdx.x; o < n_out; o += blockDim.x) {
                     const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
-                    dstf[o] = enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, a.magic_q)] : qnan);
+                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? fr[i + 4u * __umulhi(i, a.magic_q)] : qnan);
                 }
             }
         }
@@ -769,12 +782,12 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         const uint32_t nq = cur.d.nq, rc = cur.d.rc;
         // lane l: where slots l and l + 32 come from (the first ring_count slots are the session's ring, carried
         // over from earlier pushes; the rest are this push's quanta), already offset to this lane's 16 bytes
-        const float *ring_base = a.ring + (size_t)cur.d.session * g.half_quanta * Q;
         const uint32_t j0 = lane - rc, j1 = lane + 32u - rc;                 // push quantum behind slot lane / lane + 32
         const uint32_t a0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j0 & 31u);
         const uint32_t b0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j1 & 31u), b1 = __shfl_sync(0xFFFFFFFFu, cur.idx1, j1 & 31u);
-        const float *src0 = lane < rc ? ring_base + (size_t)lane * Q : a.samples + (size_t)a0 * Q;
-        const float *src1 = lane + 32u < rc ? ring_base + (size_t)(lane + 32u) * Q : a.samples + (size_t)(j1 < 32u ? b0 : b1) * Q;
+        // (slots below rc were converted when they arrived -- a.staged -- and are not fetched at all)
+        const float *src0 = a.samples + (size_t)a0 * Q;
+        const float *src1 = a.samples + (size_t)(j1 < 32u ? b0 : b1) * Q;
         // ---- all quanta of the frame in flight at once: one warp-wide 16-byte-per-lane copy per 512-byte quantum.
         // Four slots per trip, addresses first and the four copies back to back (the compiler pads every isolated
         // LDGSTS with three dummy instructions; 32 instructions per quantum in the one-at-a-time form, per ncu).
@@ -785,7 +798,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         ptab[warp][lane + 32u] = src1;
         __syncwarp();
         if (gpq == 32u) {
-            for (uint32_t s0 = warp; s0 < nq; s0 += 4u * nw) {
+            for (uint32_t s0 = rc + warp; s0 < nq; s0 += 4u * nw) {
                 const float *src[4];
 #pragma unroll
                 for (int u = 0; u < 4; u++) src[u] = ptab[warp][min(s0 + (uint32_t)u * nw, 63u)] + 4u * lane;
@@ -796,7 +809,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                 }
             }
         } else {
-            for (uint32_t sl = warp; sl < nq; sl += nw) {
+            for (uint32_t sl = rc + warp; sl < nq; sl += nw) {
                 const float *src = ptab[warp][sl];
 #pragma unroll 1
                 for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(arena + (size_t)sl * pitch + 4u * gi, src + 4u * gi);
@@ -823,13 +836,21 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
             const uint32_t n_in = nq * Q, n_out = cur.n_out;
             int16_t *dstf = a.out + cur.d.off;
             const float qnan = __int_as_float(0x7FC00000);
+            // outputs below `osplit` belong to quanta that were converted when they arrived: copied from a.staged
+            const uint32_t osplit = rc ? __ldg(a.out_lo + rc) : 0u;
+            const int16_t *st = a.staged + (size_t)cur.d.session * a.nout_pad;
             if (a.out_aligned16) {
                 const uint32_t nfull = n_out >> 1, R = g.stride;
                 uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + tid;
                 const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + tid;
                 uint32_t i0 = 2u * tid * R;
                 const uint32_t di = 2u * nthr * R;                              // index step from pair p to pair p + nthr
-                auto pair = [&](uint32_t ia, const uint2 *l) -> uint32_t {
+                auto pair = [&](uint32_t p, uint32_t ia, const uint2 *l) -> uint32_t {
+                    if (2u * p + 1u < osplit) return ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
+                    if (2u * p < osplit) {                                      // the pair straddles the split
+                        const uint32_t i1 = LUT ? __ldg(a.lut + 2u * p + 1u) : ia + R;
+                        return pack_s16x2_sat((int)ld_l2(st + 2u * p), enc_s32(i1 < n_in ? arena[i1 + 4u * __umulhi(i1, mq)] : qnan));
+                    }
                     float x0, x1;
                     if (LUT) {
                         const uint2 ii = __ldg(l);
@@ -844,18 +865,18 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                 };
                 for (uint32_t p = tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
                     const bool second = p + nthr < nfull;
-                    const uint32_t va = pair(i0, lp), vb = second ? pair(i0 + di, lp + nthr) : 0u;
+                    const uint32_t va = pair(p, i0, lp), vb = second ? pair(p + nthr, i0 + di, lp + nthr) : 0u;
                     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp), "r"(va) : "memory");   // streaming: frames are written once
                     if (second) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp + nthr), "r"(vb) : "memory");
                 }
                 if ((n_out & 1u) && tid == 0u) {
                     const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
-                    dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             } else {
                 for (uint32_t o = tid; o < n_out; o += nthr) {
                     const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
-                    dstf[o] = enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             }
         };
@@ -942,9 +963,38 @@ struct AggCommitArgs {
     AggCtl *ctl_next;                // the NEXT push's control block: cleared here
 };
 
-template <bool METER>
-__global__ void __launch_bounds__(256)
-k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, float *__restrict__ ring,
+// Where a quantum that does not flush goes.  A session's waiting quanta are not kept as samples: quantum j of a
+// frame owns the outputs [out_lo[j], out_lo[j + 1]) whatever the frame's final length (the pick sequence does not
+// depend on it, App.tsx:26-30), so they are picked and encoded on arrival and only those ~43 int16 (of 128 floats at
+// 48 kHz) are kept: `staged[session][output]`.  A flush then copies that prefix instead of converting 16 KB of floats.
+struct AggAppendArgs {
+    int16_t *staged;                 // [max_sessions][nout_pad]
+    const uint32_t *out_lo;          // [half_quanta + 1]
+    const uint32_t *lut;             // pick table, or null for an integer ratio
+    uint32_t nout_pad, half_quanta, magic_half_, stride;
+};
+
+// Where one waiting quantum goes: session row, first sample index of its quantum in the frame, its outputs [olo, ohi).
+struct AggStageDesc { uint32_t row, i0, olo, ohi; };
+__device__ __forceinline__ AggStageDesc agg_stage_desc(const AggAppendArgs &ap, uint32_t slot, uint32_t quantum)
+{
+    const uint32_t s = slot / ap.half_quanta, j = slot - s * ap.half_quanta;
+    return AggStageDesc{s, j * quantum, __ldg(ap.out_lo + j), __ldg(ap.out_lo + j + 1u)};
+}
+// The outputs of that quantum, picked from `src` (its samples, in shared memory) by one warp.
+__device__ __forceinline__ void agg_stage_quantum(const AggAppendArgs &ap, const AggStageDesc &d, const float *src, uint32_t lane)
+{
+    int16_t *dst = ap.staged + (size_t)d.row * ap.nout_pad;
+    for (uint32_t o = d.olo + lane; o < d.ohi; o += 32u) {
+        const uint32_t i = (ap.lut ? __ldg(ap.lut + o) : o * ap.stride) - d.i0;   // inside the quantum by the definition of out_lo
+        dst[o] = enc_s16(src[i]);
+    }
+}
+
+// TILE quanta per block step, TILE * 4 threads (64 / 256 for large pushes; 32 / 128 keeps a small push in one wave).
+template <bool METER, uint32_t TILE>
+__global__ void __launch_bounds__(TILE * 4)
+k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, AggAppendArgs ap,
              double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl, AggCommitArgs cm)
 {
     pdl_enter();
@@ -954,72 +1004,48 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
     // copy path runs it after its loads and stores have been issued.
     const CtlHead head = ctl_head(ctl);
     const bool ok = head.status == 0u;
+    // the thread's first commit item is fetched now and stored after the append work, so that its memory round trips
+    // run under the append's (the two are independent); items beyond the grid's size are done in a loop at the end
+    const uint32_t nt = head.n_touched, k0 = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
+    uint32_t c_s = 0, c_fill = 0;
+    double c_last = 0.0;
+    if (k0 < nt) {
+        c_s = ld_l2(cm.touched + k0);
+        if (ok) { c_fill = ld_l2(cm.new_fill + k0); c_last = ld_l2(cm.new_last + k0); }
+    }
     auto commit = [&]() {
-        const uint32_t nt = head.n_touched;
-        if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
-        for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < nt; k += gridDim.x * blockDim.x) {
+        if (k0 < nt) {
+            cm.count[c_s] = 0u;
+            if (ok) { cm.fill[c_s] = c_fill; cm.last_send[c_s] = c_last; }
+        }
+        for (uint32_t k = k0 + gridDim.x * blockDim.x; k < nt; k += gridDim.x * blockDim.x) {
             const uint32_t s = ld_l2(cm.touched + k);
             cm.count[s] = 0u;
             if (ok) { cm.fill[s] = ld_l2(cm.new_fill + k); cm.last_send[s] = ld_l2(cm.new_last + k); }
         }
     };
-    if (!ok || METER) commit();
-    if (!ok) return;
+    if (!ok) { commit(); return; }
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t granules = quantum >> 2;
-    if (!METER) {
-        // A warp looks at 32 consecutive quanta per step -- one coalesced load of their ring slots, one ballot -- and
-        // copies those that stay, four at a time with all four loads in flight before the first store.  A push in
-        // which every quantum flushed costs one pass over dst_slot (6 MB for 1.5 M quanta) and nothing else.
-        const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
-        for (uint32_t base = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32u; base < n; base += warps * 32u) {
-            const uint32_t mine = base + lane < n ? ld_l2(dst_slot + base + lane) : 0xFFFFFFFFu;
-            unsigned live = __ballot_sync(0xFFFFFFFFu, mine != 0xFFFFFFFFu);
-            while (live) {
-                uint32_t q[4], slot[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    q[u] = live ? (uint32_t)__ffs((int)live) - 1u : 32u;          // warp-uniform
-                    if (live) live &= live - 1u;
-                    slot[u] = __shfl_sync(0xFFFFFFFFu, mine, q[u] & 31u);
-                    if (q[u] == 32u) slot[u] = 0xFFFFFFFFu;
-                }
-                if (granules == 32u) {                              // the 128-sample quantum: one float4 per lane
-                    float4 v[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++)
-                        if (slot[u] != 0xFFFFFFFFu) v[u] = __ldg(reinterpret_cast<const float4 *>(samples + (size_t)(base + q[u]) * quantum) + lane);
-#pragma unroll
-                    for (int u = 0; u < 4; u++)
-                        if (slot[u] != 0xFFFFFFFFu) reinterpret_cast<float4 *>(ring + (size_t)slot[u] * quantum)[lane] = v[u];
-                } else {
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        if (slot[u] == 0xFFFFFFFFu) continue;
-                        const float4 *s4 = reinterpret_cast<const float4 *>(samples + (size_t)(base + q[u]) * quantum);
-                        float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)slot[u] * quantum);
-                        for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = __ldg(s4 + gi);
-                    }
-                }
-            }
-        }
-        commit();
-        return;
-    }
-    constexpr uint32_t TILE = 64;
+    constexpr uint32_t NW = TILE / 8u, MW = TILE / 32u;          // warps per block; warps whose lanes meter
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t pitch = quantum + 4u;
     float *arena = reinterpret_cast<float *>(smem_raw);
     __shared__ uint32_t slot_s[TILE];
+    __shared__ AggStageDesc desc_s[TILE];                          // worked out once per quantum (one thread each), not once per lane
     for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
         __syncthreads();
         uint32_t slot = 0xFFFFFFFFu;
         if (threadIdx.x < TILE && i0 + threadIdx.x < n) slot = ld_l2(dst_slot + i0 + threadIdx.x);
-        if (threadIdx.x < TILE) slot_s[threadIdx.x] = slot;
+        if (threadIdx.x < TILE) {
+            slot_s[threadIdx.x] = slot;
+            if (slot != 0xFFFFFFFFu) desc_s[threadIdx.x] = agg_stage_desc(ap, slot, quantum);
+        }
         const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
         if (live == 0) continue;
         if (granules == 32u) {                           // the 128-sample quantum: one warp-wide copy per quantum, no division
-            for (uint32_t t = warp; t < TILE; t += 8u)
+            for (uint32_t t = warp; t < TILE; t += NW)
                 if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
         } else {
             for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
@@ -1029,18 +1055,18 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         }
         cp_async_wait_all();
         __syncthreads();
-        if (slot != 0xFFFFFFFFu) {                        // threads 0..63: the meter of slot t
+        if (METER && slot != 0xFFFFFFFFu) {               // threads 0 .. TILE-1: the meter of slot t
             ring_rms[slot] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
         }
-        // copy out: warps 2..7 start at once, warps 0 and 1 join when their meter lanes are done
-        for (uint32_t t = (warp + 6u) & 7u; t < TILE; t += 8u) {
+        // the quanta's outputs, picked from the staged copies: the other warps start at once, the metering warps join
+        // when their lanes are done.  (Picking straight from global memory -- every third float of a quantum per lane --
+        // was tried for the unmetered case: 300 us per 2^20 quanta, latency-bound at a third of the DRAM rate.)
+        for (uint32_t t = (warp + NW - MW) % NW; t < TILE; t += NW) {
             const uint32_t sl = slot_s[t];
-            if (sl == 0xFFFFFFFFu) continue;
-            const float4 *s4 = reinterpret_cast<const float4 *>(arena + (size_t)t * pitch);
-            float4 *d4 = reinterpret_cast<float4 *>(ring + (size_t)sl * quantum);
-            for (uint32_t gi = lane; gi < granules; gi += 32u) d4[gi] = s4[gi];
+            if (sl != 0xFFFFFFFFu) agg_stage_quantum(ap, desc_s[t], arena + (size_t)t * pitch, lane);
         }
     }
+    commit();
 }
 
 __global__ void k_agg_reset(uint32_t *__restrict__ fill, double *__restrict__ last_send, uint32_t first, uint32_t n, double now_ms)

@@ -19,7 +19,9 @@ struct pcmb200_aggregator {
     double rate = 0;
     bool meter = false;
     // persistent device state
-    float *ring = nullptr;                 // [max_sessions][half_quanta][quantum]
+    int16_t *staged = nullptr;             // [max_sessions][nout_pad]: the waiting quanta of a session, ALREADY converted
+    uint32_t *out_lo = nullptr;            // [half_quanta + 1] first output whose pick falls at or after quantum j
+    uint32_t nout_pad = 0;                 // nout_max rounded up to 8 samples
     double *ring_rms = nullptr;            // [max_sessions][half_quanta] rms of every waiting quantum (meter)
     uint32_t *fill = nullptr, *count = nullptr, *cursor = nullptr;   // [max_sessions]
     double *last_send = nullptr, *level = nullptr;                   // [max_sessions]
@@ -112,7 +114,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b, ab, ctl, (unsigned long long)out_capacity);
 
     AggConvertArgs ca{};
-    ca.samples = samples; ca.ring = a->ring; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
+    ca.samples = samples; ca.staged = a->staged; ca.out_lo = a->out_lo; ca.nout_pad = a->nout_pad; ca.sorted = a->sorted; ca.fdesc = a->fdesc; ca.fdesc_off = a->fdesc_off;
     ca.nout_of = a->nout_of; ca.lut = a->lut; ca.out = out; ca.rms_at = a->rms_at; ca.ctl = ctl; ca.G = a->G;
     ca.magic_q = magic_for(a->geo.quantum); ca.out_aligned16 = aligned(out, 16) ? 1 : 0; ca.hint = ctx->tune.store_hint;
     // frames <= quanta; a frame has about desired_ms worth of quanta, so n / G blocks is an upper bound
@@ -141,17 +143,25 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
                              : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
         agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
     }
+    const AggAppendArgs apd{a->staged, a->out_lo, a->lut, a->nout_pad, a->geo.half_quanta, magic_for(a->geo.half_quanta), a->geo.stride};
     const AggCommitArgs cm{a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, ctl_next};
-    if (a->meter) {
+    if (a->meter)
         agg_launch(ctx, k_agg_levels, blocks_t128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
                    a->level, ctl);
-        const unsigned long long tiles = ((unsigned long long)n + 63ull) / 64ull;
-        agg_launch(ctx, k_agg_append<true>, (unsigned)(tiles < cap ? tiles : cap), 256, a->append_smem, samples, a->dst_slot, a->ring, a->ring_rms, n,
-                   a->geo.quantum, ctl, cm);
-    } else {
-        const unsigned long long warps_blocks = ((unsigned long long)n + 255ull) / 256ull;   // 8 warps x 32 quanta per block step
-        agg_launch(ctx, k_agg_append<false>, (unsigned)(warps_blocks < cap ? warps_blocks : cap), 256, 0, samples, a->dst_slot, a->ring, a->ring_rms, n,
-                   a->geo.quantum, ctl, cm);
+    {
+        // 64 quanta per 256-thread block step; a push small enough to fit one wave of the smaller blocks takes 32 per 128
+        const bool small = ctx->tune.agg_append_tile ? ctx->tune.agg_append_tile == 32 : n <= 32u * 12u * (uint32_t)ctx->sm_count;
+        const unsigned tile = small ? 32u : 64u;
+        const unsigned long long tiles = ((unsigned long long)n + tile - 1) / tile;
+        const unsigned grid = (unsigned)(tiles < cap ? tiles : cap);
+        const size_t smem = small ? a->append_smem / 2 : a->append_smem;
+        if (a->meter) {
+            if (small) agg_launch(ctx, k_agg_append<true, 32>, grid, 128, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+            else agg_launch(ctx, k_agg_append<true, 64>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+        } else {
+            if (small) agg_launch(ctx, k_agg_append<false, 32>, grid, 128, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+            else agg_launch(ctx, k_agg_append<false, 64>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+        }
     }
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(a->h_ctl, ctl, sizeof(AggCtl), cudaMemcpyDeviceToHost, st));
@@ -195,7 +205,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     // Frame arithmetic for every possible frame length, once.  The pick sequence floor(idx), idx += ratio
     // (App.tsx:26-30) does not depend on the input length -- a shorter frame uses a prefix of it -- so ONE
     // table serves every frame length; the per-length part is only the output length (App.tsx:24).
-    std::vector<uint32_t> h_nout, h_lut;
+    std::vector<uint32_t> h_nout, h_lut, h_out_lo;
     try {
         h_nout.assign(max_frame_quanta + 1, 0);
         for (uint32_t nq = 1; nq <= max_frame_quanta; nq++) {
@@ -207,6 +217,14 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
             h_lut.assign((size_t)a->nout_max + 1, 0xFFFFFFFFu);        // one entry of padding: the convert kernel reads the table in pairs
             build_index_table((size_t)max_frame_quanta * quantum, in_rate, a->nout_max, h_lut.data());
         }
+        // out_lo[j]: the first output whose pick index is >= j * quantum (picks never decrease with the output index),
+        // i.e. quantum j of a frame owns the outputs [out_lo[j], out_lo[j + 1]) -- whatever the frame's final length
+        h_out_lo.assign((size_t)max_frame_quanta + 1, 0);
+        for (uint32_t j = 0, o = 0; j <= max_frame_quanta; j++) {
+            const unsigned long long lim = (unsigned long long)j * quantum;
+            while (o < a->nout_max && (a->geo.stride ? (unsigned long long)o * a->geo.stride : (unsigned long long)h_lut[o]) < lim) o++;
+            h_out_lo[j] = o;
+        }
     } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
 
     // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
@@ -217,9 +235,10 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
 
     cudaError_t e = cudaSuccess;
     const size_t S = max_sessions, P = max_push_quanta;
-    const size_t ring_floats = S * max_frame_quanta * quantum;
+    a->nout_pad = (a->nout_max + 7u) & ~7u;
 #define AGG_STEP(call) if (e == cudaSuccess) e = (call)
-    AGG_STEP(agg_alloc(&a->ring, ring_floats));
+    AGG_STEP(agg_alloc(&a->staged, S * (size_t)a->nout_pad));
+    AGG_STEP(agg_alloc(&a->out_lo, (size_t)max_frame_quanta + 1));
     AGG_STEP(agg_alloc(&a->ring_rms, S * max_frame_quanta));
     AGG_STEP(agg_alloc(&a->fill, S));
     AGG_STEP(agg_alloc(&a->count, S));
@@ -257,7 +276,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(cudaMemsetAsync(a->count, 0, S * 4, ctx->stream));
     AGG_STEP(cudaMemsetAsync(a->last_send, 0, S * 8, ctx->stream));
     AGG_STEP(cudaMemsetAsync(a->level, 0, S * 8, ctx->stream));
-    AGG_STEP(cudaMemsetAsync(a->ring, 0, ring_floats * 4, ctx->stream));
+    AGG_STEP(cudaMemsetAsync(a->staged, 0, S * (size_t)a->nout_pad * 2, ctx->stream));
+    AGG_STEP(cudaMemcpyAsync(a->out_lo, h_out_lo.data(), h_out_lo.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     AGG_STEP(cudaMemsetAsync(a->ring_rms, 0, S * max_frame_quanta * 8, ctx->stream));
     AGG_STEP(cudaMemcpyAsync(a->nout_of, h_nout.data(), h_nout.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
     if (a->geo.stride == 0) AGG_STEP(cudaMemcpyAsync(a->lut, h_lut.data(), h_lut.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -271,7 +291,10 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
         AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
         AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
     }
-    AGG_STEP(cudaFuncSetAttribute(k_agg_append<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<true, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<false, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<true, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<false, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
 #undef AGG_STEP
     if (e != cudaSuccess) {
@@ -291,7 +314,7 @@ extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *
     if (!a) return PCMB200_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    void *dev[] = {a->ring, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
+    void *dev[] = {a->staged, a->out_lo, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
                    a->d_arrival, a->d_stage, a->touched, a->sorted, a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill,
                    a->flushed, a->new_last, a->rms_at, a->sums_a, a->sums_b, a->fdesc, a->fdesc_off, a->f_session,
                    a->f_len, a->f_off, a->d_out, a->ctl};
