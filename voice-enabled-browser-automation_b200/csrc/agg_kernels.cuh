@@ -11,15 +11,17 @@
 //   3 k_agg_scatter  sorted[cursor[s]++] = i   (atomic, so the order inside a session is arbitrary ...)
 //   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
 //                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
-//                    writes scratch (the session's new state, per-quantum flush marks and ring slots).
+//                    writes scratch (the session's new state, per-quantum flush marks and staging slots).
 //   5 scan           over quanta: frame index and output offset of every flush, in flush order
 //                    (= ascending i); its apply pass also emits the caller's frame arrays.
-//   6 k_agg_convert_one / _pipe   every flushed frame: its quanta are staged into shared memory with async
-//                    copies -- from the session's ring (quanta carried over from earlier pushes) or
-//                    straight from the push (never written to the ring at all) -- then picked, encoded,
-//                    stored; with the meter on, each quantum's rms is computed from the staged copy.
+//   6 k_agg_convert_one / _pipe   every flushed frame: the quanta carried over from earlier pushes were
+//                    picked and encoded when they arrived (step 8) and are a ready int16 prefix in
+//                    staged[session][] -- copied; this push's quanta are brought into shared memory with
+//                    async copies straight from the push, picked, encoded, stored; with the meter on,
+//                    each of those quanta's rms is computed from the shared-memory copy.
 //   7 k_agg_levels   level = max(rms, level * 0.85) along each session's flushed quanta, in order
-//   8 k_agg_append   quanta that did not flush go to their session's ring (with their rms)
+//   8 k_agg_append   quanta that did not flush are converted NOW: the outputs whose pick falls inside the
+//                    quantum go to staged[session][out_lo[slot] .. out_lo[slot + 1]) (and its rms is stored)
 //   9 (commit, inside the append kernel)   fill / lastSend take their new values; per-push counters are cleared
 // Steps 6-9 look at the push's status word first: if any check failed (unknown session, a buffer
 // longer than max_frame_quanta, too many frames, output too small) they change nothing, which IS the
@@ -40,7 +42,7 @@ struct AggCtl {                  // lives in device memory; copied to the host a
     uint32_t status;
     uint32_t n_touched;
     uint32_t n_frames;
-    uint32_t reserved_;          // (was a count of the quanta that went to a ring: a million threads updating one word cost
+    uint32_t reserved_;          // (was a count of the quanta that did not flush: a million threads updating one word cost
                                  //  more than the early exit it bought the append kernel)
     unsigned long long out_total;   // output samples incl. the padding of every frame to 8 samples
     uint32_t n_listed;           // running total of the per-session index lists (k_agg_reserve)
@@ -50,7 +52,7 @@ struct AggCtl {                  // lives in device memory; copied to the host a
 struct AggFrameDesc {
     uint32_t session;
     uint32_t nq;                 // quanta in the frame
-    uint32_t ring_count;         // of which the first ring_count come from the session's ring
+    uint32_t ring_count;         // of which the first ring_count were waiting in staged[session] (the name predates the int16 staging)
     uint32_t pos;                // the rest: sorted[pos], sorted[pos + 1], ...
 };
 
@@ -377,7 +379,7 @@ __device__ inline void sort_indices(uint32_t *a, uint32_t m)
 
 struct AggWalkOut {
     uint32_t *fl_nq, *fl_ring, *fl_pos;   // [n] per quantum: frame length in quanta if it flushes (else 0), ...
-    uint32_t *dst_slot;                   // [n] ring slot of a quantum that does not flush, else 0xFFFFFFFF
+    uint32_t *dst_slot;                   // [n] staging slot (session * half_quanta*2 + position) of a quantum that does not flush, else 0xFFFFFFFF
     uint32_t *new_fill, *flushed;         // [touched] new fill; push quanta of the session that flushed
     double *new_last;                     // [touched] new lastSend
 };
@@ -706,7 +708,7 @@ k_agg_convert_pipe(AggGeom g, AggConvertArgs a)
         }
 
         if (METER) {
-            // lane <-> slot; ring-carried quanta were metered when they were appended
+            // lane <-> slot; the quanta carried over from earlier pushes were metered when they were appended
             const uint32_t m_warps = (T + 31u) >> 5;
             const uint32_t rot = m_warps < nw ? (it * m_warps) % nw : 0u;
             for (uint32_t sl = (((warp + nw - rot) % nw) << 5) + lane; sl < T; sl += blockDim.x) {
@@ -780,8 +782,8 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
     const uint32_t dst_lane = smem_u32(arena) + 16u * lane, pitch_b = pitch * 4u;
     for (uint32_t it = 0;; it++) {
         const uint32_t nq = cur.d.nq, rc = cur.d.rc;
-        // lane l: where slots l and l + 32 come from (the first ring_count slots are the session's ring, carried
-        // over from earlier pushes; the rest are this push's quanta), already offset to this lane's 16 bytes
+        // lane l: where slots l and l + 32 come from (the first ring_count slots were carried over from earlier
+        // pushes; the rest are this push's quanta), already offset to this lane's 16 bytes
         const uint32_t j0 = lane - rc, j1 = lane + 32u - rc;                 // push quantum behind slot lane / lane + 32
         const uint32_t a0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j0 & 31u);
         const uint32_t b0 = __shfl_sync(0xFFFFFFFFu, cur.idx0, j1 & 31u), b1 = __shfl_sync(0xFFFFFFFFu, cur.idx1, j1 & 31u);
@@ -883,7 +885,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         if (!METER) {
             picks(threadIdx.x, bd);
         } else {
-            // lane <-> slot; ring-carried quanta were metered when they were appended.  A quantum's sum of squares is a
+            // lane <-> slot; carried-over quanta were metered when they were appended.  A quantum's sum of squares is a
             // 128-long dependent chain (~1 300 clocks) during which the arena cannot be refilled, so the metering warps
             // start on it at once and the OTHER warps share the picks; which warps meter rotates from frame to frame so
             // that the chains do not always land on the same scheduler.
@@ -910,7 +912,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
 
 // ---- 7: levels ---------------------------------------------------------------------------------------------------
 // App.tsx:271 along every touched session's FLUSHED quanta, in arrival order: first the quanta that were
-// waiting in its ring (their rms was stored when they were appended), then this push's.
+// waiting from earlier pushes (their rms was stored in ring_rms when they were appended), then this push's.
 __global__ void __launch_bounds__(128)
 k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count, const uint32_t *__restrict__ cursor,
              const uint32_t *__restrict__ fill, const uint32_t *__restrict__ flushed, const double *__restrict__ ring_rms,
@@ -948,11 +950,12 @@ k_agg_levels(AggGeom g, const uint32_t *__restrict__ touched, const uint32_t *__
 }
 
 // ---- 8: append ------------------------------------------------------------------------------------------------------
-// Quanta that did not flush go to their ring slot.  Without the meter: one warp per quantum, 128-bit
-// copies, nothing else.  With the meter the quantum's rms must be accumulated in sample order by ONE
-// lane (handing a running sum from lane to lane costs ~15 warp-instructions per sample), so a CTA stages
-// 64 consecutive quanta of the push in shared memory (16-byte async copies, slot pitch quantum + 4 floats), lane t
-// meters slot t exactly like kernel 2c, and the warps then copy the slots out to the rings.
+// Quanta that did not flush are converted where they stand (AggAppendArgs below).  A CTA brings TILE (32 or 64)
+// consecutive quanta of the push into shared memory with 16-byte async copies (slot pitch quantum + 4 floats) --
+// picking straight from global memory was latency-bound, 300 vs 230 us per 2^20 quanta -- and its warps then
+// pick + encode each waiting quantum's outputs into staged[session][].  With the meter on, lane t first meters
+// slot t exactly like kernel 2c: the rms must be accumulated in sample order by ONE lane (handing a running sum
+// from lane to lane costs ~15 warp-instructions per sample).
 // What the commit step needs (it rides in the append kernel: one launch fewer per push).
 struct AggCommitArgs {
     const uint32_t *touched;
