@@ -162,7 +162,11 @@ PCMB200_API int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in_de
  * (:281-282), and resets buffer and lastSend (:286-287).  The wall clock is injected: arrival_ms[i]
  * is performance.now() at quantum i.  Sessions of one aggregator share the capture rate.
  * Session state, buffers and the flush plan of every push live on the GPU (no host threads).
- *   quantum           samples per quantum, a multiple of 4 (the AudioWorklet quantum is 128)
+ * A session's waiting quanta are kept CONVERTED (the int16 outputs each quantum owns do not depend on
+ * the frame's final length, App.tsx:26-30), so device memory per session is about
+ * 2 * N_out(max_frame_quanta * quantum) + 8 * max_frame_quanta + 28 bytes -- 3 KB for 32 quanta at 48 kHz
+ * (a buffer of samples would be 16 KB).
+ *   quantum          samples per quantum, a multiple of 4 (the AudioWorklet quantum is 128)
  *   max_frame_quanta  longest frame, in quanta (a push that would exceed it is rejected whole); one frame
  *                     must fit on chip: max_frame_quanta * (quantum + 4) * 4 bytes <= 200 KB
  *   max_push_quanta   most quanta in one push;   max_out_samples_per_push  output arena (host path)
@@ -278,8 +282,9 @@ PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
  * "slice_bytes" (host pipeline slice), "meter_kernel", "ws_smem_kb", "ws_pairs", "ws_depth", "ws_rows", "ws_chunk",
  * "ws_cvt_quanta" (kernel 2d: frames of at least this many quanta widen float -> double in hardware; 0 = never);
  * for the aggregator "agg_block" / "agg_stage_kb" (convert kernel: threads per CTA, staging memory per step; read
- * when an aggregator is created), "agg_persistent" (convert grid = the CTAs resident at once) and "agg_pdl" (the
- * kernels of a push are chained by programmatic dependent launch; 0 = plain launches).
+ * when an aggregator is created), "agg_persistent" (convert grid = the CTAs resident at once), "agg_pdl" (the
+ * kernels of a push are chained by programmatic dependent launch; 0 = plain launches), "agg_walk_regs" (flush-rule
+ * kernel: index lists of up to 32 or 4 quanta in registers; 0 = chosen from the previous push).
  * "overlap_ticks" = 1 changes behaviour, not just speed: consecutive device-resident dense integer-ratio
  * calls on this context may then OVERLAP on the GPU (the next tick's blocks start while the previous
  * tick's last wave drains; programmatic dependent launch).  Only for callers whose consecutive calls

@@ -240,15 +240,18 @@ def test_aggregator_device_resident_push_and_wait(ctx):
         b.free()
 
 
-@pytest.mark.parametrize("rate, max_q", [(96000, 64), (96000, 96), (88200, 64), (16000, 32), (8000, 32), (24000, 32), (192000, 96)])
+@pytest.mark.parametrize("rate, max_q", [(96000, 64), (96000, 96), (88200, 64), (16000, 32), (8000, 32), (24000, 32), (192000, 96),
+                                         (22050, 32), (11025, 32), (32000, 32), (47999, 32), (48001, 32), (12345.678, 32), (176400, 96)])
 def test_aggregator_long_frames(ctx, rate, max_q):
     """60 ms at 96 kHz is 45-46 quanta per frame: more than one warp's worth of push quanta per frame, and
     -- with pushes cut at uneven places -- more than 32 quanta carried over in a session's buffer.  max_q = 64
     takes the one-frame-per-step convert kernel (descriptors in registers, two index registers per lane),
     max_q = 96 the general one; 88.2 kHz adds the pick table.  The low rates run the one-frame kernel at ratio 1
     (16 kHz: encode only), 1.5 (24 kHz, table) and 0.5 (8 kHz: twice as many outputs as inputs, table).
+    The second line of rates: picks by table at ratios whose per-quantum output count varies from quantum to quantum
+    (the staging of waiting quanta cuts the output sequence at exactly those places).
     Frames and levels against the oracle."""
-    rng = np.random.RandomState(rate // 100 + max_q)
+    rng = np.random.RandomState(int(rate) // 100 + max_q)
     S, q_ms = 23, 128e3 / rate
     nq = int(400 / q_ms)
     audio = (rng.uniform(-1.05, 1.05, size=(S, nq, 128)) * rng.uniform(0.1, 1, size=(S, 1, 1))).astype(np.float32)
@@ -315,14 +318,16 @@ def test_aggregator_unaligned_device_output(ctx, rate, max_q):
 
 
 @pytest.mark.parametrize("knobs", [dict(agg_pdl=0), dict(agg_persistent=0), dict(agg_block=64), dict(agg_block=256),
-                                   dict(agg_block=128, agg_stage_kb=68), dict(agg_block=256, agg_stage_kb=51, agg_pdl=0)])
+                                   dict(agg_block=128, agg_stage_kb=68), dict(agg_block=256, agg_stage_kb=51, agg_pdl=0),
+                                   dict(agg_walk_regs=4), dict(agg_walk_regs=32)])
 @pytest.mark.parametrize("rate", [48000, 44100])
 def test_aggregator_every_kernel_form(ctx, knobs, rate):
     """The tuning knobs choose between kernel forms (one frame per step with descriptors in registers / several
     frames per step with shared-memory descriptors; persistent or oversized grid; plain or programmatic dependent
-    launches).  Every form must give the oracle's frames and levels: 700 sessions, buffers carried across three
+    launches; the flush-rule kernel sorting its lists of 9-12 quanta in registers or -- forced to the streaming
+    build -- in global memory).  Every form must give the oracle's frames and levels: 700 sessions, buffers carried across three
     pushes, sessions interleaved at random, the meter on."""
-    defaults = dict(agg_pdl=1, agg_persistent=1, agg_block=128, agg_stage_kb=20)
+    defaults = dict(agg_pdl=1, agg_persistent=1, agg_block=128, agg_stage_kb=20, agg_walk_regs=0)
     rng = np.random.RandomState(sum(knobs.values()) + rate // 100)
     S, q_ms, per_push = 700, 128e3 / rate, (10, 9, 12)
     try:

@@ -384,6 +384,11 @@ struct AggWalkOut {
     double *new_last;                     // [touched] new lastSend
 };
 
+// MREG: the longest index list kept in registers (longer ones are sorted in global memory).  32 covers a 60 ms frame
+// arriving in one push, at 96 registers per thread -- 640 threads per SM, which is what a push of 2^20 sessions with
+// ONE quantum each then pays for: 51 us, against 20 for the MREG = 4 build of the same code.  The host picks the
+// build from the shape of the previous push (quanta per touched session); either is correct for any push.
+template <uint32_t MREG>
 __global__ void __launch_bounds__(128)
 k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count,
            const uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted, const uint32_t *__restrict__ fill,
@@ -415,22 +420,22 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     };
     // The rule is sequential in `last`, but the addresses are not: arrival times are fetched in batches of 8 (one
     // memory round trip per batch instead of one per quantum -- the kernel was a chain of dependent misses).
-    constexpr uint32_t B = 8;
-    if (m <= 32u) {
+    constexpr uint32_t B = MREG < 8u ? MREG : 8u;
+    if (m <= MREG) {
         // The usual case (~23 quanta per 60 ms, 1 per push when streaming): the index list lives in registers.
         // Arrival order by a bitonic network -- 240 compare-exchanges, no memory traffic, no divergence; the
         // in-place insertion sort this replaces stored to the list on every step and then waited for its own
         // stores to come back from L2 (a third of the kernel, ncu).
-        uint32_t v[32];
+        uint32_t v[MREG];
 #pragma unroll
-        for (int u = 0; u < 32; u++) v[u] = (uint32_t)u < m ? ld_l2(list + u) : 0xFFFFFFFFu;
+        for (int u = 0; u < (int)MREG; u++) v[u] = (uint32_t)u < m ? ld_l2(list + u) : 0xFFFFFFFFu;
         if (m > 1u) {
 #pragma unroll
-            for (int kk = 2; kk <= 32; kk <<= 1) {
+            for (int kk = 2; kk <= (int)MREG; kk <<= 1) {
 #pragma unroll
                 for (int jj = kk >> 1; jj > 0; jj >>= 1) {
 #pragma unroll
-                    for (int i = 0; i < 32; i++) {
+                    for (int i = 0; i < (int)MREG; i++) {
                         const int l = i ^ jj;
                         if (l > i) {
                             const uint32_t lo = min(v[i], v[l]), hi = max(v[i], v[l]);
@@ -442,10 +447,10 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 32; u++) if ((uint32_t)u < m) list[u] = v[u];  // the convert and level kernels read it
+            for (int u = 0; u < (int)MREG; u++) if ((uint32_t)u < m) list[u] = v[u];  // the convert and level kernels read it
         }
 #pragma unroll
-        for (int b0 = 0; b0 < 32; b0 += (int)B) {
+        for (int b0 = 0; b0 < (int)MREG; b0 += (int)B) {
             if ((uint32_t)b0 < m) {
                 double at[B];
 #pragma unroll
@@ -458,7 +463,7 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
         // quanta after the last flush stay in the session's buffer: behind what was there if nothing flushed
         const uint32_t first_slot = s * g.half_quanta + (frame_start == 0u ? c0 : 0u);
 #pragma unroll
-        for (int u = 0; u < 32; u++)
+        for (int u = 0; u < (int)MREG; u++)
             if ((uint32_t)u < m) o.dst_slot[v[u]] = (uint32_t)u >= frame_start ? first_slot + ((uint32_t)u - frame_start) : 0xFFFFFFFFu;
     } else {
         sort_indices(list, m);
@@ -759,7 +764,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
     };
     struct Frame {
         Desc d;
-        uint32_t idx0, idx1, n_out;
+        uint32_t idx0, idx1, n_out, osplit;                                   // outputs below osplit were converted on arrival
     };
     auto fetch_desc = [&](uint32_t fi) -> Desc {
         const uint4 raw = __ldcg(reinterpret_cast<const uint4 *>(a.fdesc + fi));   // {session, nq, ring_count, pos}
@@ -772,6 +777,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
         fr.idx0 = lane < npush ? ld_l2(a.sorted + d.pos + lane) : 0u;
         fr.idx1 = lane + 32u < npush ? ld_l2(a.sorted + d.pos + lane + 32u) : 0u;
         fr.n_out = __ldg(a.nout_of + d.nq);
+        fr.osplit = d.rc ? __ldg(a.out_lo + d.rc) : 0u;
         return fr;
     };
     const uint32_t stride_f = gridDim.x;
@@ -818,6 +824,16 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
             }
         }
         __syncwarp();                                      // the next trip rewrites the table
+        // The outputs of the carried-over quanta (converted when they arrived, a.staged) ride in the SAME round trip: the
+        // arena slots below rc hold nothing, and rc quanta's outputs fit there at any ratio >= quantum / (quantum + 4) / 2
+        // (8 kHz and up).  Fetching them in `picks`, after the wait, cost every such frame a second trip to DRAM -- the
+        // whole time of a streaming flush (1 new quantum, 22 carried over: 1.5 ms per 2^20 frames of 4.4 KB traffic each).
+        const uint32_t osplit = cur.osplit, pre_chunks = (osplit * 2u + 15u) >> 4;
+        const bool pre_smem = pre_chunks * 16u <= rc * pitch_b;                 // block-uniform
+        const int16_t *st = a.staged + (size_t)cur.d.session * a.nout_pad;
+        if (pre_smem)
+            for (uint32_t c = threadIdx.x; c < pre_chunks; c += bd)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(arena) + 16u * c), "l"(st + 8u * c) : "memory");
         asm volatile("cp.async.commit_group;" ::: "memory");
         // the frame after this one: its descriptor is here already (fetched a trip ago), so its index list can be asked
         // for now; and the descriptor of the frame after that.  Both land while this frame's copies are in flight.
@@ -838,20 +854,30 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
             const uint32_t n_in = nq * Q, n_out = cur.n_out;
             int16_t *dstf = a.out + cur.d.off;
             const float qnan = __int_as_float(0x7FC00000);
-            // outputs below `osplit` belong to quanta that were converted when they arrived: copied from a.staged
-            const uint32_t osplit = rc ? __ldg(a.out_lo + rc) : 0u;
-            const int16_t *st = a.staged + (size_t)cur.d.session * a.nout_pad;
+            // outputs below `osplit` belong to quanta that were converted when they arrived: they sit at the front of
+            // the arena (or, at ratios below 1/2, still in a.staged)
+            const uint32_t *pre32 = reinterpret_cast<const uint32_t *>(arena);
+            const int16_t *pre16 = reinterpret_cast<const int16_t *>(arena);
+            auto staged16 = [&](uint32_t o) -> int16_t { return pre_smem ? pre16[o] : ld_l2(st + o); };
             if (a.out_aligned16) {
                 const uint32_t nfull = n_out >> 1, R = g.stride;
-                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + tid;
-                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + tid;
-                uint32_t i0 = 2u * tid * R;
+                // the whole 16-byte pieces of that prefix are a straight copy (a streaming flush is 22 carried-over quanta
+                // and one new one: through the pair loop below the copy cost 30 instructions per pair, and the kernel was
+                // issue-bound at 1 090 warp-instructions per frame, ncu)
+                const uint32_t p0 = pre_smem ? (osplit >> 3) << 2 : 0u;         // first pair the pair loop handles
+                for (uint32_t c = tid; c < (p0 >> 2); c += nthr) {
+                    const uint4 v = reinterpret_cast<const uint4 *>(arena)[c];
+                    asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<uint4 *>(dstf) + c), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+                }
+                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + p0 + tid;
+                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + p0 + tid;
+                uint32_t i0 = 2u * (p0 + tid) * R;
                 const uint32_t di = 2u * nthr * R;                              // index step from pair p to pair p + nthr
                 auto pair = [&](uint32_t p, uint32_t ia, const uint2 *l) -> uint32_t {
-                    if (2u * p + 1u < osplit) return ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
+                    if (2u * p + 1u < osplit) return pre_smem ? pre32[p] : ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
                     if (2u * p < osplit) {                                      // the pair straddles the split
                         const uint32_t i1 = LUT ? __ldg(a.lut + 2u * p + 1u) : ia + R;
-                        return pack_s16x2_sat((int)ld_l2(st + 2u * p), enc_s32(i1 < n_in ? arena[i1 + 4u * __umulhi(i1, mq)] : qnan));
+                        return pack_s16x2_sat((int)staged16(2u * p), enc_s32(i1 < n_in ? arena[i1 + 4u * __umulhi(i1, mq)] : qnan));
                     }
                     float x0, x1;
                     if (LUT) {
@@ -865,7 +891,7 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                     }
                     return pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
                 };
-                for (uint32_t p = tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
+                for (uint32_t p = p0 + tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
                     const bool second = p + nthr < nfull;
                     const uint32_t va = pair(p, i0, lp), vb = second ? pair(p + nthr, i0 + di, lp + nthr) : 0u;
                     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp), "r"(va) : "memory");   // streaming: frames are written once
@@ -873,12 +899,12 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                 }
                 if ((n_out & 1u) && tid == 0u) {
                     const uint32_t o = n_out - 1u, i = LUT ? __ldg(a.lut + o) : o * R;
-                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                    dstf[o] = o < osplit ? staged16(o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             } else {
                 for (uint32_t o = tid; o < n_out; o += nthr) {
                     const uint32_t i = LUT ? __ldg(a.lut + o) : o * g.stride;
-                    dstf[o] = o < osplit ? ld_l2(st + o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
+                    dstf[o] = o < osplit ? staged16(o) : enc_s16(i < n_in ? arena[i + 4u * __umulhi(i, mq)] : qnan);
                 }
             }
         };
@@ -973,42 +999,45 @@ struct AggCommitArgs {
 struct AggAppendArgs {
     int16_t *staged;                 // [max_sessions][nout_pad]
     const uint32_t *out_lo;          // [half_quanta + 1]
-    const uint32_t *lut;             // pick table, or null for an integer ratio
-    uint32_t nout_pad, half_quanta, magic_half_, stride;
+    const uint32_t *lut;             // pick table (one entry of padding), or null for an integer ratio
+    uint32_t nout_pad, half_quanta, stride;
+    uint32_t pairs, magic_pairs;     // aligned output PAIRS a quantum's outputs can touch (the most over all positions), >= 2
 };
 
-// Where one waiting quantum goes: session row, first sample index of its quantum in the frame, its outputs [olo, ohi).
+// Where one waiting quantum goes: session row (0xFFFFFFFF: the quantum flushed, nothing to do), first sample index of
+// its quantum in the frame, its outputs [olo, ohi).
 struct AggStageDesc { uint32_t row, i0, olo, ohi; };
 __device__ __forceinline__ AggStageDesc agg_stage_desc(const AggAppendArgs &ap, uint32_t slot, uint32_t quantum)
 {
     const uint32_t s = slot / ap.half_quanta, j = slot - s * ap.half_quanta;
     return AggStageDesc{s, j * quantum, __ldg(ap.out_lo + j), __ldg(ap.out_lo + j + 1u)};
 }
-// The outputs of that quantum, picked from `src` (its samples, in shared memory) by one warp.
-__device__ __forceinline__ void agg_stage_quantum(const AggAppendArgs &ap, const AggStageDesc &d, const float *src, uint32_t lane)
-{
-    int16_t *dst = ap.staged + (size_t)d.row * ap.nout_pad;
-    for (uint32_t o = d.olo + lane; o < d.ohi; o += 32u) {
-        const uint32_t i = (ap.lut ? __ldg(ap.lut + o) : o * ap.stride) - d.i0;   // inside the quantum by the definition of out_lo
-        dst[o] = enc_s16(src[i]);
-    }
-}
 
 // TILE quanta per block step, TILE * 4 threads (64 / 256 for large pushes; 32 / 128 keeps a small push in one wave).
+// The picks: a work item is one ALIGNED PAIR of outputs of one quantum of the tile, items dealt to threads round-robin
+// (item f -> quantum f / pairs, pair f % pairs).  The warp-per-quantum form this replaces ran two passes of 32 lanes
+// over ~43 outputs with 16-bit stores and ~26 instructions of per-quantum preamble per warp: 82 of the kernel's 109
+// warp-instructions per quantum (ncu, 2^20 quanta that all wait: issue-active 50 %, 211 us).  Now 43 of 72, 191 us.
+// What is left is not the kernel's to give: a software-pipelined persistent form (slots read two tiles ahead, tile
+// k+1 in flight into a second buffer while tile k is picked) measured 206 us, the plain ring copy this design
+// replaced 176 us for 1.7x the bytes -- every form lands on ~2^20 scattered row activations per push (one 86-byte
+// write per session, plus the read that completes its partial sectors: DRAM moves 0.63 + 0.15 GB for 0.54 + 0.09).
+// (register budget stated: left alone, ptxas settles on 32 registers and spills the prefetched commit item)
 template <bool METER, uint32_t TILE>
-__global__ void __launch_bounds__(TILE * 4)
+__global__ void __launch_bounds__(TILE * 4, (METER ? 256 : 384) / TILE)
 k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, AggAppendArgs ap,
              double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl, AggCommitArgs cm)
 {
     pdl_enter();
     // ---- 9: commit.  fill / lastSend of every touched session take their new values (only if the push stands) and
     // the per-push counters are cleared (always: the next push starts from clean counters).  The append work neither
-    // reads nor writes any of this, so where the commit sits in the kernel is only a matter of overlap: the plain
-    // copy path runs it after its loads and stores have been issued.
+    // reads nor writes any of this, so where the commit sits in the kernel is only a matter of overlap: the thread's
+    // first commit item is fetched now and stored after the append work, so that its memory round trips run under the
+    // append's; items beyond the grid's size are done in a loop at the end.  (One call site: as a lambda called from
+    // two places the commit was not inlined, its captures went through the stack, and the very first thing a thread
+    // did was to wait for the prefetch it was supposed to overlap -- 5 % of the kernel's stall samples.)
     const CtlHead head = ctl_head(ctl);
     const bool ok = head.status == 0u;
-    // the thread's first commit item is fetched now and stored after the append work, so that its memory round trips
-    // run under the append's (the two are independent); items beyond the grid's size are done in a loop at the end
     const uint32_t nt = head.n_touched, k0 = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x == 0 && threadIdx.x == 0) *cm.ctl_next = AggCtl{};
     uint32_t c_s = 0, c_fill = 0;
@@ -1017,59 +1046,83 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         c_s = ld_l2(cm.touched + k0);
         if (ok) { c_fill = ld_l2(cm.new_fill + k0); c_last = ld_l2(cm.new_last + k0); }
     }
-    auto commit = [&]() {
-        if (k0 < nt) {
-            cm.count[c_s] = 0u;
-            if (ok) { cm.fill[c_s] = c_fill; cm.last_send[c_s] = c_last; }
-        }
-        for (uint32_t k = k0 + gridDim.x * blockDim.x; k < nt; k += gridDim.x * blockDim.x) {
-            const uint32_t s = ld_l2(cm.touched + k);
-            cm.count[s] = 0u;
-            if (ok) { cm.fill[s] = ld_l2(cm.new_fill + k); cm.last_send[s] = ld_l2(cm.new_last + k); }
-        }
-    };
-    if (!ok) { commit(); return; }
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t granules = quantum >> 2;
-    constexpr uint32_t NW = TILE / 8u, MW = TILE / 32u;          // warps per block; warps whose lanes meter
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const uint32_t pitch = quantum + 4u;
-    float *arena = reinterpret_cast<float *>(smem_raw);
-    __shared__ uint32_t slot_s[TILE];
-    __shared__ AggStageDesc desc_s[TILE];                          // worked out once per quantum (one thread each), not once per lane
-    for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
-        __syncthreads();
-        uint32_t slot = 0xFFFFFFFFu;
-        if (threadIdx.x < TILE && i0 + threadIdx.x < n) slot = ld_l2(dst_slot + i0 + threadIdx.x);
-        if (threadIdx.x < TILE) {
-            slot_s[threadIdx.x] = slot;
-            if (slot != 0xFFFFFFFFu) desc_s[threadIdx.x] = agg_stage_desc(ap, slot, quantum);
-        }
-        const int live = __syncthreads_count(slot != 0xFFFFFFFFu);
-        if (live == 0) continue;
-        if (granules == 32u) {                           // the 128-sample quantum: one warp-wide copy per quantum, no division
-            for (uint32_t t = warp; t < TILE; t += NW)
-                if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
-        } else {
-            for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
-                const uint32_t t = idx / granules, gi = idx - t * granules;
-                if (slot_s[t] != 0xFFFFFFFFu) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+    if (ok) {
+        constexpr uint32_t DEAD = 0xFFFFFFFFu, NW = TILE / 8u;     // warps per block
+        const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+        const uint32_t granules = quantum >> 2;
+        extern __shared__ __align__(128) unsigned char smem_raw[];
+        const uint32_t pitch = quantum + 4u;
+        float *arena = reinterpret_cast<float *>(smem_raw);
+        __shared__ AggStageDesc desc_s[TILE];                      // worked out once per quantum (one thread each), not once per item
+        for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
+            __syncthreads();
+            uint32_t slot = DEAD;
+            if (threadIdx.x < TILE) {
+                if (i0 + threadIdx.x < n) slot = ld_l2(dst_slot + i0 + threadIdx.x);
+                AggStageDesc d{DEAD, 0u, 0u, 0u};
+                if (slot != DEAD) d = agg_stage_desc(ap, slot, quantum);
+                desc_s[threadIdx.x] = d;
+            }
+            const int live = __syncthreads_count(slot != DEAD);
+            if (live == 0) continue;
+            if (granules == 32u) {                       // the 128-sample quantum: one warp-wide copy per quantum, no division
+                for (uint32_t t = warp; t < TILE; t += NW)
+                    if (desc_s[t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
+            } else {
+                for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
+                    const uint32_t t = idx / granules, gi = idx - t * granules;
+                    if (desc_s[t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+                }
+            }
+            cp_async_wait_all();
+            __syncthreads();
+            auto picks = [&](uint32_t tid, uint32_t nthr) {
+                for (uint32_t f = tid; f < TILE * ap.pairs; f += nthr) {
+                    const uint32_t t = __umulhi(f, ap.magic_pairs), q = f - t * ap.pairs;
+                    const AggStageDesc d = desc_s[t];
+                    const uint32_t p = (d.olo & ~1u) + 2u * q;                  // the pair (p, p + 1), p even
+                    if (d.row == DEAD || p >= d.ohi) continue;
+                    const bool lo_ok = p >= d.olo, hi_ok = p + 1u < d.ohi;      // at least one holds
+                    uint32_t ia, ib;
+                    if (ap.lut) {
+                        const uint2 ii = __ldg(reinterpret_cast<const uint2 *>(ap.lut + p));
+                        ia = ii.x; ib = ii.y;
+                    } else {
+                        ia = p * ap.stride; ib = ia + ap.stride;
+                    }
+                    // picks of [olo, ohi) lie inside the quantum by the definition of out_lo
+                    const float *src = arena + (size_t)t * pitch;
+                    const float x0 = lo_ok ? src[ia - d.i0] : 0.0f, x1 = hi_ok ? src[ib - d.i0] : 0.0f;
+                    const uint32_t v = pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
+                    int16_t *dst = ap.staged + (size_t)d.row * ap.nout_pad + p;
+                    if (lo_ok && hi_ok) *reinterpret_cast<uint32_t *>(dst) = v;
+                    else if (lo_ok) dst[0] = (int16_t)(v & 0xFFFFu);
+                    else dst[1] = (int16_t)(v >> 16);
+                }
+            };
+            if (METER) {
+                // threads 0 .. TILE-1 meter slot t (a 128-long dependent chain each); the other three quarters of the
+                // block share the picks meanwhile
+                if (threadIdx.x < TILE) {
+                    if (slot != DEAD)
+                        ring_rms[slot] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
+                } else {
+                    picks(threadIdx.x - TILE, blockDim.x - TILE);
+                }
+            } else {
+                picks(threadIdx.x, blockDim.x);
             }
         }
-        cp_async_wait_all();
-        __syncthreads();
-        if (METER && slot != 0xFFFFFFFFu) {               // threads 0 .. TILE-1: the meter of slot t
-            ring_rms[slot] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
-        }
-        // the quanta's outputs, picked from the staged copies: the other warps start at once, the metering warps join
-        // when their lanes are done.  (Picking straight from global memory -- every third float of a quantum per lane --
-        // was tried for the unmetered case: 300 us per 2^20 quanta, latency-bound at a third of the DRAM rate.)
-        for (uint32_t t = (warp + NW - MW) % NW; t < TILE; t += NW) {
-            const uint32_t sl = slot_s[t];
-            if (sl != 0xFFFFFFFFu) agg_stage_quantum(ap, desc_s[t], arena + (size_t)t * pitch, lane);
-        }
     }
-    commit();
+    if (k0 < nt) {
+        cm.count[c_s] = 0u;
+        if (ok) { cm.fill[c_s] = c_fill; cm.last_send[c_s] = c_last; }
+    }
+    for (uint32_t k = k0 + gridDim.x * blockDim.x; k < nt; k += gridDim.x * blockDim.x) {
+        const uint32_t s = ld_l2(cm.touched + k);
+        cm.count[s] = 0u;
+        if (ok) { cm.fill[s] = ld_l2(cm.new_fill + k); cm.last_send[s] = ld_l2(cm.new_last + k); }
+    }
 }
 
 __global__ void k_agg_reset(uint32_t *__restrict__ fill, double *__restrict__ last_send, uint32_t first, uint32_t n, double now_ms)

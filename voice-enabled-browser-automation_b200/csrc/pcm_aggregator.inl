@@ -43,6 +43,8 @@ struct pcmb200_aggregator {
     AggCtl *ctl = nullptr;                 // device: two blocks, used by alternate pushes (see agg_enqueue)
     int ctl_idx = 0;
     AggCtl *h_ctl = nullptr;               // pinned copy
+    uint32_t pairs = 2;                    // aligned output pairs per quantum, at most (append kernel)
+    uint32_t prev_n = 0;                   // quanta in the previous push (with h_ctl->n_touched: which walk kernel to take)
     // convert kernel geometry
     uint32_t G = 1;
     size_t convert_pipe_smem = 0, convert_one_smem = 0, append_smem = 0;
@@ -108,7 +110,15 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     agg_launch(ctx, k_agg_reserve, blocks_t, 256, 0, a->touched, a->count, a->cursor, ctl);
     agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, ctl);
     AggWalkOut wo{a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill, a->flushed, a->new_last};
-    agg_launch(ctx, k_agg_walk, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
+    // which build of the walk kernel: index lists of up to 32 quanta in registers (640 threads per SM), or up to 4 (2.5x
+    // the threads) when the previous push averaged at most two quanta per touched session -- the streaming regime.
+    // h_ctl still holds the previous push's record (it was waited for: one push may be pending).  Both are correct for
+    // any push; a wrong guess costs time only.
+    const bool short_lists = ctx->tune.agg_walk_regs == 4 ||
+        (ctx->tune.agg_walk_regs == 0 && a->prev_n != 0 && a->h_ctl->n_touched != 0 && a->prev_n <= 2u * a->h_ctl->n_touched);
+    a->prev_n = n;
+    if (short_lists) agg_launch(ctx, k_agg_walk<4>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
+    else agg_launch(ctx, k_agg_walk<32>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     agg_launch(ctx, k_scan_reduce, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b);
     agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b, ab, ctl, (unsigned long long)out_capacity);
@@ -143,14 +153,14 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
                              : (a->lut ? k_agg_convert_pipe<false, true> : k_agg_convert_pipe<false, false>);
         agg_launch(ctx, kern, (unsigned)conv_blocks, conv_threads, a->convert_pipe_smem, a->geo, ca);
     }
-    const AggAppendArgs apd{a->staged, a->out_lo, a->lut, a->nout_pad, a->geo.half_quanta, magic_for(a->geo.half_quanta), a->geo.stride};
+    const AggAppendArgs apd{a->staged, a->out_lo, a->lut, a->nout_pad, a->geo.half_quanta, a->geo.stride, a->pairs, magic_for(a->pairs)};
     const AggCommitArgs cm{a->touched, a->count, a->fill, a->last_send, a->new_fill, a->new_last, ctl_next};
     if (a->meter)
         agg_launch(ctx, k_agg_levels, blocks_t128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
                    a->level, ctl);
     {
         // 64 quanta per 256-thread block step; a push small enough to fit one wave of the smaller blocks takes 32 per 128
-        const bool small = ctx->tune.agg_append_tile ? ctx->tune.agg_append_tile == 32 : n <= 32u * 12u * (uint32_t)ctx->sm_count;
+        const bool small = n <= 32u * 12u * (uint32_t)ctx->sm_count;
         const unsigned tile = small ? 32u : 64u;
         const unsigned long long tiles = ((unsigned long long)n + tile - 1) / tile;
         const unsigned grid = (unsigned)(tiles < cap ? tiles : cap);
@@ -225,6 +235,11 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
             while (o < a->nout_max && (a->geo.stride ? (unsigned long long)o * a->geo.stride : (unsigned long long)h_lut[o]) < lim) o++;
             h_out_lo[j] = o;
         }
+        // the append kernel deals out aligned output pairs: the most any quantum position can touch
+        a->pairs = 2;
+        for (uint32_t j = 0; j < max_frame_quanta; j++)
+            if (h_out_lo[j + 1] > h_out_lo[j])
+                a->pairs = std::max(a->pairs, ((h_out_lo[j + 1] + 1u) / 2u) - (h_out_lo[j] / 2u));
     } catch (const std::bad_alloc &) { delete a; return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed"); }
 
     // frames per convert step: as many whole worst-case frames as fit in ~64 KB, at least one
