@@ -869,16 +869,24 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                     const uint4 v = reinterpret_cast<const uint4 *>(arena)[c];
                     asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(reinterpret_cast<uint4 *>(dstf) + c), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
                 }
-                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + p0 + tid;
-                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + p0 + tid;
-                uint32_t i0 = 2u * (p0 + tid) * R;
-                const uint32_t di = 2u * nthr * R;                              // index step from pair p to pair p + nthr
-                auto pair = [&](uint32_t p, uint32_t ia, const uint2 *l) -> uint32_t {
-                    if (2u * p + 1u < osplit) return pre_smem ? pre32[p] : ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
-                    if (2u * p < osplit) {                                      // the pair straddles the split
-                        const uint32_t i1 = LUT ? __ldg(a.lut + 2u * p + 1u) : ia + R;
-                        return pack_s16x2_sat((int)staged16(2u * p), enc_s32(i1 < n_in ? arena[i1 + 4u * __umulhi(i1, mq)] : qnan));
+                // the few pairs left of the prefix (less than one 16-byte piece, and the pair that straddles the split if
+                // osplit is odd) each by one thread; kept out of the main loop, whose pairs then need no test
+                const uint32_t psplit = min((osplit + 1u) >> 1, nfull);
+                for (uint32_t p = p0 + tid; p < psplit; p += nthr) {
+                    uint32_t v;
+                    if (2u * p + 1u < osplit) {
+                        v = pre_smem ? pre32[p] : ld_l2(reinterpret_cast<const uint32_t *>(st) + p);
+                    } else {
+                        const uint32_t i1 = LUT ? __ldg(a.lut + 2u * p + 1u) : (2u * p + 1u) * R;
+                        v = pack_s16x2_sat((int)staged16(2u * p), enc_s32(i1 < n_in ? arena[i1 + 4u * __umulhi(i1, mq)] : qnan));
                     }
+                    reinterpret_cast<uint32_t *>(dstf)[p] = v;
+                }
+                uint32_t *dp = reinterpret_cast<uint32_t *>(dstf) + psplit + tid;
+                const uint2 *lp = reinterpret_cast<const uint2 *>(a.lut) + psplit + tid;
+                uint32_t i0 = 2u * (psplit + tid) * R;
+                const uint32_t di = 2u * nthr * R;                              // index step from pair p to pair p + nthr
+                auto pair = [&](uint32_t ia, const uint2 *l) -> uint32_t {
                     float x0, x1;
                     if (LUT) {
                         const uint2 ii = __ldg(l);
@@ -891,9 +899,9 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
                     }
                     return pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
                 };
-                for (uint32_t p = p0 + tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
+                for (uint32_t p = psplit + tid; p < nfull; p += 2u * nthr, dp += 2u * nthr, lp += 2u * nthr, i0 += 2u * di) {
                     const bool second = p + nthr < nfull;
-                    const uint32_t va = pair(p, i0, lp), vb = second ? pair(p + nthr, i0 + di, lp + nthr) : 0u;
+                    const uint32_t va = pair(i0, lp), vb = second ? pair(i0 + di, lp + nthr) : 0u;
                     asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp), "r"(va) : "memory");   // streaming: frames are written once
                     if (second) asm volatile("st.global.cs.b32 [%0], %1;" ::"l"(dp + nthr), "r"(vb) : "memory");
                 }
@@ -1022,8 +1030,11 @@ __device__ __forceinline__ AggStageDesc agg_stage_desc(const AggAppendArgs &ap, 
 // k+1 in flight into a second buffer while tile k is picked) measured 206 us, the plain ring copy this design
 // replaced 176 us for 1.7x the bytes -- every form lands on ~2^20 scattered row activations per push (one 86-byte
 // write per session, plus the read that completes its partial sectors: DRAM moves 0.63 + 0.15 GB for 0.54 + 0.09).
+// SUB tiles per trip (1 or 4): the slots of SUB * TILE quanta are read in one coalesced request and a trip whose quanta
+// all flushed costs one round trip, not SUB -- a push in which every quantum flushes (65 536 sessions x 23) is nothing
+// but such trips, 24 us of them with SUB = 1.
 // (register budget stated: left alone, ptxas settles on 32 registers and spills the prefetched commit item)
-template <bool METER, uint32_t TILE>
+template <bool METER, uint32_t TILE, uint32_t SUB>
 __global__ void __launch_bounds__(TILE * 4, (METER ? 256 : 384) / TILE)
 k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst_slot, AggAppendArgs ap,
              double *__restrict__ ring_rms, uint32_t n, uint32_t quantum, const AggCtl *__restrict__ ctl, AggCommitArgs cm)
@@ -1053,64 +1064,71 @@ k_agg_append(const float *__restrict__ samples, const uint32_t *__restrict__ dst
         extern __shared__ __align__(128) unsigned char smem_raw[];
         const uint32_t pitch = quantum + 4u;
         float *arena = reinterpret_cast<float *>(smem_raw);
-        __shared__ AggStageDesc desc_s[TILE];                      // worked out once per quantum (one thread each), not once per item
-        for (uint32_t i0 = blockIdx.x * TILE; i0 < n; i0 += gridDim.x * TILE) {
-            __syncthreads();
+        static_assert(SUB >= 1 && SUB <= 4, "one slot per thread");
+        constexpr uint32_t ST = TILE * SUB;                        // quanta per trip
+        __shared__ uint32_t slot_s[ST];
+        __shared__ AggStageDesc desc_s[ST];                        // worked out once per quantum (one thread each), not once per item
+        for (uint32_t s0 = blockIdx.x * ST; s0 < n; s0 += gridDim.x * ST) {
             uint32_t slot = DEAD;
-            if (threadIdx.x < TILE) {
-                if (i0 + threadIdx.x < n) slot = ld_l2(dst_slot + i0 + threadIdx.x);
-                AggStageDesc d{DEAD, 0u, 0u, 0u};
-                if (slot != DEAD) d = agg_stage_desc(ap, slot, quantum);
-                desc_s[threadIdx.x] = d;
+            if (threadIdx.x < ST && s0 + threadIdx.x < n) slot = ld_l2(dst_slot + s0 + threadIdx.x);
+            // (a barrier: the previous trip's picks are over, its shared memory may be rewritten)
+            if (__syncthreads_count(slot != DEAD) == 0) continue;
+            if (threadIdx.x < ST) {
+                slot_s[threadIdx.x] = slot;
+                desc_s[threadIdx.x] = slot != DEAD ? agg_stage_desc(ap, slot, quantum) : AggStageDesc{DEAD, 0u, 0u, 0u};
             }
-            const int live = __syncthreads_count(slot != DEAD);
-            if (live == 0) continue;
-            if (granules == 32u) {                       // the 128-sample quantum: one warp-wide copy per quantum, no division
-                for (uint32_t t = warp; t < TILE; t += NW)
-                    if (desc_s[t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
-            } else {
-                for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
-                    const uint32_t t = idx / granules, gi = idx - t * granules;
-                    if (desc_s[t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
-                }
-            }
-            cp_async_wait_all();
-            __syncthreads();
-            auto picks = [&](uint32_t tid, uint32_t nthr) {
-                for (uint32_t f = tid; f < TILE * ap.pairs; f += nthr) {
-                    const uint32_t t = __umulhi(f, ap.magic_pairs), q = f - t * ap.pairs;
-                    const AggStageDesc d = desc_s[t];
-                    const uint32_t p = (d.olo & ~1u) + 2u * q;                  // the pair (p, p + 1), p even
-                    if (d.row == DEAD || p >= d.ohi) continue;
-                    const bool lo_ok = p >= d.olo, hi_ok = p + 1u < d.ohi;      // at least one holds
-                    uint32_t ia, ib;
-                    if (ap.lut) {
-                        const uint2 ii = __ldg(reinterpret_cast<const uint2 *>(ap.lut + p));
-                        ia = ii.x; ib = ii.y;
-                    } else {
-                        ia = p * ap.stride; ib = ia + ap.stride;
-                    }
-                    // picks of [olo, ohi) lie inside the quantum by the definition of out_lo
-                    const float *src = arena + (size_t)t * pitch;
-                    const float x0 = lo_ok ? src[ia - d.i0] : 0.0f, x1 = hi_ok ? src[ib - d.i0] : 0.0f;
-                    const uint32_t v = pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
-                    int16_t *dst = ap.staged + (size_t)d.row * ap.nout_pad + p;
-                    if (lo_ok && hi_ok) *reinterpret_cast<uint32_t *>(dst) = v;
-                    else if (lo_ok) dst[0] = (int16_t)(v & 0xFFFFu);
-                    else dst[1] = (int16_t)(v >> 16);
-                }
-            };
-            if (METER) {
-                // threads 0 .. TILE-1 meter slot t (a 128-long dependent chain each); the other three quarters of the
-                // block share the picks meanwhile
-                if (threadIdx.x < TILE) {
-                    if (slot != DEAD)
-                        ring_rms[slot] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
+            for (uint32_t sub = 0; sub < SUB; sub++) {
+                const uint32_t q0 = sub * TILE, i0 = s0 + q0;
+                // (a barrier again: descriptors visible, the previous tile's picks over) does any quantum of this tile wait?
+                if (__syncthreads_or(threadIdx.x / TILE == sub && slot != DEAD) == 0) continue;
+                if (granules == 32u) {                   // the 128-sample quantum: one warp-wide copy per quantum, no division
+                    for (uint32_t t = warp; t < TILE; t += NW)
+                        if (desc_s[q0 + t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * lane, samples + (size_t)(i0 + t) * quantum + 4u * lane);
                 } else {
-                    picks(threadIdx.x - TILE, blockDim.x - TILE);
+                    for (uint32_t idx = threadIdx.x; idx < TILE * granules; idx += blockDim.x) {
+                        const uint32_t t = idx / granules, gi = idx - t * granules;
+                        if (desc_s[q0 + t].row != DEAD) cp_async_16(arena + (size_t)t * pitch + 4u * gi, samples + (size_t)(i0 + t) * quantum + 4u * gi);
+                    }
                 }
-            } else {
-                picks(threadIdx.x, blockDim.x);
+                cp_async_wait_all();
+                __syncthreads();
+                auto picks = [&](uint32_t tid, uint32_t nthr) {
+                    for (uint32_t f = tid; f < TILE * ap.pairs; f += nthr) {
+                        const uint32_t t = __umulhi(f, ap.magic_pairs), q = f - t * ap.pairs;
+                        const AggStageDesc d = desc_s[q0 + t];
+                        const uint32_t p = (d.olo & ~1u) + 2u * q;              // the pair (p, p + 1), p even
+                        if (d.row == DEAD || p >= d.ohi) continue;
+                        const bool lo_ok = p >= d.olo, hi_ok = p + 1u < d.ohi;  // at least one holds
+                        uint32_t ia, ib;
+                        if (ap.lut) {
+                            const uint2 ii = __ldg(reinterpret_cast<const uint2 *>(ap.lut + p));
+                            ia = ii.x; ib = ii.y;
+                        } else {
+                            ia = p * ap.stride; ib = ia + ap.stride;
+                        }
+                        // picks of [olo, ohi) lie inside the quantum by the definition of out_lo
+                        const float *src = arena + (size_t)t * pitch;
+                        const float x0 = lo_ok ? src[ia - d.i0] : 0.0f, x1 = hi_ok ? src[ib - d.i0] : 0.0f;
+                        const uint32_t v = pack_s16x2_sat(enc_s32(x0), enc_s32(x1));
+                        int16_t *dst = ap.staged + (size_t)d.row * ap.nout_pad + p;
+                        if (lo_ok && hi_ok) *reinterpret_cast<uint32_t *>(dst) = v;
+                        else if (lo_ok) dst[0] = (int16_t)(v & 0xFFFFu);
+                        else dst[1] = (int16_t)(v >> 16);
+                    }
+                };
+                if (METER) {
+                    // threads 0 .. TILE-1 meter slot t (a 128-long dependent chain each); the other three quarters of
+                    // the block share the picks meanwhile
+                    if (threadIdx.x < TILE) {
+                        const uint32_t sl = slot_s[q0 + threadIdx.x];
+                        if (sl != DEAD)
+                            ring_rms[sl] = quantum_rms_cvt(reinterpret_cast<const float4 *>(arena + (size_t)threadIdx.x * pitch), quantum);
+                    } else {
+                        picks(threadIdx.x - TILE, blockDim.x - TILE);
+                    }
+                } else {
+                    picks(threadIdx.x, blockDim.x);
+                }
             }
         }
     }
