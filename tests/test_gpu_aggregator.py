@@ -99,9 +99,9 @@ def test_aggregator_rejects_out_of_range_session(ctx):
     agg.close()
 
 
-def _session_frames(x, t, rate, last0=0.0):
+def _session_frames(x, t, rate, last0=0.0, desired_ms=60.0):
     """Oracle frames of one session: x [nq, 128] quanta, t [nq] arrival times."""
-    flush, last = oracle.aggregator_plan(t, 60.0, last0)
+    flush, last = oracle.aggregator_plan(t, desired_ms, last0)
     frames, start = [], 0
     for q in np.nonzero(flush)[0]:
         buf = x[start:q + 1].reshape(1, -1)
@@ -238,6 +238,62 @@ def test_aggregator_device_resident_push_and_wait(ctx):
     agg.close()
     for b in d.values():
         b.free()
+
+
+@pytest.mark.parametrize("rate, knobs", [(48000, {}), (44100, {}), (48000, dict(agg_walk_regs=32))])
+def test_aggregator_streaming_regime_at_scale(ctx, rate, knobs):
+    """The regime a live server runs in, at a size that takes the large-push kernels: 60 000 sessions, every push
+    carries ONE quantum of most sessions (a few send two, a few skip), the flushes (16 ms here, ~6 quanta) fall in
+    different pushes for different sessions.  After the first push the library takes the kernels built for short
+    lists (4-entry flush-rule kernel, one tile per append trip); every flushed frame is mostly quanta converted on
+    arrival in earlier pushes plus one or two new ones.  With agg_walk_regs = 32 the other builds run on the same
+    pushes.  Every frame against the oracle, levels of every 16th session."""
+    rng = np.random.RandomState(int(rate) // 100 + len(knobs))
+    S, q_ms, desired, n_push = 60000, 128e3 / rate, 16.0, 12
+    try:
+        ctx.tune(**knobs)
+        agg = pcm_frontend.Aggregator(ctx, S, rate, desired_ms=desired, max_frame_quanta=16, max_push_quanta=2 * S, max_out_samples=S * 360)
+        agg.set_meter(True)
+        agg.reset_range(0, S, 0.0)
+        start_t = desired * rng.rand(S)                    # so that the sessions flush in different pushes
+        period = q_ms + rng.uniform(-0.05, 0.05, S)
+        done = np.zeros(S, np.int64)
+        audio, times, got = [], [], {}
+        for p in range(n_push):
+            u = rng.rand(S)
+            m = np.where(u < 0.03, 0, np.where(u < 0.06, 2, 1)) if p else np.ones(S, np.int64)
+            sess = np.repeat(np.arange(S, dtype=np.uint32), m)
+            k = done[sess] + (np.arange(sess.size) - np.repeat(np.cumsum(m) - m, m))
+            t = start_t[sess] + (k + 1) * period[sess]
+            order = np.lexsort((sess, t))
+            sess, t, k = sess[order], t[order], k[order]
+            x = (rng.uniform(-1.1, 1.1, size=(sess.size, 128)) * rng.uniform(0.05, 1, size=(sess.size, 1))).astype(np.float32)
+            audio.append((sess, k, x)); times.append(t)
+            done += m
+            for s_, pcm in agg.push(sess, t, x):
+                got.setdefault(s_, []).append(pcm)
+        levels = agg.levels(0, S)
+        agg.close()
+    finally:
+        ctx.tune(agg_walk_regs=0)
+    all_s = np.concatenate([a[0] for a in audio]); all_k = np.concatenate([a[1] for a in audio])
+    all_x = np.concatenate([a[2] for a in audio]); all_t = np.concatenate(times)
+    order = np.lexsort((all_k, all_s))
+    all_s, all_x, all_t = all_s[order], all_x[order], all_t[order]
+    bounds = np.searchsorted(all_s, np.arange(S + 1))
+    n_frames = 0
+    for s_ in range(S):
+        a, b = bounds[s_], bounds[s_ + 1]
+        want, flushed_q, _ = _session_frames(all_x[a:b], all_t[a:b], rate, desired_ms=desired)
+        have = got.get(s_, [])
+        assert len(have) == len(want), (s_, len(have), len(want))
+        for u_, v_ in zip(have, want):
+            assert u_.size == v_.size and np.array_equal(u_, v_), s_
+        n_frames += len(want)
+        if s_ % 16 == 0:
+            want_lv = oracle.level_meter(all_x[a:a + flushed_q].reshape(-1))[-1] if flushed_q else 0.0
+            assert levels[s_:s_ + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], (s_, levels[s_], want_lv)
+    assert n_frames >= S                                   # ~32 ms of audio per session against 16 ms flushes
 
 
 @pytest.mark.parametrize("rate, max_q", [(96000, 64), (96000, 96), (88200, 64), (16000, 32), (8000, 32), (24000, 32), (192000, 96),

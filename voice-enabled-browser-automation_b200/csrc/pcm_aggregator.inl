@@ -159,18 +159,22 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
         agg_launch(ctx, k_agg_levels, blocks_t128, 128, 0, a->geo, a->touched, a->count, a->cursor, a->fill, a->flushed, a->ring_rms, a->rms_at,
                    a->level, ctl);
     {
-        // 64 quanta per 256-thread block step, four steps per trip; a push small enough to fit one wave of the smaller
-        // blocks takes 32 per 128, one step per trip (parallelism matters more than round trips there)
+        // 64 quanta per 256-thread block step, four steps per trip when most quanta of the push are expected to flush
+        // (trips with nothing to do then cost a quarter) and one when most are expected to wait (streaming: the previous
+        // push had short lists; measured 3 % faster that way); a push small enough to fit one wave of the smaller blocks
+        // takes 32 per 128, one step per trip (parallelism matters more than round trips there)
         const bool small = n <= 32u * 12u * (uint32_t)ctx->sm_count;
-        const unsigned per_trip = small ? 32u : 256u;
+        const unsigned per_trip = small ? 32u : short_lists ? 64u : 256u;
         const unsigned long long trips = ((unsigned long long)n + per_trip - 1) / per_trip;
         const unsigned grid = (unsigned)(trips < cap ? trips : cap);
         const size_t smem = small ? a->append_smem / 2 : a->append_smem;
         if (a->meter) {
             if (small) agg_launch(ctx, k_agg_append<true, 32, 1>, grid, 128, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+            else if (short_lists) agg_launch(ctx, k_agg_append<true, 64, 1>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
             else agg_launch(ctx, k_agg_append<true, 64, 4>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
         } else {
             if (small) agg_launch(ctx, k_agg_append<false, 32, 1>, grid, 128, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
+            else if (short_lists) agg_launch(ctx, k_agg_append<false, 64, 1>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
             else agg_launch(ctx, k_agg_append<false, 64, 4>, grid, 256, smem, samples, a->dst_slot, apd, a->ring_rms, n, a->geo.quantum, ctl, cm);
         }
     }
@@ -309,6 +313,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     }
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<true, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<false, 64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<true, 64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_append<false, 64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<true, 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_append<false, 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->append_smem));
     AGG_STEP(cudaStreamSynchronize(ctx->stream));     // the host vectors above go out of scope
