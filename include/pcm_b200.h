@@ -284,7 +284,9 @@ PCMB200_API int pcmb200_timer_stop(pcmb200_ctx *ctx, float *milliseconds);
  * for the aggregator "agg_block" / "agg_stage_kb" (convert kernel: threads per CTA, staging memory per step; read
  * when an aggregator is created), "agg_persistent" (convert grid = the CTAs resident at once), "agg_pdl" (the
  * kernels of a push are chained by programmatic dependent launch; 0 = plain launches), "agg_walk_regs" (flush-rule
- * kernel: index lists of up to 32 or 4 quanta in registers; 0 = chosen from the previous push).
+ * kernel: index lists of up to 32 or 4 quanta in registers; 0 = chosen from the previous push; 4 also selects the other
+ * kernels built for one-quantum-per-session pushes) and "agg_warp_frames" (0: those pushes keep the CTA-per-frame
+ * convert kernel).
  * "overlap_ticks" = 1 changes behaviour, not just speed: consecutive device-resident dense integer-ratio
  * calls on this context may then OVERLAP on the GPU (the next tick's blocks start while the previous
  * tick's last wave drains; programmatic dependent launch).  Only for callers whose consecutive calls

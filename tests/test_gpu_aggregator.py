@@ -240,14 +240,14 @@ def test_aggregator_device_resident_push_and_wait(ctx):
         b.free()
 
 
-@pytest.mark.parametrize("rate, knobs", [(48000, {}), (44100, {}), (48000, dict(agg_walk_regs=32))])
+@pytest.mark.parametrize("rate, knobs", [(48000, {}), (44100, {}), (48000, dict(agg_walk_regs=32)), (48000, dict(agg_warp_frames=0))])
 def test_aggregator_streaming_regime_at_scale(ctx, rate, knobs):
     """The regime a live server runs in, at a size that takes the large-push kernels: 60 000 sessions, every push
     carries ONE quantum of most sessions (a few send two, a few skip), the flushes (16 ms here, ~6 quanta) fall in
     different pushes for different sessions.  After the first push the library takes the kernels built for short
-    lists (4-entry flush-rule kernel, one tile per append trip); every flushed frame is mostly quanta converted on
-    arrival in earlier pushes plus one or two new ones.  With agg_walk_regs = 32 the other builds run on the same
-    pushes.  Every frame against the oracle, levels of every 16th session."""
+    lists (4-entry flush-rule kernel, one tile per append trip, one frame per warp in the convert kernel); every
+    flushed frame is mostly quanta converted on arrival in earlier pushes plus one or two new ones.  With
+    agg_walk_regs = 32 the other builds run on the same pushes, with agg_warp_frames = 0 the CTA-per-frame convert.  Every frame against the oracle, levels of every 16th session."""
     rng = np.random.RandomState(int(rate) // 100 + len(knobs))
     S, q_ms, desired, n_push = 60000, 128e3 / rate, 16.0, 12
     try:
@@ -275,7 +275,7 @@ def test_aggregator_streaming_regime_at_scale(ctx, rate, knobs):
         levels = agg.levels(0, S)
         agg.close()
     finally:
-        ctx.tune(agg_walk_regs=0)
+        ctx.tune(agg_walk_regs=0, agg_warp_frames=1)
     all_s = np.concatenate([a[0] for a in audio]); all_k = np.concatenate([a[1] for a in audio])
     all_x = np.concatenate([a[2] for a in audio]); all_t = np.concatenate(times)
     order = np.lexsort((all_k, all_s))
@@ -375,15 +375,16 @@ def test_aggregator_unaligned_device_output(ctx, rate, max_q):
 
 @pytest.mark.parametrize("knobs", [dict(agg_pdl=0), dict(agg_persistent=0), dict(agg_block=64), dict(agg_block=256),
                                    dict(agg_block=128, agg_stage_kb=68), dict(agg_block=256, agg_stage_kb=51, agg_pdl=0),
-                                   dict(agg_walk_regs=4), dict(agg_walk_regs=32)])
+                                   dict(agg_walk_regs=4), dict(agg_walk_regs=32), dict(agg_walk_regs=4, agg_warp_frames=0)])
 @pytest.mark.parametrize("rate", [48000, 44100])
 def test_aggregator_every_kernel_form(ctx, knobs, rate):
     """The tuning knobs choose between kernel forms (one frame per step with descriptors in registers / several
     frames per step with shared-memory descriptors; persistent or oversized grid; plain or programmatic dependent
     launches; the flush-rule kernel sorting its lists of 9-12 quanta in registers or -- forced to the streaming
-    build -- in global memory).  Every form must give the oracle's frames and levels: 700 sessions, buffers carried across three
+    build -- in global memory, and with it the warp-per-frame convert kernel taking frames of 9-12 new quanta through
+    its four-slot window three times over).  Every form must give the oracle's frames and levels: 700 sessions, buffers carried across three
     pushes, sessions interleaved at random, the meter on."""
-    defaults = dict(agg_pdl=1, agg_persistent=1, agg_block=128, agg_stage_kb=20, agg_walk_regs=0)
+    defaults = dict(agg_pdl=1, agg_persistent=1, agg_block=128, agg_stage_kb=20, agg_walk_regs=0, agg_warp_frames=1)
     rng = np.random.RandomState(sum(knobs.values()) + rate // 100)
     S, q_ms, per_push = 700, 128e3 / rate, (10, 9, 12)
     try:

@@ -944,6 +944,89 @@ k_agg_convert_one(AggGeom g, AggConvertArgs a)
     }
 }
 
+// ---- 6 (streaming form): convert, one frame per WARP ---------------------------------------------------------------
+// A server that forwards quanta as they arrive pushes ONE quantum per session at a time: a flushing frame is then
+// ~22 carried-over quanta -- 1.9 KB of outputs that were converted on arrival and only need copying -- and one new
+// quantum.  k_agg_convert_one gives such a frame a whole CTA and an arena sized for the longest frame: ten frames in
+// flight per SM at 2.4 KB each, 1.39 ms per 2^20 frames (0.52 of the HBM peak, bound by bytes in flight; ncu).  Here a
+// warp owns a frame: the carried-over outputs go global -> registers -> global in 16-byte pieces, the new quanta
+// pass through a four-slot window of shared memory private to the warp (outputs [out_lo[j], out_lo[j + 4]) need
+// quanta j .. j + 3 only), no block barrier anywhere, 40 frames in flight per SM.  Any frame is handled correctly --
+// a long one takes several windows, one after the other -- so the host may pick this kernel on a guess (the previous
+// push had short lists) without anything depending on the guess being right.
+constexpr uint32_t kWarpWindow = 4;
+template <bool METER, bool LUT>
+__global__ void __launch_bounds__(128, METER ? 8 : 10)
+k_agg_convert_warp(AggGeom g, AggConvertArgs a)
+{
+    pdl_enter();
+    const CtlHead head = ctl_head(a.ctl);
+    if (head.status != 0u) return;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr uint32_t W = kWarpWindow;
+    const uint32_t Q = g.quantum, pitch = Q + 4u, gpq = Q >> 2, mq = a.magic_q;
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u, nw = blockDim.x >> 5;
+    float *win = reinterpret_cast<float *>(smem_raw) + (size_t)warp * W * pitch;
+    const uint32_t n_frames = head.n_frames;
+    const float qnan = __int_as_float(0x7FC00000);
+    for (uint32_t f = blockIdx.x * nw + warp; f < n_frames; f += gridDim.x * nw) {
+        const AggFrameDesc d = ld_l2(a.fdesc + f);                             // {session, nq, ring_count, pos}
+        const unsigned long long off = ld_l2(a.fdesc_off + f);
+        const uint32_t nq = d.nq, rc = d.ring_count, n_in = nq * Q;
+        const uint32_t n_out = __ldg(a.nout_of + nq), osplit = rc ? __ldg(a.out_lo + rc) : 0u;
+        int16_t *dst = a.out + off;
+        const int16_t *st = a.staged + (size_t)d.session * a.nout_pad;
+        // the first new quanta are asked for before anything else is waited for
+        const uint32_t cnt0 = min(W, nq - rc);
+        uint32_t idx = lane < cnt0 ? ld_l2(a.sorted + d.pos + lane) : 0u;
+        // ---- the carried-over outputs [0, osplit): a straight copy, four 16-byte pieces per lane per trip, loads first
+        uint32_t done = 0;
+        if (a.out_aligned16) {
+            const uint32_t chunks = osplit >> 3;
+            const uint4 *src4 = reinterpret_cast<const uint4 *>(st);
+            uint4 *dst4 = reinterpret_cast<uint4 *>(dst);
+            for (uint32_t c0 = lane; c0 < chunks; c0 += 128u) {
+                uint4 v[4];
+#pragma unroll
+                for (uint32_t u = 0; u < 4u; u++) if (c0 + 32u * u < chunks) v[u] = __ldcg(src4 + c0 + 32u * u);
+#pragma unroll
+                for (uint32_t u = 0; u < 4u; u++)
+                    if (c0 + 32u * u < chunks)
+                        asm volatile("st.global.cs.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(dst4 + c0 + 32u * u), "r"(v[u].x), "r"(v[u].y), "r"(v[u].z), "r"(v[u].w) : "memory");
+            }
+            done = chunks << 3;
+        }
+        for (uint32_t o = done + lane; o < osplit; o += 32u) dst[o] = ld_l2(st + o);
+        // ---- the new quanta, W at a time through the warp's window
+        for (uint32_t j0 = rc; j0 < nq; j0 += W) {
+            const uint32_t cnt = min(W, nq - j0);
+            if (j0 != rc) idx = lane < cnt ? ld_l2(a.sorted + d.pos + (j0 - rc) + lane) : 0u;
+            __syncwarp();                                                      // the previous window's picks are over
+            for (uint32_t t = 0; t < cnt; t++) {
+                const float *src = a.samples + (size_t)__shfl_sync(0xFFFFFFFFu, idx, t) * Q;
+                for (uint32_t gi = lane; gi < gpq; gi += 32u) cp_async_16(win + (size_t)t * pitch + 4u * gi, src + 4u * gi);
+            }
+            cp_async_wait_all();
+            __syncwarp();
+            // outputs whose pick falls in these quanta; the last window also takes the outputs whose pick lies beyond
+            // the frame (undefined in the reference, i.e. NaN, i.e. 0)
+            const uint32_t o_lo = __ldg(a.out_lo + j0), o_hi = j0 + cnt < nq ? __ldg(a.out_lo + j0 + cnt) : n_out;
+            const uint32_t base = j0 * Q;
+            for (uint32_t o = o_lo + lane; o < o_hi; o += 32u) {
+                const uint32_t is = LUT ? __ldg(a.lut + o) : o * g.stride;
+                float x = qnan;
+                if (is < n_in) {
+                    const uint32_t li = is - base;
+                    x = win[li + 4u * __umulhi(li, mq)];
+                }
+                dst[o] = enc_s16(x);
+            }
+            if (METER && lane < cnt)
+                a.rms_at[d.pos + (j0 - rc) + lane] = quantum_rms_cvt(reinterpret_cast<const float4 *>(win + (size_t)lane * pitch), Q);
+        }
+    }
+}
+
 // ---- 7: levels ---------------------------------------------------------------------------------------------------
 // App.tsx:271 along every touched session's FLUSHED quanta, in arrival order: first the quanta that were
 // waiting from earlier pushes (their rms was stored in ring_rms when they were appended), then this push's.

@@ -43,6 +43,8 @@ struct pcmb200_aggregator {
     AggCtl *ctl = nullptr;                 // device: two blocks, used by alternate pushes (see agg_enqueue)
     int ctl_idx = 0;
     AggCtl *h_ctl = nullptr;               // pinned copy
+    unsigned warp_grid[2] = {0, 0};        // k_agg_convert_warp: resident CTAs on the whole device, without / with the meter
+    size_t convert_warp_smem = 0;
     uint32_t pairs = 2;                    // aligned output pairs per quantum, at most (append kernel)
     uint32_t prev_n = 0;                   // quanta in the previous push (with h_ctl->n_touched: which walk kernel to take)
     // convert kernel geometry
@@ -133,7 +135,20 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const unsigned long long cap = (unsigned long long)ctx->sm_count * 32ull;
     if (conv_blocks > cap) conv_blocks = cap;
     const unsigned conv_threads = (unsigned)ctx->tune.agg_block;
-    if (a->G == 1 && a->geo.half_quanta <= 64 && conv_threads <= 128) {
+    if (short_lists && ctx->tune.agg_warp_frames) {
+        // the previous push had about one quantum per session: frames will be mostly carried-over outputs plus a
+        // quantum or two -- a warp per frame (correct for any frame, fast for those)
+        auto kern = a->meter ? (a->lut ? k_agg_convert_warp<true, true> : k_agg_convert_warp<true, false>)
+                             : (a->lut ? k_agg_convert_warp<false, true> : k_agg_convert_warp<false, false>);
+        unsigned &resident = a->warp_grid[a->meter ? 1 : 0];
+        if (resident == 0) {
+            int per_sm = 0;
+            CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, a->convert_warp_smem));
+            resident = (unsigned)(std::max(per_sm, 1) * ctx->sm_count);
+        }
+        const unsigned long long want = ((unsigned long long)n + 3) / 4;        // four frames per CTA trip, at most n frames
+        agg_launch(ctx, kern, (unsigned)std::min<unsigned long long>(want, resident), 128u, a->convert_warp_smem, a->geo, ca);
+    } else if (a->G == 1 && a->geo.half_quanta <= 64 && conv_threads <= 128) {
         // one frame per step and at most 64 quanta per frame: descriptors in registers, no meta buffers
         auto kern = a->meter ? (a->lut ? k_agg_convert_one<true, true> : k_agg_convert_one<true, false>)
                              : (a->lut ? k_agg_convert_one<false, true> : k_agg_convert_one<false, false>);
@@ -251,6 +266,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     a->G = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, ((size_t)ctx->tune.agg_stage_kb * 1024) / ((size_t)max_frame_quanta * slot_bytes)));
     a->convert_pipe_smem = agg_arena_bytes(a->G, max_frame_quanta, quantum) + 2 * (size_t)agg_meta_layout(a->G, a->G * max_frame_quanta).bytes;
     a->convert_one_smem = agg_arena_bytes(1, max_frame_quanta, quantum);
+    a->convert_warp_smem = (size_t)4 * kWarpWindow * slot_bytes;               // four warps, one window each
     a->append_smem = (((size_t)64 * slot_bytes + 127) & ~(size_t)127);
 
     cudaError_t e = cudaSuccess;
@@ -305,6 +321,10 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
     AGG_STEP(cudaFuncSetAttribute(k_agg_convert_pipe<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_pipe_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_warp<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_warp_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_warp<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_warp_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_warp<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_warp_smem));
+    AGG_STEP(cudaFuncSetAttribute(k_agg_convert_warp<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_warp_smem));
     if (a->G == 1 && max_frame_quanta <= 64) {
         AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));
         AGG_STEP(cudaFuncSetAttribute(k_agg_convert_one<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)a->convert_one_smem));

@@ -64,6 +64,7 @@ struct Tuning {
     int agg_block = 128;     // aggregator convert kernel: threads per CTA ...
     int agg_stage_kb = 20;   // ... and shared memory for the frames of one step (read when an aggregator is created);
                              //     measured best: one ~23-quanta frame per step, 128 threads (profiles/r02_sweep_aggregator.jsonl)
+    int agg_warp_frames = 1; // aggregator: pushes that follow a push of short lists convert their frames one per warp (agg_kernels.cuh)
     int agg_walk_regs = 0;   // aggregator walk kernel: index lists of up to 32 or up to 4 quanta in registers (0 = by the previous push)
     int agg_persistent = 1;  // aggregator convert kernel (one-frame form): grid = the CTAs resident at once
     int agg_pdl = 1;         // aggregator: the kernels of a push are chained by programmatic dependent launch (agg_kernels.cuh: pdl_enter)
@@ -1259,6 +1260,9 @@ int pcmb200_tune(pcmb200_ctx *ctx, const char *key, long long value)
     } else if (k == "agg_stage_kb") {
         NEED(value >= 8 && value <= 200, "pcmb200_tune: agg_stage_kb must be in [8, 200]");
         ctx->tune.agg_stage_kb = (int)value;
+    } else if (k == "agg_warp_frames") {
+        NEED(value == 0 || value == 1, "pcmb200_tune: agg_warp_frames must be 0 or 1");
+        ctx->tune.agg_warp_frames = (int)value;
     } else if (k == "agg_walk_regs") {
         NEED(value == 0 || value == 4 || value == 32, "pcmb200_tune: agg_walk_regs must be 0, 4 or 32");
         ctx->tune.agg_walk_regs = (int)value;
