@@ -42,8 +42,9 @@ struct AggCtl {                  // lives in device memory; copied to the host a
     uint32_t status;
     uint32_t n_touched;
     uint32_t n_frames;
-    uint32_t reserved_;          // (was a count of the quanta that did not flush: a million threads updating one word cost
-                                 //  more than the early exit it bought the append kernel)
+    uint32_t any_multi;          // some session has more than one quantum in this push (set by k_agg_count, one atomic per block).
+                                 // Clear in the streaming regime: every index list is its session's single quantum, and the
+                                 // reserve and scatter steps have nothing to do (30 of a 2^20-session push's 290 us)
     unsigned long long out_total;   // output samples incl. the padding of every frame to 8 samples
     uint32_t n_listed;           // running total of the per-session index lists (k_agg_reserve)
     uint32_t pad_;
@@ -86,13 +87,13 @@ __device__ __forceinline__ AggFrameDesc ld_l2(const AggFrameDesc *p)
 // The head of the push's control block, fetched ONCE per block (thread 0, through L2) and handed to every thread:
 // a million threads asking L2 for the same word cost several microseconds per kernel.  Every thread of the block
 // must call it (it holds a barrier), right after pdl_enter().
-struct CtlHead { uint32_t status, n_touched, n_frames; };
+struct CtlHead { uint32_t status, n_touched, n_frames, any_multi; };
 __device__ __forceinline__ CtlHead ctl_head(const AggCtl *ctl)
 {
     __shared__ uint4 head;
-    if (threadIdx.x == 0) head = __ldcg(reinterpret_cast<const uint4 *>(ctl));   // {status, n_touched, n_frames, -}
+    if (threadIdx.x == 0) head = __ldcg(reinterpret_cast<const uint4 *>(ctl));   // {status, n_touched, n_frames, any_multi}
     __syncthreads();
-    return CtlHead{head.x, head.y, head.z};
+    return CtlHead{head.x, head.y, head.z, head.w};
 }
 
 __device__ __forceinline__ void pdl_enter()
@@ -139,20 +140,24 @@ __device__ __forceinline__ uint32_t block_reserve256(uint32_t v, uint32_t *count
 
 __global__ void __launch_bounds__(256)
 k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sessions, uint32_t *__restrict__ count,
-            uint32_t *__restrict__ touched, AggCtl *__restrict__ ctl)
+            uint32_t *__restrict__ touched, uint32_t *__restrict__ touched_idx, AggCtl *__restrict__ ctl)
 {
     pdl_enter();
     __shared__ uint32_t sm[9];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t s = 0;
-    bool first = false;
+    bool first = false, again = false;
     if (i < n) {
         s = __ldg(sessions + i);
         if (s >= max_sessions) atomicOr(&ctl->status, AGG_ST_BAD_SESSION);
-        else first = atomicAdd(count + s, 1u) == 0u;                  // the first toucher lists the session
+        else {
+            first = atomicAdd(count + s, 1u) == 0u;                    // the first toucher lists the session ...
+            again = !first;
+        }
     }
     const uint32_t at = block_reserve256(first ? 1u : 0u, &ctl->n_touched, sm);
-    if (first) touched[at] = s;
+    if (first) { touched[at] = s; touched_idx[at] = i; }               // ... and its own index: the whole list if nobody follows
+    if (__syncthreads_or(again) && threadIdx.x == 0) atomicOr(&ctl->any_multi, 1u);
 }
 
 // ---- 2: reserve --------------------------------------------------------------------------------------------
@@ -165,7 +170,9 @@ k_agg_reserve(const uint32_t *__restrict__ touched, const uint32_t *__restrict__
     pdl_enter();
     __shared__ uint32_t sm[9];
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = k < ctl_head(ctl).n_touched;
+    const CtlHead head = ctl_head(ctl);
+    if (!head.any_multi) return;                                       // single-quantum lists: the walk kernel needs no cursor
+    const bool live = k < head.n_touched;
     const uint32_t s = live ? ld_l2(touched + k) : 0u, c = live ? ld_l2(count + s) : 0u;
     const uint32_t at = block_reserve256(c, &ctl->n_listed, sm);       // one atomic per block
     if (live) cursor[s] = at;
@@ -332,7 +339,8 @@ k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__res
               const AggCtl *__restrict__ ctl)
 {
     pdl_enter();
-    if (ctl_head(ctl).status != 0u) return;
+    const CtlHead head = ctl_head(ctl);
+    if (head.status != 0u || !head.any_multi) return;                  // (single-quantum lists are written by the walk kernel)
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     sorted[atomicAdd(cursor + __ldg(sessions + i), 1u)] = i;
@@ -390,8 +398,8 @@ struct AggWalkOut {
 // build from the shape of the previous push (quanta per touched session); either is correct for any push.
 template <uint32_t MREG>
 __global__ void __launch_bounds__(128)
-k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ count,
-           const uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted, const uint32_t *__restrict__ fill,
+k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__restrict__ touched, const uint32_t *__restrict__ touched_idx,
+           const uint32_t *__restrict__ count, uint32_t *__restrict__ cursor, uint32_t *__restrict__ sorted, const uint32_t *__restrict__ fill,
            const double *__restrict__ last_send, AggWalkOut o, AggCtl *__restrict__ ctl)
 {
     pdl_enter();
@@ -399,7 +407,20 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     if (head.status != 0u) return;
     const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= head.n_touched) return;
-    const uint32_t s = ld_l2(touched + k), m = ld_l2(count + s), base = ld_l2(cursor + s) - m;
+    // No session with two quanta in this push (the streaming regime): the list of touched session k is the index its
+    // one quantum left in touched_idx, it goes to sorted[k], and cursor gets the value the scatter step would have left
+    // (one past the list) for the level kernel.
+    const bool single = head.any_multi == 0u;
+    const uint32_t s = ld_l2(touched + k);
+    uint32_t m = 1u, base = k, only = 0u;
+    if (single) {
+        only = ld_l2(touched_idx + k);
+        sorted[k] = only;
+        cursor[s] = k + 1u;
+    } else {
+        m = ld_l2(count + s);
+        base = ld_l2(cursor + s) - m;
+    }
     uint32_t *list = sorted + base;
     const uint32_t c0 = ld_l2(fill + s);
     uint32_t f = c0, ring_cnt = c0, frame_start = 0;
@@ -420,6 +441,15 @@ k_agg_walk(AggGeom g, const double *__restrict__ arrival, const uint32_t *__rest
     };
     // The rule is sequential in `last`, but the addresses are not: arrival times are fetched in batches of 8 (one
     // memory round trip per batch instead of one per quantum -- the kernel was a chain of dependent misses).
+    if (single) {                                                              // one quantum, one rule, done
+        rule(only, arrival[only], 0u);
+        if (too_long) { atomicOr(&ctl->status, AGG_ST_FRAME_TOO_LONG); return; }
+        o.dst_slot[only] = frame_start == 0u ? s * g.half_quanta + c0 : 0xFFFFFFFFu;
+        o.new_fill[k] = f;
+        o.new_last[k] = last;
+        o.flushed[k] = frame_start;
+        return;
+    }
     constexpr uint32_t B = MREG < 8u ? MREG : 8u;
     if (m <= MREG) {
         // The usual case (~23 quanta per 60 ms, 1 per push when streaming): the index list lives in registers.

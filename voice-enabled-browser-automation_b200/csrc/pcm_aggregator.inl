@@ -31,6 +31,7 @@ struct pcmb200_aggregator {
     uint32_t *d_sessions = nullptr;        // staging when the caller's arrays are host memory
     double *d_arrival = nullptr;
     float *d_stage = nullptr;
+    uint32_t *touched_idx = nullptr;       // [touched] the push index of the session's first quantum
     uint32_t *touched = nullptr, *sorted = nullptr, *fl_nq = nullptr, *fl_ring = nullptr, *fl_pos = nullptr,
              *dst_slot = nullptr, *new_fill = nullptr, *flushed = nullptr;
     double *new_last = nullptr, *rms_at = nullptr;
@@ -107,7 +108,7 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const uint32_t max_touched = std::min(n, a->geo.max_sessions);
     const unsigned blocks_n = (n + 255u) / 256u, blocks_t = (max_touched + 255u) / 256u, blocks_t128 = (max_touched + 127u) / 128u;
     const unsigned scan_blocks = (n + kScanBlock - 1) / kScanBlock;
-    agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, ctl);
+    agg_launch(ctx, k_agg_count, blocks_n, 256, 0, sessions, n, a->geo.max_sessions, a->count, a->touched, a->touched_idx, ctl);
     ScanArgs sa{n, a->fl_nq, a->nout_of, ctl};
     agg_launch(ctx, k_agg_reserve, blocks_t, 256, 0, a->touched, a->count, a->cursor, ctl);
     agg_launch(ctx, k_agg_scatter, blocks_n, 256, 0, sessions, n, a->cursor, a->sorted, ctl);
@@ -119,8 +120,8 @@ int agg_enqueue(pcmb200_ctx *ctx, pcmb200_aggregator *a, uint32_t n, const uint3
     const bool short_lists = ctx->tune.agg_walk_regs == 4 ||
         (ctx->tune.agg_walk_regs == 0 && a->prev_n != 0 && a->h_ctl->n_touched != 0 && a->prev_n <= 2u * a->h_ctl->n_touched);
     a->prev_n = n;
-    if (short_lists) agg_launch(ctx, k_agg_walk<4>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
-    else agg_launch(ctx, k_agg_walk<32>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
+    if (short_lists) agg_launch(ctx, k_agg_walk<4>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->touched_idx, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
+    else agg_launch(ctx, k_agg_walk<32>, blocks_t128, 128, 0, a->geo, arrival, a->touched, a->touched_idx, a->count, a->cursor, a->sorted, a->fill, a->last_send, wo, ctl);
     ScanApplyB ab{sessions, a->fl_ring, a->fl_pos, frame_session, frame_len, frame_offset, a->fdesc, a->fdesc_off, max_frames};
     agg_launch(ctx, k_scan_reduce, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b);
     agg_launch(ctx, k_scan_apply, scan_blocks, kScanThreads, 0, sa, a->sums_a, a->sums_b, ab, ctl, (unsigned long long)out_capacity);
@@ -287,6 +288,7 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     AGG_STEP(agg_alloc(&a->d_arrival, P));
     // d_stage (a whole push of samples) is allocated on the first push whose samples are host memory
     AGG_STEP(agg_alloc(&a->touched, P));
+    AGG_STEP(agg_alloc(&a->touched_idx, P));
     AGG_STEP(agg_alloc(&a->sorted, P));
     AGG_STEP(agg_alloc(&a->fl_nq, P));
     AGG_STEP(agg_alloc(&a->fl_ring, P));
@@ -356,7 +358,7 @@ extern "C" int pcmb200_aggregator_destroy(pcmb200_ctx *ctx, pcmb200_aggregator *
     if (!a) return PCMB200_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    void *dev[] = {a->staged, a->out_lo, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
+    void *dev[] = {a->touched_idx, a->staged, a->out_lo, a->ring_rms, a->fill, a->count, a->cursor, a->last_send, a->level, a->nout_of, a->lut, a->d_sessions,
                    a->d_arrival, a->d_stage, a->touched, a->sorted, a->fl_nq, a->fl_ring, a->fl_pos, a->dst_slot, a->new_fill,
                    a->flushed, a->new_last, a->rms_at, a->sums_a, a->sums_b, a->fdesc, a->fdesc_off, a->f_session,
                    a->f_len, a->f_off, a->d_out, a->ctl};
