@@ -10,4 +10,5 @@ python $P/summarize.py launches $O/r02_launches_agg_stream.csv > $P/r02_launches
 for k in coal3:coal3 meter960:meter960 meter2944:meter2944 agg_convert:agg_convert agg_walk:agg_walk agg_append:agg_append_stream agg_convert_flush:agg_convert_stream_flush; do
   python $P/summarize.py raw $O/r02_prof_${k%%:*}.ncu-rep > $P/r02_kernel_${k##*:}_raw.txt
 done
+[ -f $O/r02_scatter_probe.jsonl ] && cp $O/r02_scatter_probe.jsonl $P/
 tail -2 $O/r02_pytest_gpu.log

@@ -27,5 +27,6 @@ timeout 300 python tools/run_configs.py --agg-stream 1048576 > $O/r02_plain_stre
 ncu --set full --clock-control none --import-source on -k regex:k_agg_append -s 6 -c 1 -o $O/r02_prof_agg_append python tools/run_configs.py --agg-stream 1048576 > $O/r02_ncu_agg_append.log 2>&1
 timeout 300 python tools/run_configs.py --agg-stream 1048576 > $O/r02_plain_stream3.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:k_agg_convert_warp -s 21 -c 1 -o $O/r02_prof_agg_convert_flush python tools/run_configs.py --agg-stream 1048576 > $O/r02_ncu_agg_convert_flush.log 2>&1
+[ -x tools/scatter_probe ] && timeout 120 ./tools/scatter_probe > $O/r02_scatter_probe.jsonl 2>&1
 timeout 300 python tools/run_configs.py --sweep-agg > $O/r02_sweep_aggregator.jsonl 2> $O/r02_sweep_aggregator.err
 ls -la $O | tail -30
