@@ -8,13 +8,14 @@
 // One push of n quanta (quantum i belongs to sessions[i], arrived at arrival[i]):
 //   1 k_agg_count    count[s]++ per quantum; the first toucher of a session appends it to `touched`
 //   2 k_agg_reserve  where each touched session's index list starts (one atomic per block: the lists may sit in any order)
+//                    (steps 2 and 3 return at once when no session has two quanta in the push: AggCtl::any_multi)
 //   3 k_agg_scatter  sorted[cursor[s]++] = i   (atomic, so the order inside a session is arbitrary ...)
 //   4 k_agg_walk     ... one thread per touched session sorts its list by i (arrival order) and runs the
 //                    reference's rule over it: fill++, flush when arrival - lastSend >= desiredMs.  It only
 //                    writes scratch (the session's new state, per-quantum flush marks and staging slots).
 //   5 scan           over quanta: frame index and output offset of every flush, in flush order
 //                    (= ascending i); its apply pass also emits the caller's frame arrays.
-//   6 k_agg_convert_one / _pipe   every flushed frame: the quanta carried over from earlier pushes were
+//   6 k_agg_convert_one / _pipe / _warp   every flushed frame: the quanta carried over from earlier pushes were
 //                    picked and encoded when they arrived (step 8) and are a ready int16 prefix in
 //                    staged[session][] -- copied; this push's quanta are brought into shared memory with
 //                    async copies straight from the push, picked, encoded, stored; with the meter on,
