@@ -166,7 +166,7 @@ PCMB200_API int pcmb200_frames_encode_meter(pcmb200_ctx *ctx, const float *in_de
  * the frame's final length, App.tsx:26-30), so device memory per session is about
  * 2 * N_out(max_frame_quanta * quantum) + 8 * max_frame_quanta + 28 bytes -- 3 KB for 32 quanta at 48 kHz
  * (a buffer of samples would be 16 KB).
- *   quantum          samples per quantum, a multiple of 4 (the AudioWorklet quantum is 128)
+ *   quantum          samples per quantum, a multiple of 4, at most 876 (the AudioWorklet quantum is 128)
  *   max_frame_quanta  longest frame, in quanta (a push that would exceed it is rejected whole); one frame
  *                     must fit on chip: max_frame_quanta * (quantum + 4) * 4 bytes <= 200 KB
  *   max_push_quanta   most quanta in one push;   max_out_samples_per_push  output arena (host path)

@@ -508,3 +508,18 @@ def test_aggregator_fuzz_with_rejected_pushes(ctx, seed):
             assert a.size == b.size and np.array_equal(a, b), s
         want_lv = oracle.level_meter(audio[s, :start].reshape(-1))[-1]
         assert levels[s:s + 1].view(np.uint64)[0] == np.array([want_lv]).view(np.uint64)[0], s
+
+
+def test_aggregator_quantum_limit(ctx):
+    """A quantum the append kernel could not stage 64 of is refused when the aggregator is created, with a message that
+    says so (not by a CUDA error on the first push); the largest allowed one works."""
+    with pytest.raises(pcm_frontend.PcmError) as ei:
+        pcm_frontend.Aggregator(ctx, 4, 48000, quantum=1024, max_frame_quanta=4, max_push_quanta=64, max_out_samples=1 << 14)
+    assert "quantum too long" in str(ei.value)
+    agg = pcm_frontend.Aggregator(ctx, 4, 48000, quantum=876, max_frame_quanta=4, max_push_quanta=64, max_out_samples=1 << 14)
+    agg.reset_range(0, 4, 0.0)
+    x = np.linspace(-1, 1, 3 * 876, dtype=np.float32).reshape(3, 876)
+    frames = agg.push(np.array([1, 1, 1]), np.array([10.0, 30.0, 61.0]), x)
+    agg.close()
+    assert len(frames) == 1 and frames[0][0] == 1
+    assert np.array_equal(frames[0][1], oracle.frames(x.reshape(1, -1), 3 * 876, 48000)[0])

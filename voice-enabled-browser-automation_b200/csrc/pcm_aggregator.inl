@@ -223,6 +223,8 @@ extern "C" int pcmb200_aggregator_create(pcmb200_ctx *ctx, uint32_t max_sessions
     NEED((size_t)max_frame_quanta * (slot_bytes + 8) <= 200 * 1024,
          "pcmb200_aggregator_create: max_frame_quanta * quantum is too long to stage one frame on chip (limit ~200 KB, "
          "e.g. 387 quanta of 128 samples = 1 s at 48 kHz)");
+    // the append kernel brings 64 quanta at a time into shared memory (and the warp-per-frame convert kernel 16)
+    NEED((size_t)64 * slot_bytes <= 220 * 1024, "pcmb200_aggregator_create: quantum too long (at most 876 samples; the AudioWorklet quantum is 128)");
     CU(cudaSetDevice(ctx->device));
     pcmb200_aggregator *a = new (std::nothrow) pcmb200_aggregator();
     if (!a) return fail(ctx, PCMB200_ERR_NOMEM, "pcmb200_aggregator_create: host allocation failed");
