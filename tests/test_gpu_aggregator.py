@@ -373,6 +373,49 @@ def test_aggregator_unaligned_device_output(ctx, rate, max_q):
         b.free()
 
 
+@pytest.mark.parametrize("shift", [0, 1])
+@pytest.mark.parametrize("rate", [48000, 44100])
+def test_aggregator_streaming_device_output_canaries(ctx, rate, shift):
+    """One quantum per session per push, everything in device memory: after the first push the frames are converted
+    one per warp (k_agg_convert_warp), mostly by copying the outputs staged on arrival.  The output pointer is 16-byte
+    aligned (shift 0: 16-byte copies) or only 2-byte aligned (shift 1: 16-bit stores); the frames must be the
+    oracle's and nothing around or between them may be written."""
+    rng = np.random.RandomState(7 + shift)
+    S, nq, q_ms = 500, 26, 128e3 / rate
+    agg = pcm_frontend.Aggregator(ctx, S, rate, max_frame_quanta=32, max_push_quanta=S, max_out_samples=16)
+    agg.reset_range(0, S, 0.0)
+    x = rng.uniform(-1.05, 1.05, size=(nq, S, 128)).astype(np.float32)
+    t_all = (np.arange(nq) + 1) * q_ms
+    flush, _ = oracle.aggregator_plan(t_all, 60.0, 0.0)
+    fq = int(np.nonzero(flush)[0][0]) + 1                           # the push on which every session flushes
+    n_out = oracle.resample_len(fq * 128, rate)
+    pad = (n_out + 7) // 8 * 8
+    d = {k: ctx.device_buffer(v) for k, v in dict(s=S * 4, t=S * 8, x=S * 512, o=(S * pad + 16) * 2, fl=S * 4, fo=S * 8).items()}
+    d["s"].upload(np.arange(S, dtype=np.uint32))
+    try:
+        for p in range(nq):
+            d["t"].upload(np.full(S, t_all[p])); d["x"].upload(np.ascontiguousarray(x[p]))
+            d["o"].upload(np.full(S * pad + 16, 0x2222, np.int16))
+            agg.push_device(S, d["s"].ptr, d["t"].ptr, d["x"].ptr, d["o"].ptr + 2 * shift, S * pad, None, d["fl"].ptr, d["fo"].ptr, S)
+            nf, ns = agg.wait()
+            raw = d["o"].download(np.int16, S * pad + 16)
+            if p + 1 != fq:
+                assert nf == 0 and ns == 0 and (raw == 0x2222).all(), p
+                continue
+            assert nf == S and ns == S * pad
+            fl, fo = d["fl"].download(np.uint32, S), d["fo"].download(np.uint64, S)
+            assert (fl == n_out).all() and (fo == np.arange(S) * pad).all()
+            assert (raw[:shift] == 0x2222).all() and (raw[shift + S * pad:] == 0x2222).all()
+            got = raw[shift:shift + S * pad].reshape(S, pad)
+            xs = x[:fq].transpose(1, 0, 2).reshape(S, fq * 128)
+            assert np.array_equal(got[:, :n_out], oracle.frames(np.ascontiguousarray(xs), fq * 128, rate, threads=4))
+            assert (got[:, n_out:] == 0x2222).all()                  # the padding between frames is left alone
+    finally:
+        agg.close()
+        for b in d.values():
+            b.free()
+
+
 @pytest.mark.parametrize("knobs", [dict(agg_pdl=0), dict(agg_persistent=0), dict(agg_block=64), dict(agg_block=256),
                                    dict(agg_block=128, agg_stage_kb=68), dict(agg_block=256, agg_stage_kb=51, agg_pdl=0),
                                    dict(agg_walk_regs=4), dict(agg_walk_regs=32), dict(agg_walk_regs=4, agg_warp_frames=0)])
