@@ -286,7 +286,7 @@ __device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &
 // grand totals: it publishes n_frames / out_total and checks the two capacities.  Frames emitted by earlier blocks
 // of a push that then turns out too large are harmless: emit_frame never writes past max_frames, and nothing
 // downstream runs once the status word is set.
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kScanThreads, 5)         // (a push of 1.5 M quanta is 736 blocks: one wave at five per SM)
 k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__restrict__ sums_b, ScanApplyB ap,
              AggCtl *__restrict__ ctl, unsigned long long out_capacity)
 {
@@ -313,16 +313,22 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__
     pa = 0; pb = 0;
 #pragma unroll
     for (int w = 0; w < kScanThreads / 32; w++) { pa += red_a[w]; pb += red_b[w]; }
-    uint32_t ea = xa + (uint32_t)pa;
-    unsigned long long eb = (unsigned long long)xb + pb;
+    // The block's frames are first listed in shared memory (quantum index and output offset within the block, in frame
+    // order), then emitted with thread <-> frame: the stores to the five per-frame arrays are then contiguous across a
+    // warp.  Emitted straight from the scan, a thread wrote its (up to) eight frames one after the other, every store 32
+    // sectors wide and every frame's loads queued behind the previous frame's stores: 54 us for 2^20 frames.
+    __shared__ uint32_t st_idx[kScanBlock], st_off[kScanBlock];
+    {
+        uint32_t la = xa, lb = xb;
 #pragma unroll
-    for (int k = 0; k < kScanItems; k++) {
-        const uint32_t idx = base + threadIdx.x * kScanItems + k;
-        if (idx < len) {
-            if (va[k]) emit_frame(a, ap, idx, ea, eb);       // quantum idx flushes frame number ea
+        for (int k = 0; k < kScanItems; k++) {
+            if (va[k]) { st_idx[la] = base + threadIdx.x * kScanItems + k; st_off[la] = lb; }
+            la += va[k]; lb += vb[k];
         }
-        ea += va[k]; eb += vb[k];
     }
+    __syncthreads();
+    for (uint32_t r = threadIdx.x; r < ta; r += kScanThreads)
+        emit_frame(a, ap, st_idx[r], (uint32_t)pa + r, pb + st_off[r]);   // quantum st_idx[r] flushes frame number pa + r
     if (blockIdx.x == gridDim.x - 1u && threadIdx.x == 0u) {
         const unsigned long long total_a = pa + ta, total_b = pb + tb;
         ctl->n_frames = (uint32_t)total_a;
