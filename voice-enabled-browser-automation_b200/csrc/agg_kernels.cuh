@@ -269,22 +269,10 @@ struct ScanApplyB {
     uint32_t max_frames;
 };
 
-// Emits frame number `f` / output offset `off` for flushing quantum idx.
-__device__ __forceinline__ void emit_frame(const ScanArgs &a, const ScanApplyB &ap, uint32_t idx, uint32_t f, unsigned long long off)
-{
-    if (f >= ap.max_frames) return;
-    const uint32_t nq = ld_l2(a.fl_nq + idx), s = ap.sessions[idx];
-    if (ap.frame_session) ap.frame_session[f] = s;
-    if (ap.frame_len) ap.frame_len[f] = __ldg(a.nout_of + nq);
-    if (ap.frame_offset) ap.frame_offset[f] = off;
-    ap.fdesc[f] = AggFrameDesc{s, nq, ld_l2(ap.fl_ring + idx), ld_l2(ap.fl_pos + idx)};
-    ap.fdesc_off[f] = off;
-}
-
 // Second pass: every block adds up the totals of the blocks before it (a few hundred numbers: cheaper than a third
 // kernel whose only job was to scan them), rescans its own items and emits the frames.  The last block knows the
 // grand totals: it publishes n_frames / out_total and checks the two capacities.  Frames emitted by earlier blocks
-// of a push that then turns out too large are harmless: emit_frame never writes past max_frames, and nothing
+// of a push that then turns out too large are harmless: nothing is written past max_frames, and nothing
 // downstream runs once the status word is set.
 __global__ void __launch_bounds__(kScanThreads, 5)         // (a push of 1.5 M quanta is 736 blocks: one wave at five per SM)
 k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__restrict__ sums_b, ScanApplyB ap,
@@ -327,8 +315,35 @@ k_scan_apply(ScanArgs a, const uint32_t *__restrict__ sums_a, const uint32_t *__
         }
     }
     __syncthreads();
-    for (uint32_t r = threadIdx.x; r < ta; r += kScanThreads)
-        emit_frame(a, ap, st_idx[r], (uint32_t)pa + r, pb + st_off[r]);   // quantum st_idx[r] flushes frame number pa + r
+    // four frames per trip, everything they need asked for before anything is stored (the per-frame arrays may alias
+    // as far as the compiler knows, so a frame's loads would otherwise wait behind the previous frame's stores)
+    for (uint32_t r0 = threadIdx.x; r0 < ta; r0 += 4u * kScanThreads) {
+        uint32_t e_nq[4], e_s[4], e_rc[4], e_pos[4], e_len[4];
+#pragma unroll
+        for (uint32_t u = 0; u < 4u; u++) {
+            const uint32_t r = r0 + u * kScanThreads;
+            e_nq[u] = e_s[u] = e_rc[u] = e_pos[u] = 0u;
+            if (r < ta) {
+                const uint32_t idx = st_idx[r];
+                e_nq[u] = ld_l2(a.fl_nq + idx); e_s[u] = ap.sessions[idx];
+                e_rc[u] = ld_l2(ap.fl_ring + idx); e_pos[u] = ld_l2(ap.fl_pos + idx);
+            }
+        }
+#pragma unroll
+        for (uint32_t u = 0; u < 4u; u++) e_len[u] = __ldg(a.nout_of + e_nq[u]);
+#pragma unroll
+        for (uint32_t u = 0; u < 4u; u++) {
+            const uint32_t r = r0 + u * kScanThreads, f = (uint32_t)pa + r;  // quantum st_idx[r] flushes frame number pa + r
+            if (r < ta && f < ap.max_frames) {
+                const unsigned long long off = pb + st_off[r];
+                if (ap.frame_session) ap.frame_session[f] = e_s[u];
+                if (ap.frame_len) ap.frame_len[f] = e_len[u];
+                if (ap.frame_offset) ap.frame_offset[f] = off;
+                ap.fdesc[f] = AggFrameDesc{e_s[u], e_nq[u], e_rc[u], e_pos[u]};
+                ap.fdesc_off[f] = off;
+            }
+        }
+    }
     if (blockIdx.x == gridDim.x - 1u && threadIdx.x == 0u) {
         const unsigned long long total_a = pa + ta, total_b = pb + tb;
         ctl->n_frames = (uint32_t)total_a;
