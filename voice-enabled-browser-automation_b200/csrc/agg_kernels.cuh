@@ -103,6 +103,13 @@ __device__ __forceinline__ void pdl_enter()
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// Do two neighbouring lanes of this warp hold the same (valid) session?  All 32 lanes must call.
+__device__ __forceinline__ bool warp_has_neighbours(uint32_t s, uint32_t lane)
+{
+    const uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, s, 1);
+    return __any_sync(0xFFFFFFFFu, lane != 0u && prev == s && s != 0xFFFFFFFFu) != 0;
+}
+
 // ---- 1: count ------------------------------------------------------------------------------------------
 // Exclusive scan of one value per thread over a 256-thread block (all threads must call); `total` = the block's sum.
 __device__ __forceinline__ uint32_t block_exscan256(uint32_t v, uint32_t *warp_sums, uint32_t &total)
@@ -146,13 +153,30 @@ k_agg_count(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t max_sess
     pdl_enter();
     __shared__ uint32_t sm[9];
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t s = 0;
+    uint32_t s = 0xFFFFFFFFu;
     bool first = false, again = false;
     if (i < n) {
         s = __ldg(sessions + i);
-        if (s >= max_sessions) atomicOr(&ctl->status, AGG_ST_BAD_SESSION);
-        else {
-            first = atomicAdd(count + s, 1u) == 0u;                    // the first toucher lists the session ...
+        if (s >= max_sessions) { atomicOr(&ctl->status, AGG_ST_BAD_SESSION); s = 0xFFFFFFFFu; }
+    }
+    {
+        // Lanes of a warp that hold quanta of the SAME session (a push grouped by session: 23 neighbours) add to its
+        // counter once, through one of them: 32 atomics on one address from one warp serialise (count 25 us instead of
+        // 11 per 1.5 M quanta, measured).  Finding the groups (match.any) costs 9 us per 1.5 M quanta when every lane
+        // holds a different session, so it is done only in warps where two neighbouring lanes agree.
+        const uint32_t lane = threadIdx.x & 31u;
+        if (warp_has_neighbours(s, lane)) {
+            const unsigned peers = __match_any_sync(0xFFFFFFFFu, s);
+            const uint32_t leader = (uint32_t)__ffs((int)peers) - 1u;
+            uint32_t old = 0u;
+            if (lane == leader && s != 0xFFFFFFFFu) old = atomicAdd(count + s, (uint32_t)__popc(peers));
+            old = __shfl_sync(0xFFFFFFFFu, old, (int)leader);
+            if (s != 0xFFFFFFFFu) {
+                first = old == 0u && lane == leader;                   // the first toucher lists the session ...
+                again = !first;
+            }
+        } else if (s != 0xFFFFFFFFu) {
+            first = atomicAdd(count + s, 1u) == 0u;
             again = !first;
         }
     }
@@ -363,9 +387,19 @@ k_agg_scatter(const uint32_t *__restrict__ sessions, uint32_t n, uint32_t *__res
     pdl_enter();
     const CtlHead head = ctl_head(ctl);
     if (head.status != 0u || !head.any_multi) return;                  // (single-quantum lists are written by the walk kernel)
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    sorted[atomicAdd(cursor + __ldg(sessions + i), 1u)] = i;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31u;
+    const uint32_t s = i < n ? __ldg(sessions + i) : 0xFFFFFFFFu;
+    // one atomic per session per warp where neighbouring lanes share a session, as in the count step
+    if (warp_has_neighbours(s, lane)) {
+        const unsigned peers = __match_any_sync(0xFFFFFFFFu, s);
+        const uint32_t leader = (uint32_t)__ffs((int)peers) - 1u;
+        uint32_t at = 0u;
+        if (lane == leader && i < n) at = atomicAdd(cursor + s, (uint32_t)__popc(peers));
+        at = __shfl_sync(0xFFFFFFFFu, at, (int)leader);
+        if (i < n) sorted[at + (uint32_t)__popc(peers & ((1u << lane) - 1u))] = i;
+    } else if (i < n) {
+        sorted[atomicAdd(cursor + s, 1u)] = i;
+    }
 }
 
 // ---- 4: walk -------------------------------------------------------------------------------------------------
